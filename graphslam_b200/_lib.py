@@ -1,0 +1,102 @@
+"""ctypes binding of libgraphslam_cuda.so (include/graphslam_cuda.h).  Fails loudly if the library
+is missing: there is no Python / CPU fallback for the optimiser."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+c_double_p = C.POINTER(C.c_double)
+c_u64_p = C.POINTER(C.c_uint64)
+c_i32_p = C.POINTER(C.c_int32)
+
+GS_OK, GS_EINVAL, GS_ENOTSPD, GS_EDUPKEY, GS_ENOKEY, GS_ECUDA, GS_ENCCL, GS_ENOTCONVERGED, GS_ENAN = range(9)
+STATUS_NAMES = ["GS_OK", "GS_EINVAL", "GS_ENOTSPD", "GS_EDUPKEY", "GS_ENOKEY", "GS_ECUDA", "GS_ENCCL",
+                "GS_ENOTCONVERGED", "GS_ENAN"]
+
+
+class GsParams(C.Structure):
+    _fields_ = [("max_iterations", C.c_int), ("rel_error_tol", C.c_double), ("abs_error_tol", C.c_double),
+                ("error_tol", C.c_double), ("lambda_initial", C.c_double), ("lambda_factor", C.c_double),
+                ("lambda_upper", C.c_double), ("lambda_lower", C.c_double), ("min_model_fidelity", C.c_double),
+                ("diagonal_damping", C.c_int), ("jacobian_mode", C.c_int), ("pcg_rel_tol", C.c_double),
+                ("pcg_max_iters", C.c_int), ("device", C.c_int), ("rank", C.c_int), ("world_size", C.c_int),
+                ("reserved", C.c_int * 8)]
+
+
+class GsStats(C.Structure):
+    _fields_ = [("iterations", C.c_int), ("outer_loops", C.c_int), ("inner_iterations", C.c_int),
+                ("converged", C.c_int), ("chi2_initial", C.c_double), ("chi2_final", C.c_double),
+                ("lambda_final", C.c_double), ("pcg_iterations_total", C.c_int64), ("ms_structure", C.c_double),
+                ("ms_linearize", C.c_double), ("ms_solve", C.c_double), ("ms_update", C.c_double),
+                ("ms_total", C.c_double), ("edges_per_sec", C.c_double), ("gn_iters_per_sec", C.c_double),
+                ("reserved", C.c_double * 8)]
+
+    def as_dict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        d["gpu_launches"] = int(self.reserved[0])
+        return d
+
+
+# every symbol include/graphslam_cuda.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "gs_default_params": (None, [C.POINTER(GsParams)]),
+    "gs_version": (C.c_int, []),
+    "gs_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(GsParams)]),
+    "gs_destroy": (C.c_int, [C.c_void_p]),
+    "gs_set_params": (C.c_int, [C.c_void_p, C.POINTER(GsParams)]),
+    "gs_add_vertex": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
+    "gs_add_prior": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p, c_double_p]),
+    "gs_add_between": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, c_double_p, c_double_p]),
+    "gs_add_batch": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p, C.c_size_t, c_u64_p, c_u64_p,
+                               c_double_p, c_double_p]),
+    "gs_prepare": (C.c_int, [C.c_void_p]),
+    "gs_optimize": (C.c_int, [C.c_void_p, C.POINTER(GsStats)]),
+    "gs_get_pose": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
+    "gs_get_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p, C.POINTER(C.c_size_t)]),
+    "gs_set_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p]),
+    "gs_chi2": (C.c_int, [C.c_void_p, c_double_p]),
+    "gs_num_vertices": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
+    "gs_num_factors": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
+    "gs_get_pattern": (C.c_int, [C.c_void_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t)]),
+    "gs_get_system": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
+    "gs_solve_linear": (C.c_int, [C.c_void_p, C.c_double, c_double_p, C.POINTER(C.c_int), c_double_p]),
+    "gs_get_trace": (C.c_int, [C.c_void_p, C.c_size_t, c_double_p, c_double_p, c_i32_p, C.POINTER(C.c_size_t)]),
+    "gs_last_error": (C.c_char_p, [C.c_void_p]),
+    "gs_compose_reference": (None, [c_double_p, c_double_p, c_double_p]),
+    "gs_compose": (None, [c_double_p, c_double_p, c_double_p]),
+    "gs_closest_keyframe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, c_u64_p, c_double_p]),
+}
+
+# host-only debug entries (not in the public header): the product's own host code, callable on a CPU box
+DEBUG_SIGNATURES = {
+    "gs_host_pattern": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t),
+                                  c_i32_p]),
+    "gs_host_between": (C.c_int, [c_double_p] * 4 + [C.c_int] + [c_double_p] * 8),
+}
+
+_LIB = None
+
+
+def lib_path() -> str:
+    return _build.LIB
+
+
+def load(build_if_missing: bool = True) -> C.CDLL:
+    """Load libgraphslam_cuda.so; raise if it cannot be found or built."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        if not build_if_missing:
+            raise RuntimeError(f"{path} is missing: run `python -m graphslam_b200.build` (no CPU fallback exists)")
+        _build.build()
+    lib = C.CDLL(path)
+    for name, (res, args) in {**SIGNATURES, **DEBUG_SIGNATURES}.items():
+        fn = getattr(lib, name)          # AttributeError = missing export = broken build
+        fn.restype = res
+        fn.argtypes = args
+    _LIB = lib
+    return lib

@@ -1,0 +1,988 @@
+// libgraphslam_cuda: C ABI (include/graphslam_cuda.h) + Levenberg-Marquardt driver.
+//
+// The driver restates gtsam::LevenbergMarquardtOptimizer::optimize() with default parameters —
+// what reference src/graph/src/graph.cpp:119 calls — as: k_assemble -> [k_minv -> PCG] per
+// tryLambda -> k_retract + k_chi2 -> accept/reject on three scalars read back per try.
+// The PCG loop itself never synchronises with the host: coefficients live in device memory and
+// iterations are replayed from a CUDA graph in batches, a `done` flag turning the tail into no-ops.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/graphslam_cuda.h"
+#include "kernels.cuh"
+
+namespace {
+
+using gs::HostStructure;
+using gs::Scalars;
+using gs::Tile;
+
+constexpr int kPcgBatch = 32;  // PCG iterations per CUDA-graph launch
+
+double now_ms() {
+  using namespace std::chrono;
+  return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t alloc(size_t count) {
+    if (count <= n && p) return cudaSuccess;
+    release();
+    n = count;
+    if (count == 0) return cudaSuccess;
+    return cudaMalloc(&p, count * sizeof(T));
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  ~DevBuf() { release(); }
+};
+
+bool spd_information(const double* cov9, double* om6) {
+  // symmetrise, Cholesky test, invert via adjugate
+  const double a00 = cov9[0], a11 = cov9[4], a22 = cov9[8];
+  const double a01 = 0.5 * (cov9[1] + cov9[3]), a02 = 0.5 * (cov9[2] + cov9[6]), a12 = 0.5 * (cov9[5] + cov9[7]);
+  if (!(a00 > 0.0)) return false;
+  const double l00 = std::sqrt(a00), l10 = a01 / l00, l20 = a02 / l00;
+  const double d1 = a11 - l10 * l10;
+  if (!(d1 > 0.0)) return false;
+  const double l11 = std::sqrt(d1), l21 = (a12 - l20 * l10) / l11;
+  const double d2 = a22 - l20 * l20 - l21 * l21;
+  if (!(d2 > 0.0) || !std::isfinite(d2)) return false;
+  gs::Sym3 q{a00, a01, a02, a11, a12, a22};
+  const gs::Sym3 r = gs::inverse_spd(q);
+  om6[0] = r.a00; om6[1] = r.a01; om6[2] = r.a02; om6[3] = r.a11; om6[4] = r.a12; om6[5] = r.a22;
+  for (int k = 0; k < 6; ++k)
+    if (!std::isfinite(om6[k])) return false;
+  return true;
+}
+
+}  // namespace
+
+struct gs_graph {
+  gs_params prm;
+  std::string err;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+  // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
+  std::vector<uint64_t> keys;
+  std::vector<double> xyt;  // current values, 3 per vertex, insertion order
+  std::unordered_map<uint64_t, int> key2ins;
+  bool keys_sequential = true;  // keys[k] == keys[0] + k  -> no hash lookups needed
+  std::vector<int> e1, e2;      // insertion indices of id_1, id_2
+  std::vector<double> ez;       // 3 per factor
+  std::vector<double> eom;      // information, 6 per factor
+  std::vector<int> pr_v;
+  std::vector<double> pr_xyt, pr_om;
+
+  // ---- dense order
+  std::vector<int> ins2dense, dense2ins;
+  bool identity_order = true;
+
+  bool topo_dirty = true;       // factors/vertices added since the last structure build
+  bool host_values_fresh = true;  // host xyt newer than (or equal to) device poses
+  bool device_values_valid = false;
+  bool system_valid = false;    // H, b assembled at the current device poses
+
+  HostStructure S;
+  int N = 0, E = 0, P = 0;
+
+  // ---- device
+  DevBuf<double4> d_pose, d_pose_try, d_pr_pose;
+  DevBuf<int2> d_eij;
+  DevBuf<double2> d_zt, d_zr, d_o01, d_o23, d_o45;
+  DevBuf<int> d_pr_idx, d_crowptr, d_cblk, d_orowptr, d_ocol;
+  DevBuf<uint32_t> d_ccode;
+  DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part;
+  DevBuf<Tile> d_atiles, d_stiles;
+  DevBuf<Scalars> d_sc;
+  DevBuf<unsigned int> d_counter;
+  Scalars* h_sc = nullptr;  // pinned mirror
+  int grid_v = 0, grid_v3 = 0, grid_e = 0;
+
+  cudaGraph_t pcg_graph = nullptr;
+  cudaGraphExec_t pcg_exec = nullptr;
+
+  // ---- last optimise trace
+  std::vector<double> tr_err, tr_lambda;
+  std::vector<int32_t> tr_tries;
+  int64_t launches = 0;
+
+  gs_status fail(gs_status s, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    err = buf;
+    return s;
+  }
+  int find(uint64_t key) const {
+    if (keys.empty()) return -1;
+    if (keys_sequential) {
+      if (key < keys[0]) return -1;
+      const uint64_t d = key - keys[0];
+      return d < keys.size() ? (int)d : -1;
+    }
+    auto it = key2ins.find(key);
+    return it == key2ins.end() ? -1 : it->second;
+  }
+};
+
+#define GS_CUDA(g, call)                                                                         \
+  do {                                                                                           \
+    cudaError_t e__ = (call);                                                                    \
+    if (e__ != cudaSuccess)                                                                      \
+      return (g)->fail(GS_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+  } while (0)
+
+namespace {
+
+void destroy_graph_exec(gs_graph* g) {
+  if (g->pcg_exec) cudaGraphExecDestroy(g->pcg_exec);
+  if (g->pcg_graph) cudaGraphDestroy(g->pcg_graph);
+  g->pcg_exec = nullptr;
+  g->pcg_graph = nullptr;
+}
+
+gs::SpmvArgs spmv_args(gs_graph* g, const double* p, double* y, int mode) {
+  gs::SpmvArgs a;
+  a.tiles = g->d_stiles.p;
+  a.orowptr = g->d_orowptr.p;
+  a.ocol = g->d_ocol.p;
+  a.Ho = g->d_Ho.p;
+  a.Hd = g->d_Hd.p;
+  a.dscale = g->prm.diagonal_damping ? g->d_dscale.p : nullptr;
+  a.p = p;
+  a.y = y;
+  a.part = g->d_part.p;
+  a.sc = g->d_sc.p;
+  a.counter = g->d_counter.p;
+  a.nnzo = g->S.nnzo;
+  a.N = g->N;
+  a.mode = mode;
+  return a;
+}
+
+gs::PcgArgs pcg_args(gs_graph* g) {
+  gs::PcgArgs a;
+  a.b = g->d_b.p;
+  a.Minv = g->d_Minv.p;
+  a.x = g->d_x.p;
+  a.r = g->d_r.p;
+  a.z = g->d_z.p;
+  a.p = g->d_p.p;
+  a.Ap = g->d_Ap.p;
+  a.part = g->d_part.p;
+  a.sc = g->d_sc.p;
+  a.counter = g->d_counter.p + 1;
+  a.N = g->N;
+  return a;
+}
+
+void launch_pcg_iteration(gs_graph* g) {
+  gs::k_spmv<<<(unsigned)g->S.stiles.size(), gs::kThreads, 0, g->stream>>>(spmv_args(g, g->d_p.p, g->d_Ap.p, 0));
+  gs::k_pcg_update<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
+  gs::k_pcg_dir<<<g->grid_v3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->N);
+}
+
+gs_status capture_pcg_graph(gs_graph* g) {
+  destroy_graph_exec(g);
+  GS_CUDA(g, cudaStreamBeginCapture(g->stream, cudaStreamCaptureModeThreadLocal));
+  for (int it = 0; it < kPcgBatch; ++it) launch_pcg_iteration(g);
+  GS_CUDA(g, cudaStreamEndCapture(g->stream, &g->pcg_graph));
+  GS_CUDA(g, cudaGraphInstantiate(&g->pcg_exec, g->pcg_graph, 0));
+  return GS_OK;
+}
+
+// sort keys -> dense order; identity when keys were inserted in increasing order (the reference's ids)
+void build_dense_order(gs_graph* g) {
+  const int n = (int)g->keys.size();
+  g->identity_order = true;
+  for (int k = 1; k < n; ++k)
+    if (g->keys[k] <= g->keys[k - 1]) {
+      g->identity_order = false;
+      break;
+    }
+  g->dense2ins.resize(n);
+  g->ins2dense.resize(n);
+  for (int k = 0; k < n; ++k) g->dense2ins[k] = k;
+  if (!g->identity_order)
+    std::sort(g->dense2ins.begin(), g->dense2ins.end(), [&](int a, int b) { return g->keys[a] < g->keys[b]; });
+  for (int k = 0; k < n; ++k) g->ins2dense[g->dense2ins[k]] = k;
+}
+
+gs_status download_values(gs_graph* g) {
+  if (!g->device_values_valid || g->host_values_fresh) return GS_OK;
+  const int n = g->N;  // vertices present at the last upload
+  std::vector<double4> tmp(n);
+  GS_CUDA(g, cudaMemcpyAsync(tmp.data(), g->d_pose.p, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  for (int d = 0; d < n; ++d) {
+    const int k = g->dense2ins[d];
+    g->xyt[3 * k] = tmp[d].x;
+    g->xyt[3 * k + 1] = tmp[d].y;
+    g->xyt[3 * k + 2] = std::atan2(tmp[d].w, tmp[d].z);
+  }
+  g->host_values_fresh = true;
+  return GS_OK;
+}
+
+gs_status upload_values(gs_graph* g) {
+  const int n = g->N;
+  std::vector<double4> tmp(n);
+  for (int d = 0; d < n; ++d) {
+    const int k = g->dense2ins[d];
+    tmp[d] = make_double4(g->xyt[3 * k], g->xyt[3 * k + 1], std::cos(g->xyt[3 * k + 2]), std::sin(g->xyt[3 * k + 2]));
+  }
+  GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp.data(), sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  g->device_values_valid = true;
+  g->system_valid = false;
+  return GS_OK;
+}
+
+template <typename T>
+gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
+  GS_CUDA(g, d.alloc(std::max<size_t>(h.size(), 1)));
+  if (!h.empty())
+    GS_CUDA(g, cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, g->stream));
+  return GS_OK;
+}
+
+gs_status prepare(gs_graph* g, double* ms_out) {
+  if (ms_out) *ms_out = 0.0;
+  if (!g->topo_dirty) {
+    if (g->host_values_fresh && !g->device_values_valid) return upload_values(g);
+    return GS_OK;
+  }
+  const double t0 = now_ms();
+  // values may live on the device (warm start, graph.cpp:130): bring them home before re-indexing
+  if (gs_status s = download_values(g)) return s;
+  if (g->keys.empty()) return g->fail(GS_EINVAL, "graph has no vertices");
+  build_dense_order(g);
+  const int N = (int)g->keys.size(), E = (int)g->e1.size(), P = (int)g->pr_v.size();
+  std::vector<int> di(E), dj(E), dp(P);
+  for (int k = 0; k < E; ++k) {
+    di[k] = g->ins2dense[g->e1[k]];
+    dj[k] = g->ins2dense[g->e2[k]];
+  }
+  for (int k = 0; k < P; ++k) dp[k] = g->ins2dense[g->pr_v[k]];
+  gs::build_structure(N, E, di.data(), dj.data(), P, dp.data(), g->S);
+  const HostStructure& S = g->S;
+  g->N = N;
+  g->E = E;
+  g->P = P;
+  // canonical-order factor arrays
+  std::vector<int2> eij(E);
+  std::vector<double2> zt(E), zr(E), o01(E), o23(E), o45(E);
+  for (int k = 0; k < E; ++k) {
+    const int s = S.perm[k];
+    eij[k] = make_int2(S.ci[k], S.cj[k]);
+    zt[k] = make_double2(g->ez[3 * s], g->ez[3 * s + 1]);
+    zr[k] = make_double2(std::cos(g->ez[3 * s + 2]), std::sin(g->ez[3 * s + 2]));
+    o01[k] = make_double2(g->eom[6 * s], g->eom[6 * s + 1]);
+    o23[k] = make_double2(g->eom[6 * s + 2], g->eom[6 * s + 3]);
+    o45[k] = make_double2(g->eom[6 * s + 4], g->eom[6 * s + 5]);
+  }
+  std::vector<double4> prp(P);
+  for (int k = 0; k < P; ++k)
+    prp[k] = make_double4(g->pr_xyt[3 * k], g->pr_xyt[3 * k + 1], std::cos(g->pr_xyt[3 * k + 2]), std::sin(g->pr_xyt[3 * k + 2]));
+  if (gs_status s = upload(g, g->d_eij, eij)) return s;
+  if (gs_status s = upload(g, g->d_zt, zt)) return s;
+  if (gs_status s = upload(g, g->d_zr, zr)) return s;
+  if (gs_status s = upload(g, g->d_o01, o01)) return s;
+  if (gs_status s = upload(g, g->d_o23, o23)) return s;
+  if (gs_status s = upload(g, g->d_o45, o45)) return s;
+  if (gs_status s = upload(g, g->d_pr_idx, dp)) return s;
+  if (gs_status s = upload(g, g->d_pr_pose, prp)) return s;
+  if (gs_status s = upload(g, g->d_pr_om, g->pr_om)) return s;
+  if (gs_status s = upload(g, g->d_crowptr, S.crowptr)) return s;
+  if (gs_status s = upload(g, g->d_ccode, S.c_code)) return s;
+  if (gs_status s = upload(g, g->d_cblk, S.c_blk)) return s;
+  if (gs_status s = upload(g, g->d_orowptr, S.orowptr)) return s;
+  if (gs_status s = upload(g, g->d_ocol, S.ocol)) return s;
+  if (gs_status s = upload(g, g->d_atiles, S.atiles)) return s;
+  if (gs_status s = upload(g, g->d_stiles, S.stiles)) return s;
+  const size_t n3 = 3 * (size_t)N;
+  GS_CUDA(g, g->d_pose.alloc(N));
+  GS_CUDA(g, g->d_pose_try.alloc(N));
+  GS_CUDA(g, g->d_Ho.alloc(std::max<size_t>(9 * (size_t)S.nnzo, 1)));
+  GS_CUDA(g, g->d_Hd.alloc(6 * (size_t)N));
+  GS_CUDA(g, g->d_Minv.alloc(6 * (size_t)N));
+  GS_CUDA(g, g->d_b.alloc(n3));
+  GS_CUDA(g, g->d_x.alloc(n3));
+  GS_CUDA(g, g->d_r.alloc(n3));
+  GS_CUDA(g, g->d_z.alloc(n3));
+  GS_CUDA(g, g->d_p.alloc(n3));
+  GS_CUDA(g, g->d_Ap.alloc(n3));
+  GS_CUDA(g, g->d_dscale.alloc(n3));
+  g->grid_v = (N + gs::kThreads - 1) / gs::kThreads;
+  g->grid_v3 = (int)((n3 + gs::kThreads - 1) / gs::kThreads);
+  g->grid_e = (E + P + gs::kThreads - 1) / gs::kThreads;
+  size_t maxgrid = std::max<size_t>({S.atiles.size(), S.stiles.size(), (size_t)g->grid_v3, (size_t)g->grid_e, 1});
+  GS_CUDA(g, g->d_part.alloc(2 * maxgrid));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));  // staging vectors go out of scope
+  g->topo_dirty = false;
+  g->device_values_valid = false;
+  if (gs_status s = upload_values(g)) return s;
+  if (gs_status s = capture_pcg_graph(g)) return s;
+  if (ms_out) *ms_out = now_ms() - t0;
+  return GS_OK;
+}
+
+gs_status read_scalars(gs_graph* g) {
+  GS_CUDA(g, cudaMemcpyAsync(g->h_sc, g->d_sc.p, sizeof(Scalars), cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  return GS_OK;
+}
+
+gs_status write_scalars(gs_graph* g) {
+  GS_CUDA(g, cudaMemcpyAsync(g->d_sc.p, g->h_sc, sizeof(Scalars), cudaMemcpyHostToDevice, g->stream));
+  return GS_OK;
+}
+
+gs::AsmArgs asm_args(gs_graph* g) {
+  gs::AsmArgs a;
+  a.tiles = g->d_atiles.p;
+  a.crowptr = g->d_crowptr.p;
+  a.c_code = g->d_ccode.p;
+  a.c_blk = g->d_cblk.p;
+  a.e_ij = g->d_eij.p;
+  a.e_zt = g->d_zt.p;
+  a.e_zr = g->d_zr.p;
+  a.e_o01 = g->d_o01.p;
+  a.e_o23 = g->d_o23.p;
+  a.e_o45 = g->d_o45.p;
+  a.pr_idx = g->d_pr_idx.p;
+  a.pr_pose = g->d_pr_pose.p;
+  a.pr_om = g->d_pr_om.p;
+  a.pose = g->d_pose.p;
+  a.Ho = g->d_Ho.p;
+  a.Hd = g->d_Hd.p;
+  a.b = g->d_b.p;
+  a.part = g->d_part.p;
+  a.sc = g->d_sc.p;
+  a.counter = g->d_counter.p + 2;
+  a.nnzo = g->S.nnzo;
+  a.N = g->N;
+  return a;
+}
+
+// linearise + assemble at the current device poses (async)
+gs_status launch_assemble(gs_graph* g) {
+  const unsigned grid = (unsigned)g->S.atiles.size();
+  if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT)
+    gs::k_assemble<1><<<grid, gs::kThreads, gs::kAsmSmemBytes, g->stream>>>(asm_args(g));
+  else
+    gs::k_assemble<0><<<grid, gs::kThreads, gs::kAsmSmemBytes, g->stream>>>(asm_args(g));
+  g->launches += 1;
+  if (g->prm.diagonal_damping) {
+    gs::k_dscale<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->d_dscale.p, g->N);
+    g->launches += 1;
+  }
+  GS_CUDA(g, cudaGetLastError());
+  g->system_valid = true;
+  return GS_OK;
+}
+
+gs_status launch_chi2(gs_graph* g, const double4* pose) {
+  gs::Chi2Args a;
+  a.e_ij = g->d_eij.p;
+  a.e_zt = g->d_zt.p;
+  a.e_zr = g->d_zr.p;
+  a.e_o01 = g->d_o01.p;
+  a.e_o23 = g->d_o23.p;
+  a.e_o45 = g->d_o45.p;
+  a.pr_idx = g->d_pr_idx.p;
+  a.pr_pose = g->d_pr_pose.p;
+  a.pr_om = g->d_pr_om.p;
+  a.pose = pose;
+  a.part = g->d_part.p;
+  a.sc = g->d_sc.p;
+  a.counter = g->d_counter.p + 3;
+  a.E = g->E;
+  a.P = g->P;
+  gs::k_chi2<<<std::max(g->grid_e, 1), gs::kThreads, 0, g->stream>>>(a);
+  g->launches += 1;
+  GS_CUDA(g, cudaGetLastError());
+  return GS_OK;
+}
+
+// Solve (H + lambda D) x = -b by block-Jacobi PCG; result in d_x.  H, b must be assembled.
+gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_out, int* done_out) {
+  Scalars* h = g->h_sc;
+  std::memset(h, 0, sizeof(Scalars));
+  h->lambda = lambda;
+  h->tol2 = g->prm.pcg_rel_tol * g->prm.pcg_rel_tol;
+  h->max_iters = g->prm.pcg_max_iters;
+  if (gs_status s = write_scalars(g)) return s;
+  gs::k_minv<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
+                                                        g->d_sc.p, g->d_Minv.p, g->N);
+  gs::k_pcg_init<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
+  g->launches += 2;
+  GS_CUDA(g, cudaGetLastError());
+  for (;;) {
+    GS_CUDA(g, cudaGraphLaunch(g->pcg_exec, g->stream));
+    if (gs_status s = read_scalars(g)) return s;
+    if (h->done) break;
+  }
+  g->launches += 3 * (int64_t)h->iters;  // kernels that did work (the no-op tail of the last batch is not counted)
+  if (iters_out) *iters_out = h->iters;
+  if (relres_out) *relres_out = h->rr0 > 0.0 ? std::sqrt(h->rr / h->rr0) : 0.0;
+  if (done_out) *done_out = h->done;
+  return GS_OK;
+}
+
+float elapsed(gs_graph* g) {
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, g->ev0, g->ev1);
+  return ms;
+}
+
+}  // namespace
+
+// =================================================================================================
+extern "C" {
+
+void gs_default_params(gs_params* p) {
+  if (!p) return;
+  std::memset(p, 0, sizeof *p);
+  p->max_iterations = 100;
+  p->rel_error_tol = 1e-5;
+  p->abs_error_tol = 1e-5;
+  p->error_tol = 0.0;
+  p->lambda_initial = 1e-5;
+  p->lambda_factor = 10.0;
+  p->lambda_upper = 1e5;
+  p->lambda_lower = 0.0;
+  p->min_model_fidelity = 1e-3;
+  p->diagonal_damping = 0;
+  p->jacobian_mode = GS_JACOBIAN_GTSAM_DEFAULT;
+  p->pcg_rel_tol = 1e-12;
+  p->pcg_max_iters = 100000;
+  p->device = -1;
+  p->rank = 0;
+  p->world_size = 1;
+}
+
+int gs_version(void) { return GS_VERSION_MAJOR * 1000 + GS_VERSION_MINOR; }
+
+gs_status gs_create(gs_graph** out, const gs_params* params) {
+  if (!out) return GS_EINVAL;
+  *out = nullptr;
+  gs_graph* g = new (std::nothrow) gs_graph();
+  if (!g) return GS_EINVAL;
+  if (params) g->prm = *params;
+  else gs_default_params(&g->prm);
+  *out = g;  // returned even on failure so that gs_last_error can be read; caller destroys it
+  if (g->prm.world_size != 1 || g->prm.rank != 0)
+    return g->fail(GS_EINVAL, "multi-rank graphs are created with gs_create_distributed");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return g->fail(GS_ECUDA, "no CUDA device (%s); libgraphslam_cuda has no CPU fallback",
+                   e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (g->prm.device >= 0) GS_CUDA(g, cudaSetDevice(g->prm.device));
+  GS_CUDA(g, cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking));
+  GS_CUDA(g, cudaEventCreate(&g->ev0));
+  GS_CUDA(g, cudaEventCreate(&g->ev1));
+  GS_CUDA(g, g->d_sc.alloc(1));
+  GS_CUDA(g, g->d_counter.alloc(8));
+  GS_CUDA(g, cudaMemsetAsync(g->d_counter.p, 0, 8 * sizeof(unsigned int), g->stream));
+  GS_CUDA(g, cudaMemsetAsync(g->d_sc.p, 0, sizeof(Scalars), g->stream));
+  GS_CUDA(g, cudaMallocHost(&g->h_sc, sizeof(Scalars)));
+  GS_CUDA(g, cudaFuncSetAttribute(gs::k_assemble<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, gs::kAsmSmemBytes));
+  GS_CUDA(g, cudaFuncSetAttribute(gs::k_assemble<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, gs::kAsmSmemBytes));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  return GS_OK;
+}
+
+gs_status gs_destroy(gs_graph* g) {
+  if (!g) return GS_EINVAL;
+  if (g->stream) cudaStreamSynchronize(g->stream);
+  destroy_graph_exec(g);
+  if (g->h_sc) cudaFreeHost(g->h_sc);
+  if (g->ev0) cudaEventDestroy(g->ev0);
+  if (g->ev1) cudaEventDestroy(g->ev1);
+  if (g->stream) cudaStreamDestroy(g->stream);
+  delete g;
+  return GS_OK;
+}
+
+gs_status gs_set_params(gs_graph* g, const gs_params* p) {
+  if (!g || !p) return GS_EINVAL;
+  if (p->world_size != g->prm.world_size || p->rank != g->prm.rank || p->device != g->prm.device)
+    return g->fail(GS_EINVAL, "device/rank/world_size are fixed at gs_create");
+  const bool mode_changed = p->jacobian_mode != g->prm.jacobian_mode || p->diagonal_damping != g->prm.diagonal_damping;
+  g->prm = *p;
+  if (mode_changed) g->system_valid = false;
+  return GS_OK;
+}
+
+gs_status gs_add_vertex(gs_graph* g, uint64_t key, const double pose[3]) {
+  if (!g || !pose) return GS_EINVAL;
+  if (!(std::isfinite(pose[0]) && std::isfinite(pose[1]) && std::isfinite(pose[2])))
+    return g->fail(GS_EINVAL, "non-finite pose for key %llu", (unsigned long long)key);
+  if (g->find(key) >= 0) return g->fail(GS_EDUPKEY, "key %llu already present", (unsigned long long)key);
+  if (gs_status s = download_values(g)) return s;
+  const int idx = (int)g->keys.size();
+  if (g->keys_sequential && idx > 0 && key != g->keys[0] + (uint64_t)idx) {
+    g->keys_sequential = false;
+    g->key2ins.reserve(g->keys.size() * 2);
+    for (int k = 0; k < idx; ++k) g->key2ins[g->keys[k]] = k;
+  }
+  if (!g->keys_sequential) g->key2ins[key] = idx;
+  g->keys.push_back(key);
+  g->xyt.insert(g->xyt.end(), pose, pose + 3);
+  g->topo_dirty = true;
+  return GS_OK;
+}
+
+gs_status gs_add_prior(gs_graph* g, uint64_t key, const double pose[3], const double cov9[9]) {
+  if (!g || !pose || !cov9) return GS_EINVAL;
+  const int v = g->find(key);
+  if (v < 0) return g->fail(GS_ENOKEY, "prior on unknown key %llu", (unsigned long long)key);
+  double om[6];
+  if (!spd_information(cov9, om)) return g->fail(GS_ENOTSPD, "prior covariance on key %llu is not SPD", (unsigned long long)key);
+  g->pr_v.push_back(v);
+  g->pr_xyt.insert(g->pr_xyt.end(), pose, pose + 3);
+  g->pr_om.insert(g->pr_om.end(), om, om + 6);
+  g->topo_dirty = true;
+  return GS_OK;
+}
+
+gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3], const double cov9[9]) {
+  if (!g || !d || !cov9) return GS_EINVAL;
+  const int a = g->find(k1), b = g->find(k2);
+  if (a < 0 || b < 0)
+    return g->fail(GS_ENOKEY, "between factor names unknown key %llu", (unsigned long long)(a < 0 ? k1 : k2));
+  if (a == b) return g->fail(GS_EINVAL, "between factor from key %llu to itself", (unsigned long long)k1);
+  if (!(std::isfinite(d[0]) && std::isfinite(d[1]) && std::isfinite(d[2]))) return g->fail(GS_EINVAL, "non-finite delta");
+  double om[6];
+  if (!spd_information(cov9, om))
+    return g->fail(GS_ENOTSPD, "covariance of factor %llu->%llu is not SPD", (unsigned long long)k1, (unsigned long long)k2);
+  g->e1.push_back(a);
+  g->e2.push_back(b);
+  g->ez.insert(g->ez.end(), d, d + 3);
+  g->eom.insert(g->eom.end(), om, om + 6);
+  g->topo_dirty = true;
+  return GS_OK;
+}
+
+gs_status gs_add_batch(gs_graph* g, size_t nv, const uint64_t* keys, const double* poses, size_t ne, const uint64_t* k1,
+                       const uint64_t* k2, const double* deltas, const double* cov9s) {
+  if (!g) return GS_EINVAL;
+  if ((nv && (!keys || !poses)) || (ne && (!k1 || !k2 || !deltas || !cov9s))) return g->fail(GS_EINVAL, "null array");
+  g->keys.reserve(g->keys.size() + nv);
+  g->xyt.reserve(g->xyt.size() + 3 * nv);
+  for (size_t k = 0; k < nv; ++k)
+    if (gs_status s = gs_add_vertex(g, keys[k], poses + 3 * k)) return s;
+  g->e1.reserve(g->e1.size() + ne);
+  g->e2.reserve(g->e2.size() + ne);
+  g->ez.reserve(g->ez.size() + 3 * ne);
+  g->eom.reserve(g->eom.size() + 6 * ne);
+  for (size_t k = 0; k < ne; ++k)
+    if (gs_status s = gs_add_between(g, k1[k], k2[k], deltas + 3 * k, cov9s + 9 * k)) return s;
+  return GS_OK;
+}
+
+gs_status gs_prepare(gs_graph* g) {
+  if (!g) return GS_EINVAL;
+  return prepare(g, nullptr);
+}
+
+gs_status gs_optimize(gs_graph* g, gs_stats* st) {
+  if (!g) return GS_EINVAL;
+  const double t_begin = now_ms();
+  gs_stats local;
+  std::memset(&local, 0, sizeof local);
+  double ms_structure = 0.0;
+  if (gs_status s = prepare(g, &ms_structure)) return s;
+  local.ms_structure = ms_structure;
+  const gs_params& P = g->prm;
+  Scalars* h = g->h_sc;
+  g->tr_err.clear();
+  g->tr_lambda.clear();
+  g->tr_tries.clear();
+  g->launches = 0;
+
+  // error at the initial values
+  if (gs_status s = launch_chi2(g, g->d_pose.p)) return s;
+  if (gs_status s = read_scalars(g)) return s;
+  double error = 0.5 * h->chi2;
+  if (!std::isfinite(error)) return g->fail(GS_ENAN, "initial chi2 is not finite");
+  local.chi2_initial = 2.0 * error;
+  g->tr_err.push_back(error);
+  double lambda = P.lambda_initial;
+  int iterations = 0;
+  gs_status rc = GS_OK;
+  const double eps = std::numeric_limits<double>::epsilon();
+
+  while (iterations < P.max_iterations) {
+    const double current_error = error;
+    // ---- iterate(): linearise once
+    GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
+    if (gs_status s = launch_assemble(g)) return s;
+    GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
+    GS_CUDA(g, cudaEventSynchronize(g->ev1));
+    local.ms_linearize += elapsed(g);
+    local.outer_loops += 1;
+    int tries = 0;
+    for (;;) {  // tryLambda
+      ++tries;
+      local.inner_iterations += 1;
+      GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
+      int pit = 0, done = 0;
+      double relres = 0.0;
+      if (gs_status s = pcg_solve(g, lambda, &pit, &relres, &done)) return s;
+      GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
+      GS_CUDA(g, cudaEventSynchronize(g->ev1));
+      local.ms_solve += elapsed(g);
+      local.pcg_iterations_total += pit;
+      const bool solved = (done == 1);
+      if (done == 3) rc = GS_ENOTCONVERGED;
+      bool step_ok = false, stop_search = false;
+      double new_error = std::numeric_limits<double>::infinity();
+      if (solved || done == 3) {
+        // linear.error(0) - linear.error(delta) = -delta.b - 0.5 delta.H.delta  (undamped H)
+        GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
+        gs::k_spmv<<<(unsigned)g->S.stiles.size(), gs::kThreads, 0, g->stream>>>(spmv_args(g, g->d_x.p, g->d_Ap.p, 1));
+        if (gs_status s = read_scalars(g)) return s;
+        const double dHd = h->dot;
+        gs::k_dot<<<g->grid_v3, gs::kThreads, 0, g->stream>>>(g->d_x.p, g->d_b.p, 3 * g->N, g->d_part.p, g->d_sc.p,
+                                                              g->d_counter.p + 4);
+        if (gs_status s = read_scalars(g)) return s;
+        const double db = h->dot;
+        g->launches += 2;
+        const double lin_change = -db - 0.5 * dHd;
+        if (lin_change >= 0.0) {
+          gs::k_retract<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_pose.p, g->d_x.p, g->d_pose_try.p, g->N);
+          g->launches += 1;
+          if (gs_status s = launch_chi2(g, g->d_pose_try.p)) return s;
+          if (gs_status s = read_scalars(g)) return s;
+          new_error = 0.5 * h->chi2;
+          const double cost_change = error - new_error;
+          if (lin_change > eps * error) {
+            const double fidelity = cost_change / lin_change;
+            step_ok = fidelity > P.min_model_fidelity;
+          }
+          if (std::fabs(cost_change) < P.rel_error_tol * error) stop_search = true;
+        }
+        GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
+        GS_CUDA(g, cudaEventSynchronize(g->ev1));
+        local.ms_update += elapsed(g);
+      }
+      if (step_ok) {
+        g->tr_lambda.push_back(lambda);
+        std::swap(g->d_pose.p, g->d_pose_try.p);  // accept: candidate becomes current
+        g->host_values_fresh = false;
+        g->system_valid = false;
+        error = new_error;
+        lambda = std::max(P.lambda_lower, lambda / P.lambda_factor);
+        ++iterations;
+        break;
+      } else if (!stop_search) {
+        lambda *= P.lambda_factor;
+        if (lambda >= P.lambda_upper) break;
+      } else {
+        break;
+      }
+    }
+    g->tr_tries.push_back(tries);
+    g->tr_err.push_back(error);
+    if (!std::isfinite(error)) {
+      rc = g->fail(GS_ENAN, "chi2 became non-finite");
+      break;
+    }
+    // ---- checkConvergence(relTol, absTol, errTol, currentError, newError)
+    if (iterations >= P.max_iterations) break;
+    if (error <= P.error_tol) { local.converged = 1; break; }
+    const double abs_dec = current_error - error;
+    const double rel_dec = current_error != 0.0 ? abs_dec / current_error : 0.0;
+    if ((P.rel_error_tol != 0.0 && rel_dec <= P.rel_error_tol) || abs_dec <= P.abs_error_tol) { local.converged = 1; break; }
+  }
+  local.iterations = iterations;
+  local.chi2_final = 2.0 * error;
+  local.lambda_final = lambda;
+  local.ms_total = now_ms() - t_begin;
+  local.edges_per_sec = local.ms_linearize > 0 ? (double)g->E * local.outer_loops / (local.ms_linearize * 1e-3) : 0.0;
+  const double t_iter = local.ms_total - local.ms_structure;
+  local.gn_iters_per_sec = t_iter > 0 ? local.outer_loops / (t_iter * 1e-3) : 0.0;
+  local.reserved[0] = (double)g->launches;
+  if (st) *st = local;
+  return rc;
+}
+
+gs_status gs_get_pose(gs_graph* g, uint64_t key, double out[3]) {
+  if (!g || !out) return GS_EINVAL;
+  const int v = g->find(key);
+  if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)key);
+  if (gs_status s = download_values(g)) return s;
+  out[0] = g->xyt[3 * v];
+  out[1] = g->xyt[3 * v + 1];
+  out[2] = std::atan2(std::sin(g->xyt[3 * v + 2]), std::cos(g->xyt[3 * v + 2]));
+  return GS_OK;
+}
+
+gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* n) {
+  if (!g) return GS_EINVAL;
+  const size_t nv = g->keys.size();
+  if (n) *n = nv;
+  if (!keys && !xyt) return GS_OK;
+  if (cap < nv) return g->fail(GS_EINVAL, "capacity %zu < %zu vertices", cap, nv);
+  if (gs_status s = download_values(g)) return s;
+  if (g->dense2ins.size() != nv) build_dense_order(g);
+  for (size_t d = 0; d < nv; ++d) {
+    const int k = g->dense2ins[d];
+    if (keys) keys[d] = g->keys[k];
+    if (xyt) {
+      xyt[3 * d] = g->xyt[3 * k];
+      xyt[3 * d + 1] = g->xyt[3 * k + 1];
+      xyt[3 * d + 2] = std::atan2(std::sin(g->xyt[3 * k + 2]), std::cos(g->xyt[3 * k + 2]));
+    }
+  }
+  return GS_OK;
+}
+
+gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt) {
+  if (!g || (n && (!keys || !xyt))) return GS_EINVAL;
+  if (gs_status s = download_values(g)) return s;
+  for (size_t k = 0; k < n; ++k) {
+    const int v = g->find(keys[k]);
+    if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[k]);
+    g->xyt[3 * v] = xyt[3 * k];
+    g->xyt[3 * v + 1] = xyt[3 * k + 1];
+    g->xyt[3 * v + 2] = xyt[3 * k + 2];
+  }
+  g->host_values_fresh = true;
+  g->device_values_valid = false;
+  g->system_valid = false;
+  if (!g->topo_dirty) return upload_values(g);
+  return GS_OK;
+}
+
+gs_status gs_chi2(gs_graph* g, double* chi2) {
+  if (!g || !chi2) return GS_EINVAL;
+  if (gs_status s = prepare(g, nullptr)) return s;
+  if (gs_status s = launch_chi2(g, g->d_pose.p)) return s;
+  if (gs_status s = read_scalars(g)) return s;
+  *chi2 = g->h_sc->chi2;
+  return GS_OK;
+}
+
+gs_status gs_num_vertices(const gs_graph* g, size_t* n) {
+  if (!g || !n) return GS_EINVAL;
+  *n = g->keys.size();
+  return GS_OK;
+}
+
+gs_status gs_num_factors(const gs_graph* g, size_t* n) {
+  if (!g || !n) return GS_EINVAL;
+  *n = g->e1.size() + g->pr_v.size();
+  return GS_OK;
+}
+
+gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* nnzb) {
+  if (!g) return GS_EINVAL;
+  if (gs_status s = prepare(g, nullptr)) return s;
+  if (nnzb) *nnzb = (size_t)g->S.nnzo + g->N;
+  if (!rowptr && !colidx) return GS_OK;
+  std::vector<int32_t> rp, ci;
+  g->S.full_pattern(rp, ci);
+  if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
+  if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
+  return GS_OK;
+}
+
+gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) {
+  if (!g) return GS_EINVAL;
+  if (gs_status s = prepare(g, nullptr)) return s;
+  if (gs_status s = launch_assemble(g)) return s;
+  if (gs_status s = read_scalars(g)) return s;
+  if (chi2) *chi2 = g->h_sc->chi2;
+  const int N = g->N, nnzo = g->S.nnzo;
+  if (b) {
+    GS_CUDA(g, cudaMemcpyAsync(b, g->d_b.p, sizeof(double) * 3 * N, cudaMemcpyDeviceToHost, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  }
+  if (blocks) {
+    std::vector<double> ho(9 * (size_t)std::max(nnzo, 1)), hd(6 * (size_t)N);
+    if (nnzo) GS_CUDA(g, cudaMemcpyAsync(ho.data(), g->d_Ho.p, sizeof(double) * 9 * nnzo, cudaMemcpyDeviceToHost, g->stream));
+    GS_CUDA(g, cudaMemcpyAsync(hd.data(), g->d_Hd.p, sizeof(double) * 6 * N, cudaMemcpyDeviceToHost, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+    size_t w = 0;
+    const HostStructure& S = g->S;
+    auto put_off = [&](int k) {
+      for (int m = 0; m < 9; ++m) blocks[9 * w + m] = ho[(size_t)m * nnzo + k];
+      ++w;
+    };
+    for (int r = 0; r < N; ++r) {
+      int k = S.orowptr[r];
+      const int k1 = S.orowptr[r + 1];
+      while (k < k1 && S.ocol[k] < r) put_off(k++);
+      const double d00 = hd[r], d01 = hd[(size_t)N + r], d02 = hd[2 * (size_t)N + r];
+      const double d11 = hd[3 * (size_t)N + r], d12 = hd[4 * (size_t)N + r], d22 = hd[5 * (size_t)N + r];
+      const double full[9] = {d00, d01, d02, d01, d11, d12, d02, d12, d22};
+      std::memcpy(blocks + 9 * w, full, sizeof full);
+      ++w;
+      while (k < k1) put_off(k++);
+    }
+  }
+  return GS_OK;
+}
+
+gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual) {
+  if (!g) return GS_EINVAL;
+  if (gs_status s = prepare(g, nullptr)) return s;
+  if (!g->system_valid)
+    if (gs_status s = launch_assemble(g)) return s;
+  int done = 0;
+  if (gs_status s = pcg_solve(g, lambda, pcg_iters, rel_residual, &done)) return s;
+  if (delta) {
+    GS_CUDA(g, cudaMemcpyAsync(delta, g->d_x.p, sizeof(double) * 3 * g->N, cudaMemcpyDeviceToHost, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  }
+  if (done == 2) return g->fail(GS_ENAN, "PCG breakdown (p^T A p <= 0 or NaN)");
+  if (done == 3) return g->fail(GS_ENOTCONVERGED, "PCG reached pcg_max_iters");
+  return GS_OK;
+}
+
+gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n) {
+  if (!g) return GS_EINVAL;
+  const size_t m = g->tr_tries.size();
+  if (n) *n = m;
+  if (!errors && !lambdas && !tries) return GS_OK;
+  if (cap < m) return g->fail(GS_EINVAL, "capacity %zu < %zu outer iterations", cap, m);
+  if (errors) std::copy(g->tr_err.begin(), g->tr_err.end(), errors);
+  if (lambdas) {
+    std::fill(lambdas, lambdas + m, 0.0);
+    std::copy(g->tr_lambda.begin(), g->tr_lambda.end(), lambdas);
+  }
+  if (tries) std::copy(g->tr_tries.begin(), g->tr_tries.end(), tries);
+  return GS_OK;
+}
+
+const char* gs_last_error(const gs_graph* g) { return g ? g->err.c_str() : "null graph"; }
+
+void gs_compose_reference(const double a[3], const double b[3], double out[3]) {
+  // graph.hpp:30-43, restated with both quirks
+  const double cos_th = std::cos(a[2]);
+  const double sin_th = std::sin(a[2]);
+  const double dx = b[0], dy = b[1], dth = b[2];
+  const double x = (cos_th * dx) + (-sin_th * dy);
+  const double y = (sin_th * dx) + (cos_th * dy);
+  double th = a[2] + dth;
+  th = std::fmod(th + M_PI, 2 * M_PI) - M_PI;
+  out[0] = x;
+  out[1] = y;
+  out[2] = th;
+}
+
+void gs_compose(const double a[3], const double b[3], double out[3]) {
+  const double c = std::cos(a[2]), s = std::sin(a[2]);
+  const double x = a[0] + c * b[0] - s * b[1];
+  const double y = a[1] + s * b[0] + c * b[1];
+  const double th = a[2] + b[2];
+  out[0] = x;
+  out[1] = y;
+  out[2] = std::atan2(std::sin(th), std::cos(th));
+}
+
+gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist) {
+  if (!g || !out_key || skip < 0) return GS_EINVAL;
+  const int v = g->find(key);
+  if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)key);
+  const int nv = (int)g->keys.size();
+  if (nv <= skip) return g->fail(GS_ENOKEY, "not enough keyframes (%d <= skip %d)", nv, skip);
+  if (gs_status s = prepare(g, nullptr)) return s;
+  const int count = nv - skip;
+  // query pose from the device copy (insertion order -> dense index)
+  double4 q;
+  GS_CUDA(g, cudaMemcpyAsync(&q, g->d_pose.p + g->ins2dense[v], sizeof q, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  DevBuf<int> d_order;
+  const int* order = nullptr;
+  if (!g->identity_order) {
+    std::vector<int> ord(g->ins2dense.begin(), g->ins2dense.begin() + count);
+    GS_CUDA(g, d_order.alloc(count));
+    GS_CUDA(g, cudaMemcpyAsync(d_order.p, ord.data(), sizeof(int) * count, cudaMemcpyHostToDevice, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+    order = d_order.p;
+  }
+  double* d_best = g->d_part.p;
+  int* d_idx = reinterpret_cast<int*>(g->d_part.p + 1);
+  gs::k_closest<<<1, gs::kThreads, 0, g->stream>>>(g->d_pose.p, order, count, q.x, q.y, d_best, d_idx);
+  double bd;
+  int bi;
+  GS_CUDA(g, cudaMemcpyAsync(&bd, d_best, sizeof bd, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaMemcpyAsync(&bi, d_idx, sizeof bi, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  *out_key = g->keys[bi];
+  if (out_dist) *out_dist = bd;
+  return GS_OK;
+}
+
+// ---- host-only debug entries (no device needed): exercise the product's own host code on a CPU box
+gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,
+                          size_t* nnzb, int32_t* perm) {
+  if (n <= 0 || e < 0 || (e && (!ei || !ej))) return GS_EINVAL;
+  HostStructure S;
+  gs::build_structure(n, e, ei, ej, 0, nullptr, S);
+  if (nnzb) *nnzb = (size_t)S.nnzo + n;
+  if (rowptr || colidx) {
+    std::vector<int32_t> rp, ci;
+    S.full_pattern(rp, ci);
+    if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
+    if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
+  }
+  if (perm) std::memcpy(perm, S.perm.data(), sizeof(int32_t) * e);
+  return GS_OK;
+}
+
+// one factor, host evaluation of the same inline functions the kernels use
+gs_status gs_host_between(const double pi[3], const double pj[3], const double z[3], const double cov9[9], int mode,
+                          double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],
+                          double bi[3], double bj[3]) {
+  double om[6];
+  if (!spd_information(cov9, om)) return GS_ENOTSPD;
+  const double4 a = make_double4(pi[0], pi[1], std::cos(pi[2]), std::sin(pi[2]));
+  const double4 b = make_double4(pj[0], pj[1], std::cos(pj[2]), std::sin(pj[2]));
+  const double2 zt = make_double2(z[0], z[1]), zr = make_double2(std::cos(z[2]), std::sin(z[2]));
+  gs::BetweenLin L;
+  if (mode == 0) gs::between_linearize<0>(a, b, zt, zr, L);
+  else gs::between_linearize<1>(a, b, zt, zr, L);
+  gs::Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
+  double off[9], dg[6], bv[3];
+  gs::normal_pieces(O, L.Ai, L.Aj, L.e, off, dg, bv);
+  const double fi[9] = {dg[0], dg[1], dg[2], dg[1], dg[3], dg[4], dg[2], dg[4], dg[5]};
+  std::memcpy(Hii, fi, sizeof fi);
+  std::memcpy(Hij, off, sizeof off);
+  std::memcpy(bi, bv, sizeof bv);
+  gs::normal_pieces(O, L.Aj, L.Ai, L.e, off, dg, bv);
+  const double fj[9] = {dg[0], dg[1], dg[2], dg[1], dg[3], dg[4], dg[2], dg[4], dg[5]};
+  std::memcpy(Hjj, fj, sizeof fj);
+  std::memcpy(bj, bv, sizeof bv);
+  std::memcpy(e, L.e, sizeof L.e);
+  std::memcpy(Ai, L.Ai.m, sizeof L.Ai.m);
+  std::memcpy(Aj, L.Aj.m, sizeof L.Aj.m);
+  return GS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,153 @@
+/* libgraphslam_cuda — B200-native (sm_100a) pose-graph optimisation backend, C ABI.
+ *
+ * Drop-in boundary for the optimiser behind Sergimech/GraphSLAM's `src/graph` node.  The node keeps
+ * its verbs (prior_factor / new_factor / loop_factor / solve, reference
+ * src/graph/src/graph.cpp:27-132); what it hands to GTSAM today
+ * (gtsam::NonlinearFactorGraph + gtsam::Values + LevenbergMarquardtOptimizer, graph.cpp:6-7,119)
+ * it hands to this library instead.  Each entry point cites the reference call it replaces.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; the caller owns every pointer it passes, inputs are copied
+ *    before return; no exceptions cross the ABI; no global state (graph.cpp:5-10's globals live in
+ *    gs_graph).
+ *  - poses / deltas are (x, y, theta) doubles; covariances are float64[9] row-major exactly as
+ *    common/Pose2DWithCovariance.msg:2 and graph.hpp:45-58 (covariance_to_eigen).
+ *  - keys are arbitrary uint64 (gtsam::Key); dense index = rank in sorted key order
+ *    (= key-1 for the reference's ids, graph.cpp:31,48,68,75).
+ *  - a gs_graph is single-writer (the reference runs on one ros::spin() thread, graph.cpp:214);
+ *    all device work runs on one per-graph CUDA stream; gs_optimize is synchronous on return.
+ *  - there is NO CPU fallback: without a CUDA device gs_create returns GS_ECUDA.
+ */
+#ifndef GRAPHSLAM_CUDA_H
+#define GRAPHSLAM_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS_VERSION_MAJOR 0
+#define GS_VERSION_MINOR 1
+
+typedef struct gs_graph gs_graph; /* opaque; owns all host and device memory */
+
+typedef enum {
+  GS_OK = 0,
+  GS_EINVAL = 1,        /* bad argument */
+  GS_ENOTSPD = 2,       /* covariance not symmetric positive definite (GTSAM would throw, graph.cpp:45,83,103) */
+  GS_EDUPKEY = 3,       /* gs_add_vertex with an existing key (gtsam::Values::insert would throw) */
+  GS_ENOKEY = 4,        /* factor or query names an unknown key */
+  GS_ECUDA = 5,         /* CUDA runtime failure, see gs_last_error */
+  GS_ENCCL = 6,         /* NCCL failure (multi-GPU) */
+  GS_ENOTCONVERGED = 7, /* PCG hit pcg_max_iters before pcg_rel_tol */
+  GS_ENAN = 8           /* non-finite chi2 */
+} gs_status;
+
+enum { GS_JACOBIAN_GTSAM_DEFAULT = 0, GS_JACOBIAN_EXACT = 1 };
+
+/* Defaults == gtsam::LevenbergMarquardtParams defaults, i.e. what graph.cpp:119 runs with. */
+typedef struct gs_params {
+  int max_iterations;        /* 100   */
+  double rel_error_tol;      /* 1e-5  */
+  double abs_error_tol;      /* 1e-5  */
+  double error_tol;          /* 0     */
+  double lambda_initial;     /* 1e-5  */
+  double lambda_factor;      /* 10    */
+  double lambda_upper;       /* 1e5   */
+  double lambda_lower;       /* 0     */
+  double min_model_fidelity; /* 1e-3  */
+  int diagonal_damping;      /* 0 (lambda*I); 1 = lambda*diag(H) clipped to [1e-6,1e32] */
+  int jacobian_mode;         /* GS_JACOBIAN_GTSAM_DEFAULT */
+  double pcg_rel_tol;        /* 1e-12: |r|_2 <= tol*|g|_2 */
+  int pcg_max_iters;         /* 100000 */
+  int device;                /* CUDA device ordinal, -1 = current */
+  int rank;                  /* multi-GPU: this process's rank (0)      */
+  int world_size;            /* multi-GPU: number of ranks (1)          */
+  int reserved[8];
+} gs_params;
+
+typedef struct gs_stats {
+  int iterations;            /* accepted outer LM iterations                                  */
+  int outer_loops;           /* linearisations performed (= iterate() calls)                  */
+  int inner_iterations;      /* tryLambda calls (linear solves)                               */
+  int converged;             /* 1 if a GTSAM stop test fired, 0 if max_iterations             */
+  double chi2_initial;       /* 2 * graph.error(initial)                                      */
+  double chi2_final;
+  double lambda_final;
+  int64_t pcg_iterations_total;
+  double ms_structure;       /* structure build + upload (0 if topology unchanged)            */
+  double ms_linearize;       /* linearise + assemble kernels, summed                          */
+  double ms_solve;           /* PCG, summed                                                   */
+  double ms_update;          /* retract + chi2 + model-fidelity kernels, summed               */
+  double ms_total;           /* wall time of gs_optimize                                      */
+  double edges_per_sec;      /* E * outer_loops / ms_linearize                                */
+  double gn_iters_per_sec;   /* outer_loops / (ms_total - ms_structure)                       */
+  double reserved[8];
+} gs_stats;
+
+void gs_default_params(gs_params* p);
+int gs_version(void);
+
+/* lifecycle — replaces the file-scope `graph` / `initial` objects, graph.cpp:6-7 */
+gs_status gs_create(gs_graph** out, const gs_params* params /* NULL = defaults */);
+gs_status gs_destroy(gs_graph* g);
+gs_status gs_set_params(gs_graph* g, const gs_params* params);
+
+/* initial.insert(key, Pose2)                                   graph.cpp:58, 86 */
+gs_status gs_add_vertex(gs_graph* g, uint64_t key, const double pose_xyt[3]);
+/* graph.add(PriorFactor<Pose2>(key, pose, Gaussian::Covariance(Q)))   graph.cpp:45, 57 */
+gs_status gs_add_prior(gs_graph* g, uint64_t key, const double pose_xyt[3], const double cov9[9]);
+/* graph.add(BetweenFactor<Pose2>(k1, k2, Pose2(dx,dy,dth), Gaussian::Covariance(Q)))
+ *                                                               graph.cpp:83-92 (odometry), 103-111 (loop) */
+gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double delta_xyt[3], const double cov9[9]);
+/* bulk form of the two calls above (nv vertices then ne between-factors), same semantics */
+gs_status gs_add_batch(gs_graph* g, size_t nv, const uint64_t* keys, const double* poses_xyt, size_t ne,
+                       const uint64_t* k1, const uint64_t* k2, const double* deltas_xyt, const double* cov9s);
+
+/* upload pending vertices/factors and (re)build the sparse structure now; gs_optimize does this
+ * lazily.  Separates one-off topology work from the per-iteration path for measurement. */
+gs_status gs_prepare(gs_graph* g);
+
+/* gtsam::LevenbergMarquardtOptimizer(graph, initial).optimize(); result kept as the next initial
+ * values (warm start)                                           graph.cpp:119, 130 */
+gs_status gs_optimize(gs_graph* g, gs_stats* stats /* nullable */);
+
+/* poses_opti.at<Pose2>(id).x()/y()/theta()                      graph.cpp:123-125 */
+gs_status gs_get_pose(gs_graph* g, uint64_t key, double out_xyt[3]);
+/* all poses in sorted-key order, AoS (x,y,theta), theta in (-pi,pi]; keys/xyt may be NULL */
+gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* n);
+/* overwrite current values (initial.update)                     */
+gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt);
+/* 2 * graph.error(values) at the current values                 */
+gs_status gs_chi2(gs_graph* g, double* chi2);
+gs_status gs_num_vertices(const gs_graph* g, size_t* n);
+gs_status gs_num_factors(const gs_graph* g, size_t* n);          /* graph.nrFactors(), graph.cpp:60 */
+
+/* ---- parity hooks (integer structure must match the oracle bit-exactly) ---- */
+/* sorted unique 3x3 block pattern of H incl. the diagonal; pass NULLs to query nnzb */
+gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr /* N+1 */, int32_t* colidx /* nnzb */, size_t* nnzb);
+/* linearise at the current values: blocks[nnzb*9] row-major on the pattern above, b[3N] = sum J^T Omega e */
+gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2);
+/* solve (H + lambda*I) delta = -b at the current linearisation by block-Jacobi PCG; delta[3N] */
+gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual);
+/* per-outer-iteration trace of the last gs_optimize: errors[n+1] (= chi2/2, [0] initial), lambdas[n], tries[n] */
+gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n);
+
+const char* gs_last_error(const gs_graph* g);
+
+/* host helpers: graph.hpp:30-43 restated bit-for-bit (input_1's translation dropped, one-sided fmod wrap) */
+void gs_compose_reference(const double a_xyt[3], const double b_xyt[3], double out_xyt[3]);
+/* the correct SE(2) a (+) b (gtsam::Pose2::compose), theta wrapped by atan2 */
+void gs_compose(const double a_xyt[3], const double b_xyt[3], double out_xyt[3]);
+
+/* closest_keyframe service, graph.cpp:146-178: nearest (Euclidean x,y) vertex to `key` among all but
+ * the last `skip` vertices (insertion order), ties -> lowest index (strict '<', graph.cpp:162).
+ * Returns GS_ENOKEY if fewer than skip+1 vertices exist (service returns false). */
+gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAPHSLAM_CUDA_H */

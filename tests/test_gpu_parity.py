@@ -1,0 +1,278 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on identical inputs.
+
+Tolerances (BASELINE.json north_star): chi2 within 1e-9 relative, poses within 1e-6 (theta modulo 2pi), FP64;
+graph indexing and assembly sparsity bit-exact.  Linearisation pieces are compared at 1e-11 relative to the
+block scale (pure rounding / summation-order differences)."""
+import os
+
+import numpy as np
+import pytest
+
+from graphslam_b200 import _lib, graph, synth
+from oracle import gs_oracle as O
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+CHI2_RTOL = 1e-9
+POSE_ATOL = 1e-6
+
+
+def _load(g, **params):
+    G = graph.Graph(**params)
+    G.add_graph(g)
+    return G
+
+
+def _pose_diff(a, b):
+    d = np.abs(a[:, :2] - b[:, :2]).max()
+    return max(d, np.abs(O.wrap_pi(a[:, 2] - b[:, 2])).max())
+
+
+def _check_system(g, mode=0):
+    prob = O.Problem.from_graph(g)
+    with _load(g, jacobian_mode=mode) as G:
+        rowptr, colidx, blocks, b, chi2 = G.system()
+        orp, oci = prob.pattern()
+        assert np.array_equal(rowptr, orp) and np.array_equal(colidx, oci)          # bit-exact integers
+        h, ob, ochi2 = prob.linearize(g.init, mode)
+        _, _, oblocks = prob.bsr(h)
+        scale = np.abs(oblocks).max()
+        assert np.abs(blocks - oblocks).max() <= 1e-11 * scale
+        assert np.abs(b - ob).max() <= 1e-11 * np.abs(ob).max()
+        assert chi2 == pytest.approx(ochi2, rel=1e-12)
+        assert G.chi2() == pytest.approx(prob.chi2(g.init), rel=1e-12)
+    return prob
+
+
+@pytest.mark.parametrize("cid,n,kw", [("C1", None, {}), ("C1", None, dict(full_cov=True)), ("C3", 20000, dict(full_cov=True)),
+                                      ("C4", 3000, {}), ("C2", 30000, {})])
+def test_linearize_assemble_parity(cid, n, kw):
+    _check_system(synth.config(cid, n=n, **kw), 0)
+
+
+def test_linearize_assemble_parity_exact_jacobians():
+    _check_system(synth.config("C4", n=2000, full_cov=True), 1)
+
+
+def test_hub_and_duplicate_edges_assemble():
+    """A hub vertex with more factor sides than one shared-memory chunk, >256 duplicates of one pair,
+    both directions of a pair, isolated vertices."""
+    rng = np.random.default_rng(9)
+    n = 400
+    base = synth.manhattan(n, seed=77, target_edges=600)
+    i, j = base.dense_edges()
+    hub_j = rng.integers(1, n - 5, 700)
+    dup = np.full(300, 7)
+    ei = np.r_[i, np.zeros(700, np.int64), dup, np.full(40, 9)]
+    ej = np.r_[j, hub_j, np.full(300, 3), np.full(40, 7)]
+    ne = len(ei)
+    z = synth.between(base.gt[ei], base.gt[ej]) + 0.01 * rng.normal(size=(ne, 3))
+    cov = np.tile(np.diag([0.01, 0.02, 0.005]).reshape(9), (ne, 1))
+    g = synth.PoseGraph("hub", base.keys, base.init, base.gt, (ei + 1).astype(np.uint64), (ej + 1).astype(np.uint64), z, cov)
+    prob = _check_system(g, 0)
+    with _load(g) as G:
+        d, it, rr = G.solve_linear(1e-3)
+        h, b, _ = prob.linearize(g.init)
+        want = O.solve_damped(h, b, 1e-3)
+        assert rr <= 1e-12
+        assert np.abs(d - want).max() <= 1e-7 * max(1.0, np.abs(want).max())
+
+
+def test_pcg_matches_direct_solve():
+    g = synth.config("C1")
+    prob = O.Problem.from_graph(g)
+    h, b, _ = prob.linearize(g.init)
+    with _load(g) as G:
+        for lam in (1e-5, 1e-2, 10.0):
+            d, it, rr = G.solve_linear(lam)
+            want = O.solve_damped(h, b, lam)
+            assert rr <= 1e-12 and it > 0
+            res = (h @ d.ravel() + lam * d.ravel() + b.ravel())
+            assert np.linalg.norm(res) <= 1e-10 * np.linalg.norm(b)
+            assert np.abs(d - want).max() <= 1e-8 * np.abs(want).max()
+
+
+def _trace_parity(g, mode=0, gold=None, **oparams):
+    prob = O.Problem.from_graph(g)
+    ox, otr = O.lm_optimize(prob, g.init, O.LMParams(jacobian_mode=mode, **oparams))
+    with _load(g, jacobian_mode=mode, **oparams) as G:
+        st = G.optimize()
+        errors, lambdas, tries = G.trace()
+        keys, x = G.poses()
+        assert np.array_equal(keys, np.sort(g.keys))
+        assert st["iterations"] == otr.iterations
+        assert tries.tolist() == otr.tries                                   # same accept/reject sequence
+        assert np.allclose(errors, otr.errors, rtol=CHI2_RTOL, atol=0)       # chi2_k within 1e-9 relative, every k
+        assert np.allclose(lambdas, otr.lambdas, rtol=1e-12)
+        assert st["chi2_final"] == pytest.approx(2 * otr.errors[-1], rel=CHI2_RTOL)
+        assert _pose_diff(x, ox) <= POSE_ATOL
+        assert G.chi2() == pytest.approx(st["chi2_final"], rel=1e-12)
+    if gold is not None:
+        gd = np.load(os.path.join(GOLDEN, gold))
+        assert st["iterations"] == int(gd["iterations"])
+        assert np.allclose(errors, gd["errors"], rtol=CHI2_RTOL)
+        assert _pose_diff(x, gd["poses"]) <= POSE_ATOL
+    return st
+
+
+def test_lm_trace_parity_c1_full_config():
+    st = _trace_parity(synth.config("C1"), gold="c1_lm.npz")
+    assert st["converged"] == 1 and st["pcg_iterations_total"] > 0 and st["gpu_launches"] > 0
+
+
+def test_lm_trace_parity_full_cov_golden():
+    _trace_parity(synth.config("C3", n=2500, full_cov=True), gold="c3_small.npz")
+
+
+def test_lm_trace_parity_exact_jacobians_golden():
+    _trace_parity(synth.config("C4", n=1200), mode=1, gold="c4_small_exact.npz")
+
+
+def test_lm_trace_parity_c2_30k():
+    _trace_parity(synth.config("C2", n=30000))
+
+
+def test_lm_pure_dead_reckoning_with_rejections():
+    """Far initial guess: exercises lambda increases (rejected tries) on both sides."""
+    g = synth.manhattan(600, seed=21, target_edges=900, sigma_th=0.05)
+    _trace_parity(g)
+
+
+def test_diagonal_damping_parity():
+    _trace_parity(synth.config("C3", n=1600), diagonal_damping=True)
+
+
+def test_deterministic_bitwise_and_edge_order_invariant():
+    g = synth.config("C3", n=6000)
+    outs = []
+    for perm_seed in (None, None, 3):
+        gg = g
+        if perm_seed is not None:
+            sh = np.random.default_rng(perm_seed).permutation(g.e)
+            gg = synth.PoseGraph(g.name, g.keys, g.init, g.gt, g.k1[sh], g.k2[sh], g.z[sh], g.cov[sh])
+        with _load(gg) as G:
+            _, _, blocks, b, chi2 = G.system()
+            G.optimize()
+            outs.append((blocks.copy(), b.copy(), G.poses()[1].copy()))
+    for k in range(3):
+        assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])   # run-to-run
+        assert np.array_equal(outs[0][2], outs[1][2])
+    # edge insertion order does not change a single bit of H, b or the result (no duplicate pairs here)
+    assert np.array_equal(outs[0][0], outs[2][0]) and np.array_equal(outs[0][1], outs[2][1])
+    assert np.array_equal(outs[0][2], outs[2][2])
+
+
+def test_unsorted_sparse_keys():
+    """Arbitrary uint64 keys in arbitrary insertion order: dense index = rank of the key."""
+    g = synth.config("C3", n=900)
+    rng = np.random.default_rng(4)
+    newkeys = np.sort(rng.choice(10**12, g.n, replace=False).astype(np.uint64)) + np.uint64(5)
+    k1, k2 = newkeys[g.k1.astype(np.int64) - 1], newkeys[g.k2.astype(np.int64) - 1]
+    ins = rng.permutation(g.n)
+    prob = O.Problem.from_graph(g)
+    ox, otr = O.lm_optimize(prob, g.init)
+    with graph.Graph() as G:
+        G.add_batch(newkeys[ins], g.init[ins], [], [], np.zeros((0, 3)), np.zeros((0, 9)))
+        G.add_prior(int(newkeys[0]), g.prior_pose, g.prior_cov)
+        G.add_batch([], np.zeros((0, 3)), k1, k2, g.z, g.cov)
+        rowptr, colidx = G.pattern()
+        orp, oci = prob.pattern()
+        assert np.array_equal(rowptr, orp) and np.array_equal(colidx, oci)
+        st = G.optimize()
+        keys, x = G.poses()
+        assert np.array_equal(keys, newkeys)
+        assert st["iterations"] == otr.iterations and _pose_diff(x, ox) <= POSE_ATOL
+        assert np.allclose(G.pose(int(newkeys[17])), x[17])
+
+
+def test_incremental_warm_start_matches_oracle():
+    """graph.cpp:130 warm start: add a batch of keyframes, re-optimise from the previous optimum."""
+    full = synth.config("C5", n=1500)
+    first = full.prefix(1000)
+    prob1 = O.Problem.from_graph(first)
+    x1, _ = O.lm_optimize(prob1, first.init)
+    with _load(first) as G:
+        G.optimize()
+        m = (full.k1 > 1000) | (full.k2 > 1000)
+        G.add_batch(full.keys[1000:], full.init[1000:], full.k1[m], full.k2[m], full.z[m], full.cov[m])
+        st = G.optimize()
+        _, x = G.poses()
+    init2 = np.vstack([x1, full.init[1000:]])
+    prob2 = O.Problem.from_graph(full)
+    x2, tr2 = O.lm_optimize(prob2, init2)
+    assert st["iterations"] == tr2.iterations
+    assert st["chi2_final"] == pytest.approx(2 * tr2.errors[-1], rel=CHI2_RTOL)
+    assert _pose_diff(x, x2) <= POSE_ATOL
+
+
+def test_graph_node_verbs_replay():
+    """prior_factor / new_factor / loop_factor / solve in the reference's call order (graph.cpp:180-200)."""
+    g = synth.manhattan(300, seed=5, target_edges=420)
+    node = graph.GraphNode()
+    i, j = g.dense_edges()
+    by_arrival = {}
+    for k in range(g.e):
+        by_arrival.setdefault(int(max(i[k], j[k])), []).append(k)
+    node.registration_callback(dict(first_frame_flag=True))
+    for kf in range(1, g.n):
+        reg = dict(keyframe_flag=True, loop_closure_flag=False)
+        for k in by_arrival.get(kf, []):
+            f = dict(id_1=int(g.k1[k]), id_2=int(g.k2[k]), delta=g.z[k], covariance=g.cov[k])
+            if i[k] < j[k]:
+                reg["factor_new"] = f
+            else:
+                reg["loop_closure_flag"] = True
+                reg["factor_loop"] = f
+        node.registration_callback(reg)
+    assert node.graph.num_vertices == g.n and node.graph.num_factors == g.e + 1
+    init = np.array([kf["pose_opti"] for kf in node.keyframes])
+    st = node.solve()
+    prob = O.Problem.from_graph(g)
+    ox, otr = O.lm_optimize(prob, init)
+    x = np.array([kf["pose_opti"] for kf in node.keyframes])
+    assert st["iterations"] == otr.iterations and _pose_diff(x, ox) <= POSE_ATOL
+    # closest_keyframe service (graph.cpp:146-178): all but the last 10, strict '<' -> lowest index
+    key, dist = node.closest_keyframe(g.n)
+    d = np.hypot(x[:g.n - 10, 0] - x[-1, 0], x[:g.n - 10, 1] - x[-1, 1])
+    assert key == int(np.argmin(d)) + 1 and dist == pytest.approx(d.min(), rel=1e-14)
+
+
+def test_error_codes():
+    with graph.Graph() as G:
+        G.add_vertex(1, [0, 0, 0])
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.add_vertex(1, [0, 0, 0])
+        assert e.value.status == _lib.GS_EDUPKEY
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.add_between(1, 2, [1, 0, 0], np.eye(3).reshape(9))
+        assert e.value.status == _lib.GS_ENOKEY
+        G.add_vertex(2, [1, 0, 0])
+        bad = np.diag([1.0, -1.0, 1.0]).reshape(9)          # scanner.hpp:72 can produce sigma_th^2 <= 0
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.add_between(1, 2, [1, 0, 0], bad)
+        assert e.value.status == _lib.GS_ENOTSPD
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.add_between(1, 1, [1, 0, 0], np.eye(3).reshape(9))
+        assert e.value.status == _lib.GS_EINVAL
+
+
+@pytest.mark.parametrize("cid,n", [("C3", 250_000), ("C4", 60_000)])
+def test_large_graph_properties(cid, n):
+    """Sizes the oracle's direct solve cannot reach in seconds: size-independent properties instead."""
+    g = synth.config(cid, n=n)
+    prob = O.Problem.from_graph(g)
+    with _load(g, max_iterations=3) as G:
+        rowptr, colidx = G.pattern()
+        orp, oci = prob.pattern()
+        assert np.array_equal(rowptr, orp) and np.array_equal(colidx, oci)
+        assert G.chi2() == pytest.approx(prob.chi2(g.init), rel=1e-11)
+        # PCG solves the damped normal equations of the oracle's own linearisation
+        h, b, _ = prob.linearize(g.init)
+        d, it, rr = G.solve_linear(1e-5)
+        res = h @ d.ravel() + 1e-5 * d.ravel() + b.ravel()
+        assert rr <= 1e-12 and np.linalg.norm(res) <= 1e-9 * np.linalg.norm(b)
+        st = G.optimize()
+        errors, _, _ = G.trace()
+        assert np.all(np.diff(errors) < 0)                                   # every accepted step lowers chi2
+        _, x = G.poses()
+        assert 2 * prob.error(x) == pytest.approx(st["chi2_final"], rel=1e-10)   # oracle re-evaluates the result

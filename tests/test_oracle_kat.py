@@ -1,0 +1,166 @@
+"""Known-answer tests that pin the oracle (the reference ships none: SURVEY.md §4, §8(c))."""
+import math
+import os
+
+import numpy as np
+import pytest
+
+from graphslam_b200 import synth
+from oracle import gs_oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+I9 = np.eye(3).reshape(9)
+
+
+def test_compose_reference_quirks():
+    # reference graph.hpp:37-38 drops input_1's translation
+    out = O.compose_reference([10.0, -4.0, 0.0], [1.0, 2.0, 0.5])
+    assert out[0] == 1.0 and out[1] == 2.0 and out[2] == pytest.approx(0.5)
+    # graph.hpp:40: fmod wrap leaves theta < -pi unwrapped
+    out = O.compose_reference([0.0, 0.0, -3.0], [0.0, 0.0, -0.5])
+    assert out[2] == pytest.approx(-3.5)
+    # ... but wraps theta > pi
+    out = O.compose_reference([0.0, 0.0, 3.0], [0.0, 0.0, 0.5])
+    assert out[2] == pytest.approx(3.5 - 2 * math.pi)
+    # rotation of the delta by theta_1
+    out = O.compose_reference([5.0, 5.0, math.pi / 2], [1.0, 0.0, 0.0])
+    assert out[0] == pytest.approx(0.0, abs=1e-16) and out[1] == pytest.approx(1.0)
+
+
+def test_compose_reference_table():
+    tab = np.load(os.path.join(GOLDEN, "compose_reference.npz"))
+    for a, b, want in zip(tab["a"], tab["b"], tab["out"]):
+        assert np.array_equal(O.compose_reference(a, b), want)
+
+
+def test_compose_correct():
+    out = O.compose(np.array([1.0, 2.0, math.pi / 2]), np.array([1.0, 0.0, math.pi]))
+    assert np.allclose(out, [1.0, 3.0, -math.pi / 2])
+
+
+def test_between_jacobians_finite_difference():
+    rng = np.random.default_rng(7)
+    for mode in (O.JAC_EXACT,):
+        for _ in range(20):
+            pi, pj, z = rng.normal(size=(3, 3))
+            z[2] = O.wrap_pi(pj[2] - pi[2] + 0.05 * rng.normal())
+            e0, ai, aj = O.between_residual(pi[None], pj[None], z[None], mode)
+            h = 1e-6
+            for col in range(3):
+                d = np.zeros((1, 3)); d[0, col] = h
+                ep, _, _ = O.between_residual(O.retract(pi[None], d), pj[None], z[None], mode)
+                em, _, _ = O.between_residual(O.retract(pi[None], -d), pj[None], z[None], mode)
+                assert np.allclose((ep - em)[0] / (2 * h), ai[0][:, col], atol=1e-8)
+                ep, _, _ = O.between_residual(pi[None], O.retract(pj[None], d), z[None], mode)
+                em, _, _ = O.between_residual(pi[None], O.retract(pj[None], -d), z[None], mode)
+                assert np.allclose((ep - em)[0] / (2 * h), aj[0][:, col], atol=1e-8)
+
+
+def test_gtsam_default_jacobian_is_exact_at_zero_rotation_error():
+    rng = np.random.default_rng(3)
+    pi, pj = rng.normal(size=(2, 3))
+    z = synth.between(pi, pj)          # zero residual -> D = I -> both modes agree
+    _, a0, b0 = O.between_residual(pi[None], pj[None], z[None], O.JAC_GTSAM_DEFAULT)
+    _, a1, b1 = O.between_residual(pi[None], pj[None], z[None], O.JAC_EXACT)
+    assert np.allclose(a0, a1, atol=1e-12) and np.allclose(b0, b1, atol=1e-12)
+
+
+def test_prior_residual_sign_and_jacobian():
+    x = np.array([[0.3, -0.2, 0.1]])
+    prior = np.zeros((1, 3))
+    e, a = O.prior_residual(x, prior, O.JAC_EXACT)
+    h = 1e-6
+    for col in range(3):
+        d = np.zeros((1, 3)); d[0, col] = h
+        ep, _ = O.prior_residual(O.retract(x, d), prior)
+        em, _ = O.prior_residual(O.retract(x, -d), prior)
+        assert np.allclose((ep - em)[0] / (2 * h), a[0][:, col], atol=1e-8)
+    # e = -Local(x^-1 o prior) = Local-ish of x in its own frame: theta component = +theta_x
+    assert e[0, 2] == pytest.approx(0.1)
+
+
+def test_two_pose_chain_closed_form():
+    # prior at origin + one between factor: optimum = prior (+) delta exactly, chi2 = 0
+    delta = np.array([1.0, 0.5, 0.3])
+    prob = O.Problem(2, [0], [1], delta[None], I9[None] * 0.01, [0], np.zeros((1, 3)), I9[None] * 0.01)
+    x, tr = O.lm_optimize(prob, np.array([[0.2, -0.1, 0.05], [0.7, 0.9, 0.6]]))
+    assert np.allclose(x[0], 0.0, atol=1e-9)
+    assert np.allclose(x[1], O.compose(np.zeros(3), delta), atol=1e-9)
+    assert tr.errors[-1] < 1e-16
+
+
+def test_triangle_against_dense_normal_equations():
+    # 3 poses, inconsistent loop: one GN step from the oracle's sparse path == dense numpy solve
+    z = np.array([[1.0, 0.0, 2.0], [1.0, 0.0, 2.2], [1.0, 0.1, 2.1]])
+    prob = O.Problem(3, [0, 1, 2], [1, 2, 0], z, I9[None].repeat(3, 0) * 0.04, [0], np.zeros((1, 3)), I9[None] * 0.01)
+    x0 = np.array([[0.0, 0.0, 0.0], [1.1, 0.1, 2.0], [0.6, 0.9, -2.0]])
+    h, b, chi2 = prob.linearize(x0)
+    hd = h.toarray()
+    assert np.allclose(hd, hd.T, atol=1e-12)
+    t = prob.edge_terms(x0)
+    dense = np.zeros((9, 9))
+    rhs = np.zeros(9)
+    for k, (i, j) in enumerate(zip(prob.ei, prob.ej)):
+        J = np.zeros((3, 9)); J[:, 3 * i:3 * i + 3] = t["a_i"][k]; J[:, 3 * j:3 * j + 3] = t["a_j"][k]
+        dense += J.T @ prob.omega[k] @ J
+        rhs += J.T @ prob.omega[k] @ t["e"][k]
+    ep, ap = O.prior_residual(x0[[0]], np.zeros((1, 3)))
+    dense[:3, :3] += ap[0].T @ prob.prior_omega[0] @ ap[0]
+    rhs[:3] += ap[0].T @ prob.prior_omega[0] @ ep[0]
+    assert np.allclose(hd, dense, atol=1e-10)
+    assert np.allclose(b.ravel(), rhs, atol=1e-10)
+    lam = 1e-5
+    want = np.linalg.solve(dense + lam * np.eye(9), -rhs)
+    got = O.solve_damped(h, b, lam).ravel()
+    assert np.allclose(got, want, rtol=1e-10, atol=1e-12)
+    x, tr = O.lm_optimize(prob, x0)
+    assert tr.errors[-1] < tr.errors[0] and tr.iterations >= 2
+
+
+def test_gauge_invariance_of_edge_chi2():
+    g = synth.manhattan(200, seed=11, target_edges=320)
+    prob = O.Problem.from_graph(g)
+    prob.prior_idx = np.zeros(0, dtype=np.int64)         # remove the gauge prior
+    c0 = prob.chi2(g.init)
+    T = np.array([3.0, -2.0, 0.7])
+    moved = O.compose(T[None].repeat(g.n, 0), g.init)
+    assert prob.chi2(moved) == pytest.approx(c0, rel=1e-10)
+
+
+def test_pattern_merges_duplicates_and_directions():
+    prob = O.Problem(4, [0, 1, 1, 3, 0], [1, 0, 2, 1, 1], np.zeros((5, 3)), I9[None].repeat(5, 0), [0],
+                     np.zeros((1, 3)), I9[None])
+    rowptr, colidx = prob.pattern()
+    assert rowptr.tolist() == [0, 2, 6, 8, 10]
+    assert colidx.tolist() == [0, 1, 0, 1, 2, 3, 1, 2, 1, 3]
+
+
+def test_information_rejects_non_spd():
+    bad = np.array([1.0, 0, 0, 0, -1.0, 0, 0, 0, 1.0])
+    with pytest.raises(ValueError):
+        O.information(bad[None])
+
+
+def test_lm_trace_golden_c1():
+    """The oracle's own LM trace on C1 is frozen: any change to the restated GTSAM semantics shows up here."""
+    gold = np.load(os.path.join(GOLDEN, "c1_lm.npz"))
+    g = synth.config("C1")
+    assert g.e == int(gold["e"]) and g.n == int(gold["n"])
+    prob = O.Problem.from_graph(g)
+    x, tr = O.lm_optimize(prob, g.init)
+    assert tr.iterations == int(gold["iterations"])
+    assert tr.tries == gold["tries"].tolist()
+    assert np.allclose(tr.errors, gold["errors"], rtol=1e-9)
+    assert np.allclose(x[:, :2], gold["poses"][:, :2], atol=1e-7)
+    assert np.allclose(O.wrap_pi(x[:, 2] - gold["poses"][:, 2]), 0, atol=1e-7)
+
+
+def test_generator_reproducible():
+    a, b = synth.config("C2", n=5000), synth.config("C2", n=5000)
+    for f in ("init", "z", "cov", "k1", "k2"):
+        assert np.array_equal(getattr(a, f), getattr(b, f))
+    g = synth.config("C1")
+    assert 5450 <= g.e <= 5550 and g.n == 3500
+    i, j = g.dense_edges()
+    loops = i > j
+    assert loops.sum() == g.meta["n_loops"] and np.all(i[loops] - j[loops] >= 10)   # graph.cpp:15
