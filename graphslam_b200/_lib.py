@@ -31,11 +31,12 @@ class GsStats(C.Structure):
                 ("lambda_final", C.c_double), ("pcg_iterations_total", C.c_int64), ("ms_structure", C.c_double),
                 ("ms_linearize", C.c_double), ("ms_solve", C.c_double), ("ms_update", C.c_double),
                 ("ms_total", C.c_double), ("edges_per_sec", C.c_double), ("gn_iters_per_sec", C.c_double),
-                ("reserved", C.c_double * 8)]
+                ("gpu_launches", C.c_double), ("ms_device", C.c_double), ("h2d_bytes", C.c_double),
+                ("d2h_bytes", C.c_double), ("reserved", C.c_double * 4)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
-        d["gpu_launches"] = int(self.reserved[0])
+        d["gpu_launches"] = int(self.gpu_launches)
         return d
 
 
@@ -63,6 +64,8 @@ SIGNATURES = {
     "gs_get_system": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     "gs_solve_linear": (C.c_int, [C.c_void_p, C.c_double, c_double_p, C.POINTER(C.c_int), c_double_p]),
     "gs_get_trace": (C.c_int, [C.c_void_p, C.c_size_t, c_double_p, c_double_p, c_i32_p, C.POINTER(C.c_size_t)]),
+    "gs_profile_pcg": (C.c_int, [C.c_void_p, C.c_double, C.c_int, c_double_p, c_double_p]),
+    "gs_profile_outer": (C.c_int, [C.c_void_p, C.c_int, c_double_p, c_double_p]),
     "gs_last_error": (C.c_char_p, [C.c_void_p]),
     "gs_compose_reference": (None, [c_double_p, c_double_p, c_double_p]),
     "gs_compose": (None, [c_double_p, c_double_p, c_double_p]),

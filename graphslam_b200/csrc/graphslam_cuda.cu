@@ -78,7 +78,8 @@ struct gs_graph {
   gs_params prm;
   std::string err;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_begin = nullptr, ev_end = nullptr;
+  double h2d_bytes = 0.0, d2h_bytes = 0.0;  // cumulative bytes copied by the library
 
   // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
   std::vector<uint64_t> keys;
@@ -234,6 +235,7 @@ gs_status download_values(gs_graph* g) {
   std::vector<double4> tmp(n);
   GS_CUDA(g, cudaMemcpyAsync(tmp.data(), g->d_pose.p, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  g->d2h_bytes += sizeof(double4) * (double)n;
   for (int d = 0; d < n; ++d) {
     const int k = g->dense2ins[d];
     g->xyt[3 * k] = tmp[d].x;
@@ -253,6 +255,7 @@ gs_status upload_values(gs_graph* g) {
   }
   GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp.data(), sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  g->h2d_bytes += sizeof(double4) * (double)n;
   g->device_values_valid = true;
   g->system_valid = false;
   return GS_OK;
@@ -263,6 +266,7 @@ gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
   GS_CUDA(g, d.alloc(std::max<size_t>(h.size(), 1)));
   if (!h.empty())
     GS_CUDA(g, cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, g->stream));
+  g->h2d_bytes += sizeof(T) * (double)h.size();
   return GS_OK;
 }
 
@@ -350,11 +354,13 @@ gs_status prepare(gs_graph* g, double* ms_out) {
 gs_status read_scalars(gs_graph* g) {
   GS_CUDA(g, cudaMemcpyAsync(g->h_sc, g->d_sc.p, sizeof(Scalars), cudaMemcpyDeviceToHost, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  g->d2h_bytes += sizeof(Scalars);
   return GS_OK;
 }
 
 gs_status write_scalars(gs_graph* g) {
   GS_CUDA(g, cudaMemcpyAsync(g->d_sc.p, g->h_sc, sizeof(Scalars), cudaMemcpyHostToDevice, g->stream));
+  g->h2d_bytes += sizeof(Scalars);
   return GS_OK;
 }
 
@@ -503,6 +509,8 @@ gs_status gs_create(gs_graph** out, const gs_params* params) {
   GS_CUDA(g, cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking));
   GS_CUDA(g, cudaEventCreate(&g->ev0));
   GS_CUDA(g, cudaEventCreate(&g->ev1));
+  GS_CUDA(g, cudaEventCreate(&g->ev_begin));
+  GS_CUDA(g, cudaEventCreate(&g->ev_end));
   GS_CUDA(g, g->d_sc.alloc(1));
   GS_CUDA(g, g->d_counter.alloc(8));
   GS_CUDA(g, cudaMemsetAsync(g->d_counter.p, 0, 8 * sizeof(unsigned int), g->stream));
@@ -521,6 +529,8 @@ gs_status gs_destroy(gs_graph* g) {
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->ev0) cudaEventDestroy(g->ev0);
   if (g->ev1) cudaEventDestroy(g->ev1);
+  if (g->ev_begin) cudaEventDestroy(g->ev_begin);
+  if (g->ev_end) cudaEventDestroy(g->ev_end);
   if (g->stream) cudaStreamDestroy(g->stream);
   delete g;
   return GS_OK;
@@ -614,8 +624,10 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) {
   gs_stats local;
   std::memset(&local, 0, sizeof local);
   double ms_structure = 0.0;
+  const double h2d0 = g->h2d_bytes, d2h0 = g->d2h_bytes;
   if (gs_status s = prepare(g, &ms_structure)) return s;
   local.ms_structure = ms_structure;
+  GS_CUDA(g, cudaEventRecord(g->ev_begin, g->stream));
   const gs_params& P = g->prm;
   Scalars* h = g->h_sc;
   g->tr_err.clear();
@@ -725,7 +737,16 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) {
   local.edges_per_sec = local.ms_linearize > 0 ? (double)g->E * local.outer_loops / (local.ms_linearize * 1e-3) : 0.0;
   const double t_iter = local.ms_total - local.ms_structure;
   local.gn_iters_per_sec = t_iter > 0 ? local.outer_loops / (t_iter * 1e-3) : 0.0;
-  local.reserved[0] = (double)g->launches;
+  local.gpu_launches = (double)g->launches;
+  GS_CUDA(g, cudaEventRecord(g->ev_end, g->stream));
+  GS_CUDA(g, cudaEventSynchronize(g->ev_end));
+  {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, g->ev_begin, g->ev_end);
+    local.ms_device = ms;
+  }
+  local.h2d_bytes = g->h2d_bytes - h2d0;
+  local.d2h_bytes = g->d2h_bytes - d2h0;
   if (st) *st = local;
   return rc;
 }
@@ -876,6 +897,90 @@ gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas,
     std::copy(g->tr_lambda.begin(), g->tr_lambda.end(), lambdas);
   }
   if (tries) std::copy(g->tr_tries.begin(), g->tr_tries.end(), tries);
+  return GS_OK;
+}
+
+gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], double bytes[3]) {
+  if (!g || !ms || iters <= 0) return GS_EINVAL;
+  if (gs_status s = prepare(g, nullptr)) return s;
+  if (!g->system_valid)
+    if (gs_status s = launch_assemble(g)) return s;
+  Scalars* h = g->h_sc;
+  std::memset(h, 0, sizeof(Scalars));
+  h->lambda = lambda;
+  h->tol2 = 0.0;  // never converge: every profiled iteration does full work
+  h->max_iters = 1 << 30;
+  if (gs_status s = write_scalars(g)) return s;
+  gs::k_minv<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
+                                                        g->d_sc.p, g->d_Minv.p, g->N);
+  gs::k_pcg_init<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
+  for (int w = 0; w < 3; ++w) launch_pcg_iteration(g);  // warm-up
+  std::vector<cudaEvent_t> ev(4 * (size_t)iters);
+  for (auto& e : ev) GS_CUDA(g, cudaEventCreate(&e));
+  for (int it = 0; it < iters; ++it) {
+    cudaEvent_t* e = &ev[4 * (size_t)it];
+    cudaEventRecord(e[0], g->stream);
+    gs::k_spmv<<<(unsigned)g->S.stiles.size(), gs::kThreads, 0, g->stream>>>(spmv_args(g, g->d_p.p, g->d_Ap.p, 0));
+    cudaEventRecord(e[1], g->stream);
+    gs::k_pcg_update<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
+    cudaEventRecord(e[2], g->stream);
+    gs::k_pcg_dir<<<g->grid_v3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->N);
+    cudaEventRecord(e[3], g->stream);
+  }
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  GS_CUDA(g, cudaGetLastError());
+  double acc[3] = {0, 0, 0};
+  for (int it = 0; it < iters; ++it)
+    for (int k = 0; k < 3; ++k) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, ev[4 * (size_t)it + k], ev[4 * (size_t)it + k + 1]);
+      acc[k] += t;
+    }
+  for (auto& e : ev) cudaEventDestroy(e);
+  for (int k = 0; k < 3; ++k) ms[k] = acc[k] / iters;
+  if (bytes) {
+    const double N = g->N, nnzb = (double)g->S.nnzo + g->N;
+    bytes[0] = 76.0 * nnzb + 52.0 * N;                 // K3
+    bytes[1] = (4 * 24.0 + 72.0 + 3 * 24.0) * N;       // K4a: x,p,r,Ap + Minv read; x,r,z written
+    bytes[2] = 72.0 * N;                               // K4b: z,p read; p written
+  }
+  g->launches += 3 * (int64_t)(iters + 3) + 2;
+  return GS_OK;
+}
+
+gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3]) {
+  if (!g || !ms || reps <= 0) return GS_EINVAL;
+  if (gs_status s = prepare(g, nullptr)) return s;
+  GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * 3 * g->N, g->stream));
+  double acc[3] = {0, 0, 0};
+  for (int r = 0; r < reps + 1; ++r) {  // first pass is warm-up
+    float t = 0.f;
+    GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
+    if (gs_status s = launch_assemble(g)) return s;
+    GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
+    GS_CUDA(g, cudaEventSynchronize(g->ev1));
+    cudaEventElapsedTime(&t, g->ev0, g->ev1);
+    if (r) acc[0] += t;
+    GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
+    gs::k_retract<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_pose.p, g->d_x.p, g->d_pose_try.p, g->N);
+    GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
+    GS_CUDA(g, cudaEventSynchronize(g->ev1));
+    cudaEventElapsedTime(&t, g->ev0, g->ev1);
+    if (r) acc[1] += t;
+    GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
+    if (gs_status s = launch_chi2(g, g->d_pose_try.p)) return s;
+    GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
+    GS_CUDA(g, cudaEventSynchronize(g->ev1));
+    cudaEventElapsedTime(&t, g->ev0, g->ev1);
+    if (r) acc[2] += t;
+  }
+  for (int k = 0; k < 3; ++k) ms[k] = acc[k] / reps;
+  if (bytes) {
+    const double N = g->N, E = g->E, nnzb = (double)g->S.nnzo + g->N;
+    bytes[0] = 80.0 * E + 24.0 * N + 72.0 * nnzb + 24.0 * N;   // K1+K2
+    bytes[1] = 72.0 * N;                                        // K5 retract
+    bytes[2] = 80.0 * E;                                        // K5 chi2
+  }
   return GS_OK;
 }
 

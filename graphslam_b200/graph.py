@@ -210,6 +210,17 @@ class Graph:
         self._ck(self._lib.gs_get_trace(self._h, m, _dp(errors), _dp(lambdas), tries.ctypes.data_as(c_i32_p), C.byref(n)))
         return errors, lambdas[:m], tries[:m]
 
+    def profile_pcg(self, lam: float = 1e-5, iters: int = 50):
+        """Average CUDA-event duration (ms) and algorithmic bytes of the three PCG kernels."""
+        ms, by = np.zeros(3), np.zeros(3)
+        self._ck(self._lib.gs_profile_pcg(self._h, float(lam), int(iters), _dp(ms), _dp(by)))
+        return dict(zip(("spmv", "pcg_update", "pcg_dir"), zip(ms.tolist(), by.tolist())))
+
+    def profile_outer(self, reps: int = 5):
+        ms, by = np.zeros(3), np.zeros(3)
+        self._ck(self._lib.gs_profile_outer(self._h, int(reps), _dp(ms), _dp(by)))
+        return dict(zip(("assemble", "retract", "chi2"), zip(ms.tolist(), by.tolist())))
+
     def closest_keyframe(self, key: int, skip: int = 10):
         out = C.c_uint64()
         dist = C.c_double()

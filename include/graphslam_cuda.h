@@ -84,7 +84,11 @@ typedef struct gs_stats {
   double ms_total;           /* wall time of gs_optimize                                      */
   double edges_per_sec;      /* E * outer_loops / ms_linearize                                */
   double gn_iters_per_sec;   /* outer_loops / (ms_total - ms_structure)                       */
-  double reserved[8];
+  double gpu_launches;       /* kernels launched that did work (no-op graph tail excluded)    */
+  double ms_device;          /* CUDA-event time on the graph's stream, first to last kernel   */
+  double h2d_bytes;          /* host->device bytes copied by this call                        */
+  double d2h_bytes;          /* device->host bytes copied by this call                        */
+  double reserved[4];
 } gs_stats;
 
 void gs_default_params(gs_params* p);
@@ -134,6 +138,14 @@ gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2);
 gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual);
 /* per-outer-iteration trace of the last gs_optimize: errors[n+1] (= chi2/2, [0] initial), lambdas[n], tries[n] */
 gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n);
+
+/* ---- measurement hook: run `iters` real PCG iterations on the current linearisation (un-graphed, a
+ * CUDA-event pair around every launch on the graph's own stream) and return the average duration of
+ * each kernel in ms: ms[0] = BSR SpMV, ms[1] = fused x/r/z update + dots, ms[2] = direction update.
+ * bytes[0..2] receive the algorithmic bytes of one launch (SURVEY.md section 8(d) formulas). */
+gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], double bytes[3]);
+/* same for the once-per-outer-iteration kernels: ms[0] = linearise+assemble, ms[1] = retract, ms[2] = chi2 */
+gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3]);
 
 const char* gs_last_error(const gs_graph* g);
 
