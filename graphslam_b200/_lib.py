@@ -45,6 +45,8 @@ SIGNATURES = {
     "gs_default_params": (None, [C.POINTER(GsParams)]),
     "gs_version": (C.c_int, []),
     "gs_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(GsParams)]),
+    "gs_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "gs_create_distributed": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(GsParams), C.c_void_p, C.c_size_t]),
     "gs_destroy": (C.c_int, [C.c_void_p]),
     "gs_set_params": (C.c_int, [C.c_void_p, C.POINTER(GsParams)]),
     "gs_add_vertex": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
@@ -72,8 +74,23 @@ SIGNATURES = {
     "gs_closest_keyframe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, c_u64_p, c_double_p]),
 }
 
-# host-only debug entries (not in the public header): the product's own host code, callable on a CPU box
+class GsEmuProblem(C.Structure):
+    _fields_ = [("n", C.c_int32), ("e", C.c_int32), ("np", C.c_int32), ("ei", c_i32_p), ("ej", c_i32_p), ("z", c_double_p),
+                ("om", c_double_p), ("prior_idx", c_i32_p), ("prior_xyt", c_double_p), ("prior_om", c_double_p),
+                ("xyt", c_double_p)]
+
+
+class GsEmuResult(C.Structure):
+    _fields_ = [("blocks", c_double_p), ("b", c_double_p), ("delta", c_double_p), ("xyt_new", c_double_p),
+                ("chi2", C.c_double), ("chi2_check", C.c_double), ("chi2_new", C.c_double), ("dHd", C.c_double),
+                ("db", C.c_double), ("rel_residual", C.c_double), ("pcg_iters", C.c_int32), ("pcg_done", C.c_int32),
+                ("n_ghost_total", C.c_int32), ("n_pairs_total", C.c_int32), ("halo_send_total", C.c_int32)]
+
+
+# test-only entries (include/graphslam_cuda_debug.h): the product's own host code, callable on a CPU box
 DEBUG_SIGNATURES = {
+    "gs_emu_run": (C.c_int, [C.POINTER(GsEmuProblem), C.c_int, C.c_int, C.c_double, C.c_int, C.c_double,
+                             C.POINTER(GsEmuResult)]),
     "gs_host_pattern": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t),
                                   c_i32_p]),
     "gs_host_between": (C.c_int, [c_double_p] * 4 + [C.c_int] + [c_double_p] * 8),

@@ -5,6 +5,11 @@
 // tryLambda -> k_retract + k_chi2 -> accept/reject on three scalars read back per try.
 // The PCG loop itself never synchronises with the host: coefficients live in device memory and
 // iterations are replayed from a CUDA graph in batches, a `done` flag turning the tail into no-ops.
+//
+// Multi-GPU (one process per GPU, gs_create_distributed): every rank receives the same graph
+// through the same calls and keeps the block rows of its vertex range.  NCCL carries the halo
+// exchange of p (per SpMV) and of the poses (per retract), and all-gathers of the segment sums of
+// the dot products, which every rank then adds in the same fixed order.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -12,6 +17,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -19,13 +25,13 @@
 #include <vector>
 
 #include "../../include/graphslam_cuda.h"
+#include "comm.hpp"
 #include "kernels.cuh"
 
 namespace {
 
-using gs::HostStructure;
+using gs::LocalStructure;
 using gs::Scalars;
-using gs::Tile;
 
 constexpr int kPcgBatch = 32;  // PCG iterations per CUDA-graph launch
 
@@ -81,6 +87,11 @@ struct gs_graph {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_begin = nullptr, ev_end = nullptr;
   double h2d_bytes = 0.0, d2h_bytes = 0.0;  // cumulative bytes copied by the library
 
+  // ---- multi-GPU
+  int world = 1, rank = 0;
+  ncclComm_t comm = nullptr;
+  bool use_graph = true;
+
   // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
   std::vector<uint64_t> keys;
   std::vector<double> xyt;  // current values, 3 per vertex, insertion order
@@ -96,26 +107,29 @@ struct gs_graph {
   std::vector<int> ins2dense, dense2ins;
   bool identity_order = true;
 
-  bool topo_dirty = true;       // factors/vertices added since the last structure build
+  bool topo_dirty = true;         // factors/vertices added since the last structure build
   bool host_values_fresh = true;  // host xyt newer than (or equal to) device poses
   bool device_values_valid = false;
-  bool system_valid = false;    // H, b assembled at the current device poses
+  bool system_valid = false;      // H, b assembled at the current device poses
 
-  HostStructure S;
+  LocalStructure S;
+  std::vector<int> di, dj, dp, perm;  // dense endpoints (caller's order), dense prior rows, canonical order
   int N = 0, E = 0, P = 0;
+  int n_own = 0, n_loc = 0;
+  int e_count = 0;  // factors this rank is the counting side of
 
   // ---- device
-  DevBuf<double4> d_pose, d_pose_try, d_pr_pose;
+  DevBuf<double4> d_pose, d_pose_try, d_pr_pose, d_pose_all;
   DevBuf<int2> d_eij;
   DevBuf<double2> d_zt, d_zr, d_o01, d_o23, d_o45;
-  DevBuf<int> d_pr_idx, d_crowptr, d_cblk, d_orowptr, d_ocol;
+  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_cblk, d_rbase, d_rwidth, d_rcol, d_rblk, d_segtile, d_send_rows;
   DevBuf<uint32_t> d_ccode;
-  DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part;
-  DevBuf<Tile> d_atiles, d_stiles;
+  DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part, d_segs, d_sendbuf;
   DevBuf<Scalars> d_sc;
   DevBuf<unsigned int> d_counter;
   Scalars* h_sc = nullptr;  // pinned mirror
-  int grid_v = 0, grid_v3 = 0, grid_e = 0;
+  size_t hstride = 1;
+  int grid_rows = 1, grid_flat3 = 1, part_stride = 1;
 
   cudaGraph_t pcg_graph = nullptr;
   cudaGraphExec_t pcg_exec = nullptr;
@@ -153,6 +167,13 @@ struct gs_graph {
       return (g)->fail(GS_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
   } while (0)
 
+#define GS_NCCL(g, call)                                                                         \
+  do {                                                                                           \
+    ncclResult_t r__ = (call);                                                                   \
+    if (r__ != ncclSuccess)                                                                      \
+      return (g)->fail(GS_ENCCL, "%s:%d %s: %s", __FILE__, __LINE__, #call, gs::nccl().GetErrorString(r__)); \
+  } while (0)
+
 namespace {
 
 void destroy_graph_exec(gs_graph* g) {
@@ -162,27 +183,60 @@ void destroy_graph_exec(gs_graph* g) {
   g->pcg_graph = nullptr;
 }
 
-gs::SpmvArgs spmv_args(gs_graph* g, const double* p, double* y, int mode) {
-  gs::SpmvArgs a;
-  a.tiles = g->d_stiles.p;
-  a.orowptr = g->d_orowptr.p;
-  a.ocol = g->d_ocol.p;
+gs::ReduceCtx reduce_ctx(gs_graph* g, int counter_slot) {
+  gs::ReduceCtx c;
+  c.part = g->d_part.p;
+  c.part_stride = g->part_stride;
+  c.segs = g->d_segs.p;
+  c.seg_tile = g->d_segtile.p;
+  c.spr = gs::kSegments / g->world;
+  c.rank = g->rank;
+  c.world = g->world;
+  c.counter = g->d_counter.p + counter_slot;
+  c.sc = g->d_sc.p;
+  return c;
+}
+
+gs::AsmView asm_view(gs_graph* g, const double4* pose) {
+  gs::AsmView a;
+  a.cs.base = g->d_cbase.p;
+  a.cs.width = g->d_cwidth.p;
+  a.c_code = g->d_ccode.p;
+  a.c_blk = g->d_cblk.p;
+  a.f.ij = g->d_eij.p;
+  a.f.zt = g->d_zt.p;
+  a.f.zr = g->d_zr.p;
+  a.f.o01 = g->d_o01.p;
+  a.f.o23 = g->d_o23.p;
+  a.f.o45 = g->d_o45.p;
+  a.pr.row = g->d_pr_row.p;
+  a.pr.pose = g->d_pr_pose.p;
+  a.pr.om = g->d_pr_om.p;
+  a.pose = pose;
   a.Ho = g->d_Ho.p;
+  a.hstride = g->hstride;
   a.Hd = g->d_Hd.p;
-  a.dscale = g->prm.diagonal_damping ? g->d_dscale.p : nullptr;
-  a.p = p;
-  a.y = y;
-  a.part = g->d_part.p;
-  a.sc = g->d_sc.p;
-  a.counter = g->d_counter.p;
-  a.nnzo = g->S.nnzo;
-  a.N = g->N;
-  a.mode = mode;
+  a.b = g->d_b.p;
+  a.n_own = g->n_own;
   return a;
 }
 
-gs::PcgArgs pcg_args(gs_graph* g) {
-  gs::PcgArgs a;
+gs::SpmvView spmv_view(gs_graph* g) {
+  gs::SpmvView a;
+  a.rs.base = g->d_rbase.p;
+  a.rs.width = g->d_rwidth.p;
+  a.r_col = g->d_rcol.p;
+  a.r_blk = g->d_rblk.p;
+  a.Ho = g->d_Ho.p;
+  a.hstride = g->hstride;
+  a.Hd = g->d_Hd.p;
+  a.dscale = g->prm.diagonal_damping ? g->d_dscale.p : nullptr;
+  a.n_own = g->n_own;
+  return a;
+}
+
+gs::PcgView pcg_view(gs_graph* g) {
+  gs::PcgView a;
   a.b = g->d_b.p;
   a.Minv = g->d_Minv.p;
   a.x = g->d_x.p;
@@ -190,24 +244,73 @@ gs::PcgArgs pcg_args(gs_graph* g) {
   a.z = g->d_z.p;
   a.p = g->d_p.p;
   a.Ap = g->d_Ap.p;
-  a.part = g->d_part.p;
-  a.sc = g->d_sc.p;
-  a.counter = g->d_counter.p + 1;
-  a.N = g->N;
+  a.n_own = g->n_own;
   return a;
 }
 
-void launch_pcg_iteration(gs_graph* g) {
-  gs::k_spmv<<<(unsigned)g->S.stiles.size(), gs::kThreads, 0, g->stream>>>(spmv_args(g, g->d_p.p, g->d_Ap.p, 0));
-  gs::k_pcg_update<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
-  gs::k_pcg_dir<<<g->grid_v3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->N);
+// ---- multi-rank plumbing (no-ops on a single rank) ------------------------------------------------
+// ghost slots of `vec` (width doubles per vertex) <- owner ranks' current values
+gs_status halo_exchange(gs_graph* g, double* vec, int width) {
+  if (g->world == 1) return GS_OK;
+  const LocalStructure& S = g->S;
+  const int nsend = (int)S.send_rows.size();
+  if (nsend) {
+    const int n = nsend * width;
+    gs::k_pack<<<(n + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(vec, g->d_send_rows.p, nsend, width,
+                                                                                      g->d_sendbuf.p);
+    g->launches += 1;
+  }
+  if (S.peers.empty()) return GS_OK;
+  gs::NcclApi& nc = gs::nccl();
+  GS_NCCL(g, nc.GroupStart());
+  for (const gs::HaloPeer& hp : S.peers) {
+    if (hp.send_cnt)
+      GS_NCCL(g, nc.Send(g->d_sendbuf.p + (size_t)hp.send_off * width, (size_t)hp.send_cnt * width, ncclDouble, hp.rank,
+                         g->comm, g->stream));
+    if (hp.ghost_cnt)
+      GS_NCCL(g, nc.Recv(vec + ((size_t)g->n_own + hp.ghost_off) * width, (size_t)hp.ghost_cnt * width, ncclDouble, hp.rank,
+                         g->comm, g->stream));
+  }
+  GS_NCCL(g, nc.GroupEnd());
+  return GS_OK;
+}
+
+// after a reducing kernel: all-gather the segment sums, then the scalar step on every rank
+gs_status finish_reduce(gs_graph* g, int nq, int op) {
+  if (g->world == 1) return GS_OK;
+  const int spr = gs::kSegments / g->world;
+  const size_t chunk = (size_t)nq * spr;
+  GS_NCCL(g, gs::nccl().AllGather(g->d_segs.p + g->rank * chunk, g->d_segs.p, chunk, ncclDouble, g->comm, g->stream));
+  gs::k_scalars<<<1, 32, 0, g->stream>>>(g->d_segs.p, nq, spr, op, g->d_sc.p);
+  g->launches += 1;
+  return GS_OK;
+}
+
+gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode) {
+  if (gs_status s = halo_exchange(g, p, 3)) return s;
+  gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, y, reduce_ctx(g, 0), mode);
+  return finish_reduce(g, 1, mode == 0 ? gs::OP_PAP : gs::OP_DOT);
+}
+
+gs_status launch_pcg_iteration(gs_graph* g) {
+  if (gs_status s = launch_spmv(g, g->d_p.p, g->d_Ap.p, 0)) return s;
+  gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
+  if (gs_status s = finish_reduce(g, 2, gs::OP_UPDATE)) return s;
+  gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->n_own);
+  return GS_OK;
 }
 
 gs_status capture_pcg_graph(gs_graph* g) {
   destroy_graph_exec(g);
+  if (!g->use_graph) return GS_OK;
+  const int64_t keep = g->launches;
   GS_CUDA(g, cudaStreamBeginCapture(g->stream, cudaStreamCaptureModeThreadLocal));
-  for (int it = 0; it < kPcgBatch; ++it) launch_pcg_iteration(g);
-  GS_CUDA(g, cudaStreamEndCapture(g->stream, &g->pcg_graph));
+  gs_status rc = GS_OK;
+  for (int it = 0; it < kPcgBatch && rc == GS_OK; ++it) rc = launch_pcg_iteration(g);
+  cudaError_t ce = cudaStreamEndCapture(g->stream, &g->pcg_graph);
+  g->launches = keep;
+  if (rc != GS_OK) return rc;
+  GS_CUDA(g, ce);
   GS_CUDA(g, cudaGraphInstantiate(&g->pcg_exec, g->pcg_graph, 0));
   return GS_OK;
 }
@@ -229,11 +332,24 @@ void build_dense_order(gs_graph* g) {
   for (int k = 0; k < n; ++k) g->ins2dense[g->dense2ins[k]] = k;
 }
 
+// device values -> host xyt.  Multi-rank: collective (every rank broadcasts its owned range).
 gs_status download_values(gs_graph* g) {
   if (!g->device_values_valid || g->host_values_fresh) return GS_OK;
   const int n = g->N;  // vertices present at the last upload
   std::vector<double4> tmp(n);
-  GS_CUDA(g, cudaMemcpyAsync(tmp.data(), g->d_pose.p, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
+  const double4* src = g->d_pose.p;
+  if (g->world > 1) {
+    gs::NcclApi& nc = gs::nccl();
+    GS_NCCL(g, nc.GroupStart());
+    for (int q = 0; q < g->world; ++q) {
+      const int b = g->S.part.row_begin(q), e = g->S.part.row_end(q);
+      if (e > b)
+        GS_NCCL(g, nc.Broadcast(g->d_pose.p, g->d_pose_all.p + b, (size_t)(e - b) * 4, ncclDouble, q, g->comm, g->stream));
+    }
+    GS_NCCL(g, nc.GroupEnd());
+    src = g->d_pose_all.p;
+  }
+  GS_CUDA(g, cudaMemcpyAsync(tmp.data(), src, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   g->d2h_bytes += sizeof(double4) * (double)n;
   for (int d = 0; d < n; ++d) {
@@ -246,14 +362,16 @@ gs_status download_values(gs_graph* g) {
   return GS_OK;
 }
 
+// host xyt -> device poses of this rank (owned rows, then ghosts)
 gs_status upload_values(gs_graph* g) {
-  const int n = g->N;
-  std::vector<double4> tmp(n);
-  for (int d = 0; d < n; ++d) {
+  const int n = g->n_loc;
+  std::vector<double4> tmp(std::max(n, 1));
+  for (int l = 0; l < n; ++l) {
+    const int d = l < g->n_own ? g->S.v0 + l : g->S.ghosts[l - g->n_own];
     const int k = g->dense2ins[d];
-    tmp[d] = make_double4(g->xyt[3 * k], g->xyt[3 * k + 1], std::cos(g->xyt[3 * k + 2]), std::sin(g->xyt[3 * k + 2]));
+    tmp[l] = make_double4(g->xyt[3 * k], g->xyt[3 * k + 1], std::cos(g->xyt[3 * k + 2]), std::sin(g->xyt[3 * k + 2]));
   }
-  GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp.data(), sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
+  if (n) GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp.data(), sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   g->h2d_bytes += sizeof(double4) * (double)n;
   g->device_values_valid = true;
@@ -282,70 +400,103 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (g->keys.empty()) return g->fail(GS_EINVAL, "graph has no vertices");
   build_dense_order(g);
   const int N = (int)g->keys.size(), E = (int)g->e1.size(), P = (int)g->pr_v.size();
-  std::vector<int> di(E), dj(E), dp(P);
+  g->di.resize(E);
+  g->dj.resize(E);
+  g->dp.resize(P);
   for (int k = 0; k < E; ++k) {
-    di[k] = g->ins2dense[g->e1[k]];
-    dj[k] = g->ins2dense[g->e2[k]];
+    g->di[k] = g->ins2dense[g->e1[k]];
+    g->dj[k] = g->ins2dense[g->e2[k]];
   }
-  for (int k = 0; k < P; ++k) dp[k] = g->ins2dense[g->pr_v[k]];
-  gs::build_structure(N, E, di.data(), dj.data(), P, dp.data(), g->S);
-  const HostStructure& S = g->S;
+  for (int k = 0; k < P; ++k) g->dp[k] = g->ins2dense[g->pr_v[k]];
+  gs::canonical_order(N, E, g->di.data(), g->dj.data(), g->perm);
+  gs::build_local_structure(N, E, g->di.data(), g->dj.data(), g->perm, P, g->dp.data(), g->world, g->rank, g->S);
+  const LocalStructure& S = g->S;
   g->N = N;
   g->E = E;
   g->P = P;
-  // canonical-order factor arrays
-  std::vector<int2> eij(E);
-  std::vector<double2> zt(E), zr(E), o01(E), o23(E), o45(E);
-  for (int k = 0; k < E; ++k) {
-    const int s = S.perm[k];
-    eij[k] = make_int2(S.ci[k], S.cj[k]);
-    zt[k] = make_double2(g->ez[3 * s], g->ez[3 * s + 1]);
-    zr[k] = make_double2(std::cos(g->ez[3 * s + 2]), std::sin(g->ez[3 * s + 2]));
-    o01[k] = make_double2(g->eom[6 * s], g->eom[6 * s + 1]);
-    o23[k] = make_double2(g->eom[6 * s + 2], g->eom[6 * s + 3]);
-    o45[k] = make_double2(g->eom[6 * s + 4], g->eom[6 * s + 5]);
+  g->n_own = S.n_own;
+  g->n_loc = S.n_own + S.n_ghost;
+  // factor arrays in storage (SELL) order; padding slots are never referenced
+  const int FS = S.fsell.slots;
+  std::vector<int2> eij(FS, make_int2(0, 0));
+  std::vector<double2> zt(FS, make_double2(0, 0)), zr(FS, make_double2(1, 0)), o01(FS, make_double2(0, 0)),
+      o23(FS, make_double2(0, 0)), o45(FS, make_double2(0, 0));
+  for (int q = 0; q < FS; ++q) {
+    const int s = S.f_src[q];
+    if (s < 0) continue;
+    eij[q] = make_int2(S.f_i[q], S.f_j[q]);
+    zt[q] = make_double2(g->ez[3 * s], g->ez[3 * s + 1]);
+    zr[q] = make_double2(std::cos(g->ez[3 * s + 2]), std::sin(g->ez[3 * s + 2]));
+    o01[q] = make_double2(g->eom[6 * s], g->eom[6 * s + 1]);
+    o23[q] = make_double2(g->eom[6 * s + 2], g->eom[6 * s + 3]);
+    o45[q] = make_double2(g->eom[6 * s + 4], g->eom[6 * s + 5]);
   }
-  std::vector<double4> prp(P);
-  for (int k = 0; k < P; ++k)
-    prp[k] = make_double4(g->pr_xyt[3 * k], g->pr_xyt[3 * k + 1], std::cos(g->pr_xyt[3 * k + 2]), std::sin(g->pr_xyt[3 * k + 2]));
+  g->e_count = 0;
+  for (uint32_t code : S.c_code)
+    if (code != gs::kPadCode && (code & 4u) && (code & 3u) < 2) g->e_count++;
+  std::vector<double4> prp(S.P_loc);
+  std::vector<double> prom(6 * (size_t)S.P_loc);
+  for (int k = 0; k < S.P_loc; ++k) {
+    const int s = S.pr_src[k];
+    prp[k] = make_double4(g->pr_xyt[3 * s], g->pr_xyt[3 * s + 1], std::cos(g->pr_xyt[3 * s + 2]), std::sin(g->pr_xyt[3 * s + 2]));
+    for (int m = 0; m < 6; ++m) prom[6 * (size_t)k + m] = g->pr_om[6 * (size_t)s + m];
+  }
+  std::vector<int> segtile(S.seg_tile, S.seg_tile + gs::kSegments + 1);
   if (gs_status s = upload(g, g->d_eij, eij)) return s;
   if (gs_status s = upload(g, g->d_zt, zt)) return s;
   if (gs_status s = upload(g, g->d_zr, zr)) return s;
   if (gs_status s = upload(g, g->d_o01, o01)) return s;
   if (gs_status s = upload(g, g->d_o23, o23)) return s;
   if (gs_status s = upload(g, g->d_o45, o45)) return s;
-  if (gs_status s = upload(g, g->d_pr_idx, dp)) return s;
+  if (gs_status s = upload(g, g->d_pr_row, S.pr_row)) return s;
   if (gs_status s = upload(g, g->d_pr_pose, prp)) return s;
-  if (gs_status s = upload(g, g->d_pr_om, g->pr_om)) return s;
-  if (gs_status s = upload(g, g->d_crowptr, S.crowptr)) return s;
+  if (gs_status s = upload(g, g->d_pr_om, prom)) return s;
+  if (gs_status s = upload(g, g->d_cbase, S.csell.base)) return s;
+  if (gs_status s = upload(g, g->d_cwidth, S.csell.width)) return s;
   if (gs_status s = upload(g, g->d_ccode, S.c_code)) return s;
   if (gs_status s = upload(g, g->d_cblk, S.c_blk)) return s;
-  if (gs_status s = upload(g, g->d_orowptr, S.orowptr)) return s;
-  if (gs_status s = upload(g, g->d_ocol, S.ocol)) return s;
-  if (gs_status s = upload(g, g->d_atiles, S.atiles)) return s;
-  if (gs_status s = upload(g, g->d_stiles, S.stiles)) return s;
-  const size_t n3 = 3 * (size_t)N;
-  GS_CUDA(g, g->d_pose.alloc(N));
-  GS_CUDA(g, g->d_pose_try.alloc(N));
-  GS_CUDA(g, g->d_Ho.alloc(std::max<size_t>(9 * (size_t)S.nnzo, 1)));
-  GS_CUDA(g, g->d_Hd.alloc(6 * (size_t)N));
-  GS_CUDA(g, g->d_Minv.alloc(6 * (size_t)N));
+  if (gs_status s = upload(g, g->d_rbase, S.rsell.base)) return s;
+  if (gs_status s = upload(g, g->d_rwidth, S.rsell.width)) return s;
+  if (gs_status s = upload(g, g->d_rcol, S.r_col)) return s;
+  if (gs_status s = upload(g, g->d_rblk, S.r_blk)) return s;
+  if (gs_status s = upload(g, g->d_segtile, segtile)) return s;
+  if (gs_status s = upload(g, g->d_send_rows, S.send_rows)) return s;
+  const size_t n3 = 3 * (size_t)std::max(S.n_own, 1), nl3 = 3 * (size_t)std::max(g->n_loc, 1);
+  g->hstride = (size_t)std::max(S.bsell.slots, 1);
+  GS_CUDA(g, g->d_pose.alloc(std::max(g->n_loc, 1)));
+  GS_CUDA(g, g->d_pose_try.alloc(std::max(g->n_loc, 1)));
+  if (g->world > 1) GS_CUDA(g, g->d_pose_all.alloc(N));
+  GS_CUDA(g, g->d_Ho.alloc(9 * g->hstride));
+  GS_CUDA(g, cudaMemsetAsync(g->d_Ho.p, 0, sizeof(double) * 9 * g->hstride, g->stream));  // padding slots stay 0
+  GS_CUDA(g, g->d_Hd.alloc(2 * n3));
+  GS_CUDA(g, g->d_Minv.alloc(2 * n3));
   GS_CUDA(g, g->d_b.alloc(n3));
-  GS_CUDA(g, g->d_x.alloc(n3));
+  GS_CUDA(g, g->d_x.alloc(nl3));
   GS_CUDA(g, g->d_r.alloc(n3));
   GS_CUDA(g, g->d_z.alloc(n3));
-  GS_CUDA(g, g->d_p.alloc(n3));
+  GS_CUDA(g, g->d_p.alloc(nl3));
   GS_CUDA(g, g->d_Ap.alloc(n3));
   GS_CUDA(g, g->d_dscale.alloc(n3));
-  g->grid_v = (N + gs::kThreads - 1) / gs::kThreads;
-  g->grid_v3 = (int)((n3 + gs::kThreads - 1) / gs::kThreads);
-  g->grid_e = (E + P + gs::kThreads - 1) / gs::kThreads;
-  size_t maxgrid = std::max<size_t>({S.atiles.size(), S.stiles.size(), (size_t)g->grid_v3, (size_t)g->grid_e, 1});
-  GS_CUDA(g, g->d_part.alloc(2 * maxgrid));
+  GS_CUDA(g, g->d_sendbuf.alloc(4 * std::max<size_t>(S.send_rows.size(), 1)));
+  GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * nl3, g->stream));
+  GS_CUDA(g, cudaMemsetAsync(g->d_p.p, 0, sizeof(double) * nl3, g->stream));
+  g->grid_rows = std::max(S.ntiles, 1);
+  g->grid_flat3 = (int)((3 * (size_t)S.n_own + gs::kThreads - 1) / gs::kThreads);
+  if (g->grid_flat3 < 1) g->grid_flat3 = 1;
+  g->part_stride = g->grid_rows;
+  GS_CUDA(g, g->d_part.alloc(2 * (size_t)g->part_stride));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));  // staging vectors go out of scope
   g->topo_dirty = false;
   g->device_values_valid = false;
   if (gs_status s = upload_values(g)) return s;
+  if (g->world > 1) {
+    // establish every NCCL connection outside stream capture: one halo exchange per width, one all-gather
+    if (gs_status s = halo_exchange(g, g->d_p.p, 3)) return s;
+    if (gs_status s = halo_exchange(g, reinterpret_cast<double*>(g->d_pose_try.p), 4)) return s;
+    const size_t chunk = 2 * (size_t)(gs::kSegments / g->world);
+    GS_NCCL(g, gs::nccl().AllGather(g->d_segs.p + g->rank * chunk, g->d_segs.p, chunk, ncclDouble, g->comm, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  }
   if (gs_status s = capture_pcg_graph(g)) return s;
   if (ms_out) *ms_out = now_ms() - t0;
   return GS_OK;
@@ -364,43 +515,16 @@ gs_status write_scalars(gs_graph* g) {
   return GS_OK;
 }
 
-gs::AsmArgs asm_args(gs_graph* g) {
-  gs::AsmArgs a;
-  a.tiles = g->d_atiles.p;
-  a.crowptr = g->d_crowptr.p;
-  a.c_code = g->d_ccode.p;
-  a.c_blk = g->d_cblk.p;
-  a.e_ij = g->d_eij.p;
-  a.e_zt = g->d_zt.p;
-  a.e_zr = g->d_zr.p;
-  a.e_o01 = g->d_o01.p;
-  a.e_o23 = g->d_o23.p;
-  a.e_o45 = g->d_o45.p;
-  a.pr_idx = g->d_pr_idx.p;
-  a.pr_pose = g->d_pr_pose.p;
-  a.pr_om = g->d_pr_om.p;
-  a.pose = g->d_pose.p;
-  a.Ho = g->d_Ho.p;
-  a.Hd = g->d_Hd.p;
-  a.b = g->d_b.p;
-  a.part = g->d_part.p;
-  a.sc = g->d_sc.p;
-  a.counter = g->d_counter.p + 2;
-  a.nnzo = g->S.nnzo;
-  a.N = g->N;
-  return a;
-}
-
 // linearise + assemble at the current device poses (async)
 gs_status launch_assemble(gs_graph* g) {
-  const unsigned grid = (unsigned)g->S.atiles.size();
   if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT)
-    gs::k_assemble<1><<<grid, gs::kThreads, gs::kAsmSmemBytes, g->stream>>>(asm_args(g));
+    gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, g->d_pose.p), reduce_ctx(g, 2));
   else
-    gs::k_assemble<0><<<grid, gs::kThreads, gs::kAsmSmemBytes, g->stream>>>(asm_args(g));
+    gs::k_assemble<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, g->d_pose.p), reduce_ctx(g, 2));
   g->launches += 1;
+  if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
   if (g->prm.diagonal_damping) {
-    gs::k_dscale<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->d_dscale.p, g->N);
+    gs::k_dscale<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->d_dscale.p, g->n_own);
     g->launches += 1;
   }
   GS_CUDA(g, cudaGetLastError());
@@ -408,27 +532,25 @@ gs_status launch_assemble(gs_graph* g) {
   return GS_OK;
 }
 
+// chi2 at `pose` (ghost slots must be current)
 gs_status launch_chi2(gs_graph* g, const double4* pose) {
-  gs::Chi2Args a;
-  a.e_ij = g->d_eij.p;
-  a.e_zt = g->d_zt.p;
-  a.e_zr = g->d_zr.p;
-  a.e_o01 = g->d_o01.p;
-  a.e_o23 = g->d_o23.p;
-  a.e_o45 = g->d_o45.p;
-  a.pr_idx = g->d_pr_idx.p;
-  a.pr_pose = g->d_pr_pose.p;
-  a.pr_om = g->d_pr_om.p;
-  a.pose = pose;
-  a.part = g->d_part.p;
-  a.sc = g->d_sc.p;
-  a.counter = g->d_counter.p + 3;
-  a.E = g->E;
-  a.P = g->P;
-  gs::k_chi2<<<std::max(g->grid_e, 1), gs::kThreads, 0, g->stream>>>(a);
+  gs::k_chi2<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, pose), reduce_ctx(g, 3));
   g->launches += 1;
+  if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
   GS_CUDA(g, cudaGetLastError());
   return GS_OK;
+}
+
+void launch_pcg_setup(gs_graph* g) {
+  gs::k_minv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
+                                                           g->d_sc.p, g->d_Minv.p, g->n_own);
+  gs::k_pcg_init<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
+  g->launches += 2;
+}
+
+int64_t launches_per_pcg_iteration(const gs_graph* g) {
+  if (g->world == 1) return 3;
+  return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
 }
 
 // Solve (H + lambda D) x = -b by block-Jacobi PCG; result in d_x.  H, b must be assembled.
@@ -439,17 +561,22 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
   h->tol2 = g->prm.pcg_rel_tol * g->prm.pcg_rel_tol;
   h->max_iters = g->prm.pcg_max_iters;
   if (gs_status s = write_scalars(g)) return s;
-  gs::k_minv<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
-                                                        g->d_sc.p, g->d_Minv.p, g->N);
-  gs::k_pcg_init<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
-  g->launches += 2;
+  launch_pcg_setup(g);
+  if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
   GS_CUDA(g, cudaGetLastError());
+  const int64_t keep = g->launches;
   for (;;) {
-    GS_CUDA(g, cudaGraphLaunch(g->pcg_exec, g->stream));
+    if (g->pcg_exec) {
+      GS_CUDA(g, cudaGraphLaunch(g->pcg_exec, g->stream));
+    } else {
+      for (int it = 0; it < kPcgBatch; ++it)
+        if (gs_status s = launch_pcg_iteration(g)) return s;
+    }
     if (gs_status s = read_scalars(g)) return s;
     if (h->done) break;
   }
-  g->launches += 3 * (int64_t)h->iters;  // kernels that did work (the no-op tail of the last batch is not counted)
+  // kernels that did work (the no-op tail of the last batch is not counted)
+  g->launches = keep + launches_per_pcg_iteration(g) * (int64_t)h->iters;
   if (iters_out) *iters_out = h->iters;
   if (relres_out) *relres_out = h->rr0 > 0.0 ? std::sqrt(h->rr / h->rr0) : 0.0;
   if (done_out) *done_out = h->done;
@@ -460,6 +587,31 @@ float elapsed(gs_graph* g) {
   float ms = 0.f;
   cudaEventElapsedTime(&ms, g->ev0, g->ev1);
   return ms;
+}
+
+gs_status create_common(gs_graph* g) {
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return g->fail(GS_ECUDA, "no CUDA device (%s); libgraphslam_cuda has no CPU fallback",
+                   e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (g->prm.device >= 0) GS_CUDA(g, cudaSetDevice(g->prm.device));
+  GS_CUDA(g, cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking));
+  GS_CUDA(g, cudaEventCreate(&g->ev0));
+  GS_CUDA(g, cudaEventCreate(&g->ev1));
+  GS_CUDA(g, cudaEventCreate(&g->ev_begin));
+  GS_CUDA(g, cudaEventCreate(&g->ev_end));
+  GS_CUDA(g, g->d_sc.alloc(1));
+  GS_CUDA(g, g->d_counter.alloc(8));
+  GS_CUDA(g, g->d_segs.alloc(2 * gs::kSegments));
+  GS_CUDA(g, cudaMemsetAsync(g->d_counter.p, 0, 8 * sizeof(unsigned int), g->stream));
+  GS_CUDA(g, cudaMemsetAsync(g->d_sc.p, 0, sizeof(Scalars), g->stream));
+  GS_CUDA(g, cudaMemsetAsync(g->d_segs.p, 0, 2 * gs::kSegments * sizeof(double), g->stream));
+  GS_CUDA(g, cudaMallocHost(&g->h_sc, sizeof(Scalars)));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  const char* env = std::getenv("GS_PCG_GRAPH");
+  g->use_graph = !(env && env[0] == '0');
+  return GS_OK;
 }
 
 }  // namespace
@@ -500,25 +652,42 @@ gs_status gs_create(gs_graph** out, const gs_params* params) {
   *out = g;  // returned even on failure so that gs_last_error can be read; caller destroys it
   if (g->prm.world_size != 1 || g->prm.rank != 0)
     return g->fail(GS_EINVAL, "multi-rank graphs are created with gs_create_distributed");
-  int ndev = 0;
-  cudaError_t e = cudaGetDeviceCount(&ndev);
-  if (e != cudaSuccess || ndev == 0)
-    return g->fail(GS_ECUDA, "no CUDA device (%s); libgraphslam_cuda has no CPU fallback",
-                   e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
-  if (g->prm.device >= 0) GS_CUDA(g, cudaSetDevice(g->prm.device));
-  GS_CUDA(g, cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking));
-  GS_CUDA(g, cudaEventCreate(&g->ev0));
-  GS_CUDA(g, cudaEventCreate(&g->ev1));
-  GS_CUDA(g, cudaEventCreate(&g->ev_begin));
-  GS_CUDA(g, cudaEventCreate(&g->ev_end));
-  GS_CUDA(g, g->d_sc.alloc(1));
-  GS_CUDA(g, g->d_counter.alloc(8));
-  GS_CUDA(g, cudaMemsetAsync(g->d_counter.p, 0, 8 * sizeof(unsigned int), g->stream));
-  GS_CUDA(g, cudaMemsetAsync(g->d_sc.p, 0, sizeof(Scalars), g->stream));
-  GS_CUDA(g, cudaMallocHost(&g->h_sc, sizeof(Scalars)));
-  GS_CUDA(g, cudaFuncSetAttribute(gs::k_assemble<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, gs::kAsmSmemBytes));
-  GS_CUDA(g, cudaFuncSetAttribute(gs::k_assemble<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, gs::kAsmSmemBytes));
-  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  return create_common(g);
+}
+
+gs_status gs_nccl_unique_id(void* out, size_t cap, size_t* n) {
+  if (n) *n = sizeof(ncclUniqueId);
+  if (!out) return GS_OK;
+  if (cap < sizeof(ncclUniqueId)) return GS_EINVAL;
+  if (!gs::nccl().load().empty()) return GS_ENCCL;
+  ncclUniqueId id;
+  if (gs::nccl().GetUniqueId(&id) != ncclSuccess) return GS_ENCCL;
+  std::memcpy(out, &id, sizeof id);
+  return GS_OK;
+}
+
+gs_status gs_create_distributed(gs_graph** out, const gs_params* params, const void* nccl_id, size_t id_bytes) {
+  if (!out) return GS_EINVAL;
+  *out = nullptr;
+  gs_graph* g = new (std::nothrow) gs_graph();
+  if (!g) return GS_EINVAL;
+  if (params) g->prm = *params;
+  else gs_default_params(&g->prm);
+  *out = g;
+  const int w = g->prm.world_size, r = g->prm.rank;
+  if (!(w == 1 || w == 2 || w == 4 || w == 8) || r < 0 || r >= w)
+    return g->fail(GS_EINVAL, "world_size must be 1, 2, 4 or 8 and 0 <= rank < world_size (got rank %d of %d)", r, w);
+  g->world = w;
+  g->rank = r;
+  if (gs_status s = create_common(g)) return s;
+  if (w > 1) {
+    if (!nccl_id || id_bytes != sizeof(ncclUniqueId)) return g->fail(GS_EINVAL, "nccl_id must be %zu bytes", sizeof(ncclUniqueId));
+    const std::string why = gs::nccl().load();
+    if (!why.empty()) return g->fail(GS_ENCCL, "%s", why.c_str());
+    ncclUniqueId id;
+    std::memcpy(&id, nccl_id, sizeof id);
+    GS_NCCL(g, gs::nccl().CommInitRank(&g->comm, w, id, r));
+  }
   return GS_OK;
 }
 
@@ -526,6 +695,7 @@ gs_status gs_destroy(gs_graph* g) {
   if (!g) return GS_EINVAL;
   if (g->stream) cudaStreamSynchronize(g->stream);
   destroy_graph_exec(g);
+  if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->ev0) cudaEventDestroy(g->ev0);
   if (g->ev1) cudaEventDestroy(g->ev1);
@@ -675,18 +845,19 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) {
       if (solved || done == 3) {
         // linear.error(0) - linear.error(delta) = -delta.b - 0.5 delta.H.delta  (undamped H)
         GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
-        gs::k_spmv<<<(unsigned)g->S.stiles.size(), gs::kThreads, 0, g->stream>>>(spmv_args(g, g->d_x.p, g->d_Ap.p, 1));
+        if (gs_status s = launch_spmv(g, g->d_x.p, g->d_Ap.p, 1)) return s;
         if (gs_status s = read_scalars(g)) return s;
         const double dHd = h->dot;
-        gs::k_dot<<<g->grid_v3, gs::kThreads, 0, g->stream>>>(g->d_x.p, g->d_b.p, 3 * g->N, g->d_part.p, g->d_sc.p,
-                                                              g->d_counter.p + 4);
+        gs::k_dot<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_x.p, g->d_b.p, g->n_own, reduce_ctx(g, 4));
+        if (gs_status s = finish_reduce(g, 1, gs::OP_DOT)) return s;
         if (gs_status s = read_scalars(g)) return s;
         const double db = h->dot;
         g->launches += 2;
         const double lin_change = -db - 0.5 * dHd;
         if (lin_change >= 0.0) {
-          gs::k_retract<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_pose.p, g->d_x.p, g->d_pose_try.p, g->N);
+          gs::k_retract<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_pose.p, g->d_x.p, g->d_pose_try.p, g->n_own);
           g->launches += 1;
+          if (gs_status s = halo_exchange(g, reinterpret_cast<double*>(g->d_pose_try.p), 4)) return s;
           if (gs_status s = launch_chi2(g, g->d_pose_try.p)) return s;
           if (gs_status s = read_scalars(g)) return s;
           new_error = 0.5 * h->chi2;
@@ -704,6 +875,7 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) {
       if (step_ok) {
         g->tr_lambda.push_back(lambda);
         std::swap(g->d_pose.p, g->d_pose_try.p);  // accept: candidate becomes current
+        std::swap(g->d_pose.n, g->d_pose_try.n);
         g->host_values_fresh = false;
         g->system_valid = false;
         error = new_error;
@@ -823,10 +995,9 @@ gs_status gs_num_factors(const gs_graph* g, size_t* n) {
 gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* nnzb) {
   if (!g) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;
-  if (nnzb) *nnzb = (size_t)g->S.nnzo + g->N;
-  if (!rowptr && !colidx) return GS_OK;
   std::vector<int32_t> rp, ci;
-  g->S.full_pattern(rp, ci);
+  gs::global_pattern(g->N, g->E, g->di.data(), g->dj.data(), rp, ci);
+  if (nnzb) *nnzb = ci.size();
   if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
   if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
   return GS_OK;
@@ -834,36 +1005,42 @@ gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* 
 
 gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) {
   if (!g) return GS_EINVAL;
+  if (g->world != 1) return g->fail(GS_EINVAL, "gs_get_system is a single-rank parity hook");
   if (gs_status s = prepare(g, nullptr)) return s;
   if (gs_status s = launch_assemble(g)) return s;
   if (gs_status s = read_scalars(g)) return s;
   if (chi2) *chi2 = g->h_sc->chi2;
-  const int N = g->N, nnzo = g->S.nnzo;
+  const int N = g->N;
+  const size_t hs = g->hstride;
   if (b) {
     GS_CUDA(g, cudaMemcpyAsync(b, g->d_b.p, sizeof(double) * 3 * N, cudaMemcpyDeviceToHost, g->stream));
     GS_CUDA(g, cudaStreamSynchronize(g->stream));
   }
   if (blocks) {
-    std::vector<double> ho(9 * (size_t)std::max(nnzo, 1)), hd(6 * (size_t)N);
-    if (nnzo) GS_CUDA(g, cudaMemcpyAsync(ho.data(), g->d_Ho.p, sizeof(double) * 9 * nnzo, cudaMemcpyDeviceToHost, g->stream));
+    std::vector<double> ho(9 * hs), hd(6 * (size_t)N);
+    GS_CUDA(g, cudaMemcpyAsync(ho.data(), g->d_Ho.p, sizeof(double) * 9 * hs, cudaMemcpyDeviceToHost, g->stream));
     GS_CUDA(g, cudaMemcpyAsync(hd.data(), g->d_Hd.p, sizeof(double) * 6 * N, cudaMemcpyDeviceToHost, g->stream));
     GS_CUDA(g, cudaStreamSynchronize(g->stream));
     size_t w = 0;
-    const HostStructure& S = g->S;
-    auto put_off = [&](int k) {
-      for (int m = 0; m < 9; ++m) blocks[9 * w + m] = ho[(size_t)m * nnzo + k];
+    const LocalStructure& S = g->S;
+    auto put_off = [&](int word) {
+      const int pos = word >> 1;
+      const bool tr = word & 1;
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) blocks[9 * w + 3 * r + c] = ho[(size_t)(tr ? 3 * c + r : 3 * r + c) * hs + pos];
       ++w;
     };
     for (int r = 0; r < N; ++r) {
-      int k = S.orowptr[r];
-      const int k1 = S.orowptr[r + 1];
-      while (k < k1 && S.ocol[k] < r) put_off(k++);
+      const int sl = r / gs::kSlice, wd = S.rsell.width[sl];
+      int s = 0;
+      auto col_at = [&](int k) { return S.r_col[S.rsell.pos(r, k)]; };
+      while (s < wd && col_at(s) >= 0 && col_at(s) < r) put_off(S.r_blk[S.rsell.pos(r, s++)]);
       const double d00 = hd[r], d01 = hd[(size_t)N + r], d02 = hd[2 * (size_t)N + r];
       const double d11 = hd[3 * (size_t)N + r], d12 = hd[4 * (size_t)N + r], d22 = hd[5 * (size_t)N + r];
       const double full[9] = {d00, d01, d02, d01, d11, d12, d02, d12, d22};
       std::memcpy(blocks + 9 * w, full, sizeof full);
       ++w;
-      while (k < k1) put_off(k++);
+      while (s < wd && col_at(s) >= 0) put_off(S.r_blk[S.rsell.pos(r, s++)]);
     }
   }
   return GS_OK;
@@ -871,6 +1048,7 @@ gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) {
 
 gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual) {
   if (!g) return GS_EINVAL;
+  if (g->world != 1 && delta) return g->fail(GS_EINVAL, "gs_solve_linear returns delta on a single rank only");
   if (gs_status s = prepare(g, nullptr)) return s;
   if (!g->system_valid)
     if (gs_status s = launch_assemble(g)) return s;
@@ -911,20 +1089,21 @@ gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], do
   h->tol2 = 0.0;  // never converge: every profiled iteration does full work
   h->max_iters = 1 << 30;
   if (gs_status s = write_scalars(g)) return s;
-  gs::k_minv<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
-                                                        g->d_sc.p, g->d_Minv.p, g->N);
-  gs::k_pcg_init<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
-  for (int w = 0; w < 3; ++w) launch_pcg_iteration(g);  // warm-up
+  launch_pcg_setup(g);
+  if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
+  for (int w = 0; w < 3; ++w)
+    if (gs_status s = launch_pcg_iteration(g)) return s;  // warm-up
   std::vector<cudaEvent_t> ev(4 * (size_t)iters);
   for (auto& e : ev) GS_CUDA(g, cudaEventCreate(&e));
   for (int it = 0; it < iters; ++it) {
     cudaEvent_t* e = &ev[4 * (size_t)it];
     cudaEventRecord(e[0], g->stream);
-    gs::k_spmv<<<(unsigned)g->S.stiles.size(), gs::kThreads, 0, g->stream>>>(spmv_args(g, g->d_p.p, g->d_Ap.p, 0));
+    if (gs_status s = launch_spmv(g, g->d_p.p, g->d_Ap.p, 0)) return s;
     cudaEventRecord(e[1], g->stream);
-    gs::k_pcg_update<<<g->grid_v, gs::kThreads, 0, g->stream>>>(pcg_args(g));
+    gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
+    if (gs_status s = finish_reduce(g, 2, gs::OP_UPDATE)) return s;
     cudaEventRecord(e[2], g->stream);
-    gs::k_pcg_dir<<<g->grid_v3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->N);
+    gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->n_own);
     cudaEventRecord(e[3], g->stream);
   }
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
@@ -939,19 +1118,19 @@ gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], do
   for (auto& e : ev) cudaEventDestroy(e);
   for (int k = 0; k < 3; ++k) ms[k] = acc[k] / iters;
   if (bytes) {
-    const double N = g->N, nnzb = (double)g->S.nnzo + g->N;
+    const double N = g->n_own, nnzb = (double)g->S.nnzo_own + g->n_own;
     bytes[0] = 76.0 * nnzb + 52.0 * N;                 // K3
     bytes[1] = (4 * 24.0 + 72.0 + 3 * 24.0) * N;       // K4a: x,p,r,Ap + Minv read; x,r,z written
     bytes[2] = 72.0 * N;                               // K4b: z,p read; p written
   }
-  g->launches += 3 * (int64_t)(iters + 3) + 2;
+  g->launches += launches_per_pcg_iteration(g) * (int64_t)(iters + 3) + 2;
   return GS_OK;
 }
 
 gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3]) {
   if (!g || !ms || reps <= 0) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;
-  GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * 3 * g->N, g->stream));
+  GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * 3 * std::max(g->n_loc, 1), g->stream));
   double acc[3] = {0, 0, 0};
   for (int r = 0; r < reps + 1; ++r) {  // first pass is warm-up
     float t = 0.f;
@@ -962,7 +1141,8 @@ gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3])
     cudaEventElapsedTime(&t, g->ev0, g->ev1);
     if (r) acc[0] += t;
     GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
-    gs::k_retract<<<g->grid_v, gs::kThreads, 0, g->stream>>>(g->d_pose.p, g->d_x.p, g->d_pose_try.p, g->N);
+    gs::k_retract<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_pose.p, g->d_x.p, g->d_pose_try.p, g->n_own);
+    if (gs_status s = halo_exchange(g, reinterpret_cast<double*>(g->d_pose_try.p), 4)) return s;
     GS_CUDA(g, cudaEventRecord(g->ev1, g->stream));
     GS_CUDA(g, cudaEventSynchronize(g->ev1));
     cudaEventElapsedTime(&t, g->ev0, g->ev1);
@@ -976,7 +1156,7 @@ gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3])
   }
   for (int k = 0; k < 3; ++k) ms[k] = acc[k] / reps;
   if (bytes) {
-    const double N = g->N, E = g->E, nnzb = (double)g->S.nnzo + g->N;
+    const double N = g->n_own, E = g->e_count, nnzb = (double)g->S.nnzo_own + g->n_own;
     bytes[0] = 80.0 * E + 24.0 * N + 72.0 * nnzb + 24.0 * N;   // K1+K2
     bytes[1] = 72.0 * N;                                        // K5 retract
     bytes[2] = 80.0 * E;                                        // K5 chi2
@@ -1012,6 +1192,7 @@ void gs_compose(const double a[3], const double b[3], double out[3]) {
 
 gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist) {
   if (!g || !out_key || skip < 0) return GS_EINVAL;
+  if (g->world != 1) return g->fail(GS_EINVAL, "gs_closest_keyframe runs on a single-rank graph");
   const int v = g->find(key);
   if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)key);
   const int nv = (int)g->keys.size();
@@ -1048,16 +1229,16 @@ gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out
 gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,
                           size_t* nnzb, int32_t* perm) {
   if (n <= 0 || e < 0 || (e && (!ei || !ej))) return GS_EINVAL;
-  HostStructure S;
-  gs::build_structure(n, e, ei, ej, 0, nullptr, S);
-  if (nnzb) *nnzb = (size_t)S.nnzo + n;
-  if (rowptr || colidx) {
-    std::vector<int32_t> rp, ci;
-    S.full_pattern(rp, ci);
-    if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
-    if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
+  std::vector<int32_t> rp, ci;
+  gs::global_pattern(n, e, ei, ej, rp, ci);
+  if (nnzb) *nnzb = ci.size();
+  if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
+  if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
+  if (perm) {
+    std::vector<int> pm;
+    gs::canonical_order(n, e, ei, ej, pm);
+    std::memcpy(perm, pm.data(), sizeof(int32_t) * e);
   }
-  if (perm) std::memcpy(perm, S.perm.data(), sizeof(int32_t) * e);
   return GS_OK;
 }
 
@@ -1074,13 +1255,13 @@ gs_status gs_host_between(const double pi[3], const double pj[3], const double z
   if (mode == 0) gs::between_linearize<0>(a, b, zt, zr, L);
   else gs::between_linearize<1>(a, b, zt, zr, L);
   gs::Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-  double off[9], dg[6], bv[3];
-  gs::normal_pieces(O, L.Ai, L.Aj, L.e, off, dg, bv);
+  double dg[6], bv[3];
+  gs::diag_pieces(O, L.Ai, L.e, dg, bv);
   const double fi[9] = {dg[0], dg[1], dg[2], dg[1], dg[3], dg[4], dg[2], dg[4], dg[5]};
   std::memcpy(Hii, fi, sizeof fi);
-  std::memcpy(Hij, off, sizeof off);
   std::memcpy(bi, bv, sizeof bv);
-  gs::normal_pieces(O, L.Aj, L.Ai, L.e, off, dg, bv);
+  gs::off_block(O, L.Ai, L.Aj, Hij);
+  gs::diag_pieces(O, L.Aj, L.e, dg, bv);
   const double fj[9] = {dg[0], dg[1], dg[2], dg[1], dg[3], dg[4], dg[2], dg[4], dg[5]};
   std::memcpy(Hjj, fj, sizeof fj);
   std::memcpy(bj, bv, sizeof bv);

@@ -1,12 +1,13 @@
 // sm_100a kernels of the Gauss-Newton / Levenberg-Marquardt iteration (FP64, HBM-bound, no tensor
-// cores: no stage is a dense contraction).  Every reduction has a fixed order (no floating-point
-// atomics), so results are bit-reproducible run to run.
+// cores: no stage is a dense contraction).  One thread per block row; the per-row bodies are in
+// rows.cuh.  Every reduction runs tile (one CTA, fixed shuffle tree) -> segment (fixed-order sum of
+// the tile partials by the last CTA to finish) -> total (the kSegments segment sums added in
+// order), so results are bit-reproducible run to run AND identical for 1, 2, 4 or 8 ranks.
 //
 //   K1+K2  k_assemble        per-factor SE(2) linearisation (BetweenFactor / PriorFactor + Gaussian
-//                            whitening) fused with the block-row-owner segmented reduction into
-//                            H = sum J^T Omega J (diag planes + off-diagonal BSR planes) and b
-//   K3     k_spmv            y = (H + lambda*D) p over the BSR, products staged through shared
-//                            memory, fused p^T y partial
+//                            whitening) fused with the row-owner reduction into H = sum J^T Omega J
+//                            (diagonal planes + one stored block per vertex pair) and b
+//   K3     k_spmv            y = (H + lambda*D) p over the symmetric block storage, fused p^T y
 //   K4     k_pcg_init / k_pcg_update / k_pcg_dir   block-Jacobi PCG vector updates with fused dots
 //   K5     k_retract, k_chi2 Values::retract and graph.error
 //
@@ -14,12 +15,11 @@
 // LevenbergMarquardtOptimizer::optimize() (reference src/graph/src/graph.cpp:119); see DESIGN.md.
 #pragma once
 #include <cstdint>
-#include "se2.cuh"
-#include "structure.hpp"
+#include "rows.cuh"
 
 namespace gs {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = kTile;
 
 // Device-resident scalars: PCG coefficients never visit the host.
 struct Scalars {
@@ -31,11 +31,26 @@ struct Scalars {
   double lambda;
   double tol2;      // pcg_rel_tol^2
   double chi2;      // k_chi2 / k_assemble result
-  double dot;       // k_dot result
+  double dot;       // k_dot / plain k_spmv result
   int done;         // 0 running, 1 converged, 2 breakdown (p^T A p <= 0), 3 max iters
   int iters;
   int max_iters;
   int pad;
+};
+
+enum ReduceOp { OP_PAP = 0, OP_DOT = 1, OP_INIT = 2, OP_UPDATE = 3, OP_CHI2 = 4 };
+
+// where a kernel's reduction goes
+struct ReduceCtx {
+  double* part;            // [nq][part_stride] per-tile partials
+  int part_stride;
+  double* segs;            // [world][nq][spr] segment sums; this rank fills its own chunk
+  const int* seg_tile;     // spr+1 local tile boundaries
+  int spr;                 // segments per rank
+  int rank;
+  int world;
+  unsigned int* counter;
+  Scalars* sc;
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -78,397 +93,156 @@ __device__ __forceinline__ double final_sum(const double* part, int n, double* r
   return block_sum(s, red);
 }
 
-// ------------------------------------------------------------------------------------------------
-// K1+K2: linearise + assemble.  One CTA per tile of block rows.  Phase 1: one thread per
-// contribution (factor side) linearises it and parks its 18 numbers in shared memory.  Phase 2:
-// the owner of each output sums its contributions in list order.  Every output is written once.
-// ------------------------------------------------------------------------------------------------
-struct AsmArgs {
-  const Tile* tiles;
-  const int* crowptr;
-  const uint32_t* c_code;
-  const int* c_blk;
-  const int2* e_ij;
-  const double2* e_zt;
-  const double2* e_zr;
-  const double2* e_o01;
-  const double2* e_o23;
-  const double2* e_o45;
-  const int* pr_idx;
-  const double4* pr_pose;
-  const double* pr_om;  // 6 per prior
-  const double4* pose;
-  double* Ho;           // 9 planes of nnzo
-  double* Hd;           // 6 planes of N
-  double* b;            // 3N
-  double* part;         // per-tile chi2 partial
-  Scalars* sc;
-  unsigned int* counter;
-  int nnzo;
-  int N;
-};
+// total of quantity q = the kSegments segment sums in global segment order
+__device__ __forceinline__ double seg_total(const double* segs, int q, int nq, int spr) {
+  double t = 0.0;
+  for (int g = 0; g < kSegments; ++g) t += __ldcg(segs + ((size_t)(g / spr) * nq + q) * spr + (g % spr));
+  return t;
+}
 
-constexpr int kAsmSmemBytes = (18 * kAsmChunk + 9 * kAsmRows + 8) * 8 + (kAsmChunk + kAsmRows + 1 + 1) * 4;
+// the stateful scalar step that follows each reduction (one thread)
+__device__ __forceinline__ void apply_scalars(Scalars* sc, int op, double t0, double t1) {
+  switch (op) {
+    case OP_PAP:
+      if (sc->done) return;
+      sc->pAp = t0;
+      if (!(t0 > 0.0)) sc->done = 2;
+      break;
+    case OP_DOT:
+      sc->dot = t0;
+      break;
+    case OP_INIT:
+      sc->rz = t0;
+      sc->rr = t1;
+      sc->rr0 = t1;
+      sc->iters = 0;
+      sc->done = (t1 == 0.0) ? 1 : 0;
+      break;
+    case OP_UPDATE: {
+      if (sc->done) return;
+      sc->beta = t0 / sc->rz;
+      sc->rz = t0;
+      sc->rr = t1;
+      const int it = sc->iters + 1;
+      sc->iters = it;
+      if (t1 <= sc->tol2 * sc->rr0) sc->done = 1;
+      else if (!(t1 == t1)) sc->done = 2;
+      else if (it >= sc->max_iters) sc->done = 3;
+      break;
+    }
+    case OP_CHI2:
+      sc->chi2 = t0;
+      break;
+  }
+}
 
+// tile partials -> (last CTA) segment sums -> (single rank) totals and scalar step
+template <int NQ>
+__device__ __forceinline__ void reduce_finish(const ReduceCtx& c, const double (&v)[NQ], int op, double* red, int* flag) {
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    const double s = block_sum(v[q], red);
+    if (threadIdx.x == 0) c.part[(size_t)q * c.part_stride + blockIdx.x] = s;
+  }
+  if (last_block(c.counter, flag)) {
+    for (int q = 0; q < NQ; ++q)
+      for (int s = 0; s < c.spr; ++s) {
+        const int t0 = c.seg_tile[s], t1 = c.seg_tile[s + 1];
+        const double t = final_sum(c.part + (size_t)q * c.part_stride + t0, t1 - t0, red);
+        if (threadIdx.x == 0) c.segs[((size_t)c.rank * NQ + q) * c.spr + s] = t;
+      }
+    if (threadIdx.x == 0) {
+      if (c.world == 1) {
+        __threadfence();
+        const double a = seg_total(c.segs, 0, NQ, c.spr);
+        const double b = NQ > 1 ? seg_total(c.segs, 1, NQ, c.spr) : 0.0;
+        apply_scalars(c.sc, op, a, b);
+      }
+      *c.counter = 0u;
+    }
+  }
+}
+
+// multi-rank: runs after the all-gather of the segment sums
+__global__ void k_scalars(const double* segs, int nq, int spr, int op, Scalars* sc) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    const double a = seg_total(segs, 0, nq, spr);
+    const double b = nq > 1 ? seg_total(segs, 1, nq, spr) : 0.0;
+    apply_scalars(sc, op, a, b);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(kThreads) k_assemble(const AsmArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* S = reinterpret_cast<double*>(smem_raw);            // [18][kAsmChunk]
-  double* acc = S + 18 * kAsmChunk;                           // [9][kAsmRows]
-  double* red = acc + 9 * kAsmRows;                           // [8]
-  int* tgt = reinterpret_cast<int*>(red + 8);                 // [kAsmChunk]
-  int* srow = tgt + kAsmChunk;                                // [kAsmRows+1]
-  int* flag = srow + kAsmRows + 1;
-
-  const int tid = threadIdx.x;
-  const Tile t = a.tiles[blockIdx.x];
-  const int nr = t.r1 - t.r0;
-  for (int i = tid; i <= nr; i += kThreads) srow[i] = a.crowptr[t.r0 + i];
-  for (int i = tid; i < 9 * nr; i += kThreads) acc[(i / nr) * kAsmRows + (i % nr)] = 0.0;
-  __syncthreads();
-  const int c0 = srow[0], c1 = srow[nr];
-  double chi2 = 0.0;
-
-  for (int base = c0; base < c1; base += kAsmChunk) {
-    const int nb = min(kAsmChunk, c1 - base);
-    // ---- phase 1: linearise one factor side per thread
-    if (tid < nb) {
-      const int c = base + tid;
-      const uint32_t code = a.c_code[c];
-      const int kind = code & 3u;
-      const int idx = code >> 2;
-      double off[9], dg[6], bv[3];
-      if (kind < 2) {
-        const int2 ij = a.e_ij[idx];
-        const double2 zt = a.e_zt[idx], zr = a.e_zr[idx];
-        const double2 o01 = a.e_o01[idx], o23 = a.e_o23[idx], o45 = a.e_o45[idx];
-        const double4 pi = a.pose[ij.x], pj = a.pose[ij.y];
-        BetweenLin L;
-        between_linearize<MODE>(pi, pj, zt, zr, L);
-        Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
-        if (kind == 0) {
-          normal_pieces(O, L.Ai, L.Aj, L.e, off, dg, bv);
-          chi2 += quad_form(O, L.e);
-        } else {
-          normal_pieces(O, L.Aj, L.Ai, L.e, off, dg, bv);
-        }
-      } else {
-        const double4 pp = a.pr_pose[idx];
-        const double4 px = a.pose[a.pr_idx[idx]];
-        const double* om = a.pr_om + 6 * idx;
-        Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-        double e[3];
-        Mat3 A;
-        prior_linearize<MODE>(px, pp, e, A);
-        normal_pieces(O, A, A, e, off, dg, bv);
-        chi2 += quad_form(O, e);
-      }
-#pragma unroll
-      for (int k = 0; k < 9; ++k) S[k * kAsmChunk + tid] = off[k];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) S[(9 + k) * kAsmChunk + tid] = dg[k];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) S[(15 + k) * kAsmChunk + tid] = bv[k];
-      tgt[tid] = a.c_blk[c];
-    }
-    __syncthreads();
-    // ---- phase 2a: off-diagonal blocks; a run = contributions of one (row, col) pair
-    if (tid < nb) {
-      const int v = tgt[tid];
-      if (v >= 0 && ((v & 1) || tid == 0)) {
-        double sum[9];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) sum[k] = S[k * kAsmChunk + tid];
-        int q = tid + 1;
-        while (q < nb) {
-          const int w = tgt[q];
-          if (w < 0 || (w & 1)) break;
-#pragma unroll
-          for (int k = 0; k < 9; ++k) sum[k] += S[k * kAsmChunk + q];
-          ++q;
-        }
-        const int blk = v >> 1;
-        if (v & 1) {
-#pragma unroll
-          for (int k = 0; k < 9; ++k) a.Ho[(size_t)k * a.nnzo + blk] = sum[k];
-        } else {  // run continued from the previous chunk of this tile (same CTA wrote it)
-#pragma unroll
-          for (int k = 0; k < 9; ++k) a.Ho[(size_t)k * a.nnzo + blk] += sum[k];
-        }
-      }
-    }
-    // ---- phase 2b: diagonal block (6) and gradient (3) of each row, in list order
-    for (int u = tid; u < 9 * nr; u += kThreads) {
-      const int k = u / nr, row = u - k * nr;
-      const int lo = max(srow[row], base) - base, hi = min(srow[row + 1], base + nb) - base;
-      double s = acc[k * kAsmRows + row];
-      const double* src = S + (9 + k) * kAsmChunk;
-      for (int q = lo; q < hi; ++q) s += src[q];
-      acc[k * kAsmRows + row] = s;
-    }
-    __syncthreads();
-  }
-  for (int u = tid; u < 9 * nr; u += kThreads) {
-    const int k = u / nr, row = u - k * nr;
-    const double v = acc[k * kAsmRows + row];
-    if (k < 6) a.Hd[(size_t)k * a.N + t.r0 + row] = v;
-    else a.b[3 * (size_t)(t.r0 + row) + (k - 6)] = v;
-  }
-  chi2 = block_sum(chi2, red);
-  if (tid == 0) a.part[blockIdx.x] = chi2;
-  if (last_block(a.counter, flag)) {
-    const double s = final_sum(a.part, gridDim.x, red);
-    if (tid == 0) {
-      a.sc->chi2 = s;
-      *a.counter = 0u;
-    }
-  }
-}
-
-// ------------------------------------------------------------------------------------------------
-// K3: y = (H + lambda*D) p, fused partial of p^T y.  One CTA per tile of block rows; off-diagonal
-// block products are staged in shared memory, then each (row, component) owner adds its row's
-// products in column order, the diagonal block and the damping term.
-// ------------------------------------------------------------------------------------------------
-struct SpmvArgs {
-  const Tile* tiles;
-  const int* orowptr;
-  const int* ocol;
-  const double* Ho;
-  const double* Hd;
-  const double* dscale;  // nullptr: lambda*I ; else lambda*diag(dscale)
-  const double* p;
-  double* y;
-  double* part;
-  Scalars* sc;
-  unsigned int* counter;
-  int nnzo;
-  int N;
-  int mode;              // 0: PCG step (lambda from sc, honour sc->done, result -> sc->pAp)
-                         // 1: plain undamped product (result -> sc->dot)
-};
-
-__global__ void __launch_bounds__(kThreads) k_spmv(const SpmvArgs a) {
-  __shared__ double sp[3 * kSpmvChunk];
-  __shared__ double ys[3 * kSpmvRows];
+__global__ void __launch_bounds__(kThreads) k_assemble(const AsmView a, const ReduceCtx c) {
   __shared__ double red[8];
-  __shared__ int srow[kSpmvRows + 1];
   __shared__ int flag;
-  if (a.mode == 0 && a.sc->done) return;
-  const double lambda = (a.mode == 0) ? a.sc->lambda : 0.0;
-  const int tid = threadIdx.x;
-  const Tile t = a.tiles[blockIdx.x];
-  const int nr = t.r1 - t.r0;
-  for (int i = tid; i <= nr; i += kThreads) srow[i] = a.orowptr[t.r0 + i];
-  for (int i = tid; i < 3 * nr; i += kThreads) ys[(i / nr) * kSpmvRows + (i % nr)] = 0.0;
-  __syncthreads();
-  const int k0 = srow[0], k1 = srow[nr];
-  const size_t nz = (size_t)a.nnzo;
-  for (int base = k0; base < k1; base += kSpmvChunk) {
-    const int nb = min(kSpmvChunk, k1 - base);
-    for (int q = tid; q < nb; q += kThreads) {
-      const int k = base + q;
-      const int col = a.ocol[k];
-      const double h0 = a.Ho[k], h1 = a.Ho[nz + k], h2 = a.Ho[2 * nz + k];
-      const double h3 = a.Ho[3 * nz + k], h4 = a.Ho[4 * nz + k], h5 = a.Ho[5 * nz + k];
-      const double h6 = a.Ho[6 * nz + k], h7 = a.Ho[7 * nz + k], h8 = a.Ho[8 * nz + k];
-      const double px = a.p[3 * (size_t)col], py = a.p[3 * (size_t)col + 1], pz = a.p[3 * (size_t)col + 2];
-      sp[q] = h0 * px + h1 * py + h2 * pz;
-      sp[kSpmvChunk + q] = h3 * px + h4 * py + h5 * pz;
-      sp[2 * kSpmvChunk + q] = h6 * px + h7 * py + h8 * pz;
-    }
-    __syncthreads();
-    for (int u = tid; u < 3 * nr; u += kThreads) {
-      const int comp = u / nr, row = u - comp * nr;
-      const int lo = max(srow[row], base) - base, hi = min(srow[row + 1], base + nb) - base;
-      double s = ys[comp * kSpmvRows + row];
-      const double* src = sp + comp * kSpmvChunk;
-      for (int q = lo; q < hi; ++q) s += src[q];
-      ys[comp * kSpmvRows + row] = s;
-    }
-    __syncthreads();
-  }
-  double dot = 0.0;
-  const size_t n = (size_t)a.N;
-  for (int u = tid; u < 3 * nr; u += kThreads) {
-    const int comp = u / nr, row = u - comp * nr;
-    const size_t r = (size_t)(t.r0 + row);
-    const double px = a.p[3 * r], py = a.p[3 * r + 1], pz = a.p[3 * r + 2];
-    double d0, d1, d2, pc;
-    if (comp == 0) { d0 = a.Hd[r];         d1 = a.Hd[n + r];     d2 = a.Hd[2 * n + r]; pc = px; }
-    else if (comp == 1) { d0 = a.Hd[n + r];     d1 = a.Hd[3 * n + r]; d2 = a.Hd[4 * n + r]; pc = py; }
-    else { d0 = a.Hd[2 * n + r]; d1 = a.Hd[4 * n + r]; d2 = a.Hd[5 * n + r]; pc = pz; }
-    const double damp = a.dscale ? lambda * a.dscale[3 * r + comp] : lambda;
-    const double v = (ys[comp * kSpmvRows + row] + (d0 * px + d1 * py + d2 * pz)) + damp * pc;
-    a.y[3 * r + comp] = v;
-    dot += pc * v;
-  }
-  dot = block_sum(dot, red);
-  if (tid == 0) a.part[blockIdx.x] = dot;
-  if (last_block(a.counter, &flag)) {
-    const double s = final_sum(a.part, gridDim.x, red);
-    if (tid == 0) {
-      if (a.mode == 0) {
-        a.sc->pAp = s;
-        if (!(s > 0.0)) a.sc->done = 2;
-      } else {
-        a.sc->dot = s;
-      }
-      *a.counter = 0u;
-    }
-  }
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < a.n_own) v[0] = assemble_row<MODE>(a, r);
+  reduce_finish<1>(c, v, OP_CHI2, red, &flag);
 }
 
-// ------------------------------------------------------------------------------------------------
-// Block-Jacobi preconditioner: Minv = (H_ii + lambda*D_i)^-1, symmetric 6 planes.
-// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_chi2(const AsmView a, const ReduceCtx c) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < a.n_own) v[0] = chi2_row(a, r);
+  reduce_finish<1>(c, v, OP_CHI2, red, &flag);
+}
+
+// mode 0: PCG step (lambda from sc, honours sc->done, result -> sc->pAp)
+// mode 1: plain undamped product (result -> sc->dot)
+__global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const double* __restrict__ p, double* __restrict__ y,
+                                                    const ReduceCtx c, int mode) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  if (mode == 0 && c.sc->done) return;
+  const double lambda = (mode == 0) ? c.sc->lambda : 0.0;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < a.n_own) v[0] = spmv_row(a, p, y, r, lambda);
+  reduce_finish<1>(c, v, mode == 0 ? OP_PAP : OP_DOT, red, &flag);
+}
+
 __global__ void __launch_bounds__(kThreads) k_minv(const double* __restrict__ Hd, const double* __restrict__ dscale,
-                                                    const Scalars* sc, double* __restrict__ Minv, int N) {
+                                                    const Scalars* sc, double* __restrict__ Minv, int n_own) {
   const int v = blockIdx.x * kThreads + threadIdx.x;
-  if (v >= N) return;
-  const size_t n = (size_t)N;
-  const double lambda = sc->lambda;
-  Sym3 A{Hd[v], Hd[n + v], Hd[2 * n + v], Hd[3 * n + v], Hd[4 * n + v], Hd[5 * n + v]};
-  if (dscale) {
-    A.a00 += lambda * dscale[3 * (size_t)v];
-    A.a11 += lambda * dscale[3 * (size_t)v + 1];
-    A.a22 += lambda * dscale[3 * (size_t)v + 2];
-  } else {
-    A.a00 += lambda;
-    A.a11 += lambda;
-    A.a22 += lambda;
-  }
-  const Sym3 R = inverse_spd(A);
-  Minv[v] = R.a00;
-  Minv[n + v] = R.a01;
-  Minv[2 * n + v] = R.a02;
-  Minv[3 * n + v] = R.a11;
-  Minv[4 * n + v] = R.a12;
-  Minv[5 * n + v] = R.a22;
+  if (v < n_own) minv_row(Hd, dscale, Minv, n_own, v, sc->lambda);
 }
 
 // diagonalDamping: clip(diag(H), 1e-6, 1e32)  (GTSAM min_diagonal / max_diagonal)
-__global__ void __launch_bounds__(kThreads) k_dscale(const double* __restrict__ Hd, double* __restrict__ dscale, int N) {
+__global__ void __launch_bounds__(kThreads) k_dscale(const double* __restrict__ Hd, double* __restrict__ dscale, int n_own) {
   const int v = blockIdx.x * kThreads + threadIdx.x;
-  if (v >= N) return;
-  const size_t n = (size_t)N;
+  if (v >= n_own) return;
+  const size_t n = (size_t)n_own;
   dscale[3 * (size_t)v] = fmin(fmax(Hd[v], 1e-6), 1e32);
   dscale[3 * (size_t)v + 1] = fmin(fmax(Hd[3 * n + v], 1e-6), 1e32);
   dscale[3 * (size_t)v + 2] = fmin(fmax(Hd[5 * n + v], 1e-6), 1e32);
 }
 
-// ------------------------------------------------------------------------------------------------
-// K4: PCG vector kernels.  One thread per vertex (3 unknowns); per-CTA partials in a fixed order,
-// the last CTA to finish folds them and advances the device-side scalars.
-// ------------------------------------------------------------------------------------------------
-struct PcgArgs {
-  const double* b;     // gradient: rhs g = -b
-  const double* Minv;
-  double* x;
-  double* r;
-  double* z;
-  double* p;
-  const double* Ap;
-  double* part;        // 2 * grid
-  Scalars* sc;
-  unsigned int* counter;
-  int N;
-};
-
-__device__ __forceinline__ void apply_minv(const double* __restrict__ Minv, size_t n, size_t v, double r0, double r1,
-                                           double r2, double& z0, double& z1, double& z2) {
-  const double m00 = Minv[v], m01 = Minv[n + v], m02 = Minv[2 * n + v];
-  const double m11 = Minv[3 * n + v], m12 = Minv[4 * n + v], m22 = Minv[5 * n + v];
-  z0 = m00 * r0 + m01 * r1 + m02 * r2;
-  z1 = m01 * r0 + m11 * r1 + m12 * r2;
-  z2 = m02 * r0 + m12 * r1 + m22 * r2;
-}
-
-__global__ void __launch_bounds__(kThreads) k_pcg_init(const PcgArgs a) {
+__global__ void __launch_bounds__(kThreads) k_pcg_init(const PcgView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
-  const int v = blockIdx.x * kThreads + threadIdx.x;
-  double rz = 0.0, rr = 0.0;
-  if (v < a.N) {
-    const size_t o = 3 * (size_t)v;
-    const double r0 = -a.b[o], r1 = -a.b[o + 1], r2 = -a.b[o + 2];
-    double z0, z1, z2;
-    apply_minv(a.Minv, (size_t)a.N, (size_t)v, r0, r1, r2, z0, z1, z2);
-    a.x[o] = 0.0; a.x[o + 1] = 0.0; a.x[o + 2] = 0.0;
-    a.r[o] = r0;  a.r[o + 1] = r1;  a.r[o + 2] = r2;
-    a.z[o] = z0;  a.z[o + 1] = z1;  a.z[o + 2] = z2;
-    a.p[o] = z0;  a.p[o + 1] = z1;  a.p[o + 2] = z2;
-    rz = r0 * z0 + r1 * z1 + r2 * z2;
-    rr = r0 * r0 + r1 * r1 + r2 * r2;
-  }
-  rz = block_sum(rz, red);
-  rr = block_sum(rr, red);
-  if (threadIdx.x == 0) {
-    a.part[blockIdx.x] = rz;
-    a.part[gridDim.x + blockIdx.x] = rr;
-  }
-  if (last_block(a.counter, &flag)) {
-    const double srz = final_sum(a.part, gridDim.x, red);
-    const double srr = final_sum(a.part + gridDim.x, gridDim.x, red);
-    if (threadIdx.x == 0) {
-      a.sc->rz = srz;
-      a.sc->rr = srr;
-      a.sc->rr0 = srr;
-      a.sc->iters = 0;
-      a.sc->done = (srr == 0.0) ? 1 : 0;
-      *a.counter = 0u;
-    }
-  }
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[2] = {0.0, 0.0};
+  if (r < a.n_own) pcg_init_row(a, r, v[0], v[1]);
+  reduce_finish<2>(c, v, OP_INIT, red, &flag);
 }
 
-// x += alpha p ; r -= alpha Ap ; z = Minv r ; partials of r^T z and r^T r
-__global__ void __launch_bounds__(kThreads) k_pcg_update(const PcgArgs a) {
+__global__ void __launch_bounds__(kThreads) k_pcg_update(const PcgView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
-  if (a.sc->done) return;
-  const double alpha = a.sc->rz / a.sc->pAp;
-  const int v = blockIdx.x * kThreads + threadIdx.x;
-  double rz = 0.0, rr = 0.0;
-  if (v < a.N) {
-    const size_t o = 3 * (size_t)v;
-    const double p0 = a.p[o], p1 = a.p[o + 1], p2 = a.p[o + 2];
-    const double q0 = a.Ap[o], q1 = a.Ap[o + 1], q2 = a.Ap[o + 2];
-    a.x[o] += alpha * p0;
-    a.x[o + 1] += alpha * p1;
-    a.x[o + 2] += alpha * p2;
-    const double r0 = a.r[o] - alpha * q0, r1 = a.r[o + 1] - alpha * q1, r2 = a.r[o + 2] - alpha * q2;
-    double z0, z1, z2;
-    apply_minv(a.Minv, (size_t)a.N, (size_t)v, r0, r1, r2, z0, z1, z2);
-    a.r[o] = r0; a.r[o + 1] = r1; a.r[o + 2] = r2;
-    a.z[o] = z0; a.z[o + 1] = z1; a.z[o + 2] = z2;
-    rz = r0 * z0 + r1 * z1 + r2 * z2;
-    rr = r0 * r0 + r1 * r1 + r2 * r2;
-  }
-  rz = block_sum(rz, red);
-  rr = block_sum(rr, red);
-  if (threadIdx.x == 0) {
-    a.part[blockIdx.x] = rz;
-    a.part[gridDim.x + blockIdx.x] = rr;
-  }
-  if (last_block(a.counter, &flag)) {
-    const double srz = final_sum(a.part, gridDim.x, red);
-    const double srr = final_sum(a.part + gridDim.x, gridDim.x, red);
-    if (threadIdx.x == 0) {
-      Scalars* sc = a.sc;
-      sc->beta = srz / sc->rz;
-      sc->rz = srz;
-      sc->rr = srr;
-      const int it = sc->iters + 1;
-      sc->iters = it;
-      if (srr <= sc->tol2 * sc->rr0) sc->done = 1;
-      else if (!(srr == srr)) sc->done = 2;
-      else if (it >= sc->max_iters) sc->done = 3;
-      *a.counter = 0u;
-    }
-  }
+  if (c.sc->done) return;
+  const double alpha = c.sc->rz / c.sc->pAp;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[2] = {0.0, 0.0};
+  if (r < a.n_own) pcg_update_row(a, r, alpha, v[0], v[1]);
+  reduce_finish<2>(c, v, OP_UPDATE, red, &flag);
 }
 
-// p = z + beta p
+// p = z + beta p over the flat owned range
 __global__ void __launch_bounds__(kThreads) k_pcg_dir(const double* __restrict__ z, double* __restrict__ p,
                                                        const Scalars* sc, int n3) {
   if (sc->done) return;
@@ -477,90 +251,35 @@ __global__ void __launch_bounds__(kThreads) k_pcg_dir(const double* __restrict__
   if (i < n3) p[i] = z[i] + beta * p[i];
 }
 
-// generic dot -> sc->dot
-__global__ void __launch_bounds__(kThreads) k_dot(const double* __restrict__ u, const double* __restrict__ w, int n3,
-                                                   double* part, Scalars* sc, unsigned int* counter) {
+__global__ void __launch_bounds__(kThreads) k_dot(const double* __restrict__ u, const double* __restrict__ w, int n_own,
+                                                   const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
-  const int i = blockIdx.x * kThreads + threadIdx.x;
-  double s = (i < n3) ? u[i] * w[i] : 0.0;
-  s = block_sum(s, red);
-  if (threadIdx.x == 0) part[blockIdx.x] = s;
-  if (last_block(counter, &flag)) {
-    const double t = final_sum(part, gridDim.x, red);
-    if (threadIdx.x == 0) {
-      sc->dot = t;
-      *counter = 0u;
-    }
-  }
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < n_own) v[0] = dot_row(u, w, r);
+  reduce_finish<1>(c, v, OP_DOT, red, &flag);
 }
 
-// ------------------------------------------------------------------------------------------------
-// K5: retract and chi2
-// ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_retract(const double4* __restrict__ pose, const double* __restrict__ d,
-                                                       double4* __restrict__ out, int N) {
+                                                       double4* __restrict__ out, int n_own) {
   const int v = blockIdx.x * kThreads + threadIdx.x;
-  if (v >= N) return;
+  if (v >= n_own) return;
   const size_t o = 3 * (size_t)v;
   out[v] = retract(pose[v], d[o], d[o + 1], d[o + 2]);
 }
 
-struct Chi2Args {
-  const int2* e_ij;
-  const double2* e_zt;
-  const double2* e_zr;
-  const double2* e_o01;
-  const double2* e_o23;
-  const double2* e_o45;
-  const int* pr_idx;
-  const double4* pr_pose;
-  const double* pr_om;
-  const double4* pose;
-  double* part;
-  Scalars* sc;
-  unsigned int* counter;
-  int E;
-  int P;
-};
-
-// graph.error(values) * 2: one thread per factor, fixed chunks of kThreads edges per CTA.
-__global__ void __launch_bounds__(kThreads) k_chi2(const Chi2Args a) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  const int k = blockIdx.x * kThreads + threadIdx.x;
-  double s = 0.0;
-  if (k < a.E) {
-    const int2 ij = a.e_ij[k];
-    const double2 zt = a.e_zt[k], zr = a.e_zr[k];
-    const double2 o01 = a.e_o01[k], o23 = a.e_o23[k], o45 = a.e_o45[k];
-    double e[3];
-    between_error(a.pose[ij.x], a.pose[ij.y], zt, zr, e);
-    Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
-    s = quad_form(O, e);
-  } else if (k - a.E < a.P) {
-    const int q = k - a.E;
-    const double* om = a.pr_om + 6 * q;
-    Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-    double e[3];
-    Mat3 A;
-    prior_linearize<0>(a.pose[a.pr_idx[q]], a.pr_pose[q], e, A);
-    s = quad_form(O, e);
-  }
-  s = block_sum(s, red);
-  if (threadIdx.x == 0) a.part[blockIdx.x] = s;
-  if (last_block(a.counter, &flag)) {
-    const double t = final_sum(a.part, gridDim.x, red);
-    if (threadIdx.x == 0) {
-      a.sc->chi2 = t;
-      *a.counter = 0u;
-    }
-  }
+// halo pack: out[k*width + c] = vec[rows[k]*width + c]   (width 3: PCG vectors, 4: poses)
+__global__ void __launch_bounds__(kThreads) k_pack(const double* __restrict__ vec, const int* __restrict__ rows, int n,
+                                                    int width, double* __restrict__ out) {
+  const int i = blockIdx.x * kThreads + threadIdx.x;
+  if (i >= n * width) return;
+  const int k = i / width, c = i - k * width;
+  out[i] = vec[(size_t)rows[k] * width + c];
 }
 
 // closest_keyframe (reference graph.cpp:146-178): argmin of Euclidean distance over the first
-// `count` vertices in insertion order; ties -> lowest index.  Single CTA per 64K-vertex slab is
-// plenty: the scan is 32 B per vertex out of L2.
+// `count` vertices in insertion order; ties -> lowest index.  One CTA: the scan is 32 B per vertex.
 __global__ void __launch_bounds__(kThreads) k_closest(const double4* __restrict__ pose, const int* __restrict__ order,
                                                        int count, double qx, double qy, double* best_d, int* best_i) {
   __shared__ double sd[kThreads];

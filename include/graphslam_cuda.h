@@ -96,6 +96,15 @@ int gs_version(void);
 
 /* lifecycle — replaces the file-scope `graph` / `initial` objects, graph.cpp:6-7 */
 gs_status gs_create(gs_graph** out, const gs_params* params /* NULL = defaults */);
+/* multi-GPU, one process per GPU: every rank makes the SAME sequence of gs_add_* / gs_optimize / gs_get_poses
+ * calls with the same data; the library keeps the block rows of this rank's vertex range on params->device and
+ * exchanges halo poses / PCG direction vectors and dot-product segment sums over NCCL (libnccl.so.2 resolved at
+ * run time).  `nccl_id` is the ncclUniqueId obtained once by gs_nccl_unique_id on one rank and handed to all
+ * (any transport: MPI, torch.distributed, a file).  world_size 1, 2, 4 or 8; results are bitwise identical for
+ * every world size.  gs_get_poses / gs_get_pose / gs_optimize / gs_chi2 are collective calls. */
+gs_status gs_nccl_unique_id(void* out, size_t cap, size_t* n /* bytes needed/written */);
+gs_status gs_create_distributed(gs_graph** out, const gs_params* params /* rank, world_size, device set */,
+                                const void* nccl_id, size_t id_bytes);
 gs_status gs_destroy(gs_graph* g);
 gs_status gs_set_params(gs_graph* g, const gs_params* params);
 

@@ -1,0 +1,61 @@
+/* libgraphslam_cuda — TEST-ONLY entry points (not part of the drop-in boundary).
+ *
+ * These exercise the library's own host code on a box without a GPU: the structure build, the
+ * vertex-range partition and halo lists, and — through a CPU emulator that calls the very same
+ * __host__ __device__ per-row functions the CUDA kernels call — one linearise/assemble, a block-Jacobi
+ * PCG solve, retract and chi2 over 1, 2, 4 or 8 virtual ranks.  Nothing here is reachable from
+ * gs_create / gs_optimize: the product path has no CPU fallback and fails with GS_ECUDA without a
+ * device.  Used by tests/ only.
+ */
+#ifndef GRAPHSLAM_CUDA_DEBUG_H
+#define GRAPHSLAM_CUDA_DEBUG_H
+
+#include "graphslam_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* sorted unique block pattern (rowptr[n+1], colidx[nnzb]) and the canonical factor order `perm`
+ * of a graph over dense indices 0..n-1; any output may be NULL */
+gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,
+                          size_t* nnzb, int32_t* perm);
+
+/* one BetweenFactor evaluated on the host by the inline functions the kernels compile */
+gs_status gs_host_between(const double pi[3], const double pj[3], const double z[3], const double cov9[9], int mode,
+                          double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],
+                          double bi[3], double bj[3]);
+
+typedef struct gs_emu_problem {
+  int32_t n, e, np;            /* vertices, between-factors, priors (dense indices 0..n-1) */
+  const int32_t* ei;           /* id_1 per factor */
+  const int32_t* ej;           /* id_2 per factor */
+  const double* z;             /* 3 per factor */
+  const double* om;            /* information upper triangle, 6 per factor: 00 01 02 11 12 22 */
+  const int32_t* prior_idx;
+  const double* prior_xyt;     /* 3 per prior */
+  const double* prior_om;      /* 6 per prior */
+  const double* xyt;           /* 3 per vertex: linearisation point */
+} gs_emu_problem;
+
+typedef struct gs_emu_result {
+  double* blocks;              /* nnzb*9 on gs_host_pattern's pattern, or NULL */
+  double* b;                   /* 3n or NULL */
+  double* delta;               /* 3n or NULL: PCG solution of (H + lambda I) delta = -b */
+  double* xyt_new;             /* 3n or NULL: retract(xyt, delta) */
+  double chi2, chi2_check;     /* from the assembly pass / from the chi2 pass */
+  double chi2_new;             /* chi2 at xyt_new */
+  double dHd, db;              /* delta.H.delta (undamped), delta.b */
+  double rel_residual;
+  int32_t pcg_iters, pcg_done;
+  int32_t n_ghost_total, n_pairs_total, halo_send_total;
+} gs_emu_result;
+
+/* one outer-iteration body over `world` virtual ranks (1, 2, 4 or 8) on the CPU */
+gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
+                     double pcg_rel_tol, gs_emu_result* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAPHSLAM_CUDA_DEBUG_H */

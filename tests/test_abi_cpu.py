@@ -31,6 +31,13 @@ def test_header_symbols_all_exported(lib):
     for name in declared:
         assert hasattr(lib, name), f"{name} not exported"
     assert lib.gs_version() == 1
+    # the test-only header too
+    dbg = open(os.path.join(ROOT, "include", "graphslam_cuda_debug.h")).read()
+    dbg = re.sub(r"/\*.*?\*/", "", dbg, flags=re.S)
+    declared_dbg = set(re.findall(r"\b(gs_[a-z0-9_]+)\s*\(", dbg))
+    assert declared_dbg == set(_lib.DEBUG_SIGNATURES), declared_dbg ^ set(_lib.DEBUG_SIGNATURES)
+    for name in declared_dbg:
+        assert hasattr(lib, name), f"{name} not exported"
 
 
 def test_default_params_are_gtsam_defaults(lib):
