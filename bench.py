@@ -196,41 +196,66 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        return run_ours_distributed(args, rank, world, local_rank)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def vmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def vsum(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
 
     g = make_graph(args.config, args.n)
     K, W = args.steps, args.warmup
     peak, peak_src = load_peaks()
-    step_params = dict(max_iterations=1, rel_error_tol=0.0, abs_error_tol=0.0, pcg_rel_tol=PCG_TOL, device=local_rank)
+    step_params = dict(max_iterations=1, rel_error_tol=0.0, abs_error_tol=0.0, pcg_rel_tol=PCG_TOL)
+
+    def new_graph():
+        if world > 1:
+            return graph.distributed_graph(**step_params)
+        return graph.Graph(device=local_rank, **step_params)
 
     # ---- device-resident leg: graph uploaded and structure built before the timed region
-    G = graph.Graph(**step_params)
+    G = new_graph()
     t0 = time.time()
     G.add_graph(g)
     t_add = time.time() - t0
     t0 = time.time()
     G.prepare()
     t_prep = time.time() - t0
-    log(f"[bench] host add {t_add:.2f}s, structure build + upload {t_prep:.2f}s")
+    log(f"[bench r{rank}] host add {t_add:.2f}s, structure build + upload {t_prep:.2f}s")
     for _ in range(W):
         G.optimize()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank).start()
+    barrier()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
     stats = []
     t0 = time.time()
     for _ in range(K):
         stats.append(G.optimize())
-    torch.cuda.synchronize()
+    barrier()
     wall = time.time() - t0
-    clocks = sampler.stop()
-    dev_s = sum(s["ms_device"] for s in stats) * 1e-3
+    clocks = sampler.stop() if sampler else None
+    dev_s = vmax(sum(s["ms_device"] for s in stats) * 1e-3)     # device time, max over ranks
     value = K / dev_s
     pcg_total = sum(s["pcg_iterations_total"] for s in stats)
     solves = sum(s["inner_iterations"] for s in stats)
-    launches = sum(s["gpu_launches"] for s in stats)
-    ms_lin = sum(s["ms_linearize"] for s in stats)
-    ms_solve = sum(s["ms_solve"] for s in stats)
-    log(f"[bench] resident: {K} steps in {dev_s:.3f}s device ({wall:.3f}s wall), {pcg_total} PCG iterations, "
+    launches = vsum(float(sum(s["gpu_launches"] for s in stats)))
+    ms_lin = vmax(sum(s["ms_linearize"] for s in stats))
+    ms_solve = vmax(sum(s["ms_solve"] for s in stats))
+    ms_upd = vmax(sum(s["ms_update"] for s in stats))
+    log(f"[bench r{rank}] resident: {K} steps in {dev_s:.3f}s device ({wall:.3f}s wall), {pcg_total} PCG iterations, "
         f"chi2 {stats[0]['chi2_initial']:.6g} -> {stats[-1]['chi2_final']:.6g}")
 
     # ---- roofline of the dominant kernel, CUDA events around every launch on the library's stream
@@ -242,10 +267,10 @@ def run_ours(args):
     for name, (ms, by) in {**prof, **outer}.items():
         kernels[name] = {"ms": round(ms, 5), "algorithmic_MB": round(by / 1e6, 2), "GBps": round(by / (ms * 1e-3) / 1e9, 1),
                          "frac": round(by / (ms * 1e-3) / 1e9 / peak, 4)}
-    log("[bench] kernels: " + json.dumps(kernels))
+    log(f"[bench r{rank}] kernels: " + json.dumps(kernels))
     traffic = None
     tf = os.path.join(ROOT, "profiles", "spmv_traffic.json")
-    if os.path.exists(tf):
+    if os.path.exists(tf) and world == 1:
         try:
             traffic = json.load(open(tf)).get(f"{g.name}:{g.n}")
         except Exception:
@@ -254,7 +279,7 @@ def run_ours(args):
 
     # ---- end-to-end leg through the C ABI with host buffers: every step uploads the values and reads them back
     keys = np.ascontiguousarray(g.keys)
-    G2 = graph.Graph(**step_params)
+    G2 = new_graph()
     G2.add_graph(g)
     G2.prepare()
     x = np.ascontiguousarray(g.init)
@@ -262,59 +287,63 @@ def run_ours(args):
         G2.set_poses(keys, x)
         G2.optimize()
         _, x = G2.poses()
-    torch.cuda.synchronize()
-    h2d = d2h = 0.0
+    barrier()
+    h2d0, d2h0 = G2.transfer_bytes()
     t0 = time.time()
     for _ in range(K):
-        G2.set_poses(keys, x)            # host -> device (N x (x,y,cos,sin) doubles)
-        st = G2.optimize()
-        _, x = G2.poses()                # device -> host
-        h2d += 32.0 * g.n + st["h2d_bytes"]
-        d2h += 32.0 * g.n + st["d2h_bytes"]
-    torch.cuda.synchronize()
-    e2e_s = time.time() - t0
+        G2.set_poses(keys, x)            # host -> device (this rank's rows + halo, (x,y,cos,sin) doubles)
+        G2.optimize()
+        _, x = G2.poses()                # device -> host (all N poses on every rank)
+    barrier()
+    e2e_s = vmax(time.time() - t0)
     e2e = K / e2e_s
+    h2d1, d2h1 = G2.transfer_bytes()     # counted by the library from the copies it issued
     G2.close()
+    h2d_step = vsum(h2d1 - h2d0) / K
+    d2h_step = vsum(d2h1 - d2h0) / K
 
     # ---- CPU baseline on a bounded sample (rank 0, N = 1)
     pcg_per_lm = int(round(pcg_total / max(solves, 1)))
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         c = cpu_sample(g, args.cpu_pcg_cap, pcg_per_lm)
         cpu = {"value": 1.0 / c["sec_per_lm"], "unit": UNIT, "cores": c["threads"], "kind": "port",
                "sample": (f"1 LM iteration of oracle/cpu_ref.c (C+OpenMP) on the full graph, PCG capped at {c['pcg_run']} "
                           f"iterations ({c['ms_per_pcg']:.2f} ms each) and scaled to the {pcg_per_lm} iterations per solve "
                           f"the same algorithm needed on the GPU; linearise+update {c['ms_fixed']:.0f} ms"),
                "edges_linearized_per_sec": c["edges_per_sec"]}
-    try:
-        os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
-        rec = os.path.join(ROOT, "profiles", "pcg_iters.json")
-        d = json.load(open(rec)) if os.path.exists(rec) else {}
-        d[f"{g.name}:{g.n}"] = pcg_per_lm
-        json.dump(d, open(rec, "w"), indent=1, sort_keys=True)
-    except Exception:
-        pass
+    if rank == 0:
+        try:
+            os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
+            rec = os.path.join(ROOT, "profiles", "pcg_iters.json")
+            d = json.load(open(rec)) if os.path.exists(rec) else {}
+            d[f"{g.name}:{g.n}"] = pcg_per_lm
+            json.dump(d, open(rec, "w"), indent=1, sort_keys=True)
+        except Exception:
+            pass
 
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dev_s / K * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(g), "n_poses": g.n, "n_factors": g.e, "pcg_rel_tol": PCG_TOL,
-                       "l2": "inputs larger than L2 (H alone is %.0f MB per PCG iteration)" % (spmv_bytes / 1e6),
+                       "partition": f"vertex ranges over {world} rank(s), NCCL halo exchange + segment-sum all-gathers"
+                       if world > 1 else "single GPU",
+                       "l2": "inputs larger than L2 (H alone is %.0f MB per PCG iteration on this rank)" % (spmv_bytes / 1e6),
                        "pcg_iters_per_step": pcg_total / K, "structure_build_s": round(t_prep, 3),
                        "host_add_s": round(t_add, 3), "wall_s_timed_region": round(wall, 3)},
             "edges_linearized_per_sec": g.e * len(stats) / (ms_lin * 1e-3),
             "roofline": {"bound": "hbm", "kernel": "k_spmv", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernels": kernels},
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernels": kernels,
+                         "note": "rank 0's kernels on its own rows" if world > 1 else "whole graph"},
             "cpu_baseline": cpu,
-            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step},
             "gpu_launches": int(launches), "clocks": clocks,
-            "breakdown_ms_per_step": {"linearize_assemble": ms_lin / K, "pcg": ms_solve / K,
-                                      "update": sum(s["ms_update"] for s in stats) / K}}
-    print(json.dumps(line), flush=True)
-
-
-def run_ours_distributed(args, rank, world, local_rank):
-    raise SystemExit("bench.py: multi-GPU path not built yet")
+            "breakdown_ms_per_step": {"linearize_assemble": ms_lin / K, "pcg": ms_solve / K, "update": ms_upd / K}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def main():

@@ -61,6 +61,7 @@ SIGNATURES = {
     "gs_set_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p]),
     "gs_chi2": (C.c_int, [C.c_void_p, c_double_p]),
     "gs_num_vertices": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
+    "gs_get_transfer_bytes": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "gs_num_factors": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
     "gs_get_pattern": (C.c_int, [C.c_void_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t)]),
     "gs_get_system": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
@@ -89,6 +90,8 @@ class GsEmuResult(C.Structure):
 
 # test-only entries (include/graphslam_cuda_debug.h): the product's own host code, callable on a CPU box
 DEBUG_SIGNATURES = {
+    "gs_host_partition": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, C.c_int, C.c_int, c_i32_p, c_i32_p, c_i32_p,
+                                    c_i32_p]),
     "gs_emu_run": (C.c_int, [C.POINTER(GsEmuProblem), C.c_int, C.c_int, C.c_double, C.c_int, C.c_double,
                              C.POINTER(GsEmuResult)]),
     "gs_host_pattern": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t),

@@ -124,6 +124,34 @@ struct World {
 
 }  // namespace
 
+extern "C" gs_status gs_host_partition(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int world, int rank,
+                                       int32_t info[8], int32_t* ghosts, int32_t* peers, int32_t* send_rows) {
+  if (n <= 0 || e < 0 || !info || rank < 0 || rank >= world) return GS_EINVAL;
+  if (!(world == 1 || world == 2 || world == 4 || world == 8)) return GS_EINVAL;
+  std::vector<int> perm;
+  gs::canonical_order(n, e, ei, ej, perm);
+  LocalStructure S;
+  gs::build_local_structure(n, e, ei, ej, perm, 0, nullptr, world, rank, S);
+  info[0] = S.v0;
+  info[1] = S.v1;
+  info[2] = S.n_ghost;
+  info[3] = (int32_t)S.peers.size();
+  info[4] = (int32_t)S.send_rows.size();
+  info[5] = S.n_pairs;
+  info[6] = S.nnzo_own;
+  info[7] = S.ntiles;
+  if (ghosts) std::memcpy(ghosts, S.ghosts.data(), sizeof(int32_t) * S.ghosts.size());
+  if (peers)
+    for (size_t k = 0; k < S.peers.size(); ++k) {
+      const gs::HaloPeer& hp = S.peers[k];
+      const int32_t row[5] = {hp.rank, hp.send_off, hp.send_cnt, hp.ghost_off, hp.ghost_cnt};
+      std::memcpy(peers + 5 * k, row, sizeof row);
+    }
+  if (send_rows)
+    for (size_t k = 0; k < S.send_rows.size(); ++k) send_rows[k] = S.v0 + S.send_rows[k];  // global indices
+  return GS_OK;
+}
+
 extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
                                 double pcg_rel_tol, gs_emu_result* out) {
   if (!pb || !out || pb->n <= 0) return GS_EINVAL;

@@ -992,6 +992,13 @@ gs_status gs_num_factors(const gs_graph* g, size_t* n) {
   return GS_OK;
 }
 
+gs_status gs_get_transfer_bytes(const gs_graph* g, double* h2d, double* d2h) {
+  if (!g) return GS_EINVAL;
+  if (h2d) *h2d = g->h2d_bytes;
+  if (d2h) *d2h = g->d2h_bytes;
+  return GS_OK;
+}
+
 gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* nnzb) {
   if (!g) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;

@@ -49,14 +49,20 @@ def default_params(**overrides) -> GsParams:
 class Graph:
     """One gs_graph.  Requires a CUDA device: there is no CPU fallback."""
 
-    def __init__(self, params: GsParams | None = None, **overrides):
+    def __init__(self, params: GsParams | None = None, nccl_id: bytes | None = None, **overrides):
+        """`nccl_id` (from `nccl_unique_id()`, the same bytes on every rank) + rank / world_size / device overrides
+        create one rank of a multi-GPU graph (gs_create_distributed); every rank then makes the same calls."""
         self._lib = _lib.load()
         self._h = C.c_void_p()
         self.params = params if params is not None else default_params(**overrides)
         if params is not None:
             for k, v in overrides.items():
                 setattr(self.params, k, v)
-        st = self._lib.gs_create(C.byref(self._h), C.byref(self.params))
+        if nccl_id is not None or self.params.world_size != 1:
+            buf = C.create_string_buffer(bytes(nccl_id or b""), len(nccl_id or b""))
+            st = self._lib.gs_create_distributed(C.byref(self._h), C.byref(self.params), buf, len(nccl_id or b""))
+        else:
+            st = self._lib.gs_create(C.byref(self._h), C.byref(self.params))
         if st != _lib.GS_OK:
             msg = self._lib.gs_last_error(self._h).decode() if self._h else "gs_create failed"
             if self._h:
@@ -155,6 +161,12 @@ class Graph:
         self._ck(self._lib.gs_num_factors(self._h, C.byref(n)))
         return n.value
 
+    def transfer_bytes(self):
+        """(host->device, device->host) bytes the library has copied so far for this graph."""
+        a, b = C.c_double(), C.c_double()
+        self._ck(self._lib.gs_get_transfer_bytes(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def pose(self, key: int) -> np.ndarray:
         out = np.zeros(3)
         self._ck(self._lib.gs_get_pose(self._h, int(key), _dp(out)))
@@ -226,6 +238,34 @@ class Graph:
         dist = C.c_double()
         self._ck(self._lib.gs_closest_keyframe(self._h, int(key), int(skip), C.byref(out), C.byref(dist)))
         return out.value, dist.value
+
+
+def nccl_unique_id() -> bytes:
+    """ncclUniqueId bytes for gs_create_distributed; call on ONE rank and hand the bytes to all."""
+    lib = _lib.load()
+    n = C.c_size_t()
+    lib.gs_nccl_unique_id(None, 0, C.byref(n))
+    buf = C.create_string_buffer(n.value)
+    st = lib.gs_nccl_unique_id(buf, n.value, C.byref(n))
+    if st != _lib.GS_OK:
+        raise GraphSlamError(st, "gs_nccl_unique_id failed (libnccl.so.2 not loadable?)")
+    return buf.raw
+
+
+def distributed_graph(**overrides) -> "Graph":
+    """One rank of a multi-GPU graph inside an initialised torch.distributed job (torchrun): rank 0 draws the
+    NCCL id, torch.distributed broadcasts it, each rank binds to cuda:LOCAL_RANK."""
+    import os
+
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    dev = torch.device("cuda", local)
+    raw = nccl_unique_id() if rank == 0 else bytes(128)
+    t = torch.tensor(list(raw), dtype=torch.uint8, device=dev if dist.get_backend() == "nccl" else "cpu")
+    dist.broadcast(t, 0)
+    return Graph(nccl_id=bytes(t.cpu().tolist()), rank=rank, world_size=world, device=local, **overrides)
 
 
 def compose_reference(a, b) -> np.ndarray:

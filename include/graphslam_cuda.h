@@ -136,6 +136,8 @@ gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double
 /* 2 * graph.error(values) at the current values                 */
 gs_status gs_chi2(gs_graph* g, double* chi2);
 gs_status gs_num_vertices(const gs_graph* g, size_t* n);
+/* cumulative bytes the library has copied host->device / device->host for this graph (measurement) */
+gs_status gs_get_transfer_bytes(const gs_graph* g, double* h2d, double* d2h);
 gs_status gs_num_factors(const gs_graph* g, size_t* n);          /* graph.nrFactors(), graph.cpp:60 */
 
 /* ---- parity hooks (integer structure must match the oracle bit-exactly) ---- */

@@ -26,6 +26,12 @@ gs_status gs_host_between(const double pi[3], const double pj[3], const double z
                           double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],
                           double bi[3], double bj[3]);
 
+/* vertex-range partition of rank `rank` of `world`: info = {v0, v1, n_ghost, n_peers, n_send, n_pairs, nnzo_own,
+ * ntiles}; ghosts[n_ghost] (global, sorted); peers[5*n_peers] = {rank, send_off, send_cnt, ghost_off, ghost_cnt};
+ * send_rows[n_send] (global indices, grouped by peer).  Array outputs may be NULL (size them with n). */
+gs_status gs_host_partition(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int world, int rank,
+                            int32_t info[8], int32_t* ghosts, int32_t* peers, int32_t* send_rows);
+
 typedef struct gs_emu_problem {
   int32_t n, e, np;            /* vertices, between-factors, priors (dense indices 0..n-1) */
   const int32_t* ei;           /* id_1 per factor */

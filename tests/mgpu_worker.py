@@ -1,0 +1,58 @@
+"""Worker of tests/test_multi_gpu.py (launched by torchrun, one process per GPU): optimise the same graph on
+WORLD_SIZE ranks over NCCL and, on rank 0, on one GPU; the two must agree bitwise (fixed reduction tree)."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from graphslam_b200 import graph, synth  # noqa: E402
+
+
+def main():
+    cid = sys.argv[1] if len(sys.argv) > 1 else "C3"
+    n = int(sys.argv[2]) if len(sys.argv) > 2 else 30000
+    rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    g = synth.config(cid, n=n, full_cov=True)
+    G = graph.distributed_graph()
+    G.add_graph(g)
+    chi0 = G.chi2()
+    st = G.optimize()
+    keys, x = G.poses()
+    errors, lambdas, tries = G.trace()
+    # warm-started second solve after appending nothing: exercises values staying on the devices
+    st2 = G.optimize()
+    G.close()
+    ok = True
+    if rank == 0:
+        with graph.Graph(device=local) as G1:
+            G1.add_graph(g)
+            chi0_1 = G1.chi2()
+            st1 = G1.optimize()
+            _, x1 = G1.poses()
+            e1, l1, t1 = G1.trace()
+            st1b = G1.optimize()
+        ok = (chi0 == chi0_1 and np.array_equal(x, x1) and np.array_equal(errors, e1) and tries.tolist() == t1.tolist()
+              and st["pcg_iterations_total"] == st1["pcg_iterations_total"] and st2["chi2_final"] == st1b["chi2_final"])
+        print(f"[mgpu] world={dist.get_world_size()} N={g.n} iterations={st['iterations']} pcg={st['pcg_iterations_total']} "
+              f"chi2 {st['chi2_initial']:.6g}->{st['chi2_final']:.6g} bitwise_equal_to_single_gpu={ok} "
+              f"ms_solve {st['ms_solve']:.1f} (1 GPU: {st1['ms_solve']:.1f})", flush=True)
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.broadcast(flag, 0)
+    dist.barrier()
+    dist.destroy_process_group()
+    if int(flag.item()) != 1:
+        raise SystemExit("multi-GPU result differs from the single-GPU result")
+    if rank == 0:
+        print("MGPU_OK", flush=True)
+
+
+if __name__ == "__main__":
+    main()
