@@ -21,7 +21,7 @@ using gs::LocalStructure;
 struct VRank {
   LocalStructure S;
   int n_own = 0, n_loc = 0;
-  std::vector<int2> eij;
+  std::vector<int2> eij, cw, refs;
   std::vector<double2> zt, zr, o01, o23, o45;
   std::vector<double4> pr_pose, pose, pose_try;
   std::vector<double> pr_om, Ho, Hd, Minv, b, x, r, z, p, Ap, part;
@@ -30,14 +30,17 @@ struct VRank {
     gs::AsmView a;
     a.cs.base = S.csell.base.data();
     a.cs.width = S.csell.width.data();
-    a.c_code = S.c_code.data();
-    a.c_blk = S.c_blk.data();
+    a.c = cw.data();
+    a.ccol = S.c_col.data();
+    a.f.fs.base = S.fsell.base.data();
+    a.f.fs.width = S.fsell.width.data();
     a.f.ij = eij.data();
     a.f.zt = zt.data();
     a.f.zr = zr.data();
     a.f.o01 = o01.data();
     a.f.o23 = o23.data();
     a.f.o45 = o45.data();
+    a.pr.n = S.P_loc;
     a.pr.row = S.pr_row.data();
     a.pr.pose = pr_pose.data();
     a.pr.om = pr_om.data();
@@ -53,8 +56,7 @@ struct VRank {
     gs::SpmvView a;
     a.rs.base = S.rsell.base.data();
     a.rs.width = S.rsell.width.data();
-    a.r_col = S.r_col.data();
-    a.r_blk = S.r_blk.data();
+    a.refs = refs.data();
     a.Ho = Ho.data();
     a.hstride = hstride;
     a.Hd = Hd.data();
@@ -169,7 +171,11 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
     me.n_own = S.n_own;
     me.n_loc = S.n_own + S.n_ghost;
     const int FS = S.fsell.slots;
-    me.eij.assign(FS, make_int2(0, 0));
+    me.eij.assign(FS, make_int2(-1, -1));
+    me.cw.resize(S.c_code.size());
+    for (size_t c = 0; c < me.cw.size(); ++c) me.cw[c] = make_int2((int)S.c_code[c], S.c_blk[c]);
+    me.refs.resize(S.r_col.size());
+    for (size_t c = 0; c < me.refs.size(); ++c) me.refs[c] = make_int2(S.r_col[c], S.r_blk[c]);
     me.zt.assign(FS, make_double2(0, 0));
     me.zr.assign(FS, make_double2(1, 0));
     me.o01.assign(FS, make_double2(0, 0));
@@ -178,7 +184,7 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
     for (int s = 0; s < FS; ++s) {
       const int k = S.f_src[s];
       if (k < 0) continue;
-      me.eij[s] = make_int2(S.f_i[s], S.f_j[s]);
+      me.eij[s] = make_int2(S.f_i[s] | (S.f_count[s] ? 0 : gs::kNoCountBit), S.f_j[s]);
       me.zt[s] = make_double2(pb->z[3 * k], pb->z[3 * k + 1]);
       me.zr[s] = make_double2(std::cos(pb->z[3 * k + 2]), std::sin(pb->z[3 * k + 2]));
       me.o01[s] = make_double2(pb->om[6 * k], pb->om[6 * k + 1]);

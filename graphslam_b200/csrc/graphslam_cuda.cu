@@ -91,6 +91,7 @@ struct gs_graph {
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
   bool use_graph = true;
+  bool asm_occ3 = false;   // experiment switch (GS_ASM_OCC=3): 3 CTAs/SM for k_assemble at the cost of spills
 
   // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
   std::vector<uint64_t> keys;
@@ -120,10 +121,9 @@ struct gs_graph {
 
   // ---- device
   DevBuf<double4> d_pose, d_pose_try, d_pr_pose, d_pose_all;
-  DevBuf<int2> d_eij;
+  DevBuf<int2> d_eij, d_cw, d_refs;
   DevBuf<double2> d_zt, d_zr, d_o01, d_o23, d_o45;
-  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_cblk, d_rbase, d_rwidth, d_rcol, d_rblk, d_segtile, d_send_rows;
-  DevBuf<uint32_t> d_ccode;
+  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_rbase, d_rwidth, d_fbase, d_fwidth, d_segtile, d_send_rows, d_ccol;
   DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part, d_segs, d_sendbuf;
   DevBuf<Scalars> d_sc;
   DevBuf<unsigned int> d_counter;
@@ -201,14 +201,17 @@ gs::AsmView asm_view(gs_graph* g, const double4* pose) {
   gs::AsmView a;
   a.cs.base = g->d_cbase.p;
   a.cs.width = g->d_cwidth.p;
-  a.c_code = g->d_ccode.p;
-  a.c_blk = g->d_cblk.p;
+  a.c = g->d_cw.p;
+  a.ccol = g->d_ccol.p;
+  a.f.fs.base = g->d_fbase.p;
+  a.f.fs.width = g->d_fwidth.p;
   a.f.ij = g->d_eij.p;
   a.f.zt = g->d_zt.p;
   a.f.zr = g->d_zr.p;
   a.f.o01 = g->d_o01.p;
   a.f.o23 = g->d_o23.p;
   a.f.o45 = g->d_o45.p;
+  a.pr.n = g->S.P_loc;
   a.pr.row = g->d_pr_row.p;
   a.pr.pose = g->d_pr_pose.p;
   a.pr.om = g->d_pr_om.p;
@@ -225,8 +228,7 @@ gs::SpmvView spmv_view(gs_graph* g) {
   gs::SpmvView a;
   a.rs.base = g->d_rbase.p;
   a.rs.width = g->d_rwidth.p;
-  a.r_col = g->d_rcol.p;
-  a.r_blk = g->d_rblk.p;
+  a.refs = g->d_refs.p;
   a.Ho = g->d_Ho.p;
   a.hstride = g->hstride;
   a.Hd = g->d_Hd.p;
@@ -418,13 +420,13 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->n_loc = S.n_own + S.n_ghost;
   // factor arrays in storage (SELL) order; padding slots are never referenced
   const int FS = S.fsell.slots;
-  std::vector<int2> eij(FS, make_int2(0, 0));
+  std::vector<int2> eij(FS, make_int2(-1, -1));
   std::vector<double2> zt(FS, make_double2(0, 0)), zr(FS, make_double2(1, 0)), o01(FS, make_double2(0, 0)),
       o23(FS, make_double2(0, 0)), o45(FS, make_double2(0, 0));
   for (int q = 0; q < FS; ++q) {
     const int s = S.f_src[q];
     if (s < 0) continue;
-    eij[q] = make_int2(S.f_i[q], S.f_j[q]);
+    eij[q] = make_int2(S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q]);
     zt[q] = make_double2(g->ez[3 * s], g->ez[3 * s + 1]);
     zr[q] = make_double2(std::cos(g->ez[3 * s + 2]), std::sin(g->ez[3 * s + 2]));
     o01[q] = make_double2(g->eom[6 * s], g->eom[6 * s + 1]);
@@ -453,12 +455,20 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = upload(g, g->d_pr_om, prom)) return s;
   if (gs_status s = upload(g, g->d_cbase, S.csell.base)) return s;
   if (gs_status s = upload(g, g->d_cwidth, S.csell.width)) return s;
-  if (gs_status s = upload(g, g->d_ccode, S.c_code)) return s;
-  if (gs_status s = upload(g, g->d_cblk, S.c_blk)) return s;
+  {
+    std::vector<int2> cw(S.c_code.size());
+    for (size_t q = 0; q < cw.size(); ++q) cw[q] = make_int2((int)S.c_code[q], S.c_blk[q]);
+    if (gs_status s = upload(g, g->d_cw, cw)) return s;
+    std::vector<int2> refs(S.r_col.size());
+    for (size_t q = 0; q < refs.size(); ++q) refs[q] = make_int2(S.r_col[q], S.r_blk[q]);
+    if (gs_status s = upload(g, g->d_refs, refs)) return s;
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  }
+  if (gs_status s = upload(g, g->d_ccol, S.c_col)) return s;
+  if (gs_status s = upload(g, g->d_fbase, S.fsell.base)) return s;
+  if (gs_status s = upload(g, g->d_fwidth, S.fsell.width)) return s;
   if (gs_status s = upload(g, g->d_rbase, S.rsell.base)) return s;
   if (gs_status s = upload(g, g->d_rwidth, S.rsell.width)) return s;
-  if (gs_status s = upload(g, g->d_rcol, S.r_col)) return s;
-  if (gs_status s = upload(g, g->d_rblk, S.r_blk)) return s;
   if (gs_status s = upload(g, g->d_segtile, segtile)) return s;
   if (gs_status s = upload(g, g->d_send_rows, S.send_rows)) return s;
   const size_t n3 = 3 * (size_t)std::max(S.n_own, 1), nl3 = 3 * (size_t)std::max(g->n_loc, 1);
@@ -517,10 +527,14 @@ gs_status write_scalars(gs_graph* g) {
 
 // linearise + assemble at the current device poses (async)
 gs_status launch_assemble(gs_graph* g) {
+  const gs::AsmView av = asm_view(g, g->d_pose.p);
+  const gs::ReduceCtx rc = reduce_ctx(g, 2);
   if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT)
-    gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, g->d_pose.p), reduce_ctx(g, 2));
+    gs::k_assemble<1, 2><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+  else if (g->asm_occ3)
+    gs::k_assemble<0, 3><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
   else
-    gs::k_assemble<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, g->d_pose.p), reduce_ctx(g, 2));
+    gs::k_assemble<0, 2><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
   g->launches += 1;
   if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
   if (g->prm.diagonal_damping) {
@@ -611,6 +625,8 @@ gs_status create_common(gs_graph* g) {
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   const char* env = std::getenv("GS_PCG_GRAPH");
   g->use_graph = !(env && env[0] == '0');
+  env = std::getenv("GS_ASM_OCC");
+  g->asm_occ3 = env && env[0] == '3';
   return GS_OK;
 }
 

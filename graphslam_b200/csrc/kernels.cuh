@@ -136,7 +136,9 @@ __device__ __forceinline__ void apply_scalars(Scalars* sc, int op, double t0, do
   }
 }
 
-// tile partials -> (last CTA) segment sums -> (single rank) totals and scalar step
+// tile partials -> (last CTA) segment sums -> (single rank) totals and scalar step.
+// In the last CTA warp w folds segment w: lane l adds partials l, l+32, ... in order, then the fixed
+// butterfly; all NQ quantities in one pass, no block barrier per segment.
 template <int NQ>
 __device__ __forceinline__ void reduce_finish(const ReduceCtx& c, const double (&v)[NQ], int op, double* red, int* flag) {
 #pragma unroll
@@ -145,15 +147,26 @@ __device__ __forceinline__ void reduce_finish(const ReduceCtx& c, const double (
     if (threadIdx.x == 0) c.part[(size_t)q * c.part_stride + blockIdx.x] = s;
   }
   if (last_block(c.counter, flag)) {
-    for (int q = 0; q < NQ; ++q)
-      for (int s = 0; s < c.spr; ++s) {
-        const int t0 = c.seg_tile[s], t1 = c.seg_tile[s + 1];
-        const double t = final_sum(c.part + (size_t)q * c.part_stride + t0, t1 - t0, red);
-        if (threadIdx.x == 0) c.segs[((size_t)c.rank * NQ + q) * c.spr + s] = t;
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    for (int s = w; s < c.spr; s += (int)(blockDim.x >> 5)) {
+      const int t0 = c.seg_tile[s], t1 = c.seg_tile[s + 1];
+      double acc[NQ];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) acc[q] = 0.0;
+      for (int i = t0 + l; i < t1; i += 32) {
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) acc[q] += __ldcg(c.part + (size_t)q * c.part_stride + i);
       }
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const double t = warp_sum(acc[q]);
+        if (l == 0) c.segs[((size_t)c.rank * NQ + q) * c.spr + s] = t;
+      }
+    }
+    __threadfence();
+    __syncthreads();
     if (threadIdx.x == 0) {
       if (c.world == 1) {
-        __threadfence();
         const double a = seg_total(c.segs, 0, NQ, c.spr);
         const double b = NQ > 1 ? seg_total(c.segs, 1, NQ, c.spr) : 0.0;
         apply_scalars(c.sc, op, a, b);
@@ -173,8 +186,8 @@ __global__ void k_scalars(const double* segs, int nq, int spr, int op, Scalars* 
 }
 
 // ------------------------------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(kThreads) k_assemble(const AsmView a, const ReduceCtx c) {
+template <int MODE, int OCC>
+__global__ void __launch_bounds__(kThreads, OCC) k_assemble(const AsmView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
   const int r = blockIdx.x * kThreads + threadIdx.x;

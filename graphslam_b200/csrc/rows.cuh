@@ -35,8 +35,12 @@ struct SellView {
   const int* width;  // per slice
 };
 
+constexpr int kNoCountBit = 1 << 30;   // set in ij.x of a stored factor whose chi2 another rank counts
+constexpr int kIdxMask = kNoCountBit - 1;
+
 struct FactorView {
-  const int2* ij;       // local vertex indices of id_1, id_2
+  SellView fs;          // storage layout: slot k of home row r at base[r/32] + k*32 + r%32
+  const int2* ij;       // local vertex indices of id_1 (| kNoCountBit), id_2 ; (-1,-1) = padding slot
   const double2* zt;    // measured translation
   const double2* zr;    // (cos, sin) of the measured rotation
   const double2* o01;   // information, upper triangle 00 01 | 02 11 | 12 22
@@ -45,7 +49,8 @@ struct FactorView {
 };
 
 struct PriorView {
-  const int* row;        // local row
+  int n;                 // priors on this rank's rows
+  const int* row;        // local row, ascending
   const double4* pose;   // (x, y, cos, sin)
   const double* om;      // 6 per prior
 };
@@ -56,8 +61,8 @@ struct PriorView {
 // ------------------------------------------------------------------------------------------------
 struct AsmView {
   SellView cs;
-  const uint32_t* c_code;
-  const int* c_blk;
+  const int2* c;         // (code, block word) per contribution; code == kPadCode: padding slot
+  const int* ccol;       // local index of the contribution's other vertex
   FactorView f;
   PriorView pr;
   const double4* pose;   // n_own + n_ghost
@@ -108,6 +113,52 @@ GS_HD void store_block(double* Ho, size_t hstride, int pos, const double M[9]) {
   for (int k = 0; k < 9; ++k) Ho[(size_t)k * hstride + pos] = M[k];
 }
 
+// One factor side under GTSAM's default Jacobians (A_i = [[-c,-s,dt1],[s,-c,dt2],[0,0,-1]], A_j = I):
+// everything the row needs follows from W = Omega A_i —
+//   row is id_1:  diag += A_i^T W,  b += W^T e        row is id_2:  diag += Omega,  b += Omega e
+//   canonical off-diagonal block  M = A_lo^T Omega A_hi  =  W^T if lo is id_1, W if lo is id_2
+// W is formed at ONE place, so the two ranks that both store the block of a cut factor get the same bits.
+struct SideDefault {
+  double W[9];
+  double e[3];
+  double c, s, dt1, dt2;
+};
+
+GS_HD void side_default(const double4 pi, const double4 pj, const double2 zt, const double2 zr, const Sym3& O,
+                        SideDefault& S) {
+  const double ci = pi.z, si = pi.w, cj = pj.z, sj = pj.w;
+  const double dx = pj.x - pi.x, dy = pj.y - pi.y;
+  const double hx = ci * dx + si * dy;
+  const double hy = -si * dx + ci * dy;
+  double c = ci * cj + si * sj;
+  double s = -si * cj + ci * sj;
+  {  // Rot2::atan2(s, c) normalises
+    const double inv = 1.0 / sqrt(c * c + s * s);
+    c *= inv;
+    s *= inv;
+  }
+  const double cm = zr.x, sm = zr.y;
+  const double rx = hx - zt.x, ry = hy - zt.y;
+  S.e[0] = cm * rx + sm * ry;
+  S.e[1] = -sm * rx + cm * ry;
+  S.e[2] = atan2(s * cm - c * sm, c * cm + s * sm);
+  const double dt1 = -sj * dx + cj * dy;
+  const double dt2 = -cj * dx - sj * dy;
+  S.c = c;
+  S.s = s;
+  S.dt1 = dt1;
+  S.dt2 = dt2;
+  const double r0[3] = {O.a00, O.a01, O.a02}, r1[3] = {O.a01, O.a11, O.a12}, r2[3] = {O.a02, O.a12, O.a22};
+  const double* rows[3] = {r0, r1, r2};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const double a = rows[k][0], b = rows[k][1], d = rows[k][2];
+    S.W[3 * k + 0] = s * b - c * a;
+    S.W[3 * k + 1] = -(s * a) - c * b;
+    S.W[3 * k + 2] = (dt1 * a + dt2 * b) - d;
+  }
+}
+
 // returns the row's chi2 share (factors it is the counting side of, and its priors)
 template <int MODE>
 GS_HD double assemble_row(const AsmView& a, int r) {
@@ -116,30 +167,71 @@ GS_HD double assemble_row(const AsmView& a, int r) {
   double dg[6] = {0, 0, 0, 0, 0, 0}, bv[3] = {0, 0, 0}, acc[9];
   double chi2 = 0.0;
   int open = -1;
+  const double4 prow = ldg(a.pose + r);
+  // w is the same for the 32 rows of a slice.  The next slot's words are fetched while this slot's
+  // factor and pose are in flight; each slot is then one dependent round trip (factor + other pose).
+  int2 cw = w > 0 ? ldg(a.c + base) : make_int2((int)kPadCode, -1);
+  int ccol = w > 0 ? ldg(a.ccol + base) : 0;
   for (int s = 0; s < w; ++s) {
-    const int c = base + s * kSlice;
-    const uint32_t code = ldg(a.c_code + c);
-    if (code == kPadCode) break;
-    const int cb = ldg(a.c_blk + c);
+    const int2 cur = cw;
+    const int col = ccol;
+    if (s + 1 < w) {
+      cw = ldg(a.c + base + (s + 1) * kSlice);
+      ccol = ldg(a.ccol + base + (s + 1) * kSlice);
+    }
+    const uint32_t code = (uint32_t)cur.x;
+    if (code == kPadCode) continue;
+    const int cb = cur.y;
     const int kind = code & 3u;
     const int idx = (int)(code >> 3);
-    double d6[6], b3[3];
     if (kind < 2) {
-      const int2 ij = ldg(a.f.ij + idx);
       const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
       const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
-      const double4 pi = ldg(a.pose + ij.x), pj = ldg(a.pose + ij.y);
-      BetweenLin L;
-      between_linearize<MODE>(pi, pj, zt, zr, L);
+      const double4 pcol = ldg(a.pose + col);
       const Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
       const bool row_is_i = (kind == 0);
-      diag_pieces(O, row_is_i ? L.Ai : L.Aj, L.e, d6, b3);
-      if (code & 4u) chi2 += quad_form(O, L.e);
+      const double4 pi = row_is_i ? prow : pcol, pj = row_is_i ? pcol : prow;
+      // row is the hi endpoint of the pair (cb & 2): the lo Jacobian is the other vertex's
+      const bool lo_is_i = row_is_i != ((cb & 2) != 0);
+      double M[9];
+      if (MODE == 0) {
+        SideDefault S;
+        side_default(pi, pj, zt, zr, O, S);
+        const double* W = S.W;
+        if (row_is_i) {
+          dg[0] += S.s * W[3] - S.c * W[0];
+          dg[1] += S.s * W[4] - S.c * W[1];
+          dg[2] += S.s * W[5] - S.c * W[2];
+          dg[3] += -(S.s * W[1]) - S.c * W[4];
+          dg[4] += -(S.s * W[2]) - S.c * W[5];
+          dg[5] += (S.dt1 * W[2] + S.dt2 * W[5]) - W[8];
+#pragma unroll
+          for (int k = 0; k < 3; ++k) bv[k] += (W[k] * S.e[0] + W[3 + k] * S.e[1]) + W[6 + k] * S.e[2];
+        } else {
+          dg[0] += O.a00; dg[1] += O.a01; dg[2] += O.a02;
+          dg[3] += O.a11; dg[4] += O.a12; dg[5] += O.a22;
+          bv[0] += (O.a00 * S.e[0] + O.a01 * S.e[1]) + O.a02 * S.e[2];
+          bv[1] += (O.a01 * S.e[0] + O.a11 * S.e[1]) + O.a12 * S.e[2];
+          bv[2] += (O.a02 * S.e[0] + O.a12 * S.e[1]) + O.a22 * S.e[2];
+        }
+        if (code & 4u) chi2 += quad_form(O, S.e);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+#pragma unroll
+          for (int t = 0; t < 3; ++t) M[3 * q + t] = lo_is_i ? W[3 * t + q] : W[3 * q + t];
+      } else {
+        BetweenLin L;
+        between_linearize<MODE>(pi, pj, zt, zr, L);
+        double d6[6], b3[3];
+        diag_pieces(O, row_is_i ? L.Ai : L.Aj, L.e, d6, b3);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) dg[k] += d6[k];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) bv[k] += b3[k];
+        if (code & 4u) chi2 += quad_form(O, L.e);
+        if (cb >= 0) off_block(O, lo_is_i ? L.Ai : L.Aj, lo_is_i ? L.Aj : L.Ai, M);
+      }
       if (cb >= 0) {
-        // row is the hi endpoint of the pair (cb & 2): lo Jacobian is the other vertex's
-        const bool lo_is_i = row_is_i != ((cb & 2) != 0);
-        double M[9];
-        off_block(O, lo_is_i ? L.Ai : L.Aj, lo_is_i ? L.Aj : L.Ai, M);
         if (cb & 1) {
           if (open >= 0) store_block(a.Ho, a.hstride, open, acc);
           open = cb >> 2;
@@ -152,19 +244,18 @@ GS_HD double assemble_row(const AsmView& a, int r) {
       }
     } else {
       const double4 pp = ldg(a.pr.pose + idx);
-      const double4 px = ldg(a.pose + r);
       const double* om = a.pr.om + 6 * idx;
       const Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-      double e[3];
+      double e[3], d6[6], b3[3];
       Mat3 A;
-      prior_linearize<MODE>(px, pp, e, A);
+      prior_linearize<MODE>(prow, pp, e, A);
       diag_pieces(O, A, e, d6, b3);
       chi2 += quad_form(O, e);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) dg[k] += d6[k];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) bv[k] += b3[k];
     }
-#pragma unroll
-    for (int k = 0; k < 6; ++k) dg[k] += d6[k];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) bv[k] += b3[k];
   }
   if (open >= 0) store_block(a.Ho, a.hstride, open, acc);
 #pragma unroll
@@ -174,31 +265,39 @@ GS_HD double assemble_row(const AsmView& a, int r) {
   return chi2;
 }
 
-// graph.error contribution of row r (same counting rule as assemble_row), at `pose`
+// graph.error contribution of row r at `pose`: its priors, then the factors stored in its home
+// slots that this rank counts (same set and order as assemble_row's chi2).  The factor arrays are
+// read directly in storage order: 32 consecutive rows read 32 consecutive slots.
 GS_HD double chi2_row(const AsmView& a, int r) {
-  const int sl = r / kSlice, lane = r % kSlice;
-  const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
   double chi2 = 0.0;
+  {  // priors of this row: lower_bound in the ascending row list
+    int lo = 0, hi = a.pr.n;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (a.pr.row[mid] < r) lo = mid + 1;
+      else hi = mid;
+    }
+    for (int k = lo; k < a.pr.n && a.pr.row[k] == r; ++k) {
+      const double* om = a.pr.om + 6 * k;
+      const Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
+      double e[3];
+      Mat3 A;
+      prior_linearize<0>(ldg(a.pose + r), ldg(a.pr.pose + k), e, A);
+      chi2 += quad_form(O, e);
+    }
+  }
+  const int sl = r / kSlice, lane = r % kSlice;
+  const int base = a.f.fs.base[sl] + lane, w = a.f.fs.width[sl];
+#pragma unroll 4
   for (int s = 0; s < w; ++s) {
-    const int c = base + s * kSlice;
-    const uint32_t code = ldg(a.c_code + c);
-    if (code == kPadCode) break;
-    if (!(code & 4u)) continue;
-    const int kind = code & 3u;
-    const int idx = (int)(code >> 3);
-    double e[3];
-    if (kind < 2) {
-      const int2 ij = ldg(a.f.ij + idx);
+    const int idx = base + s * kSlice;
+    const int2 ij = ldg(a.f.ij + idx);
+    if (ij.x >= 0 && !(ij.x & kNoCountBit)) {
       const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
       const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
+      double e[3];
       between_error(ldg(a.pose + ij.x), ldg(a.pose + ij.y), zt, zr, e);
       const Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
-      chi2 += quad_form(O, e);
-    } else {
-      const double* om = a.pr.om + 6 * idx;
-      const Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-      Mat3 A;
-      prior_linearize<0>(ldg(a.pose + r), ldg(a.pr.pose + idx), e, A);
       chi2 += quad_form(O, e);
     }
   }
@@ -210,8 +309,7 @@ GS_HD double chi2_row(const AsmView& a, int r) {
 // ------------------------------------------------------------------------------------------------
 struct SpmvView {
   SellView rs;
-  const int* r_col;
-  const int* r_blk;
+  const int2* refs;      // (local column, block word) per neighbour; column < 0: padding slot
   const double* Ho;
   size_t hstride;
   const double* Hd;      // 6 planes of n_own
@@ -223,23 +321,26 @@ GS_HD double spmv_row(const SpmvView& a, const double* p, double* y, int r, doub
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
   double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+  // w is uniform over the slice; the next slot's reference is fetched while this slot's block and
+  // p are in flight, so a slot costs one dependent round trip
+  int2 nref = w > 0 ? ldg(a.refs + base) : make_int2(-1, 0);
   for (int s = 0; s < w; ++s) {
-    const int q = base + s * kSlice;
-    const int col = ldg(a.r_col + q);
-    if (col < 0) break;
-    const int rb = ldg(a.r_blk + q);
-    const int blk = rb >> 1;
-    const double* h = a.Ho + blk;
-    const double h0 = ldg(h), h1 = ldg(h + a.hstride), h2 = ldg(h + 2 * a.hstride);
-    const double h3 = ldg(h + 3 * a.hstride), h4 = ldg(h + 4 * a.hstride), h5 = ldg(h + 5 * a.hstride);
-    const double h6 = ldg(h + 6 * a.hstride), h7 = ldg(h + 7 * a.hstride), h8 = ldg(h + 8 * a.hstride);
-    const double px = p[3 * (size_t)col], py = p[3 * (size_t)col + 1], pz = p[3 * (size_t)col + 2];
-    const bool tr = rb & 1;
-    const double a01 = tr ? h3 : h1, a02 = tr ? h6 : h2, a10 = tr ? h1 : h3;
-    const double a12 = tr ? h7 : h5, a20 = tr ? h2 : h6, a21 = tr ? h5 : h7;
-    y0 += (h0 * px + a01 * py) + a02 * pz;
-    y1 += (a10 * px + h4 * py) + a12 * pz;
-    y2 += (a20 * px + a21 * py) + h8 * pz;
+    const int2 ref = nref;
+    if (s + 1 < w) nref = ldg(a.refs + base + (s + 1) * kSlice);
+    if (ref.x >= 0) {
+      const int col = ref.x, rb = ref.y;
+      const double* h = a.Ho + (rb >> 1);
+      const double h0 = ldg(h), h1 = ldg(h + a.hstride), h2 = ldg(h + 2 * a.hstride);
+      const double h3 = ldg(h + 3 * a.hstride), h4 = ldg(h + 4 * a.hstride), h5 = ldg(h + 5 * a.hstride);
+      const double h6 = ldg(h + 6 * a.hstride), h7 = ldg(h + 7 * a.hstride), h8 = ldg(h + 8 * a.hstride);
+      const double px = p[3 * (size_t)col], py = p[3 * (size_t)col + 1], pz = p[3 * (size_t)col + 2];
+      const bool tr = rb & 1;
+      const double a01 = tr ? h3 : h1, a02 = tr ? h6 : h2, a10 = tr ? h1 : h3;
+      const double a12 = tr ? h7 : h5, a20 = tr ? h2 : h6, a21 = tr ? h5 : h7;
+      y0 += (h0 * px + a01 * py) + a02 * pz;
+      y1 += (a10 * px + h4 * py) + a12 * pz;
+      y2 += (a20 * px + a21 * py) + h8 * pz;
+    }
   }
   const size_t n = (size_t)a.n_own, rr = (size_t)r;
   const double d00 = ldg(a.Hd + rr), d01 = ldg(a.Hd + n + rr), d02 = ldg(a.Hd + 2 * n + rr);

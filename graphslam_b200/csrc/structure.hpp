@@ -165,7 +165,8 @@ struct LocalStructure {
   // factors, SELL order by home row (padding slots hold a harmless dummy)
   Sell fsell;
   std::vector<int> f_src;             // storage slot -> caller's factor index, -1 padding
-  std::vector<int> f_i, f_j;          // local vertex index of id_1 / id_2 per slot
+  std::vector<int> f_i, f_j;          // local vertex index of id_1 / id_2 per slot (-1 padding)
+  std::vector<char> f_count;          // 1: this rank counts the factor's chi2 (its lo endpoint is owned)
   // priors on owned rows
   std::vector<int> pr_src;            // local prior -> caller's prior index
   std::vector<int> pr_row;            // local row
@@ -173,6 +174,7 @@ struct LocalStructure {
   Sell csell;
   std::vector<uint32_t> c_code;
   std::vector<int> c_blk;
+  std::vector<int> c_col;             // local index of the other vertex of each contribution (0 for priors/padding)
   // H blocks
   Sell bsell;
   // reference lists
@@ -232,8 +234,9 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   }
   S.fsell.build(fcnt);
   S.f_src.assign(S.fsell.slots, -1);
-  S.f_i.assign(S.fsell.slots, 0);
-  S.f_j.assign(S.fsell.slots, 0);
+  S.f_i.assign(S.fsell.slots, -1);
+  S.f_j.assign(S.fsell.slots, -1);
+  S.f_count.assign(S.fsell.slots, 0);
   std::vector<int> fpos(EL);
   {
     std::vector<int> fill(n_own, 0);
@@ -244,6 +247,7 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
       S.f_src[p] = k;
       S.f_i[p] = S.local_of(ei[k]);
       S.f_j[p] = S.local_of(ej[k]);
+      S.f_count[p] = owned(std::min(ei[k], ej[k])) ? 1 : 0;
     }
   }
 
@@ -251,10 +255,10 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   S.pr_src.clear();
   S.pr_row.clear();
   for (int p = 0; p < P; ++p)
-    if (owned(prior_idx[p])) {
-      S.pr_src.push_back(p);
-      S.pr_row.push_back(prior_idx[p] - v0);
-    }
+    if (owned(prior_idx[p])) S.pr_src.push_back(p);
+  // ascending row, caller's order within a row (the chi2 pass looks a row's priors up by bisection)
+  std::stable_sort(S.pr_src.begin(), S.pr_src.end(), [&](int a, int b) { return prior_idx[a] < prior_idx[b]; });
+  for (int p : S.pr_src) S.pr_row.push_back(prior_idx[p] - v0);
   S.P_loc = (int)S.pr_src.size();
 
   // ---- contribution lists: priors first, then factor sides in canonical order (which visits a
@@ -296,6 +300,10 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
       }
     }
   }
+
+  S.c_col.assign(S.csell.slots, 0);
+  for (int c = 0; c < S.csell.slots; ++c)
+    if (ccol[c] >= 0) S.c_col[c] = S.local_of(ccol[c]);
 
   // ---- H blocks: one per unordered pair, homed like the factors; block words of the writer rows;
   //      reference triples (global col, local col, block word) per owned row
