@@ -85,7 +85,8 @@ class GsEmuResult(C.Structure):
     _fields_ = [("blocks", c_double_p), ("b", c_double_p), ("delta", c_double_p), ("xyt_new", c_double_p),
                 ("chi2", C.c_double), ("chi2_check", C.c_double), ("chi2_new", C.c_double), ("dHd", C.c_double),
                 ("db", C.c_double), ("rel_residual", C.c_double), ("pcg_iters", C.c_int32), ("pcg_done", C.c_int32),
-                ("n_ghost_total", C.c_int32), ("n_pairs_total", C.c_int32), ("halo_send_total", C.c_int32)]
+                ("n_ghost_total", C.c_int32), ("n_pairs_total", C.c_int32), ("halo_send_total", C.c_int32),
+                ("n_factor_copies", C.c_int32), ("n_block_copies", C.c_int32)]
 
 
 # test-only entries (include/graphslam_cuda_debug.h): the product's own host code, callable on a CPU box

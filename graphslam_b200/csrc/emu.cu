@@ -21,7 +21,8 @@ using gs::LocalStructure;
 struct VRank {
   LocalStructure S;
   int n_own = 0, n_loc = 0;
-  std::vector<int2> eij, cw, refs;
+  std::vector<int2> eij, refs;
+  std::vector<int4> cw;
   std::vector<double2> zt, zr, o01, o23, o45;
   std::vector<double4> pr_pose, pose, pose_try;
   std::vector<double> pr_om, Ho, Hd, Minv, b, x, r, z, p, Ap, part;
@@ -31,9 +32,6 @@ struct VRank {
     a.cs.base = S.csell.base.data();
     a.cs.width = S.csell.width.data();
     a.c = cw.data();
-    a.ccol = S.c_col.data();
-    a.f.fs.base = S.fsell.base.data();
-    a.f.fs.width = S.fsell.width.data();
     a.f.ij = eij.data();
     a.f.zt = zt.data();
     a.f.zr = zr.data();
@@ -170,10 +168,10 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
     const LocalStructure& S = me.S;
     me.n_own = S.n_own;
     me.n_loc = S.n_own + S.n_ghost;
-    const int FS = S.fsell.slots;
+    const int FS = S.csell.slots;
     me.eij.assign(FS, make_int2(-1, -1));
     me.cw.resize(S.c_code.size());
-    for (size_t c = 0; c < me.cw.size(); ++c) me.cw[c] = make_int2((int)S.c_code[c], S.c_blk[c]);
+    for (size_t c = 0; c < me.cw.size(); ++c) me.cw[c] = make_int4((int)S.c_code[c], S.c_blk[c], S.c_col[c], S.c_blk2[c]);
     me.refs.resize(S.r_col.size());
     for (size_t c = 0; c < me.refs.size(); ++c) me.refs[c] = make_int2(S.r_col[c], S.r_blk[c]);
     me.zt.assign(FS, make_double2(0, 0));
@@ -205,7 +203,7 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
       const int d = me.global_of(l);
       me.pose[l] = make_double4(pb->xyt[3 * d], pb->xyt[3 * d + 1], std::cos(pb->xyt[3 * d + 2]), std::sin(pb->xyt[3 * d + 2]));
     }
-    me.hstride = (size_t)std::max(S.bsell.slots, 1);
+    me.hstride = (size_t)std::max(S.rsell.slots, 1);
     me.Ho.assign(9 * me.hstride, 0.0);
     const size_t n3 = 3 * (size_t)std::max(me.n_own, 1), nl3 = 3 * (size_t)std::max(me.n_loc, 1);
     me.Hd.assign(2 * n3, 0.0);
@@ -331,10 +329,14 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
   out->n_ghost_total = 0;
   out->n_pairs_total = 0;
   out->halo_send_total = 0;
+  out->n_factor_copies = 0;
+  out->n_block_copies = 0;
   for (VRank& me : W.R) {
     out->n_ghost_total += me.S.n_ghost;
     out->n_pairs_total += me.S.n_pairs;
     out->halo_send_total += (int)me.S.send_rows.size();
+    out->n_factor_copies += me.S.n_factor_copies;
+    out->n_block_copies += me.S.n_block_copies;
   }
   return GS_OK;
 }

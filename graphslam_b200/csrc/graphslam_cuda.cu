@@ -121,9 +121,10 @@ struct gs_graph {
 
   // ---- device
   DevBuf<double4> d_pose, d_pose_try, d_pr_pose, d_pose_all;
-  DevBuf<int2> d_eij, d_cw, d_refs;
+  DevBuf<int2> d_eij, d_refs;
+  DevBuf<int4> d_cw;
   DevBuf<double2> d_zt, d_zr, d_o01, d_o23, d_o45;
-  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_rbase, d_rwidth, d_fbase, d_fwidth, d_segtile, d_send_rows, d_ccol;
+  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_rbase, d_rwidth, d_segtile, d_send_rows;
   DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part, d_segs, d_sendbuf;
   DevBuf<Scalars> d_sc;
   DevBuf<unsigned int> d_counter;
@@ -202,9 +203,6 @@ gs::AsmView asm_view(gs_graph* g, const double4* pose) {
   a.cs.base = g->d_cbase.p;
   a.cs.width = g->d_cwidth.p;
   a.c = g->d_cw.p;
-  a.ccol = g->d_ccol.p;
-  a.f.fs.base = g->d_fbase.p;
-  a.f.fs.width = g->d_fwidth.p;
   a.f.ij = g->d_eij.p;
   a.f.zt = g->d_zt.p;
   a.f.zr = g->d_zr.p;
@@ -419,7 +417,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->n_own = S.n_own;
   g->n_loc = S.n_own + S.n_ghost;
   // factor arrays in storage (SELL) order; padding slots are never referenced
-  const int FS = S.fsell.slots;
+  const int FS = S.csell.slots;
   std::vector<int2> eij(FS, make_int2(-1, -1));
   std::vector<double2> zt(FS, make_double2(0, 0)), zr(FS, make_double2(1, 0)), o01(FS, make_double2(0, 0)),
       o23(FS, make_double2(0, 0)), o45(FS, make_double2(0, 0));
@@ -456,23 +454,20 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = upload(g, g->d_cbase, S.csell.base)) return s;
   if (gs_status s = upload(g, g->d_cwidth, S.csell.width)) return s;
   {
-    std::vector<int2> cw(S.c_code.size());
-    for (size_t q = 0; q < cw.size(); ++q) cw[q] = make_int2((int)S.c_code[q], S.c_blk[q]);
+    std::vector<int4> cw(S.c_code.size());
+    for (size_t q = 0; q < cw.size(); ++q) cw[q] = make_int4((int)S.c_code[q], S.c_blk[q], S.c_col[q], S.c_blk2[q]);
     if (gs_status s = upload(g, g->d_cw, cw)) return s;
     std::vector<int2> refs(S.r_col.size());
     for (size_t q = 0; q < refs.size(); ++q) refs[q] = make_int2(S.r_col[q], S.r_blk[q]);
     if (gs_status s = upload(g, g->d_refs, refs)) return s;
     GS_CUDA(g, cudaStreamSynchronize(g->stream));
   }
-  if (gs_status s = upload(g, g->d_ccol, S.c_col)) return s;
-  if (gs_status s = upload(g, g->d_fbase, S.fsell.base)) return s;
-  if (gs_status s = upload(g, g->d_fwidth, S.fsell.width)) return s;
   if (gs_status s = upload(g, g->d_rbase, S.rsell.base)) return s;
   if (gs_status s = upload(g, g->d_rwidth, S.rsell.width)) return s;
   if (gs_status s = upload(g, g->d_segtile, segtile)) return s;
   if (gs_status s = upload(g, g->d_send_rows, S.send_rows)) return s;
   const size_t n3 = 3 * (size_t)std::max(S.n_own, 1), nl3 = 3 * (size_t)std::max(g->n_loc, 1);
-  g->hstride = (size_t)std::max(S.bsell.slots, 1);
+  g->hstride = (size_t)std::max(S.rsell.slots, 1);
   GS_CUDA(g, g->d_pose.alloc(std::max(g->n_loc, 1)));
   GS_CUDA(g, g->d_pose_try.alloc(std::max(g->n_loc, 1)));
   if (g->world > 1) GS_CUDA(g, g->d_pose_all.alloc(N));

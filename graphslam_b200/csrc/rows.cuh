@@ -39,8 +39,7 @@ constexpr int kNoCountBit = 1 << 30;   // set in ij.x of a stored factor whose c
 constexpr int kIdxMask = kNoCountBit - 1;
 
 struct FactorView {
-  SellView fs;          // storage layout: slot k of home row r at base[r/32] + k*32 + r%32
-  const int2* ij;       // local vertex indices of id_1 (| kNoCountBit), id_2 ; (-1,-1) = padding slot
+  const int2* ij;       // per factor cell: local indices of id_1 (| kNoCountBit), id_2 ; (-1,-1) = no data
   const double2* zt;    // measured translation
   const double2* zr;    // (cos, sin) of the measured rotation
   const double2* o01;   // information, upper triangle 00 01 | 02 11 | 12 22
@@ -61,8 +60,8 @@ struct PriorView {
 // ------------------------------------------------------------------------------------------------
 struct AsmView {
   SellView cs;
-  const int2* c;         // (code, block word) per contribution; code == kPadCode: padding slot
-  const int* ccol;       // local index of the contribution's other vertex
+  const int4* c;         // per contribution: (code, block word, local index of the other vertex, cell wanting
+                         // the transposed block copy or -1); code == kPadCode: padding slot
   FactorView f;
   PriorView pr;
   const double4* pose;   // n_own + n_ghost
@@ -108,9 +107,16 @@ GS_HD void diag_pieces(const Sym3& O, const Mat3& Ar, const double e[3], double 
   for (int r = 0; r < 3; ++r) bv[r] = W[0 + r] * e[0] + W[3 + r] * e[1] + W[6 + r] * e[2];
 }
 
-GS_HD void store_block(double* Ho, size_t hstride, int pos, const double M[9]) {
+// the block goes to its own cell and, transposed, to the cell of the other row when that row keeps a copy
+GS_HD void store_block(double* Ho, size_t hstride, int pos, int pos2, const double M[9]) {
 #pragma unroll
   for (int k = 0; k < 9; ++k) Ho[(size_t)k * hstride + pos] = M[k];
+  if (pos2 >= 0) {
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+#pragma unroll
+      for (int t = 0; t < 3; ++t) Ho[(size_t)(3 * q + t) * hstride + pos2] = M[3 * t + q];
+  }
 }
 
 // One factor side under GTSAM's default Jacobians (A_i = [[-c,-s,dt1],[s,-c,dt2],[0,0,-1]], A_j = I):
@@ -166,19 +172,15 @@ GS_HD double assemble_row(const AsmView& a, int r) {
   const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
   double dg[6] = {0, 0, 0, 0, 0, 0}, bv[3] = {0, 0, 0}, acc[9];
   double chi2 = 0.0;
-  int open = -1;
+  int open = -1, open2 = -1;
   const double4 prow = ldg(a.pose + r);
   // w is the same for the 32 rows of a slice.  The next slot's words are fetched while this slot's
   // factor and pose are in flight; each slot is then one dependent round trip (factor + other pose).
-  int2 cw = w > 0 ? ldg(a.c + base) : make_int2((int)kPadCode, -1);
-  int ccol = w > 0 ? ldg(a.ccol + base) : 0;
+  int4 cw = w > 0 ? ldg(a.c + base) : make_int4((int)kPadCode, -1, 0, -1);
   for (int s = 0; s < w; ++s) {
-    const int2 cur = cw;
-    const int col = ccol;
-    if (s + 1 < w) {
-      cw = ldg(a.c + base + (s + 1) * kSlice);
-      ccol = ldg(a.ccol + base + (s + 1) * kSlice);
-    }
+    const int4 cur = cw;
+    const int col = cur.z;
+    if (s + 1 < w) cw = ldg(a.c + base + (s + 1) * kSlice);
     const uint32_t code = (uint32_t)cur.x;
     if (code == kPadCode) continue;
     const int cb = cur.y;
@@ -233,8 +235,9 @@ GS_HD double assemble_row(const AsmView& a, int r) {
       }
       if (cb >= 0) {
         if (cb & 1) {
-          if (open >= 0) store_block(a.Ho, a.hstride, open, acc);
+          if (open >= 0) store_block(a.Ho, a.hstride, open, open2, acc);
           open = cb >> 2;
+          open2 = cur.w;
 #pragma unroll
           for (int k = 0; k < 9; ++k) acc[k] = M[k];
         } else {
@@ -257,7 +260,7 @@ GS_HD double assemble_row(const AsmView& a, int r) {
       for (int k = 0; k < 3; ++k) bv[k] += b3[k];
     }
   }
-  if (open >= 0) store_block(a.Ho, a.hstride, open, acc);
+  if (open >= 0) store_block(a.Ho, a.hstride, open, open2, acc);
 #pragma unroll
   for (int k = 0; k < 6; ++k) a.Hd[(size_t)k * a.n_own + r] = dg[k];
 #pragma unroll
@@ -265,9 +268,9 @@ GS_HD double assemble_row(const AsmView& a, int r) {
   return chi2;
 }
 
-// graph.error contribution of row r at `pose`: its priors, then the factors stored in its home
-// slots that this rank counts (same set and order as assemble_row's chi2).  The factor arrays are
-// read directly in storage order: 32 consecutive rows read 32 consecutive slots.
+// graph.error contribution of row r at `pose`: its priors, then the factors whose counting side is
+// one of its own cells (same set and order as assemble_row's chi2).  The factor arrays are read
+// directly in cell order: 32 consecutive rows read 32 consecutive cells.
 GS_HD double chi2_row(const AsmView& a, int r) {
   double chi2 = 0.0;
   {  // priors of this row: lower_bound in the ascending row list
@@ -287,7 +290,7 @@ GS_HD double chi2_row(const AsmView& a, int r) {
     }
   }
   const int sl = r / kSlice, lane = r % kSlice;
-  const int base = a.f.fs.base[sl] + lane, w = a.f.fs.width[sl];
+  const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
 #pragma unroll 4
   for (int s = 0; s < w; ++s) {
     const int idx = base + s * kSlice;

@@ -10,14 +10,15 @@
 //                              of P owns kSegments/P consecutive segments.  Every reduction is
 //                              tile -> segment -> total in that fixed tree, so results are bitwise
 //                              identical for P = 1, 2, 4, 8.
-//   * factor storage         : SoA, in 32-row slices (SELL-32) by "home" row = the smaller endpoint
-//                              (the larger one when the smaller is owned by another rank).
+//   * factor storage         : SoA; every contribution slot owns a cell, the factor's data sits in the
+//                              cell of its "home" row = the smaller endpoint (the larger one when the
+//                              smaller is owned by another rank); see "Cells" below.
 //   * contribution lists     : per owned row, every incident factor side ordered by the other
 //                              endpoint's global index, then canonical order; SELL-32 laid out so a
 //                              warp of 32 consecutive rows reads 32 consecutive words per slot.
 //   * H off-diagonal blocks  : ONE 3x3 block per unordered vertex pair, stored in canonical
-//                              orientation M = A_lo^T Omega A_hi (lo = smaller global index) at a
-//                              SELL-32 position of its home row; the other row uses M^T.
+//                              orientation M = A_lo^T Omega A_hi (lo = smaller global index) in the
+//                              reference cell of its writer row; the other row uses M^T (shared or copied).
 //   * reference lists        : per owned row, its neighbours in global column order as
 //                              (local column, block position, transposed?) for the SpMV.
 //   * halo lists             : for each peer, the owned rows it needs (send) and the contiguous
@@ -150,36 +151,45 @@ struct HaloPeer {
   int ghost_off = 0, ghost_cnt = 0; // range of ghost slots (local index = n_own + ghost_off + k)
 };
 
+// Cells.  Every (row, slot) of a SELL list owns a storage cell at the same position: contribution
+// (row, s) owns factor cell csell.pos(row, s), reference (row, s) owns block cell rsell.pos(row, s).
+// A cell either HOLDS data (the factor / block is "homed" there, or copied there) or POINTS at the
+// home cell of another row.  Pointing shares bytes (one DRAM read serves both rows, the second comes
+// from L2) but is only chosen when the 32 rows of a slice point at nearby cells, i.e. when the
+// warp's gather stays coalesced; otherwise the structure build gives the cell its own copy, so
+// every warp-level access of every kernel touches a handful of 128-byte lines whatever the graph.
+constexpr int kShareMaxLinesFactor = 12;  // distinct 128-B lines (8 double2 per line) a slice-slot may gather factors from
+constexpr int kShareMaxLinesBlock = 8;    // distinct 128-B lines (16 doubles per line) a slice-slot may gather blocks from
+
 struct LocalStructure {
   Partition part;
   int rank = 0;
   int v0 = 0, v1 = 0;        // owned global rows [v0, v1)
   int n_own = 0, n_ghost = 0;
   int E_glob = 0, E_loc = 0, P_loc = 0;
-  int n_pairs = 0;           // stored off-diagonal blocks (unordered pairs with an owned endpoint)
+  int n_pairs = 0;           // off-diagonal blocks computed here (unordered pairs with an owned endpoint)
   int nnzo_own = 0;          // off-diagonal blocks of the owned rows of the full (non-symmetric) BSR
+  int n_factor_copies = 0;   // factor cells that hold a copy (gather would not coalesce)
+  int n_block_copies = 0;    // block cells that hold a transposed copy
   int ntiles = 0;
   int seg_tile[kSegments + 1] = {0};  // local tile ranges of the locally owned segments (first kSegments/P used)
   std::vector<int> ghosts;            // global index of ghost g (sorted)
 
-  // factors, SELL order by home row (padding slots hold a harmless dummy)
-  Sell fsell;
-  std::vector<int> f_src;             // storage slot -> caller's factor index, -1 padding
-  std::vector<int> f_i, f_j;          // local vertex index of id_1 / id_2 per slot (-1 padding)
-  std::vector<char> f_count;          // 1: this rank counts the factor's chi2 (its lo endpoint is owned)
+  // contribution lists = factor cells
+  Sell csell;
+  std::vector<uint32_t> c_code;       // (factor cell to read << 3) | count << 2 | kind ; kPadCode padding
+  std::vector<int> c_blk;             // -1, or (block cell << 2) | (row is hi endpoint << 1) | head
+  std::vector<int> c_blk2;            // -1, or block cell of the other row that wants the transposed copy
+  std::vector<int> c_col;             // local index of the other vertex (0 for priors/padding)
+  std::vector<int> f_src;             // factor cell -> caller's factor index, -1 if the cell holds no data
+  std::vector<int> f_i, f_j;          // local vertex index of id_1 / id_2 per data cell (-1 otherwise)
+  std::vector<char> f_count;          // 1: this cell is the counting side of its factor (chi2)
   // priors on owned rows
   std::vector<int> pr_src;            // local prior -> caller's prior index
-  std::vector<int> pr_row;            // local row
-  // contribution lists
-  Sell csell;
-  std::vector<uint32_t> c_code;
-  std::vector<int> c_blk;
-  std::vector<int> c_col;             // local index of the other vertex of each contribution (0 for priors/padding)
-  // H blocks
-  Sell bsell;
-  // reference lists
+  std::vector<int> pr_row;            // local row, ascending
+  // reference lists = block cells
   Sell rsell;
-  std::vector<int> r_col, r_blk;
+  std::vector<int> r_col, r_blk;      // local column (-1 padding); (block cell to read << 1) | transposed
   // halo
   std::vector<HaloPeer> peers;
   std::vector<int> send_rows;         // local owned row indices, grouped by peer, each group sorted
@@ -191,6 +201,24 @@ struct LocalStructure {
     return n_own + (int)(it - ghosts.begin());
   }
 };
+
+// distinct values of key(x) over a small array (<= 32 entries)
+template <typename F>
+inline int distinct_count(const int* v, int n, F key) {
+  int seen[kSlice];
+  int m = 0;
+  for (int a = 0; a < n; ++a) {
+    const int k = key(v[a]);
+    bool dup = false;
+    for (int b = 0; b < m; ++b)
+      if (seen[b] == k) {
+        dup = true;
+        break;
+      }
+    if (!dup) seen[m++] = k;
+  }
+  return m;
+}
 
 // Build the structure of `rank` in a world of `world` ranks.  ei/ej are global dense indices in the
 // caller's factor order; `perm` is canonical_order() of them (shared by all ranks of a process).
@@ -223,40 +251,11 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   S.E_loc = (int)loc.size();
   const int EL = S.E_loc;
 
-  // ---- factor storage: SELL by home row
-  std::vector<int> home(EL);
-  std::vector<int> fcnt(n_own, 0);
-  for (int q = 0; q < EL; ++q) {
-    const int k = perm[loc[q]];
-    const int lo = std::min(ei[k], ej[k]), hi = std::max(ei[k], ej[k]);
-    home[q] = (owned(lo) ? lo : hi) - v0;
-    fcnt[home[q]]++;
-  }
-  S.fsell.build(fcnt);
-  S.f_src.assign(S.fsell.slots, -1);
-  S.f_i.assign(S.fsell.slots, -1);
-  S.f_j.assign(S.fsell.slots, -1);
-  S.f_count.assign(S.fsell.slots, 0);
-  std::vector<int> fpos(EL);
-  {
-    std::vector<int> fill(n_own, 0);
-    for (int q = 0; q < EL; ++q) {
-      const int k = perm[loc[q]];
-      const int p = S.fsell.pos(home[q], fill[home[q]]++);
-      fpos[q] = p;
-      S.f_src[p] = k;
-      S.f_i[p] = S.local_of(ei[k]);
-      S.f_j[p] = S.local_of(ej[k]);
-      S.f_count[p] = owned(std::min(ei[k], ej[k])) ? 1 : 0;
-    }
-  }
-
-  // ---- priors on owned rows (caller's order)
+  // ---- priors on owned rows: ascending row, caller's order within a row
   S.pr_src.clear();
   S.pr_row.clear();
   for (int p = 0; p < P; ++p)
     if (owned(prior_idx[p])) S.pr_src.push_back(p);
-  // ascending row, caller's order within a row (the chi2 pass looks a row's priors up by bisection)
   std::stable_sort(S.pr_src.begin(), S.pr_src.end(), [&](int a, int b) { return prior_idx[a] < prior_idx[b]; });
   for (int p : S.pr_src) S.pr_row.push_back(prior_idx[p] - v0);
   S.P_loc = (int)S.pr_src.size();
@@ -271,110 +270,195 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
     if (owned(ej[k])) ccnt[ej[k] - v0]++;
   }
   S.csell.build(ccnt);
-  S.c_code.assign(S.csell.slots, kPadCode);
-  S.c_blk.assign(S.csell.slots, -1);
-  std::vector<int> ccol(S.csell.slots, -1);  // global column of each contribution (-1 prior)
+  const int CS = S.csell.slots;
+  S.c_code.assign(CS, kPadCode);
+  S.c_blk.assign(CS, -1);
+  S.c_blk2.assign(CS, -1);
+  S.c_col.assign(CS, 0);
+  S.f_src.assign(CS, -1);
+  S.f_i.assign(CS, -1);
+  S.f_j.assign(CS, -1);
+  S.f_count.assign(CS, 0);
+  std::vector<int> ccol(CS, -1);    // global column of each contribution (-1 prior / padding)
+  std::vector<int> chome(CS, -1);   // home cell of the contribution's factor
+  std::vector<int> cfac(CS, -1);    // caller's factor index
   {
     std::vector<int> fill(n_own, 0);
     for (int p = 0; p < S.P_loc; ++p) {
       const int row = S.pr_row[p];
       const int c = S.csell.pos(row, fill[row]++);
       S.c_code[c] = ((uint32_t)p << 3) | 4u | 2u;
-      ccol[c] = -1;
     }
     for (int q = 0; q < EL; ++q) {
       const int k = perm[loc[q]];
       const int gi = ei[k], gj = ej[k];
-      const int lo = std::min(gi, gj);
-      if (owned(gi)) {
-        const int row = gi - v0;
-        const int c = S.csell.pos(row, fill[row]++);
-        S.c_code[c] = ((uint32_t)fpos[q] << 3) | (gi == lo ? 4u : 0u) | 0u;
-        ccol[c] = gj;
+      const int lo = std::min(gi, gj), hi = std::max(gi, gj);
+      const int ci = owned(gi) ? S.csell.pos(gi - v0, fill[gi - v0]++) : -1;
+      const int cj = owned(gj) ? S.csell.pos(gj - v0, fill[gj - v0]++) : -1;
+      const int home = owned(lo) ? (gi == lo ? ci : cj) : (gi == hi ? ci : cj);
+      if (ci >= 0) {
+        S.c_code[ci] = (gi == lo ? 4u : 0u) | 0u;
+        ccol[ci] = gj;
+        chome[ci] = home;
+        cfac[ci] = k;
       }
-      if (owned(gj)) {
-        const int row = gj - v0;
-        const int c = S.csell.pos(row, fill[row]++);
-        S.c_code[c] = ((uint32_t)fpos[q] << 3) | (gj == lo ? 4u : 0u) | 1u;
-        ccol[c] = gi;
+      if (cj >= 0) {
+        S.c_code[cj] = (gj == lo ? 4u : 0u) | 1u;
+        ccol[cj] = gi;
+        chome[cj] = home;
+        cfac[cj] = k;
       }
     }
   }
+  // share or copy, per (slice, slot): cells whose factor is homed elsewhere point there only if the
+  // slice's 32 pointers stay within a few lines
+  S.n_factor_copies = 0;
+  {
+    const int ns = (n_own + kSlice - 1) / kSlice;
+    int away[kSlice], awaycell[kSlice];
+    for (int sl = 0; sl < ns; ++sl)
+      for (int s = 0; s < S.csell.width[sl]; ++s) {
+        int na = 0;
+        for (int l = 0; l < kSlice && sl * kSlice + l < n_own; ++l) {
+          const int c = S.csell.base[sl] + s * kSlice + l;
+          if (cfac[c] >= 0 && chome[c] != c) {
+            away[na] = chome[c];
+            awaycell[na++] = c;
+          }
+        }
+        if (na && distinct_count(away, na, [](int p) { return p >> 3; }) > kShareMaxLinesFactor) {
+          for (int a = 0; a < na; ++a) chome[awaycell[a]] = awaycell[a];  // keep a copy in the own cell
+          S.n_factor_copies += na;
+        }
+      }
+  }
+  for (int c = 0; c < CS; ++c) {
+    if (cfac[c] < 0) continue;
+    const int k = cfac[c];
+    S.c_code[c] |= (uint32_t)chome[c] << 3;
+    S.c_col[c] = S.local_of(ccol[c]);
+    if (chome[c] == c) {  // data cell
+      S.f_src[c] = k;
+      S.f_i[c] = S.local_of(ei[k]);
+      S.f_j[c] = S.local_of(ej[k]);
+      S.f_count[c] = (S.c_code[c] & 4u) ? 1 : 0;
+    }
+  }
 
-  S.c_col.assign(S.csell.slots, 0);
-  for (int c = 0; c < S.csell.slots; ++c)
-    if (ccol[c] >= 0) S.c_col[c] = S.local_of(ccol[c]);
-
-  // ---- H blocks: one per unordered pair, homed like the factors; block words of the writer rows;
-  //      reference triples (global col, local col, block word) per owned row
-  std::vector<int> bcnt(n_own, 0), rcnt(n_own, 0);
+  // ---- reference lists = unique neighbours per owned row, ascending global column (the
+  //      contribution lists are already in that order)
+  std::vector<int> rcnt(n_own, 0);
   S.max_degree = 0;
   for (int row = 0; row < n_own; ++row) {
-    const int g = v0 + row;
     int last = -1, deg = 0;
     for (int s = 0; s < ccnt[row]; ++s) {
       const int col = ccol[S.csell.pos(row, s)];
       if (col < 0 || col == last) continue;
       last = col;
       ++deg;
-      const int lo = std::min(g, col);
-      const bool writer = (g == lo) || !owned(lo);
-      if (writer) bcnt[row]++;
     }
     rcnt[row] = deg;
     S.max_degree = std::max(S.max_degree, deg);
   }
-  S.bsell.build(bcnt);
   S.rsell.build(rcnt);
-  S.n_pairs = 0;
-  S.nnzo_own = 0;
-  for (int row = 0; row < n_own; ++row) {
-    S.n_pairs += bcnt[row];
-    S.nnzo_own += rcnt[row];
-  }
-  S.r_col.assign(S.rsell.slots, -1);
-  S.r_blk.assign(S.rsell.slots, 0);
-  struct Ref {
-    int gcol, lcol, word;
-  };
+  const int RS = S.rsell.slots;
+  S.r_col.assign(RS, -1);
+  S.r_blk.assign(RS, 0);
   std::vector<int> rptr(n_own + 1, 0);
   for (int row = 0; row < n_own; ++row) rptr[row + 1] = rptr[row] + rcnt[row];
-  std::vector<Ref> refs((size_t)rptr[n_own]);
-  {
-    std::vector<int> rfill(rptr.begin(), rptr.end() - 1);
-    for (int row = 0; row < n_own; ++row) {
-      const int g = v0 + row;
-      int last = -1, nb = 0, bpos = -1;
-      for (int s = 0; s < ccnt[row]; ++s) {
-        const int c = S.csell.pos(row, s);
-        const int col = ccol[c];
-        if (col < 0) continue;
-        const int lo = std::min(g, col);
-        const bool writer = (g == lo) || !owned(lo);
-        if (!writer) continue;
-        const bool head = (col != last);
-        if (head) {
-          last = col;
-          bpos = S.bsell.pos(row, nb++);
-          const int lcol = S.local_of(col);
-          const int hi_row = (g != lo);  // this row is the hi endpoint -> it uses M^T
-          refs[rfill[row]++] = {col, lcol, (bpos << 1) | hi_row};
-          if (owned(col)) {  // the other endpoint is an owned row too: it references the same block
-            const int orow = col - v0;
-            refs[rfill[orow]++] = {g, row, (bpos << 1) | (hi_row ? 0 : 1)};
-          }
-        }
-        S.c_blk[c] = (bpos << 2) | ((g != lo) ? 2 : 0) | (head ? 1 : 0);
+  std::vector<int> nbr((size_t)rptr[n_own]);  // global columns, CSR
+  for (int row = 0; row < n_own; ++row) {
+    int last = -1, w = rptr[row];
+    for (int s = 0; s < ccnt[row]; ++s) {
+      const int col = ccol[S.csell.pos(row, s)];
+      if (col < 0 || col == last) continue;
+      last = col;
+      nbr[w++] = col;
+    }
+  }
+  auto ref_cell = [&](int row, int gcol) {  // block cell of reference (row -> gcol)
+    const int* b = nbr.data() + rptr[row];
+    const int* e = nbr.data() + rptr[row + 1];
+    return S.rsell.pos(row, (int)(std::lower_bound(b, e, gcol) - b));
+  };
+  // The block of pair {a, b} is computed by its writer row: the lo endpoint, or the hi one when lo
+  // belongs to another rank.  The writer's own cell holds it in canonical orientation.
+  std::vector<int> rhome(RS, -1);  // per reference cell: the cell that holds the canonical block
+  S.n_pairs = 0;
+  S.nnzo_own = rptr[n_own];
+  for (int row = 0; row < n_own; ++row) {
+    const int g = v0 + row;
+    for (int s = 0; s < rcnt[row]; ++s) {
+      const int col = nbr[rptr[row] + s];
+      const int cell = S.rsell.pos(row, s);
+      const int lo = std::min(g, col);
+      const bool writer = (g == lo) || !owned(lo);
+      S.r_col[cell] = S.local_of(col);
+      if (writer) {
+        rhome[cell] = cell;
+        S.n_pairs++;
+      } else {
+        rhome[cell] = ref_cell(lo - v0, g);
       }
     }
   }
+  // share or copy, per (slice, slot)
+  std::vector<int> rcopy(RS, -1);  // per home cell: the other row's cell that wants the transposed copy
+  S.n_block_copies = 0;
+  {
+    const int ns = (n_own + kSlice - 1) / kSlice;
+    int away[kSlice], awaycell[kSlice];
+    for (int sl = 0; sl < ns; ++sl)
+      for (int s = 0; s < S.rsell.width[sl]; ++s) {
+        int na = 0;
+        for (int l = 0; l < kSlice && sl * kSlice + l < n_own; ++l) {
+          const int c = S.rsell.base[sl] + s * kSlice + l;
+          if (rhome[c] >= 0 && rhome[c] != c) {
+            away[na] = rhome[c];
+            awaycell[na++] = c;
+          }
+        }
+        if (na && distinct_count(away, na, [](int p) { return p >> 4; }) > kShareMaxLinesBlock) {
+          for (int a = 0; a < na; ++a) {
+            rcopy[away[a]] = awaycell[a];
+            rhome[awaycell[a]] = awaycell[a];
+          }
+          S.n_block_copies += na;
+        }
+      }
+  }
   for (int row = 0; row < n_own; ++row) {
-    std::sort(refs.begin() + rptr[row], refs.begin() + rptr[row + 1], [](const Ref& a, const Ref& b) { return a.gcol < b.gcol; });
+    const int g = v0 + row;
     for (int s = 0; s < rcnt[row]; ++s) {
-      const Ref& f = refs[rptr[row] + s];
-      const int p = S.rsell.pos(row, s);
-      S.r_col[p] = f.lcol;
-      S.r_blk[p] = f.word;
+      const int col = nbr[rptr[row] + s];
+      const int cell = S.rsell.pos(row, s);
+      const int lo = std::min(g, col);
+      const bool writer = (g == lo) || !owned(lo);
+      // writer: canonical block, transposed use iff this row is the hi endpoint
+      // pointer to the lo row's cell: transposed; own transposed copy: plain
+      const int tr = writer ? (g != lo) : (rhome[cell] != cell);
+      S.r_blk[cell] = (rhome[cell] << 1) | tr;
+    }
+  }
+  // block words of the writer rows' contributions
+  for (int row = 0; row < n_own; ++row) {
+    const int g = v0 + row;
+    int last = -1, s_ref = -1;
+    for (int s = 0; s < ccnt[row]; ++s) {
+      const int c = S.csell.pos(row, s);
+      const int col = ccol[c];
+      if (col < 0) continue;
+      const bool head = (col != last);
+      if (head) {
+        last = col;
+        ++s_ref;
+      }
+      const int lo = std::min(g, col);
+      const bool writer = (g == lo) || !owned(lo);
+      if (!writer) continue;
+      const int cell = S.rsell.pos(row, s_ref);
+      S.c_blk[c] = (cell << 2) | ((g != lo) ? 2 : 0) | (head ? 1 : 0);
+      S.c_blk2[c] = rcopy[cell];
     }
   }
 

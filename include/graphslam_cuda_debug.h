@@ -55,6 +55,7 @@ typedef struct gs_emu_result {
   double rel_residual;
   int32_t pcg_iters, pcg_done;
   int32_t n_ghost_total, n_pairs_total, halo_send_total;
+  int32_t n_factor_copies, n_block_copies; /* cells that keep a copy because sharing would not coalesce */
 } gs_emu_result;
 
 /* one outer-iteration body over `world` virtual ranks (1, 2, 4 or 8) on the CPU */

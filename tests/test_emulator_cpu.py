@@ -39,7 +39,8 @@ def emu_run(lib, prob, xyt, world=1, mode=0, lam=1e-5, max_iters=5000, tol=1e-12
     assert rc == 0, rc
     return dict(blocks=blocks, b=b, delta=delta, xyt_new=xnew, chi2=res.chi2, chi2_check=res.chi2_check,
                 chi2_new=res.chi2_new, dHd=res.dHd, db=res.db, rel_residual=res.rel_residual, pcg_iters=res.pcg_iters,
-                pcg_done=res.pcg_done, n_ghost=res.n_ghost_total, n_pairs=res.n_pairs_total, halo=res.halo_send_total)
+                pcg_done=res.pcg_done, n_ghost=res.n_ghost_total, n_pairs=res.n_pairs_total, halo=res.halo_send_total,
+                fcopies=res.n_factor_copies, bcopies=res.n_block_copies)
 
 
 def _check_against_oracle(lib, g, mode=0, world=1, lam=1e-3):
@@ -81,6 +82,15 @@ def test_emulated_multi_rank_matches_oracle_and_is_bitwise_rank_invariant(lib, w
         assert np.array_equal(one[k], many[k]), k                        # not one bit depends on the partition
     for k in ("chi2", "chi2_new", "dHd", "db", "pcg_iters"):
         assert one[k] == many[k], k
+
+
+def test_share_or_copy_decision(lib):
+    """Regular graphs share every block/factor between its two rows (symmetric storage, one DRAM read);
+    irregular ones keep copies where the slice's gather would not coalesce.  Either way the numbers are the same."""
+    reg = _check_against_oracle(lib, synth.config("C3", n=4000))
+    assert reg["bcopies"] == 0 and reg["fcopies"] == 0
+    irr = _check_against_oracle(lib, synth.config("C4", n=3000))
+    assert irr["bcopies"] > 0 and irr["fcopies"] > 0
 
 
 def test_emulated_hub_duplicates_and_tiny_graphs(lib):
