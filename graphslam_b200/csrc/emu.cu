@@ -32,6 +32,7 @@ struct VRank {
     a.cs.base = S.csell.base.data();
     a.cs.width = S.csell.width.data();
     a.c = cw.data();
+    a.c_first = S.c_first.data();
     a.f.ij = eij.data();
     a.f.zt = zt.data();
     a.f.zr = zr.data();
@@ -171,7 +172,7 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
     const int FS = S.csell.slots;
     me.eij.assign(FS, make_int2(-1, -1));
     me.cw.resize(S.c_code.size());
-    for (size_t c = 0; c < me.cw.size(); ++c) me.cw[c] = make_int4((int)S.c_code[c], S.c_blk[c], S.c_col[c], S.c_blk2[c]);
+    for (size_t c = 0; c < me.cw.size(); ++c) me.cw[c] = make_int4((int)S.c_code[c], S.c_blk[c], S.c_col[c], 0);
     me.refs.resize(S.r_col.size());
     for (size_t c = 0; c < me.refs.size(); ++c) me.refs[c] = make_int2(S.r_col[c], S.r_blk[c]);
     me.zt.assign(FS, make_double2(0, 0));

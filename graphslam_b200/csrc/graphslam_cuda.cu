@@ -91,7 +91,6 @@ struct gs_graph {
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
   bool use_graph = true;
-  bool asm_occ3 = false;   // experiment switch (GS_ASM_OCC=3): 3 CTAs/SM for k_assemble at the cost of spills
 
   // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
   std::vector<uint64_t> keys;
@@ -124,7 +123,7 @@ struct gs_graph {
   DevBuf<int2> d_eij, d_refs;
   DevBuf<int4> d_cw;
   DevBuf<double2> d_zt, d_zr, d_o01, d_o23, d_o45;
-  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_rbase, d_rwidth, d_segtile, d_send_rows;
+  DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_rbase, d_rwidth, d_segtile, d_send_rows, d_cfirst;
   DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part, d_segs, d_sendbuf;
   DevBuf<Scalars> d_sc;
   DevBuf<unsigned int> d_counter;
@@ -203,6 +202,7 @@ gs::AsmView asm_view(gs_graph* g, const double4* pose) {
   a.cs.base = g->d_cbase.p;
   a.cs.width = g->d_cwidth.p;
   a.c = g->d_cw.p;
+  a.c_first = g->d_cfirst.p;
   a.f.ij = g->d_eij.p;
   a.f.zt = g->d_zt.p;
   a.f.zr = g->d_zr.p;
@@ -455,7 +455,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = upload(g, g->d_cwidth, S.csell.width)) return s;
   {
     std::vector<int4> cw(S.c_code.size());
-    for (size_t q = 0; q < cw.size(); ++q) cw[q] = make_int4((int)S.c_code[q], S.c_blk[q], S.c_col[q], S.c_blk2[q]);
+    for (size_t q = 0; q < cw.size(); ++q) cw[q] = make_int4((int)S.c_code[q], S.c_blk[q], S.c_col[q], 0);
     if (gs_status s = upload(g, g->d_cw, cw)) return s;
     std::vector<int2> refs(S.r_col.size());
     for (size_t q = 0; q < refs.size(); ++q) refs[q] = make_int2(S.r_col[q], S.r_blk[q]);
@@ -465,6 +465,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = upload(g, g->d_rbase, S.rsell.base)) return s;
   if (gs_status s = upload(g, g->d_rwidth, S.rsell.width)) return s;
   if (gs_status s = upload(g, g->d_segtile, segtile)) return s;
+  if (gs_status s = upload(g, g->d_cfirst, S.c_first)) return s;
   if (gs_status s = upload(g, g->d_send_rows, S.send_rows)) return s;
   const size_t n3 = 3 * (size_t)std::max(S.n_own, 1), nl3 = 3 * (size_t)std::max(g->n_loc, 1);
   g->hstride = (size_t)std::max(S.rsell.slots, 1);
@@ -525,11 +526,9 @@ gs_status launch_assemble(gs_graph* g) {
   const gs::AsmView av = asm_view(g, g->d_pose.p);
   const gs::ReduceCtx rc = reduce_ctx(g, 2);
   if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT)
-    gs::k_assemble<1, 2><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
-  else if (g->asm_occ3)
-    gs::k_assemble<0, 3><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+    gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
   else
-    gs::k_assemble<0, 2><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+    gs::k_assemble<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
   g->launches += 1;
   if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
   if (g->prm.diagonal_damping) {
@@ -620,8 +619,6 @@ gs_status create_common(gs_graph* g) {
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   const char* env = std::getenv("GS_PCG_GRAPH");
   g->use_graph = !(env && env[0] == '0');
-  env = std::getenv("GS_ASM_OCC");
-  g->asm_occ3 = env && env[0] == '3';
   return GS_OK;
 }
 

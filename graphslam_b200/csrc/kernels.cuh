@@ -186,8 +186,8 @@ __global__ void k_scalars(const double* segs, int nq, int spr, int op, Scalars* 
 }
 
 // ------------------------------------------------------------------------------------------------
-template <int MODE, int OCC>
-__global__ void __launch_bounds__(kThreads, OCC) k_assemble(const AsmView a, const ReduceCtx c) {
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 2) k_assemble(const AsmView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
   const int r = blockIdx.x * kThreads + threadIdx.x;
@@ -207,6 +207,9 @@ __global__ void __launch_bounds__(kThreads) k_chi2(const AsmView a, const Reduce
 
 // mode 0: PCG step (lambda from sc, honours sc->done, result -> sc->pAp)
 // mode 1: plain undamped product (result -> sc->dot)
+// (A variant that staged several slots per thread through shared memory with cp.async was measured
+//  slower on C3 — 123-165 us against 101 us — because the staging buffers cost occupancy and L1; see
+//  DESIGN.md "What did not help".)
 __global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const double* __restrict__ p, double* __restrict__ y,
                                                     const ReduceCtx c, int mode) {
   __shared__ double red[8];

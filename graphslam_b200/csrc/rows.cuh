@@ -60,8 +60,9 @@ struct PriorView {
 // ------------------------------------------------------------------------------------------------
 struct AsmView {
   SellView cs;
-  const int4* c;         // per contribution: (code, block word, local index of the other vertex, cell wanting
-                         // the transposed block copy or -1); code == kPadCode: padding slot
+  const int4* c;         // per contribution: (code, block word, local index of the other vertex, unused);
+                         // code == kPadCode: padding slot
+  const int* c_first;    // per row: first slot of its counting cells (factors with this row as lo endpoint)
   FactorView f;
   PriorView pr;
   const double4* pose;   // n_own + n_ghost
@@ -107,16 +108,9 @@ GS_HD void diag_pieces(const Sym3& O, const Mat3& Ar, const double e[3], double 
   for (int r = 0; r < 3; ++r) bv[r] = W[0 + r] * e[0] + W[3 + r] * e[1] + W[6 + r] * e[2];
 }
 
-// the block goes to its own cell and, transposed, to the cell of the other row when that row keeps a copy
-GS_HD void store_block(double* Ho, size_t hstride, int pos, int pos2, const double M[9]) {
+GS_HD void store_block(double* Ho, size_t hstride, int pos, const double M[9]) {
 #pragma unroll
   for (int k = 0; k < 9; ++k) Ho[(size_t)k * hstride + pos] = M[k];
-  if (pos2 >= 0) {
-#pragma unroll
-    for (int q = 0; q < 3; ++q)
-#pragma unroll
-      for (int t = 0; t < 3; ++t) Ho[(size_t)(3 * q + t) * hstride + pos2] = M[3 * t + q];
-  }
 }
 
 // One factor side under GTSAM's default Jacobians (A_i = [[-c,-s,dt1],[s,-c,dt2],[0,0,-1]], A_j = I):
@@ -165,107 +159,136 @@ GS_HD void side_default(const double4 pi, const double4 pj, const double2 zt, co
   }
 }
 
+// running state of one row during assembly
+struct AsmAcc {
+  double dg[6];   // diagonal block, symmetric
+  double bv[3];   // gradient
+  double acc[9];  // off-diagonal block being summed (a run of factors of one vertex pair)
+  double chi2;
+  int open;       // cell of the block in acc, -1 none
+};
+
+GS_HD void asm_begin(AsmAcc& A) {
+#pragma unroll
+  for (int k = 0; k < 6; ++k) A.dg[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) A.bv[k] = 0.0;
+  A.chi2 = 0.0;
+  A.open = -1;
+}
+
+// one BetweenFactor side: code/cb are the contribution's words, prow/pcol the poses of the row's and the
+// other vertex, (zt, zr, o01, o23, o45) the factor
+template <int MODE>
+GS_HD void asm_between(AsmAcc& A, uint32_t code, int cb, const double4 prow, const double4 pcol, const double2 zt,
+                       const double2 zr, const double2 o01, const double2 o23, const double2 o45, double* Ho,
+                       size_t hstride) {
+  const Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
+  const bool row_is_i = ((code & 3u) == 0);
+  const double4 pi = row_is_i ? prow : pcol, pj = row_is_i ? pcol : prow;
+  // row is the hi endpoint of the pair (cb & 2): the lo Jacobian is the other vertex's
+  const bool lo_is_i = row_is_i != ((cb & 2) != 0);
+  double M[9];
+  if (MODE == 0) {
+    SideDefault S;
+    side_default(pi, pj, zt, zr, O, S);
+    const double* W = S.W;
+    if (row_is_i) {
+      A.dg[0] += S.s * W[3] - S.c * W[0];
+      A.dg[1] += S.s * W[4] - S.c * W[1];
+      A.dg[2] += S.s * W[5] - S.c * W[2];
+      A.dg[3] += -(S.s * W[1]) - S.c * W[4];
+      A.dg[4] += -(S.s * W[2]) - S.c * W[5];
+      A.dg[5] += (S.dt1 * W[2] + S.dt2 * W[5]) - W[8];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) A.bv[k] += (W[k] * S.e[0] + W[3 + k] * S.e[1]) + W[6 + k] * S.e[2];
+    } else {
+      A.dg[0] += O.a00; A.dg[1] += O.a01; A.dg[2] += O.a02;
+      A.dg[3] += O.a11; A.dg[4] += O.a12; A.dg[5] += O.a22;
+      A.bv[0] += (O.a00 * S.e[0] + O.a01 * S.e[1]) + O.a02 * S.e[2];
+      A.bv[1] += (O.a01 * S.e[0] + O.a11 * S.e[1]) + O.a12 * S.e[2];
+      A.bv[2] += (O.a02 * S.e[0] + O.a12 * S.e[1]) + O.a22 * S.e[2];
+    }
+    if (code & 4u) A.chi2 += quad_form(O, S.e);
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+#pragma unroll
+      for (int t = 0; t < 3; ++t) M[3 * q + t] = lo_is_i ? W[3 * t + q] : W[3 * q + t];
+  } else {
+    BetweenLin L;
+    between_linearize<MODE>(pi, pj, zt, zr, L);
+    double d6[6], b3[3];
+    diag_pieces(O, row_is_i ? L.Ai : L.Aj, L.e, d6, b3);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) A.dg[k] += d6[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) A.bv[k] += b3[k];
+    if (code & 4u) A.chi2 += quad_form(O, L.e);
+    if (cb >= 0) off_block(O, lo_is_i ? L.Ai : L.Aj, lo_is_i ? L.Aj : L.Ai, M);
+  }
+  if (cb >= 0) {
+    if (cb & 1) {
+      if (A.open >= 0) store_block(Ho, hstride, A.open, A.acc);
+      A.open = cb >> 2;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) A.acc[k] = M[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) A.acc[k] += M[k];
+    }
+  }
+}
+
+template <int MODE>
+GS_HD void asm_prior(AsmAcc& A, const double4 prow, const double4 pp, const double* om) {
+  const Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
+  double e[3], d6[6], b3[3];
+  Mat3 J;
+  prior_linearize<MODE>(prow, pp, e, J);
+  diag_pieces(O, J, e, d6, b3);
+  A.chi2 += quad_form(O, e);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) A.dg[k] += d6[k];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) A.bv[k] += b3[k];
+}
+
+GS_HD double asm_end(AsmAcc& A, const AsmView& a, int r) {
+  if (A.open >= 0) store_block(a.Ho, a.hstride, A.open, A.acc);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) a.Hd[(size_t)k * a.n_own + r] = A.dg[k];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) a.b[3 * (size_t)r + k] = A.bv[k];
+  return A.chi2;
+}
+
 // returns the row's chi2 share (factors it is the counting side of, and its priors)
 template <int MODE>
 GS_HD double assemble_row(const AsmView& a, int r) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
-  double dg[6] = {0, 0, 0, 0, 0, 0}, bv[3] = {0, 0, 0}, acc[9];
-  double chi2 = 0.0;
-  int open = -1, open2 = -1;
+  AsmAcc A;
+  asm_begin(A);
   const double4 prow = ldg(a.pose + r);
   // w is the same for the 32 rows of a slice.  The next slot's words are fetched while this slot's
   // factor and pose are in flight; each slot is then one dependent round trip (factor + other pose).
   int4 cw = w > 0 ? ldg(a.c + base) : make_int4((int)kPadCode, -1, 0, -1);
   for (int s = 0; s < w; ++s) {
     const int4 cur = cw;
-    const int col = cur.z;
     if (s + 1 < w) cw = ldg(a.c + base + (s + 1) * kSlice);
     const uint32_t code = (uint32_t)cur.x;
     if (code == kPadCode) continue;
-    const int cb = cur.y;
-    const int kind = code & 3u;
     const int idx = (int)(code >> 3);
-    if (kind < 2) {
+    if ((code & 3u) < 2) {
       const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
       const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
-      const double4 pcol = ldg(a.pose + col);
-      const Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
-      const bool row_is_i = (kind == 0);
-      const double4 pi = row_is_i ? prow : pcol, pj = row_is_i ? pcol : prow;
-      // row is the hi endpoint of the pair (cb & 2): the lo Jacobian is the other vertex's
-      const bool lo_is_i = row_is_i != ((cb & 2) != 0);
-      double M[9];
-      if (MODE == 0) {
-        SideDefault S;
-        side_default(pi, pj, zt, zr, O, S);
-        const double* W = S.W;
-        if (row_is_i) {
-          dg[0] += S.s * W[3] - S.c * W[0];
-          dg[1] += S.s * W[4] - S.c * W[1];
-          dg[2] += S.s * W[5] - S.c * W[2];
-          dg[3] += -(S.s * W[1]) - S.c * W[4];
-          dg[4] += -(S.s * W[2]) - S.c * W[5];
-          dg[5] += (S.dt1 * W[2] + S.dt2 * W[5]) - W[8];
-#pragma unroll
-          for (int k = 0; k < 3; ++k) bv[k] += (W[k] * S.e[0] + W[3 + k] * S.e[1]) + W[6 + k] * S.e[2];
-        } else {
-          dg[0] += O.a00; dg[1] += O.a01; dg[2] += O.a02;
-          dg[3] += O.a11; dg[4] += O.a12; dg[5] += O.a22;
-          bv[0] += (O.a00 * S.e[0] + O.a01 * S.e[1]) + O.a02 * S.e[2];
-          bv[1] += (O.a01 * S.e[0] + O.a11 * S.e[1]) + O.a12 * S.e[2];
-          bv[2] += (O.a02 * S.e[0] + O.a12 * S.e[1]) + O.a22 * S.e[2];
-        }
-        if (code & 4u) chi2 += quad_form(O, S.e);
-#pragma unroll
-        for (int q = 0; q < 3; ++q)
-#pragma unroll
-          for (int t = 0; t < 3; ++t) M[3 * q + t] = lo_is_i ? W[3 * t + q] : W[3 * q + t];
-      } else {
-        BetweenLin L;
-        between_linearize<MODE>(pi, pj, zt, zr, L);
-        double d6[6], b3[3];
-        diag_pieces(O, row_is_i ? L.Ai : L.Aj, L.e, d6, b3);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) dg[k] += d6[k];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) bv[k] += b3[k];
-        if (code & 4u) chi2 += quad_form(O, L.e);
-        if (cb >= 0) off_block(O, lo_is_i ? L.Ai : L.Aj, lo_is_i ? L.Aj : L.Ai, M);
-      }
-      if (cb >= 0) {
-        if (cb & 1) {
-          if (open >= 0) store_block(a.Ho, a.hstride, open, open2, acc);
-          open = cb >> 2;
-          open2 = cur.w;
-#pragma unroll
-          for (int k = 0; k < 9; ++k) acc[k] = M[k];
-        } else {
-#pragma unroll
-          for (int k = 0; k < 9; ++k) acc[k] += M[k];
-        }
-      }
+      const double4 pcol = ldg(a.pose + cur.z);
+      asm_between<MODE>(A, code, cur.y, prow, pcol, zt, zr, o01, o23, o45, a.Ho, a.hstride);
     } else {
-      const double4 pp = ldg(a.pr.pose + idx);
-      const double* om = a.pr.om + 6 * idx;
-      const Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-      double e[3], d6[6], b3[3];
-      Mat3 A;
-      prior_linearize<MODE>(prow, pp, e, A);
-      diag_pieces(O, A, e, d6, b3);
-      chi2 += quad_form(O, e);
-#pragma unroll
-      for (int k = 0; k < 6; ++k) dg[k] += d6[k];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) bv[k] += b3[k];
+      asm_prior<MODE>(A, prow, ldg(a.pr.pose + idx), a.pr.om + 6 * idx);
     }
   }
-  if (open >= 0) store_block(a.Ho, a.hstride, open, open2, acc);
-#pragma unroll
-  for (int k = 0; k < 6; ++k) a.Hd[(size_t)k * a.n_own + r] = dg[k];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) a.b[3 * (size_t)r + k] = bv[k];
-  return chi2;
+  return asm_end(A, a, r);
 }
 
 // graph.error contribution of row r at `pose`: its priors, then the factors whose counting side is
@@ -291,10 +314,11 @@ GS_HD double chi2_row(const AsmView& a, int r) {
   }
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
+  const int first = a.c_first[r];
 #pragma unroll 4
   for (int s = 0; s < w; ++s) {
     const int idx = base + s * kSlice;
-    const int2 ij = ldg(a.f.ij + idx);
+    const int2 ij = s >= first ? ldg(a.f.ij + idx) : make_int2(-1, -1);
     if (ij.x >= 0 && !(ij.x & kNoCountBit)) {
       const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
       const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
@@ -320,6 +344,27 @@ struct SpmvView {
   int n_own;
 };
 
+// one neighbour block: y += H_rc p_c, with the stored block used transposed when `tr`
+GS_HD void spmv_slot(const double h[9], double px, double py, double pz, bool tr, double& y0, double& y1, double& y2) {
+  const double a01 = tr ? h[3] : h[1], a02 = tr ? h[6] : h[2], a10 = tr ? h[1] : h[3];
+  const double a12 = tr ? h[7] : h[5], a20 = tr ? h[2] : h[6], a21 = tr ? h[5] : h[7];
+  y0 += (h[0] * px + a01 * py) + a02 * pz;
+  y1 += (a10 * px + h[4] * py) + a12 * pz;
+  y2 += (a20 * px + a21 * py) + h[8] * pz;
+}
+
+// diagonal block, damping, store, and the row's share of p.y ; d = (00 01 02 11 12 22), l = damping per component
+GS_HD double spmv_finish(const double d[6], const double l[3], double px, double py, double pz, double y0, double y1,
+                         double y2, double* y, size_t rr) {
+  y0 = (y0 + ((d[0] * px + d[1] * py) + d[2] * pz)) + l[0] * px;
+  y1 = (y1 + ((d[1] * px + d[3] * py) + d[4] * pz)) + l[1] * py;
+  y2 = (y2 + ((d[2] * px + d[4] * py) + d[5] * pz)) + l[2] * pz;
+  y[3 * rr] = y0;
+  y[3 * rr + 1] = y1;
+  y[3 * rr + 2] = y2;
+  return (px * y0 + py * y1) + pz * y2;
+}
+
 GS_HD double spmv_row(const SpmvView& a, const double* p, double* y, int r, double lambda) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
@@ -331,37 +376,24 @@ GS_HD double spmv_row(const SpmvView& a, const double* p, double* y, int r, doub
     const int2 ref = nref;
     if (s + 1 < w) nref = ldg(a.refs + base + (s + 1) * kSlice);
     if (ref.x >= 0) {
-      const int col = ref.x, rb = ref.y;
-      const double* h = a.Ho + (rb >> 1);
-      const double h0 = ldg(h), h1 = ldg(h + a.hstride), h2 = ldg(h + 2 * a.hstride);
-      const double h3 = ldg(h + 3 * a.hstride), h4 = ldg(h + 4 * a.hstride), h5 = ldg(h + 5 * a.hstride);
-      const double h6 = ldg(h + 6 * a.hstride), h7 = ldg(h + 7 * a.hstride), h8 = ldg(h + 8 * a.hstride);
-      const double px = p[3 * (size_t)col], py = p[3 * (size_t)col + 1], pz = p[3 * (size_t)col + 2];
-      const bool tr = rb & 1;
-      const double a01 = tr ? h3 : h1, a02 = tr ? h6 : h2, a10 = tr ? h1 : h3;
-      const double a12 = tr ? h7 : h5, a20 = tr ? h2 : h6, a21 = tr ? h5 : h7;
-      y0 += (h0 * px + a01 * py) + a02 * pz;
-      y1 += (a10 * px + h4 * py) + a12 * pz;
-      y2 += (a20 * px + a21 * py) + h8 * pz;
+      const double* hp = a.Ho + (ref.y >> 1);
+      double h[9];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * a.hstride);
+      const size_t col = (size_t)ref.x;
+      spmv_slot(h, p[3 * col], p[3 * col + 1], p[3 * col + 2], ref.y & 1, y0, y1, y2);
     }
   }
   const size_t n = (size_t)a.n_own, rr = (size_t)r;
-  const double d00 = ldg(a.Hd + rr), d01 = ldg(a.Hd + n + rr), d02 = ldg(a.Hd + 2 * n + rr);
-  const double d11 = ldg(a.Hd + 3 * n + rr), d12 = ldg(a.Hd + 4 * n + rr), d22 = ldg(a.Hd + 5 * n + rr);
-  const double px = p[3 * rr], py = p[3 * rr + 1], pz = p[3 * rr + 2];
-  double l0 = lambda, l1 = lambda, l2 = lambda;
+  double d[6], l[3] = {lambda, lambda, lambda};
+#pragma unroll
+  for (int k = 0; k < 6; ++k) d[k] = ldg(a.Hd + (size_t)k * n + rr);
   if (a.dscale) {
-    l0 *= a.dscale[3 * rr];
-    l1 *= a.dscale[3 * rr + 1];
-    l2 *= a.dscale[3 * rr + 2];
+    l[0] *= a.dscale[3 * rr];
+    l[1] *= a.dscale[3 * rr + 1];
+    l[2] *= a.dscale[3 * rr + 2];
   }
-  y0 = (y0 + ((d00 * px + d01 * py) + d02 * pz)) + l0 * px;
-  y1 = (y1 + ((d01 * px + d11 * py) + d12 * pz)) + l1 * py;
-  y2 = (y2 + ((d02 * px + d12 * py) + d22 * pz)) + l2 * pz;
-  y[3 * rr] = y0;
-  y[3 * rr + 1] = y1;
-  y[3 * rr + 2] = y2;
-  return (px * y0 + py * y1) + pz * y2;
+  return spmv_finish(d, l, p[3 * rr], p[3 * rr + 1], p[3 * rr + 2], y0, y1, y2, y, rr);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -179,7 +179,7 @@ struct LocalStructure {
   Sell csell;
   std::vector<uint32_t> c_code;       // (factor cell to read << 3) | count << 2 | kind ; kPadCode padding
   std::vector<int> c_blk;             // -1, or (block cell << 2) | (row is hi endpoint << 1) | head
-  std::vector<int> c_blk2;            // -1, or block cell of the other row that wants the transposed copy
+  std::vector<int> c_first;           // per owned row: first slot whose cell is a counting side (col > row)
   std::vector<int> c_col;             // local index of the other vertex (0 for priors/padding)
   std::vector<int> f_src;             // factor cell -> caller's factor index, -1 if the cell holds no data
   std::vector<int> f_i, f_j;          // local vertex index of id_1 / id_2 per data cell (-1 otherwise)
@@ -273,7 +273,6 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   const int CS = S.csell.slots;
   S.c_code.assign(CS, kPadCode);
   S.c_blk.assign(CS, -1);
-  S.c_blk2.assign(CS, -1);
   S.c_col.assign(CS, 0);
   S.f_src.assign(CS, -1);
   S.f_i.assign(CS, -1);
@@ -403,7 +402,6 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
     }
   }
   // share or copy, per (slice, slot)
-  std::vector<int> rcopy(RS, -1);  // per home cell: the other row's cell that wants the transposed copy
   S.n_block_copies = 0;
   {
     const int ns = (n_own + kSlice - 1) / kSlice;
@@ -419,10 +417,7 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
           }
         }
         if (na && distinct_count(away, na, [](int p) { return p >> 4; }) > kShareMaxLinesBlock) {
-          for (int a = 0; a < na; ++a) {
-            rcopy[away[a]] = awaycell[a];
-            rhome[awaycell[a]] = awaycell[a];
-          }
+          for (int a = 0; a < na; ++a) rhome[awaycell[a]] = awaycell[a];  // this row computes its own copy
           S.n_block_copies += na;
         }
       }
@@ -432,18 +427,23 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
     for (int s = 0; s < rcnt[row]; ++s) {
       const int col = nbr[rptr[row] + s];
       const int cell = S.rsell.pos(row, s);
-      const int lo = std::min(g, col);
-      const bool writer = (g == lo) || !owned(lo);
-      // writer: canonical block, transposed use iff this row is the hi endpoint
-      // pointer to the lo row's cell: transposed; own transposed copy: plain
-      const int tr = writer ? (g != lo) : (rhome[cell] != cell);
-      S.r_blk[cell] = (rhome[cell] << 1) | tr;
+      // every stored block is canonical (lo orientation): the hi row uses it transposed, whether
+      // it reads the lo row's cell or its own copy
+      S.r_blk[cell] = (rhome[cell] << 1) | (g != std::min(g, col) ? 1 : 0);
     }
   }
-  // block words of the writer rows' contributions
+  // block words of the contributions whose row computes the pair's block into its own cell
+  S.c_first.assign(std::max(n_own, 1), 0);
   for (int row = 0; row < n_own; ++row) {
     const int g = v0 + row;
     int last = -1, s_ref = -1;
+    int first = ccnt[row];
+    for (int s = ccnt[row] - 1; s >= 0; --s) {
+      const int col = ccol[S.csell.pos(row, s)];
+      if (col > g) first = s;
+      else break;
+    }
+    S.c_first[row] = first;
     for (int s = 0; s < ccnt[row]; ++s) {
       const int c = S.csell.pos(row, s);
       const int col = ccol[c];
@@ -454,11 +454,9 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
         ++s_ref;
       }
       const int lo = std::min(g, col);
-      const bool writer = (g == lo) || !owned(lo);
-      if (!writer) continue;
       const int cell = S.rsell.pos(row, s_ref);
+      if (rhome[cell] != cell) continue;  // the lo row's cell is shared
       S.c_blk[c] = (cell << 2) | ((g != lo) ? 2 : 0) | (head ? 1 : 0);
-      S.c_blk2[c] = rcopy[cell];
     }
   }
 
