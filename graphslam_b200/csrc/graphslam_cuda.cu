@@ -27,6 +27,7 @@
 #include "../../include/graphslam_cuda.h"
 #include "comm.hpp"
 #include "kernels.cuh"
+#include "kernels_p2p.cuh"
 
 namespace {
 
@@ -91,6 +92,21 @@ struct gs_graph {
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
   bool use_graph = true;
+  // peer-memory path (world > 1): collectives fused into the PCG kernels over NVLink
+  bool p2p_wanted = true;                 // GS_P2P=0 keeps the NCCL-per-operation path
+  bool p2p = false;                       // windows exchanged, peer-memory kernels in use
+  char* win = nullptr;                    // this rank's exported window: header + p
+  size_t win_bytes = 0;
+  int win_generation = 0;
+  char* peer_win[gs::kMaxRanks] = {nullptr};   // peer mappings (allocation base + offset)
+  void* peer_base[gs::kMaxRanks] = {nullptr};  // what cudaIpcOpenMemHandle returned
+  int peer_generation[gs::kMaxRanks] = {0};
+  unsigned int nbr_mask = 0;
+  DevBuf<unsigned int> d_seq;             // [0] sequence base, [1] ticket
+  DevBuf<int> d_hp_tile, d_hp_row;
+  DevBuf<double*> d_hp_dst;
+  DevBuf<char> d_xchg;
+  double* pvec = nullptr;                 // direction vector p: d_p, or the window's vector
 
   // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
   std::vector<uint64_t> keys;
@@ -242,7 +258,7 @@ gs::PcgView pcg_view(gs_graph* g) {
   a.x = g->d_x.p;
   a.r = g->d_r.p;
   a.z = g->d_z.p;
-  a.p = g->d_p.p;
+  a.p = g->pvec;
   a.Ap = g->d_Ap.p;
   a.n_own = g->n_own;
   return a;
@@ -292,11 +308,68 @@ gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode) {
   return finish_reduce(g, 1, mode == 0 ? gs::OP_PAP : gs::OP_DOT);
 }
 
-gs_status launch_pcg_iteration(gs_graph* g) {
-  if (gs_status s = launch_spmv(g, g->d_p.p, g->d_Ap.p, 0)) return s;
-  gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
-  if (gs_status s = finish_reduce(g, 2, gs::OP_UPDATE)) return s;
-  gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->n_own);
+template <typename T>
+gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
+  GS_CUDA(g, d.alloc(std::max<size_t>(h.size(), 1)));
+  if (!h.empty())
+    GS_CUDA(g, cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, g->stream));
+  g->h2d_bytes += sizeof(T) * (double)h.size();
+  return GS_OK;
+}
+
+gs::P2PCtx p2p_ctx(gs_graph* g, unsigned int k_local) {
+  gs::P2PCtx x;
+  for (int q = 0; q < gs::kMaxRanks; ++q) x.win[q] = reinterpret_cast<gs::P2PWindow*>(g->peer_win[q]);
+  x.win[g->rank] = reinterpret_cast<gs::P2PWindow*>(g->win);
+  x.world = g->world;
+  x.rank = g->rank;
+  x.spr = gs::kSegments / g->world;
+  x.nbr_mask = g->nbr_mask;
+  x.seq_base = g->d_seq.p;
+  x.k_local = k_local;
+  x.ticket = g->d_seq.p + 1;
+  x.spin_limit = 2000000000LL;
+  return x;
+}
+
+// one stage of a PCG iteration (0: SpMV + p.Ap, 1: x/r/z update + r.z, r.r, 2: direction);
+// k_local = the iteration's position in the batch (peer-memory path only)
+gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
+  if (g->p2p) {
+    const gs::P2PCtx x = p2p_ctx(g, k_local);
+    if (stage == 0) {
+      gs::k_spmv_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->pvec, g->d_Ap.p, reduce_ctx(g, 0), x);
+    } else if (stage == 1) {
+      gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
+    } else {
+      gs::HaloPush h;
+      h.tile_ptr = g->d_hp_tile.p;
+      h.row = g->d_hp_row.p;
+      h.dst = g->d_hp_dst.p;
+      gs::k_dir_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x, h);
+    }
+    return GS_OK;
+  }
+  if (stage == 0) return launch_spmv(g, g->pvec, g->d_Ap.p, 0);
+  if (stage == 1) {
+    gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
+    return finish_reduce(g, 2, gs::OP_UPDATE);
+  }
+  gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->pvec, g->d_sc.p, 3 * g->n_own);
+  return GS_OK;
+}
+
+gs_status launch_pcg_iteration(gs_graph* g, unsigned int k_local) {
+  for (int stage = 0; stage < 3; ++stage)
+    if (gs_status s = launch_pcg_stage(g, stage, k_local)) return s;
+  return GS_OK;
+}
+
+// a batch of iterations; the peer-memory path then moves the sequence base
+gs_status launch_pcg_batch(gs_graph* g, int n) {
+  for (int it = 0; it < n; ++it)
+    if (gs_status s = launch_pcg_iteration(g, (unsigned int)it)) return s;
+  if (g->p2p) gs::k_p2p_advance<<<1, 32, 0, g->stream>>>(g->d_seq.p, (unsigned int)n);
   return GS_OK;
 }
 
@@ -305,13 +378,130 @@ gs_status capture_pcg_graph(gs_graph* g) {
   if (!g->use_graph) return GS_OK;
   const int64_t keep = g->launches;
   GS_CUDA(g, cudaStreamBeginCapture(g->stream, cudaStreamCaptureModeThreadLocal));
-  gs_status rc = GS_OK;
-  for (int it = 0; it < kPcgBatch && rc == GS_OK; ++it) rc = launch_pcg_iteration(g);
+  const gs_status rc = launch_pcg_batch(g, kPcgBatch);
   cudaError_t ce = cudaStreamEndCapture(g->stream, &g->pcg_graph);
   g->launches = keep;
   if (rc != GS_OK) return rc;
   GS_CUDA(g, ce);
   GS_CUDA(g, cudaGraphInstantiate(&g->pcg_exec, g->pcg_graph, 0));
+  return GS_OK;
+}
+
+// ---- peer-memory window management ---------------------------------------------------------------
+struct XchgRecord {            // what every rank tells every other rank at prepare time (128 bytes)
+  cudaIpcMemHandle_t handle;   // 64
+  long long offset;            // window pointer - allocation base
+  int generation;              // bumps when the window is reallocated
+  int will_realloc;
+  int n_own;
+  int ghost_off[gs::kMaxRanks];  // [source rank] first ghost slot filled by that rank
+  int pad[3];
+};
+static_assert(sizeof(XchgRecord) == 128, "XchgRecord must be 128 bytes");
+
+long long allocation_offset(void* ptr) {
+  // cudaIpcOpenMemHandle maps the whole underlying allocation: find our offset inside it
+  typedef int (*Fn)(unsigned long long*, size_t*, unsigned long long);
+  static Fn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    if (void* h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL)) fn = (Fn)dlsym(h, "cuMemGetAddressRange_v2");
+  }
+  if (!fn) return 0;
+  unsigned long long base = 0;
+  size_t size = 0;
+  if (fn(&base, &size, (unsigned long long)(uintptr_t)ptr) != 0) return 0;
+  return (long long)((unsigned long long)(uintptr_t)ptr - base);
+}
+
+// all-gather of one 128-byte record per rank (NCCL, through a small device buffer)
+gs_status exchange_records(gs_graph* g, const XchgRecord& mine, std::vector<XchgRecord>& all) {
+  const size_t rec = sizeof(XchgRecord);
+  GS_CUDA(g, g->d_xchg.alloc(rec * gs::kMaxRanks));
+  GS_CUDA(g, cudaMemcpyAsync(g->d_xchg.p + rec * g->rank, &mine, rec, cudaMemcpyHostToDevice, g->stream));
+  GS_NCCL(g, gs::nccl().AllGather(g->d_xchg.p + rec * g->rank, g->d_xchg.p, rec, ncclChar, g->comm, g->stream));
+  all.resize(g->world);
+  GS_CUDA(g, cudaMemcpyAsync(all.data(), g->d_xchg.p, rec * g->world, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  return GS_OK;
+}
+
+void close_peer(gs_graph* g, int q) {
+  if (g->peer_base[q]) cudaIpcCloseMemHandle(g->peer_base[q]);
+  g->peer_base[q] = nullptr;
+  g->peer_win[q] = nullptr;
+}
+
+// (re)build the window, exchange handles, map the peers, and lay out the halo pushes.  Collective.
+gs_status prepare_p2p(gs_graph* g) {
+  const LocalStructure& S = g->S;
+  const size_t need = gs::kWindowHeaderBytes + sizeof(double) * 3 * (size_t)std::max(g->n_loc, 1);
+  XchgRecord mine;
+  std::memset(&mine, 0, sizeof mine);
+  mine.will_realloc = (need > g->win_bytes) ? 1 : 0;
+  std::vector<XchgRecord> all;
+  // round 1: who reallocates?  close those mappings before anybody frees
+  if (gs_status s = exchange_records(g, mine, all)) return s;
+  for (int q = 0; q < g->world; ++q)
+    if (q != g->rank && all[q].will_realloc) close_peer(g, q);
+  if (gs_status s = exchange_records(g, mine, all)) return s;  // barrier: everybody has closed
+  if (mine.will_realloc) {
+    if (g->win) GS_CUDA(g, cudaFree(g->win));
+    g->win = nullptr;
+    const size_t two_mb = (size_t)2 << 20;
+    g->win_bytes = ((need + need / 4 + two_mb - 1) / two_mb) * two_mb;
+    GS_CUDA(g, cudaMalloc(&g->win, g->win_bytes));
+    GS_CUDA(g, cudaMemsetAsync(g->win, 0, g->win_bytes, g->stream));
+    g->win_generation += 1;
+    // the sequence numbering restarts with the fresh (zeroed) flags on every rank at once?  No: only this
+    // rank's flags are new, so keep counting — stamps only ever need to exceed what a waiter asks for.
+  }
+  g->pvec = reinterpret_cast<double*>(g->win + gs::kWindowHeaderBytes);
+  GS_CUDA(g, cudaMemsetAsync(g->pvec, 0, sizeof(double) * 3 * (size_t)std::max(g->n_loc, 1), g->stream));
+  GS_CUDA(g, cudaIpcGetMemHandle(&mine.handle, g->win));
+  mine.offset = allocation_offset(g->win);
+  mine.generation = g->win_generation;
+  mine.n_own = g->n_own;
+  for (const gs::HaloPeer& hp : S.peers) mine.ghost_off[hp.rank] = hp.ghost_off;
+  if (gs_status s = exchange_records(g, mine, all)) return s;
+  for (int q = 0; q < g->world; ++q) {
+    if (q == g->rank) continue;
+    if (g->peer_base[q] && g->peer_generation[q] == all[q].generation) continue;
+    close_peer(g, q);
+    void* base = nullptr;
+    GS_CUDA(g, cudaIpcOpenMemHandle(&base, all[q].handle, cudaIpcMemLazyEnablePeerAccess));
+    g->peer_base[q] = base;
+    g->peer_win[q] = static_cast<char*>(base) + all[q].offset;
+    g->peer_generation[q] = all[q].generation;
+  }
+  // halo pushes: my k-th send row for rank q lands in q's ghost slot ghost_off_q[me] + k
+  struct Entry {
+    int row;
+    double* dst;
+  };
+  std::vector<Entry> ent;
+  g->nbr_mask = 0;
+  for (const gs::HaloPeer& hp : S.peers) {
+    g->nbr_mask |= 1u << hp.rank;
+    double* peer_p = reinterpret_cast<double*>(g->peer_win[hp.rank] + gs::kWindowHeaderBytes);
+    const size_t slot0 = (size_t)all[hp.rank].n_own + (size_t)all[hp.rank].ghost_off[g->rank];
+    for (int k = 0; k < hp.send_cnt; ++k) ent.push_back({S.send_rows[hp.send_off + k], peer_p + 3 * (slot0 + k)});
+  }
+  std::stable_sort(ent.begin(), ent.end(), [](const Entry& a, const Entry& b) { return a.row < b.row; });
+  const int nt = g->grid_rows;
+  std::vector<int> tile_ptr(nt + 1, 0), rows(ent.size());
+  std::vector<double*> dsts(ent.size());
+  for (size_t e = 0; e < ent.size(); ++e) {
+    rows[e] = ent[e].row;
+    dsts[e] = ent[e].dst;
+    tile_ptr[ent[e].row / gs::kTile + 1]++;
+  }
+  for (int t = 0; t < nt; ++t) tile_ptr[t + 1] += tile_ptr[t];
+  if (gs_status s = upload(g, g->d_hp_tile, tile_ptr)) return s;
+  if (gs_status s = upload(g, g->d_hp_row, rows)) return s;
+  if (gs_status s = upload(g, g->d_hp_dst, dsts)) return s;
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
   return GS_OK;
 }
 
@@ -376,15 +566,6 @@ gs_status upload_values(gs_graph* g) {
   g->h2d_bytes += sizeof(double4) * (double)n;
   g->device_values_valid = true;
   g->system_valid = false;
-  return GS_OK;
-}
-
-template <typename T>
-gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
-  GS_CUDA(g, d.alloc(std::max<size_t>(h.size(), 1)));
-  if (!h.empty())
-    GS_CUDA(g, cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, g->stream));
-  g->h2d_bytes += sizeof(T) * (double)h.size();
   return GS_OK;
 }
 
@@ -481,11 +662,12 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   GS_CUDA(g, g->d_r.alloc(n3));
   GS_CUDA(g, g->d_z.alloc(n3));
   GS_CUDA(g, g->d_p.alloc(nl3));
+  g->pvec = g->d_p.p;
   GS_CUDA(g, g->d_Ap.alloc(n3));
   GS_CUDA(g, g->d_dscale.alloc(n3));
   GS_CUDA(g, g->d_sendbuf.alloc(4 * std::max<size_t>(S.send_rows.size(), 1)));
   GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * nl3, g->stream));
-  GS_CUDA(g, cudaMemsetAsync(g->d_p.p, 0, sizeof(double) * nl3, g->stream));
+  GS_CUDA(g, cudaMemsetAsync(g->pvec, 0, sizeof(double) * nl3, g->stream));
   g->grid_rows = std::max(S.ntiles, 1);
   g->grid_flat3 = (int)((3 * (size_t)S.n_own + gs::kThreads - 1) / gs::kThreads);
   if (g->grid_flat3 < 1) g->grid_flat3 = 1;
@@ -496,8 +678,12 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->device_values_valid = false;
   if (gs_status s = upload_values(g)) return s;
   if (g->world > 1) {
+    if (g->p2p_wanted) {
+      if (gs_status s = prepare_p2p(g)) return s;
+      g->p2p = true;
+    }
     // establish every NCCL connection outside stream capture: one halo exchange per width, one all-gather
-    if (gs_status s = halo_exchange(g, g->d_p.p, 3)) return s;
+    if (gs_status s = halo_exchange(g, g->pvec, 3)) return s;
     if (gs_status s = halo_exchange(g, reinterpret_cast<double*>(g->d_pose_try.p), 4)) return s;
     const size_t chunk = 2 * (size_t)(gs::kSegments / g->world);
     GS_NCCL(g, gs::nccl().AllGather(g->d_segs.p + g->rank * chunk, g->d_segs.p, chunk, ncclDouble, g->comm, g->stream));
@@ -556,8 +742,17 @@ void launch_pcg_setup(gs_graph* g) {
   g->launches += 2;
 }
 
+// peer-memory path: ghost rows of p(0) by the ordinary halo exchange, then mark them valid
+gs_status begin_p2p_solve(gs_graph* g) {
+  if (!g->p2p) return GS_OK;
+  if (gs_status s = halo_exchange(g, g->pvec, 3)) return s;
+  gs::k_p2p_begin<<<1, 32, 0, g->stream>>>(reinterpret_cast<gs::P2PWindow*>(g->win), g->d_seq.p, g->d_sc.p);
+  g->launches += 1;
+  return GS_OK;
+}
+
 int64_t launches_per_pcg_iteration(const gs_graph* g) {
-  if (g->world == 1) return 3;
+  if (g->world == 1 || g->p2p) return 3;
   return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
 }
 
@@ -571,18 +766,19 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
   if (gs_status s = write_scalars(g)) return s;
   launch_pcg_setup(g);
   if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
+  if (gs_status s = begin_p2p_solve(g)) return s;
   GS_CUDA(g, cudaGetLastError());
   const int64_t keep = g->launches;
   for (;;) {
     if (g->pcg_exec) {
       GS_CUDA(g, cudaGraphLaunch(g->pcg_exec, g->stream));
     } else {
-      for (int it = 0; it < kPcgBatch; ++it)
-        if (gs_status s = launch_pcg_iteration(g)) return s;
+      if (gs_status s = launch_pcg_batch(g, kPcgBatch)) return s;
     }
     if (gs_status s = read_scalars(g)) return s;
     if (h->done) break;
   }
+  if (h->done == 4) return g->fail(GS_ENCCL, "a peer rank did not answer within the wait limit (peer-memory PCG)");
   // kernels that did work (the no-op tail of the last batch is not counted)
   g->launches = keep + launches_per_pcg_iteration(g) * (int64_t)h->iters;
   if (iters_out) *iters_out = h->iters;
@@ -619,6 +815,11 @@ gs_status create_common(gs_graph* g) {
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   const char* env = std::getenv("GS_PCG_GRAPH");
   g->use_graph = !(env && env[0] == '0');
+  env = std::getenv("GS_P2P");
+  g->p2p_wanted = !(env && env[0] == '0');
+  GS_CUDA(g, g->d_seq.alloc(2));
+  GS_CUDA(g, cudaMemsetAsync(g->d_seq.p, 0, 2 * sizeof(unsigned int), g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
   return GS_OK;
 }
 
@@ -703,6 +904,15 @@ gs_status gs_destroy(gs_graph* g) {
   if (!g) return GS_EINVAL;
   if (g->stream) cudaStreamSynchronize(g->stream);
   destroy_graph_exec(g);
+  for (int q = 0; q < gs::kMaxRanks; ++q) close_peer(g, q);
+  if (g->comm && g->win) {
+    // nobody frees a window a peer may still have mapped: one last all-gather as a barrier (gs_destroy is collective)
+    XchgRecord mine;
+    std::memset(&mine, 0, sizeof mine);
+    std::vector<XchgRecord> all;
+    exchange_records(g, mine, all);
+  }
+  if (g->win) cudaFree(g->win);
   if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->ev0) cudaEventDestroy(g->ev0);
@@ -1106,21 +1316,20 @@ gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], do
   if (gs_status s = write_scalars(g)) return s;
   launch_pcg_setup(g);
   if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
+  if (gs_status s = begin_p2p_solve(g)) return s;
   for (int w = 0; w < 3; ++w)
-    if (gs_status s = launch_pcg_iteration(g)) return s;  // warm-up
+    if (gs_status s = launch_pcg_iteration(g, (unsigned int)w)) return s;  // warm-up
   std::vector<cudaEvent_t> ev(4 * (size_t)iters);
   for (auto& e : ev) GS_CUDA(g, cudaEventCreate(&e));
   for (int it = 0; it < iters; ++it) {
     cudaEvent_t* e = &ev[4 * (size_t)it];
-    cudaEventRecord(e[0], g->stream);
-    if (gs_status s = launch_spmv(g, g->d_p.p, g->d_Ap.p, 0)) return s;
-    cudaEventRecord(e[1], g->stream);
-    gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
-    if (gs_status s = finish_reduce(g, 2, gs::OP_UPDATE)) return s;
-    cudaEventRecord(e[2], g->stream);
-    gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->d_p.p, g->d_sc.p, 3 * g->n_own);
+    for (int stage = 0; stage < 3; ++stage) {
+      cudaEventRecord(e[stage], g->stream);
+      if (gs_status s = launch_pcg_stage(g, stage, (unsigned int)(3 + it))) return s;
+    }
     cudaEventRecord(e[3], g->stream);
   }
+  if (g->p2p) gs::k_p2p_advance<<<1, 32, 0, g->stream>>>(g->d_seq.p, (unsigned int)(3 + iters));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   GS_CUDA(g, cudaGetLastError());
   double acc[3] = {0, 0, 0};

@@ -32,10 +32,11 @@ struct Scalars {
   double tol2;      // pcg_rel_tol^2
   double chi2;      // k_chi2 / k_assemble result
   double dot;       // k_dot / plain k_spmv result
-  int done;         // 0 running, 1 converged, 2 breakdown (p^T A p <= 0), 3 max iters
+  int done;         // 0 running, 1 converged, 2 breakdown (p^T A p <= 0), 3 max iters, 4 peer wait timed out
   int iters;
   int max_iters;
-  int pad;
+  unsigned int seq0;  // peer-memory path: sequence number of this solve's first iteration
+  double rzv[2];      // peer-memory path: r^T z by iteration parity (reader and writer never share a slot)
 };
 
 enum ReduceOp { OP_PAP = 0, OP_DOT = 1, OP_INIT = 2, OP_UPDATE = 3, OP_CHI2 = 4 };
@@ -113,6 +114,8 @@ __device__ __forceinline__ void apply_scalars(Scalars* sc, int op, double t0, do
       break;
     case OP_INIT:
       sc->rz = t0;
+      sc->rzv[0] = t0;
+      sc->rzv[1] = t0;
       sc->rr = t1;
       sc->rr0 = t1;
       sc->iters = 0;

@@ -26,11 +26,15 @@ def _free_port():
         return s.getsockname()[1]
 
 
+@pytest.mark.parametrize("p2p", ["1", "0"], ids=["peer-memory", "nccl-per-op"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_nccl_path_bitwise_equals_single_gpu(world):
+def test_multi_gpu_path_bitwise_equals_single_gpu(world, p2p):
+    """p2p=1: halo rows and dot-product segment sums travel by stores into the peers' windows from inside the PCG
+    kernels; p2p=0: one NCCL call per exchange.  Both must reproduce the single-GPU bits."""
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
+    env = dict(os.environ, GS_P2P=p2p)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
            "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mgpu_worker.py"), "C3", "30000"]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
     assert res.returncode == 0 and "MGPU_OK" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
