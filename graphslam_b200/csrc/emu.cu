@@ -280,7 +280,7 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
   int it = 0, done = (rr == 0.0) ? 1 : 0;
   while (!done && it < pcg_max_iters) {
     W.halo([](VRank& v) { return v.p.data(); }, 3);
-    const double pAp = W.reduce([&](VRank& me, int r) { return gs::spmv_row(me.sv(), me.p.data(), me.Ap.data(), r, lambda); });
+    const double pAp = W.reduce([&](VRank& me, int r) { return gs::spmv_row(me.sv(), me.p.data(), me.p.data() + 3 * (size_t)me.n_own, me.Ap.data(), r, lambda); });
     if (!(pAp > 0.0)) {
       done = 2;
       break;
@@ -308,7 +308,7 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
 
   // ---- model terms, retract, new chi2
   W.halo([](VRank& v) { return v.x.data(); }, 3);
-  out->dHd = W.reduce([&](VRank& me, int r) { return gs::spmv_row(me.sv(), me.x.data(), me.Ap.data(), r, 0.0); });
+  out->dHd = W.reduce([&](VRank& me, int r) { return gs::spmv_row(me.sv(), me.x.data(), me.x.data() + 3 * (size_t)me.n_own, me.Ap.data(), r, 0.0); });
   out->db = W.reduce([&](VRank& me, int r) { return gs::dot_row(me.x.data(), me.b.data(), r); });
   for (VRank& me : W.R)
     for (int r = 0; r < me.n_own; ++r)

@@ -102,11 +102,13 @@ struct gs_graph {
   void* peer_base[gs::kMaxRanks] = {nullptr};  // what cudaIpcOpenMemHandle returned
   int peer_generation[gs::kMaxRanks] = {0};
   unsigned int nbr_mask = 0;
-  DevBuf<unsigned int> d_seq;             // [0] sequence base, [1] ticket
+  DevBuf<unsigned int> d_seq;             // [0] sequence base, [32] ticket (a line each)
+  DevBuf<gs::P2PWindow*> d_winptr;        // [rank] window pointers as the kernels see them
   DevBuf<int> d_hp_tile, d_hp_row;
   DevBuf<double*> d_hp_dst;
   DevBuf<char> d_xchg;
-  double* pvec = nullptr;                 // direction vector p: d_p, or the window's vector
+  double* pvec = nullptr;                 // direction vector p (owned rows, then the NCCL path's ghost rows)
+  double* pghost = nullptr;               // ghost rows of p: behind pvec, or in the window
 
   // ---- host copy of the graph, insertion order (what graph.cpp keeps in `graph` and `initial`)
   std::vector<uint64_t> keys;
@@ -266,7 +268,9 @@ gs::PcgView pcg_view(gs_graph* g) {
 
 // ---- multi-rank plumbing (no-ops on a single rank) ------------------------------------------------
 // ghost slots of `vec` (width doubles per vertex) <- owner ranks' current values
-gs_status halo_exchange(gs_graph* g, double* vec, int width) {
+// `ghost` = where the ghost rows land (nullptr: right behind the owned rows of `vec`)
+gs_status halo_exchange(gs_graph* g, double* vec, int width, double* ghost = nullptr) {
+  if (!ghost) ghost = vec + (size_t)g->n_own * width;
   if (g->world == 1) return GS_OK;
   const LocalStructure& S = g->S;
   const int nsend = (int)S.send_rows.size();
@@ -284,8 +288,8 @@ gs_status halo_exchange(gs_graph* g, double* vec, int width) {
       GS_NCCL(g, nc.Send(g->d_sendbuf.p + (size_t)hp.send_off * width, (size_t)hp.send_cnt * width, ncclDouble, hp.rank,
                          g->comm, g->stream));
     if (hp.ghost_cnt)
-      GS_NCCL(g, nc.Recv(vec + ((size_t)g->n_own + hp.ghost_off) * width, (size_t)hp.ghost_cnt * width, ncclDouble, hp.rank,
-                         g->comm, g->stream));
+      GS_NCCL(g, nc.Recv(ghost + (size_t)hp.ghost_off * width, (size_t)hp.ghost_cnt * width, ncclDouble, hp.rank, g->comm,
+                         g->stream));
   }
   GS_NCCL(g, nc.GroupEnd());
   return GS_OK;
@@ -304,7 +308,8 @@ gs_status finish_reduce(gs_graph* g, int nq, int op) {
 
 gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode) {
   if (gs_status s = halo_exchange(g, p, 3)) return s;
-  gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, y, reduce_ctx(g, 0), mode);
+  gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, p + 3 * (size_t)g->n_own, y, reduce_ctx(g, 0),
+                                                           mode);
   return finish_reduce(g, 1, mode == 0 ? gs::OP_PAP : gs::OP_DOT);
 }
 
@@ -319,15 +324,15 @@ gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
 
 gs::P2PCtx p2p_ctx(gs_graph* g, unsigned int k_local) {
   gs::P2PCtx x;
-  for (int q = 0; q < gs::kMaxRanks; ++q) x.win[q] = reinterpret_cast<gs::P2PWindow*>(g->peer_win[q]);
-  x.win[g->rank] = reinterpret_cast<gs::P2PWindow*>(g->win);
+  x.me = reinterpret_cast<gs::P2PWindow*>(g->win);
+  x.win = g->d_winptr.p;
   x.world = g->world;
   x.rank = g->rank;
   x.spr = gs::kSegments / g->world;
   x.nbr_mask = g->nbr_mask;
   x.seq_base = g->d_seq.p;
   x.k_local = k_local;
-  x.ticket = g->d_seq.p + 1;
+  x.ticket = g->d_seq.p + 32;   // its own 128-byte line
   x.spin_limit = 2000000000LL;
   return x;
 }
@@ -338,7 +343,8 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
   if (g->p2p) {
     const gs::P2PCtx x = p2p_ctx(g, k_local);
     if (stage == 0) {
-      gs::k_spmv_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->pvec, g->d_Ap.p, reduce_ctx(g, 0), x);
+      gs::k_spmv_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->pvec, g->pghost, g->d_Ap.p,
+                                                                   reduce_ctx(g, 0), x);
     } else if (stage == 1) {
       gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
     } else {
@@ -436,7 +442,7 @@ void close_peer(gs_graph* g, int q) {
 // (re)build the window, exchange handles, map the peers, and lay out the halo pushes.  Collective.
 gs_status prepare_p2p(gs_graph* g) {
   const LocalStructure& S = g->S;
-  const size_t need = gs::kWindowHeaderBytes + sizeof(double) * 3 * (size_t)std::max(g->n_loc, 1);
+  const size_t need = gs::kWindowHeaderBytes + sizeof(double) * 3 * (size_t)std::max(S.n_ghost, 1);
   XchgRecord mine;
   std::memset(&mine, 0, sizeof mine);
   mine.will_realloc = (need > g->win_bytes) ? 1 : 0;
@@ -457,8 +463,8 @@ gs_status prepare_p2p(gs_graph* g) {
     // the sequence numbering restarts with the fresh (zeroed) flags on every rank at once?  No: only this
     // rank's flags are new, so keep counting — stamps only ever need to exceed what a waiter asks for.
   }
-  g->pvec = reinterpret_cast<double*>(g->win + gs::kWindowHeaderBytes);
-  GS_CUDA(g, cudaMemsetAsync(g->pvec, 0, sizeof(double) * 3 * (size_t)std::max(g->n_loc, 1), g->stream));
+  g->pghost = reinterpret_cast<double*>(g->win + gs::kWindowHeaderBytes);
+  GS_CUDA(g, cudaMemsetAsync(g->pghost, 0, sizeof(double) * 3 * (size_t)std::max(S.n_ghost, 1), g->stream));
   GS_CUDA(g, cudaIpcGetMemHandle(&mine.handle, g->win));
   mine.offset = allocation_offset(g->win);
   mine.generation = g->win_generation;
@@ -485,7 +491,7 @@ gs_status prepare_p2p(gs_graph* g) {
   for (const gs::HaloPeer& hp : S.peers) {
     g->nbr_mask |= 1u << hp.rank;
     double* peer_p = reinterpret_cast<double*>(g->peer_win[hp.rank] + gs::kWindowHeaderBytes);
-    const size_t slot0 = (size_t)all[hp.rank].n_own + (size_t)all[hp.rank].ghost_off[g->rank];
+    const size_t slot0 = (size_t)all[hp.rank].ghost_off[g->rank];
     for (int k = 0; k < hp.send_cnt; ++k) ent.push_back({S.send_rows[hp.send_off + k], peer_p + 3 * (slot0 + k)});
   }
   std::stable_sort(ent.begin(), ent.end(), [](const Entry& a, const Entry& b) { return a.row < b.row; });
@@ -501,6 +507,9 @@ gs_status prepare_p2p(gs_graph* g) {
   if (gs_status s = upload(g, g->d_hp_tile, tile_ptr)) return s;
   if (gs_status s = upload(g, g->d_hp_row, rows)) return s;
   if (gs_status s = upload(g, g->d_hp_dst, dsts)) return s;
+  std::vector<gs::P2PWindow*> wins(gs::kMaxRanks, nullptr);
+  for (int q = 0; q < g->world; ++q) wins[q] = reinterpret_cast<gs::P2PWindow*>(q == g->rank ? g->win : g->peer_win[q]);
+  if (gs_status s = upload(g, g->d_winptr, wins)) return s;
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   return GS_OK;
 }
@@ -663,6 +672,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   GS_CUDA(g, g->d_z.alloc(n3));
   GS_CUDA(g, g->d_p.alloc(nl3));
   g->pvec = g->d_p.p;
+  g->pghost = g->d_p.p + 3 * (size_t)S.n_own;
   GS_CUDA(g, g->d_Ap.alloc(n3));
   GS_CUDA(g, g->d_dscale.alloc(n3));
   GS_CUDA(g, g->d_sendbuf.alloc(4 * std::max<size_t>(S.send_rows.size(), 1)));
@@ -745,7 +755,7 @@ void launch_pcg_setup(gs_graph* g) {
 // peer-memory path: ghost rows of p(0) by the ordinary halo exchange, then mark them valid
 gs_status begin_p2p_solve(gs_graph* g) {
   if (!g->p2p) return GS_OK;
-  if (gs_status s = halo_exchange(g, g->pvec, 3)) return s;
+  if (gs_status s = halo_exchange(g, g->pvec, 3, g->pghost)) return s;
   gs::k_p2p_begin<<<1, 32, 0, g->stream>>>(reinterpret_cast<gs::P2PWindow*>(g->win), g->d_seq.p, g->d_sc.p);
   g->launches += 1;
   return GS_OK;
@@ -778,6 +788,10 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
     if (gs_status s = read_scalars(g)) return s;
     if (h->done) break;
   }
+  if (g->p2p && std::getenv("GS_P2P_DEBUG") && h->spin[3] > 0)
+    std::fprintf(stderr, "[gs r%d] p2p waits of CTA 0 per iteration (clock ticks): spmv %.0f update %.0f dir %.0f over %lld iterations\n",
+                 g->rank, (double)h->spin[0] / h->spin[3], (double)h->spin[1] / h->spin[3], (double)h->spin[2] / h->spin[3],
+                 h->spin[3]);
   if (h->done == 4) return g->fail(GS_ENCCL, "a peer rank did not answer within the wait limit (peer-memory PCG)");
   // kernels that did work (the no-op tail of the last batch is not counted)
   g->launches = keep + launches_per_pcg_iteration(g) * (int64_t)h->iters;
@@ -817,8 +831,8 @@ gs_status create_common(gs_graph* g) {
   g->use_graph = !(env && env[0] == '0');
   env = std::getenv("GS_P2P");
   g->p2p_wanted = !(env && env[0] == '0');
-  GS_CUDA(g, g->d_seq.alloc(2));
-  GS_CUDA(g, cudaMemsetAsync(g->d_seq.p, 0, 2 * sizeof(unsigned int), g->stream));
+  GS_CUDA(g, g->d_seq.alloc(64));
+  GS_CUDA(g, cudaMemsetAsync(g->d_seq.p, 0, 64 * sizeof(unsigned int), g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   return GS_OK;
 }

@@ -37,6 +37,7 @@ struct Scalars {
   int max_iters;
   unsigned int seq0;  // peer-memory path: sequence number of this solve's first iteration
   double rzv[2];      // peer-memory path: r^T z by iteration parity (reader and writer never share a slot)
+  long long spin[4];  // peer-memory path: clock ticks CTA 0 spent waiting in spmv / update / dir, and the waits counted
 };
 
 enum ReduceOp { OP_PAP = 0, OP_DOT = 1, OP_INIT = 2, OP_UPDATE = 3, OP_CHI2 = 4 };
@@ -213,15 +214,15 @@ __global__ void __launch_bounds__(kThreads) k_chi2(const AsmView a, const Reduce
 // (A variant that staged several slots per thread through shared memory with cp.async was measured
 //  slower on C3 — 123-165 us against 101 us — because the staging buffers cost occupancy and L1; see
 //  DESIGN.md "What did not help".)
-__global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const double* __restrict__ p, double* __restrict__ y,
-                                                    const ReduceCtx c, int mode) {
+__global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const double* __restrict__ p, const double* __restrict__ pg,
+                                                    double* __restrict__ y, const ReduceCtx c, int mode) {
   __shared__ double red[8];
   __shared__ int flag;
   if (mode == 0 && c.sc->done) return;
   const double lambda = (mode == 0) ? c.sc->lambda : 0.0;
   const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[1] = {0.0};
-  if (r < a.n_own) v[0] = spmv_row(a, p, y, r, lambda);
+  if (r < a.n_own) v[0] = spmv_row(a, p, pg, y, r, lambda);
   reduce_finish<1>(c, v, mode == 0 ? OP_PAP : OP_DOT, red, &flag);
 }
 

@@ -1,9 +1,10 @@
 // Multi-GPU PCG iteration with the collectives fused into the kernels (NVLink peer memory, no NCCL
 // call and no extra launch inside the iteration).
 //
-// Every rank exports one "window" allocation (cudaIpc) that holds its flags, the landing zone for
-// the segment sums of all ranks, and its direction vector p (owned rows, then ghost slots).  Peers
-// map it and write into it directly:
+// Every rank exports one small "window" allocation (cudaIpc) that holds its flags, the landing zone
+// for the segment sums of all ranks, and the ghost rows of its direction vector p.  Peers map it and
+// write into it directly (the owned part of p stays in ordinary memory: keeping the whole vector in
+// the exported allocation made every kernel that streams p several times slower):
 //
 //   k_spmv_p2p    waits until its neighbours have pushed the ghost rows of p for this iteration,
 //                 multiplies, and its last CTA stores this rank's p.Ap segment sums into EVERY
@@ -25,7 +26,7 @@
 namespace gs {
 
 constexpr int kMaxRanks = kSegments;
-constexpr size_t kWindowHeaderBytes = 4096;   // flags + segment sums; p starts here
+constexpr size_t kWindowHeaderBytes = 4096;   // flags + segment sums; the ghost rows of p start here
 
 struct P2PWindow {
   unsigned int halo_flag[kMaxRanks];   // [source rank] p pushed by that rank is valid for spmv number (value - 1)
@@ -39,7 +40,9 @@ struct P2PWindow {
 static_assert(sizeof(P2PWindow) <= kWindowHeaderBytes, "window header too small");
 
 struct P2PCtx {
-  P2PWindow* win[kMaxRanks];   // win[rank] is the local window, the others are peer mappings
+  P2PWindow* me;               // the local window
+  P2PWindow* const* win;       // device array [rank]: the local window and the peer mappings (a by-value array here
+                               // would be indexed dynamically and push the whole argument block onto the stack)
   int world, rank, spr;
   unsigned int nbr_mask;       // ranks this rank exchanges halo rows with
   const unsigned int* seq_base;  // device word: iterations completed before the current batch
@@ -54,42 +57,68 @@ struct HaloPush {
   double* const* dst;          // address of its 3 doubles in the peer's window
 };
 
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+// Flags and landing zones live in THIS GPU's memory and are written by peers over NVLink; remote stores
+// become visible at this GPU's L2.  The poll is a relaxed L2 read; one gpu-scope acquire fence after
+// success orders the data reads behind it (the data itself is read past L1: __ldcg, or lines this
+// kernel has not touched before).  A system-scope acquire per poll was measured ~8x slower.
+__device__ __forceinline__ unsigned int ld_relaxed(const unsigned int* p) {
   unsigned int v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// thread 0 spins until flags[q] >= target for every q in mask; false on timeout (then sc->done = 4)
+// What one CTA learns at the top of a kernel: whether the wait succeeded, and the totals it waited for.
+struct WaitOut {
+  int ok;
+  double tot[2];
+};
+
+// Lane q of warp 0 spins until flags[q] >= target (q in mask); false on timeout (then sc->done = 4).
+// The same warp then reads the NT landed segment-sum arrays ONCE per CTA (lanes 0..7, one request)
+// and adds them in the fixed global order; everybody else takes the totals from shared memory.
+// (Letting every thread read the eight sums past L1 put ~10^5 requests per launch on a single L2
+// slice and made the three kernels 3-10x slower than their single-GPU forms.)
+template <int NT>
 __device__ __forceinline__ bool wait_flags(const unsigned int* flags, unsigned int mask, unsigned int target, Scalars* sc,
-                                           long long limit, int* sflag) {
-  if (threadIdx.x == 0) {
+                                           long long limit, WaitOut* out, int which, const double* seg0,
+                                           const double* seg1) {
+  if (threadIdx.x < 32) {
     int ok = 1;
-    const long long t0 = clock64();
-    for (int q = 0; q < kMaxRanks && ok; ++q) {
-      if (!((mask >> q) & 1u)) continue;
-      while ((int)(ld_acquire_sys(flags + q) - target) < 0) {
+    const long long w0 = clock64();
+    if (threadIdx.x < kMaxRanks && ((mask >> threadIdx.x) & 1u)) {
+      const long long t0 = clock64();
+      while ((int)(ld_relaxed(flags + threadIdx.x) - target) < 0) {
         if (clock64() - t0 > limit) {
           ok = 0;
-          sc->done = 4;
           break;
         }
       }
     }
-    *sflag = ok;
+    ok = __all_sync(0xffffffffu, ok);
+    __threadfence();
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const double* seg = t == 0 ? seg0 : seg1;
+      const double v = threadIdx.x < kSegments ? __ldcg(seg + threadIdx.x) : 0.0;
+      double acc = 0.0;
+#pragma unroll
+      for (int g = 0; g < kSegments; ++g) acc += __shfl_sync(0xffffffffu, v, g);
+      if (threadIdx.x == 0) out->tot[t] = acc;
+    }
+    if (threadIdx.x == 0) {
+      if (!ok) sc->done = 4;
+      out->ok = ok;
+      if (blockIdx.x == 0) {
+        sc->spin[which] += clock64() - w0;
+        if (which == 0) sc->spin[3] += 1;
+      }
+    }
   }
   __syncthreads();
-  return *sflag != 0;
-}
-
-__device__ __forceinline__ double total8(const double* seg) {
-  double t = 0.0;
-#pragma unroll
-  for (int g = 0; g < kSegments; ++g) t += __ldcg(seg + g);
-  return t;
+  return out->ok != 0;
 }
 
 // tile partials -> this rank's segment sums -> every rank's window, then the flag.  NQ quantities,
@@ -136,18 +165,19 @@ __device__ __forceinline__ void reduce_push(const ReduceCtx& c, const P2PCtx& x,
   }
 }
 
-__global__ void __launch_bounds__(kThreads) k_spmv_p2p(const SpmvView a, const double* __restrict__ p, double* __restrict__ y,
-                                                        const ReduceCtx c, const P2PCtx x) {
+__global__ void __launch_bounds__(kThreads) k_spmv_p2p(const SpmvView a, const double* __restrict__ p, const double* __restrict__ pg,
+                                                        double* __restrict__ y, const ReduceCtx c, const P2PCtx x) {
   __shared__ double red[8];
   __shared__ int flag;
+  __shared__ WaitOut wo;
   if (c.sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
-  P2PWindow* me = x.win[x.rank];
-  if (!wait_flags(me->halo_flag, x.nbr_mask, S + 1, c.sc, x.spin_limit, &flag)) return;
+  P2PWindow* me = x.me;
+  if (!wait_flags<0>(me->halo_flag, x.nbr_mask, S + 1, c.sc, x.spin_limit, &wo, 0, nullptr, nullptr)) return;
   const double lambda = c.sc->lambda;
   const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[1] = {0.0};
-  if (r < a.n_own) v[0] = spmv_row(a, p, y, r, lambda);
+  if (r < a.n_own) v[0] = spmv_row(a, p, pg, y, r, lambda);
   reduce_push<1>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return w->pap_flag; },
                  [](P2PWindow* w, int) { return &w->seg_pap[0][0]; }, red, &flag);
 }
@@ -155,11 +185,13 @@ __global__ void __launch_bounds__(kThreads) k_spmv_p2p(const SpmvView a, const d
 __global__ void __launch_bounds__(kThreads) k_update_p2p(const PcgView a, const ReduceCtx c, const P2PCtx x) {
   __shared__ double red[8];
   __shared__ int flag;
+  __shared__ WaitOut wo;
   if (c.sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
-  P2PWindow* me = x.win[x.rank];
-  if (!wait_flags(me->pap_flag, (1u << x.world) - 1u, S + 1, c.sc, x.spin_limit, &flag)) return;
-  const double pAp = total8(me->seg_pap[S & 1u]);
+  P2PWindow* me = x.me;
+  if (!wait_flags<1>(me->pap_flag, (1u << x.world) - 1u, S + 1, c.sc, x.spin_limit, &wo, 1, me->seg_pap[S & 1u], nullptr))
+    return;
+  const double pAp = wo.tot[0];
   if (!(pAp > 0.0)) {  // breakdown: the same on every rank, nobody goes on
     if (blockIdx.x == 0 && threadIdx.x == 0) {
       c.sc->pAp = pAp;
@@ -178,13 +210,16 @@ __global__ void __launch_bounds__(kThreads) k_update_p2p(const PcgView a, const 
 // p = z + beta p ; rows that neighbours need go straight into their ghost slots
 __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const ReduceCtx c, const P2PCtx x, const HaloPush h) {
   __shared__ int flag;
+  __shared__ WaitOut wo;
   Scalars* sc = c.sc;
   if (sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
-  P2PWindow* me = x.win[x.rank];
-  if (!wait_flags(me->rz_flag, (1u << x.world) - 1u, S + 1, sc, x.spin_limit, &flag)) return;
-  const double rz = total8(me->seg_rz[S & 1u]);
-  const double rr = total8(me->seg_rr[S & 1u]);
+  P2PWindow* me = x.me;
+  if (!wait_flags<2>(me->rz_flag, (1u << x.world) - 1u, S + 1, sc, x.spin_limit, &wo, 2, me->seg_rz[S & 1u],
+                     me->seg_rr[S & 1u]))
+    return;
+  const double rz = wo.tot[0];
+  const double rr = wo.tot[1];
   const double rz_old = sc->rzv[(S + 1u) & 1u];
   const double beta = rz / rz_old;
   const int it = (int)(S - sc->seq0) + 1;
@@ -205,14 +240,16 @@ __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const Red
   if (r < a.n_own) pcg_dir_row(a, r, beta);
   __syncthreads();
   const int e0 = h.tile_ptr[blockIdx.x], e1 = h.tile_ptr[blockIdx.x + 1];
+  bool pushed = false;
   for (int e = e0 + (int)threadIdx.x; e < e1; e += kThreads) {
     const double* src = a.p + 3 * (size_t)h.row[e];
     double* dst = h.dst[e];
     dst[0] = __ldcg(src);
     dst[1] = __ldcg(src + 1);
     dst[2] = __ldcg(src + 2);
+    pushed = true;
   }
-  __threadfence_system();
+  if (pushed) __threadfence_system();   // only the few threads that stored to a peer pay for the system fence
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned int t = atomicAdd(x.ticket, 1u);

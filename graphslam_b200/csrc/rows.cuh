@@ -365,7 +365,8 @@ GS_HD double spmv_finish(const double d[6], const double l[3], double px, double
   return (px * y0 + py * y1) + pz * y2;
 }
 
-GS_HD double spmv_row(const SpmvView& a, const double* p, double* y, int r, double lambda) {
+// p: owned rows; pg: ghost rows (local column c >= n_own reads pg + 3 (c - n_own))
+GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, double* y, int r, double lambda) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
   double y0 = 0.0, y1 = 0.0, y2 = 0.0;
@@ -380,8 +381,8 @@ GS_HD double spmv_row(const SpmvView& a, const double* p, double* y, int r, doub
       double h[9];
 #pragma unroll
       for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * a.hstride);
-      const size_t col = (size_t)ref.x;
-      spmv_slot(h, p[3 * col], p[3 * col + 1], p[3 * col + 2], ref.y & 1, y0, y1, y2);
+      const double* pc = ref.x < a.n_own ? p + 3 * (size_t)ref.x : pg + 3 * (size_t)(ref.x - a.n_own);
+      spmv_slot(h, pc[0], pc[1], pc[2], ref.y & 1, y0, y1, y2);
     }
   }
   const size_t n = (size_t)a.n_own, rr = (size_t)r;
