@@ -40,6 +40,11 @@ class GsStats(C.Structure):
         return d
 
 
+class GsG2oCounts(C.Structure):
+    _fields_ = [("vertices", C.c_size_t), ("edges", C.c_size_t), ("priors", C.c_size_t), ("fixed", C.c_size_t),
+                ("skipped_lines", C.c_size_t)]
+
+
 # every symbol include/graphslam_cuda.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "gs_default_params": (None, [C.POINTER(GsParams)]),
@@ -54,6 +59,10 @@ SIGNATURES = {
     "gs_add_between": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, c_double_p, c_double_p]),
     "gs_add_batch": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p, C.c_size_t, c_u64_p, c_u64_p,
                                c_double_p, c_double_p]),
+    "gs_add_prior_information": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p, c_double_p]),
+    "gs_add_between_information": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, c_double_p, c_double_p]),
+    "gs_load_g2o": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(GsG2oCounts)]),
+    "gs_save_g2o": (C.c_int, [C.c_void_p, C.c_char_p]),
     "gs_prepare": (C.c_int, [C.c_void_p]),
     "gs_optimize": (C.c_int, [C.c_void_p, C.POINTER(GsStats)]),
     "gs_get_pose": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
@@ -97,6 +106,8 @@ DEBUG_SIGNATURES = {
                              C.POINTER(GsEmuResult)]),
     "gs_host_pattern": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t),
                                   c_i32_p]),
+    "gs_host_g2o": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_size_t), c_u64_p, c_double_p, c_u64_p, c_u64_p,
+                              c_double_p, c_double_p, c_u64_p, c_double_p, c_double_p]),
     "gs_host_between": (C.c_int, [c_double_p] * 4 + [C.c_int] + [c_double_p] * 8),
 }
 

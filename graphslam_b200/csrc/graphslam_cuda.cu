@@ -26,6 +26,7 @@
 
 #include "../../include/graphslam_cuda.h"
 #include "comm.hpp"
+#include "g2o.hpp"
 #include "kernels.cuh"
 #include "kernels_p2p.cuh"
 
@@ -77,6 +78,19 @@ bool spd_information(const double* cov9, double* om6) {
   for (int k = 0; k < 6; ++k)
     if (!std::isfinite(om6[k])) return false;
   return true;
+}
+
+// information (inverse covariance) given directly, upper triangle I11 I12 I13 I22 I23 I33: SPD test only
+bool spd_upper(const double* o) {
+  for (int k = 0; k < 6; ++k)
+    if (!std::isfinite(o[k])) return false;
+  if (!(o[0] > 0.0)) return false;
+  const double l00 = std::sqrt(o[0]), l10 = o[1] / l00, l20 = o[2] / l00;
+  const double d1 = o[3] - l10 * l10;
+  if (!(d1 > 0.0)) return false;
+  const double l11 = std::sqrt(d1), l21 = (o[4] - l20 * l10) / l11;
+  const double d2 = o[5] - l20 * l20 - l21 * l21;
+  return d2 > 0.0;
 }
 
 }  // namespace
@@ -998,6 +1012,115 @@ gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3
   return GS_OK;
 }
 
+// noiseModel::Gaussian::Information(I) forms of the two calls above (what a g2o file carries)
+gs_status gs_add_prior_information(gs_graph* g, uint64_t key, const double pose[3], const double info6[6]) {
+  if (!g || !pose || !info6) return GS_EINVAL;
+  const int v = g->find(key);
+  if (v < 0) return g->fail(GS_ENOKEY, "prior on unknown key %llu", (unsigned long long)key);
+  if (!(std::isfinite(pose[0]) && std::isfinite(pose[1]) && std::isfinite(pose[2]))) return g->fail(GS_EINVAL, "non-finite prior");
+  if (!spd_upper(info6)) return g->fail(GS_ENOTSPD, "prior information on key %llu is not SPD", (unsigned long long)key);
+  g->pr_v.push_back(v);
+  g->pr_xyt.insert(g->pr_xyt.end(), pose, pose + 3);
+  g->pr_om.insert(g->pr_om.end(), info6, info6 + 6);
+  g->topo_dirty = true;
+  return GS_OK;
+}
+
+gs_status gs_add_between_information(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3], const double info6[6]) {
+  if (!g || !d || !info6) return GS_EINVAL;
+  const int a = g->find(k1), b = g->find(k2);
+  if (a < 0 || b < 0)
+    return g->fail(GS_ENOKEY, "between factor names unknown key %llu", (unsigned long long)(a < 0 ? k1 : k2));
+  if (a == b) return g->fail(GS_EINVAL, "between factor from key %llu to itself", (unsigned long long)k1);
+  if (!(std::isfinite(d[0]) && std::isfinite(d[1]) && std::isfinite(d[2]))) return g->fail(GS_EINVAL, "non-finite delta");
+  if (!spd_upper(info6))
+    return g->fail(GS_ENOTSPD, "information of factor %llu->%llu is not SPD", (unsigned long long)k1, (unsigned long long)k2);
+  g->e1.push_back(a);
+  g->e2.push_back(b);
+  g->ez.insert(g->ez.end(), d, d + 3);
+  g->eom.insert(g->eom.end(), info6, info6 + 6);
+  g->topo_dirty = true;
+  return GS_OK;
+}
+
+// g2o / TORO text (csrc/g2o.hpp).  Loading appends to the graph: vertices first, then priors, then
+// edges, in file order; nothing is added when the file is malformed or names an unknown/duplicate key.
+gs_status gs_load_g2o(gs_graph* g, const char* path, gs_g2o_counts* counts) {
+  if (!g || !path) return GS_EINVAL;
+  gs::G2oData d;
+  const std::string err = gs::read_g2o(path, d);
+  if (!err.empty()) return g->fail(GS_EINVAL, "%s", err.c_str());
+  // validate everything before touching the graph
+  {
+    std::unordered_map<uint64_t, int> seen;
+    seen.reserve(d.vkey.size() * 2);
+    for (uint64_t k : d.vkey) {
+      if (g->find(k) >= 0 || !seen.emplace(k, 1).second)
+        return g->fail(GS_EDUPKEY, "%s: vertex %llu already present", path, (unsigned long long)k);
+    }
+    auto known = [&](uint64_t k) { return seen.count(k) || g->find(k) >= 0; };
+    for (size_t k = 0; k < d.e1.size(); ++k) {
+      if (!known(d.e1[k]) || !known(d.e2[k]))
+        return g->fail(GS_ENOKEY, "%s: edge %zu names an unknown vertex", path, k);
+      if (d.e1[k] == d.e2[k]) return g->fail(GS_EINVAL, "%s: edge %zu joins a vertex to itself", path, k);
+      if (!spd_upper(&d.einfo[6 * k])) return g->fail(GS_ENOTSPD, "%s: information of edge %zu is not SPD", path, k);
+      if (!(std::isfinite(d.ez[3 * k]) && std::isfinite(d.ez[3 * k + 1]) && std::isfinite(d.ez[3 * k + 2])))
+        return g->fail(GS_EINVAL, "%s: non-finite measurement in edge %zu", path, k);
+    }
+    for (size_t k = 0; k < d.pkey.size(); ++k) {
+      if (!known(d.pkey[k])) return g->fail(GS_ENOKEY, "%s: prior %zu names an unknown vertex", path, k);
+      if (!spd_upper(&d.pinfo[6 * k])) return g->fail(GS_ENOTSPD, "%s: information of prior %zu is not SPD", path, k);
+    }
+    for (size_t k = 0; k < d.vkey.size(); ++k)
+      if (!(std::isfinite(d.vxyt[3 * k]) && std::isfinite(d.vxyt[3 * k + 1]) && std::isfinite(d.vxyt[3 * k + 2])))
+        return g->fail(GS_EINVAL, "%s: non-finite pose for vertex %llu", path, (unsigned long long)d.vkey[k]);
+  }
+  g->keys.reserve(g->keys.size() + d.vkey.size());
+  g->xyt.reserve(g->xyt.size() + d.vxyt.size());
+  for (size_t k = 0; k < d.vkey.size(); ++k)
+    if (gs_status s = gs_add_vertex(g, d.vkey[k], &d.vxyt[3 * k])) return s;
+  for (size_t k = 0; k < d.pkey.size(); ++k)
+    if (gs_status s = gs_add_prior_information(g, d.pkey[k], &d.pxyt[3 * k], &d.pinfo[6 * k])) return s;
+  g->e1.reserve(g->e1.size() + d.e1.size());
+  g->e2.reserve(g->e2.size() + d.e1.size());
+  g->ez.reserve(g->ez.size() + d.ez.size());
+  g->eom.reserve(g->eom.size() + d.einfo.size());
+  for (size_t k = 0; k < d.e1.size(); ++k)
+    if (gs_status s = gs_add_between_information(g, d.e1[k], d.e2[k], &d.ez[3 * k], &d.einfo[6 * k])) return s;
+  if (counts) {
+    counts->vertices = d.vkey.size();
+    counts->edges = d.e1.size();
+    counts->priors = d.pkey.size();
+    counts->fixed = d.fixed.size();
+    counts->skipped_lines = d.skipped;
+  }
+  return GS_OK;
+}
+
+// the whole graph with the CURRENT values (after gs_optimize: the optimum), loadable by gs_load_g2o
+gs_status gs_save_g2o(gs_graph* g, const char* path) {
+  if (!g || !path) return GS_EINVAL;
+  if (gs_status s = download_values(g)) return s;
+  gs::G2oData d;
+  d.vkey = g->keys;
+  d.vxyt = g->xyt;
+  d.e1.resize(g->e1.size());
+  d.e2.resize(g->e2.size());
+  for (size_t k = 0; k < g->e1.size(); ++k) {
+    d.e1[k] = g->keys[g->e1[k]];
+    d.e2[k] = g->keys[g->e2[k]];
+  }
+  d.ez = g->ez;
+  d.einfo = g->eom;
+  d.pkey.resize(g->pr_v.size());
+  for (size_t k = 0; k < g->pr_v.size(); ++k) d.pkey[k] = g->keys[g->pr_v[k]];
+  d.pxyt = g->pr_xyt;
+  d.pinfo = g->pr_om;
+  const std::string err = gs::write_g2o(path, d);
+  if (!err.empty()) return g->fail(GS_EINVAL, "%s", err.c_str());
+  return GS_OK;
+}
+
 gs_status gs_add_batch(gs_graph* g, size_t nv, const uint64_t* keys, const double* poses, size_t ne, const uint64_t* k1,
                        const uint64_t* k2, const double* deltas, const double* cov9s) {
   if (!g) return GS_EINVAL;
@@ -1477,6 +1600,37 @@ gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t
     gs::canonical_order(n, e, ei, ej, pm);
     std::memcpy(perm, pm.data(), sizeof(int32_t) * e);
   }
+  return GS_OK;
+}
+
+// the g2o reader/writer the product uses, without a graph handle: parse `in_path`, report the counts
+// {vertices, edges, priors, fixed, skipped}, optionally copy the parsed arrays out and/or write the
+// parsed content back to `out_path`
+gs_status gs_host_g2o(const char* in_path, const char* out_path, size_t counts[5], uint64_t* vkey, double* vxyt,
+                      uint64_t* e1, uint64_t* e2, double* ez, double* einfo, uint64_t* pkey, double* pxyt, double* pinfo) {
+  if (!in_path) return GS_EINVAL;
+  gs::G2oData d;
+  if (!gs::read_g2o(in_path, d).empty()) return GS_EINVAL;
+  if (counts) {
+    counts[0] = d.vkey.size();
+    counts[1] = d.e1.size();
+    counts[2] = d.pkey.size();
+    counts[3] = d.fixed.size();
+    counts[4] = d.skipped;
+  }
+  auto out = [](auto* dst, const auto& v) {
+    if (dst && !v.empty()) std::memcpy(dst, v.data(), sizeof(v[0]) * v.size());
+  };
+  out(vkey, d.vkey);
+  out(vxyt, d.vxyt);
+  out(e1, d.e1);
+  out(e2, d.e2);
+  out(ez, d.ez);
+  out(einfo, d.einfo);
+  out(pkey, d.pkey);
+  out(pxyt, d.pxyt);
+  out(pinfo, d.pinfo);
+  if (out_path && !gs::write_g2o(out_path, d).empty()) return GS_EINVAL;
   return GS_OK;
 }
 

@@ -131,6 +131,24 @@ class Graph:
         self.add_batch(np.zeros(0, np.uint64), np.zeros((0, 3)), g.k1, g.k2, g.z, g.cov)
         return self
 
+    def add_prior_information(self, key: int, pose, info6):
+        p, q = _f64(pose, 3), _f64(info6, 6)
+        self._ck(self._lib.gs_add_prior_information(self._h, int(key), _dp(p), _dp(q)))
+
+    def add_between_information(self, k1: int, k2: int, delta, info6):
+        d, q = _f64(delta, 3), _f64(info6, 6)
+        self._ck(self._lib.gs_add_between_information(self._h, int(k1), int(k2), _dp(d), _dp(q)))
+
+    def load_g2o(self, path) -> dict:
+        """Append a g2o / TORO 2-D file (all-or-nothing); returns the counts."""
+        c = _lib.GsG2oCounts()
+        self._ck(self._lib.gs_load_g2o(self._h, str(path).encode(), C.byref(c)))
+        return {k: int(getattr(c, k)) for k, _ in c._fields_}
+
+    def save_g2o(self, path):
+        """Write the whole graph with the current values (%.17g: save -> load is bit-exact)."""
+        self._ck(self._lib.gs_save_g2o(self._h, str(path).encode()))
+
     def prepare(self):
         self._ck(self._lib.gs_prepare(self._h))
 

@@ -119,6 +119,25 @@ gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double del
 gs_status gs_add_batch(gs_graph* g, size_t nv, const uint64_t* keys, const double* poses_xyt, size_t ne,
                        const uint64_t* k1, const uint64_t* k2, const double* deltas_xyt, const double* cov9s);
 
+/* the same two factors with noiseModel::Gaussian::Information(I) instead of Covariance(Q);
+ * info6 = upper triangle I11 I12 I13 I22 I23 I33 (what a g2o EDGE_SE2 line carries) */
+gs_status gs_add_prior_information(gs_graph* g, uint64_t key, const double pose_xyt[3], const double info6[6]);
+gs_status gs_add_between_information(gs_graph* g, uint64_t k1, uint64_t k2, const double delta_xyt[3],
+                                     const double info6[6]);
+
+/* g2o / TORO 2-D text format (VERTEX_SE2 / EDGE_SE2 / EDGE_PRIOR_SE2; TORO VERTEX2 / EDGE2).  The
+ * reference has no persistence: its graph lives in process globals (graph.cpp:5-10) and is lost on
+ * exit.  gs_load_g2o appends the file's vertices, priors and edges (all-or-nothing); gs_save_g2o
+ * writes the whole graph with the current values at full precision (%.17g), so save -> load
+ * reproduces the graph bit for bit (checkpoint / resume). */
+typedef struct gs_g2o_counts {
+  size_t vertices, edges, priors;
+  size_t fixed;         /* ids on FIX lines: reported, not applied (anchor with gs_add_prior as graph.cpp:57 does) */
+  size_t skipped_lines; /* lines with a tag this loader does not know */
+} gs_g2o_counts;
+gs_status gs_load_g2o(gs_graph* g, const char* path, gs_g2o_counts* counts /* nullable */);
+gs_status gs_save_g2o(gs_graph* g, const char* path);
+
 /* upload pending vertices/factors and (re)build the sparse structure now; gs_optimize does this
  * lazily.  Separates one-off topology work from the per-iteration path for measurement. */
 gs_status gs_prepare(gs_graph* g);

@@ -26,6 +26,12 @@ gs_status gs_host_between(const double pi[3], const double pj[3], const double z
                           double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],
                           double bi[3], double bj[3]);
 
+/* the g2o / TORO reader and writer behind gs_load_g2o / gs_save_g2o, without a graph handle: parse in_path,
+ * counts = {vertices, edges, priors, fixed, skipped lines}; array outputs (sized from a first call) and out_path
+ * (re-written file) may be NULL */
+gs_status gs_host_g2o(const char* in_path, const char* out_path, size_t counts[5], uint64_t* vkey, double* vxyt,
+                      uint64_t* e1, uint64_t* e2, double* ez, double* einfo, uint64_t* pkey, double* pxyt, double* pinfo);
+
 /* vertex-range partition of rank `rank` of `world`: info = {v0, v1, n_ghost, n_peers, n_send, n_pairs, nnzo_own,
  * ntiles}; ghosts[n_ghost] (global, sorted); peers[5*n_peers] = {rank, send_off, send_cnt, ghost_off, ghost_cnt};
  * send_rows[n_send] (global indices, grouped by peer).  Array outputs may be NULL (size them with n). */

@@ -283,3 +283,62 @@ def test_large_graph_properties(cid, n):
         assert np.all(np.diff(errors) < 0)                                   # every accepted step lowers chi2
         _, x = G.poses()
         assert 2 * prob.error(x) == pytest.approx(st["chi2_final"], rel=1e-10)   # oracle re-evaluates the result
+
+
+def test_g2o_checkpoint_resume_is_bit_exact(tmp_path):
+    """gs_save_g2o -> gs_load_g2o reproduces the graph bit for bit: same system, same optimum (the reference loses its
+    graph on exit, graph.cpp:5-10)."""
+    g = synth.config("C1", n=1200, full_cov=True)
+    path = tmp_path / "ckpt.g2o"
+    with _load(g) as A:
+        A.save_g2o(path)
+        _, _, blocks_a, b_a, chi2_a = A.system()
+        st_a = A.optimize()
+        _, x_a = A.poses()
+        A.save_g2o(tmp_path / "opt.g2o")
+    with graph.Graph() as B:
+        c = B.load_g2o(path)
+        assert (c["vertices"], c["edges"], c["priors"]) == (len(g.keys), len(g.k1), 1)
+        _, _, blocks_b, b_b, chi2_b = B.system()
+        assert np.array_equal(blocks_a, blocks_b) and np.array_equal(b_a, b_b) and chi2_a == chi2_b
+        st_b = B.optimize()
+        _, x_b = B.poses()
+        assert st_a["chi2_final"] == st_b["chi2_final"] and np.array_equal(x_a, x_b)
+    with graph.Graph() as R:                                   # resume from the optimum: nothing left to do
+        R.load_g2o(tmp_path / "opt.g2o")
+        assert R.chi2() == pytest.approx(st_a["chi2_final"], rel=1e-12)
+        _, x_r = R.poses()
+        assert np.array_equal(x_r, x_a)
+
+
+def test_g2o_toro_file_matches_oracle(tmp_path):
+    """A TORO-style file (VERTEX2 / EDGE2 information order) through gs_load_g2o against the oracle fed the same numbers."""
+    g = synth.config("C1", n=600)
+    om = np.array([np.linalg.inv(q.reshape(3, 3)) for q in g.cov])
+    path = tmp_path / "toro.graph"
+    with open(path, "w") as fh:
+        for k, p in zip(g.keys, g.init):
+            fh.write("VERTEX2 %d %r %r %r\n" % (k, float(p[0]), float(p[1]), float(p[2])))
+        for a, b, z, o in zip(g.k1, g.k2, g.z, om):
+            vals = list(z) + [o[0, 0], o[0, 1], o[1, 1], o[2, 2], o[0, 2], o[1, 2]]
+            fh.write("EDGE2 %d %d " % (a, b) + " ".join(repr(float(v)) for v in vals) + "\n")
+    prob = O.Problem.from_graph(g)
+    ox, otr = O.lm_optimize(prob, g.init)
+    with graph.Graph() as G:
+        G.load_g2o(path)
+        G.add_prior(g.prior_key, g.prior_pose, g.prior_cov)
+        st = G.optimize()
+        _, x = G.poses()
+    # the file carries inv(Q) computed by numpy, the oracle inverts Q itself: one extra rounding per factor
+    assert st["chi2_final"] == pytest.approx(2 * otr.errors[-1], rel=1e-8)
+    assert _pose_diff(x, ox) <= POSE_ATOL
+
+
+def test_g2o_load_is_all_or_nothing(tmp_path):
+    f = tmp_path / "bad.g2o"
+    f.write_text("VERTEX_SE2 0 0 0 0\nVERTEX_SE2 1 1 0 0\nEDGE_SE2 0 5 1 0 0 1 0 0 1 0 1\n")
+    with graph.Graph() as G:
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.load_g2o(f)
+        assert e.value.status == _lib.GS_ENOKEY
+        assert G.num_vertices == 0 and G.num_factors == 0
