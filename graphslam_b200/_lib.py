@@ -75,6 +75,8 @@ SIGNATURES = {
     "gs_get_pattern": (C.c_int, [C.c_void_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t)]),
     "gs_get_system": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     "gs_solve_linear": (C.c_int, [C.c_void_p, C.c_double, c_double_p, C.POINTER(C.c_int), c_double_p]),
+    "gs_marginal_covariance": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
+    "gs_marginal_covariances": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p]),
     "gs_get_trace": (C.c_int, [C.c_void_p, C.c_size_t, c_double_p, c_double_p, c_i32_p, C.POINTER(C.c_size_t)]),
     "gs_profile_pcg": (C.c_int, [C.c_void_p, C.c_double, C.c_int, c_double_p, c_double_p]),
     "gs_profile_outer": (C.c_int, [C.c_void_p, C.c_int, c_double_p, c_double_p]),

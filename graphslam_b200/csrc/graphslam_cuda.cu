@@ -1425,6 +1425,72 @@ gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_it
   return GS_OK;
 }
 
+// Marginals(graph, values).marginalCovariance(key): the (key, key) 3x3 block of (J^T Omega J)^-1 at the
+// current values, in the tangent space of that pose (the reference has it commented out,
+// graph.cpp:120,126-127).  Three PCG solves with unit right-hand sides per pose, undamped, on the
+// assembled system; on several ranks the owner of the pose broadcasts the three rows.
+gs_status gs_marginal_covariances(gs_graph* g, size_t n, const uint64_t* keys, double* cov9s) {
+  if (!g || (n && (!keys || !cov9s))) return GS_EINVAL;
+  for (size_t k = 0; k < n; ++k)
+    if (g->find(keys[k]) < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[k]);
+  if (gs_status s = prepare(g, nullptr)) return s;
+  if (!g->system_valid)
+    if (gs_status s = launch_assemble(g)) return s;
+  const size_t nb = sizeof(double) * 3 * (size_t)std::max(g->n_own, 1);
+  DevBuf<double> keep, row;
+  GS_CUDA(g, keep.alloc(3 * (size_t)std::max(g->n_own, 1)));
+  GS_CUDA(g, row.alloc(4));
+  GS_CUDA(g, cudaMemcpyAsync(keep.p, g->d_b.p, nb, cudaMemcpyDeviceToDevice, g->stream));
+  g->system_valid = false;   // b is borrowed for the unit right-hand sides; valid again once it is back
+  gs_status rc = GS_OK;
+  const double minus_one = -1.0;
+  for (size_t k = 0; k < n && rc == GS_OK; ++k) {
+    const int dense = g->ins2dense[g->find(keys[k])];
+    const int owner = g->world > 1 ? g->S.part.owner(dense) : 0;
+    const int local = dense - (g->world > 1 ? g->S.part.row_begin(g->rank) : 0);
+    double cols[3][3];
+    for (int c = 0; c < 3 && rc == GS_OK; ++c) {
+      GS_CUDA(g, cudaMemsetAsync(g->d_b.p, 0, nb, g->stream));
+      if (owner == g->rank)
+        GS_CUDA(g, cudaMemcpyAsync(g->d_b.p + 3 * (size_t)local + c, &minus_one, sizeof(double), cudaMemcpyHostToDevice,
+                                   g->stream));
+      int done = 0;
+      rc = pcg_solve(g, 0.0, nullptr, nullptr, &done);
+      if (rc != GS_OK) break;
+      if (done == 2) rc = g->fail(GS_ENAN, "PCG breakdown while solving for a marginal (is the graph anchored by a prior?)");
+      if (done == 3) rc = g->fail(GS_ENOTCONVERGED, "PCG reached pcg_max_iters while solving for a marginal");
+      if (rc != GS_OK) break;
+      const double* src = g->d_x.p + 3 * (size_t)(owner == g->rank ? local : 0);
+      if (g->world > 1) {
+        if (ncclResult_t r = gs::nccl().Broadcast(src, row.p, 3, ncclDouble, owner, g->comm, g->stream); r != ncclSuccess) {
+          rc = g->fail(GS_ENCCL, "ncclBroadcast: %s", gs::nccl().GetErrorString(r));
+          break;
+        }
+        src = row.p;
+      }
+      if (cudaMemcpyAsync(cols[c], src, 3 * sizeof(double), cudaMemcpyDeviceToHost, g->stream) != cudaSuccess ||
+          cudaStreamSynchronize(g->stream) != cudaSuccess) {
+        rc = g->fail(GS_ECUDA, "reading a marginal column: %s", cudaGetErrorString(cudaGetLastError()));
+        break;
+      }
+      g->d2h_bytes += 24.0;
+    }
+    if (rc != GS_OK) break;
+    double* out = cov9s + 9 * k;
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b) out[3 * a + b] = 0.5 * (cols[b][a] + cols[a][b]);   // PCG columns agree to its tolerance
+  }
+  // put the gradient back whatever happened
+  if (cudaMemcpyAsync(g->d_b.p, keep.p, nb, cudaMemcpyDeviceToDevice, g->stream) == cudaSuccess &&
+      cudaStreamSynchronize(g->stream) == cudaSuccess)
+    g->system_valid = true;
+  return rc;
+}
+
+gs_status gs_marginal_covariance(gs_graph* g, uint64_t key, double cov9[9]) {
+  return gs_marginal_covariances(g, 1, &key, cov9);
+}
+
 gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n) {
   if (!g) return GS_EINVAL;
   const size_t m = g->tr_tries.size();

@@ -185,6 +185,13 @@ class Graph:
         self._ck(self._lib.gs_get_transfer_bytes(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def marginal_covariances(self, keys) -> np.ndarray:
+        """(n, 3, 3) marginal covariances of the given poses at the current values (gtsam::Marginals)."""
+        keys = np.ascontiguousarray(np.atleast_1d(keys), dtype=np.uint64)
+        out = np.zeros((keys.shape[0], 3, 3))
+        self._ck(self._lib.gs_marginal_covariances(self._h, keys.shape[0], keys.ctypes.data_as(c_u64_p), _dp(out)))
+        return out
+
     def pose(self, key: int) -> np.ndarray:
         out = np.zeros(3)
         self._ck(self._lib.gs_get_pose(self._h, int(key), _dp(out)))

@@ -166,6 +166,13 @@ gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr /* N+1 */, int32_t* colidx
 gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2);
 /* solve (H + lambda*I) delta = -b at the current linearisation by block-Jacobi PCG; delta[3N] */
 gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual);
+/* gtsam::Marginals(graph, poses_opti).marginalCovariance(id)     graph.cpp:120, 126-127 (commented out
+ * in the reference): the 3x3 covariance of one pose in its own tangent space = the (id, id) block of
+ * (J^T Omega J)^-1 at the current values.  Three undamped PCG solves per pose on the device; cov9 row-major.
+ * On a distributed graph every rank calls it with the same keys and receives the same values. */
+gs_status gs_marginal_covariance(gs_graph* g, uint64_t key, double cov9[9]);
+gs_status gs_marginal_covariances(gs_graph* g, size_t n, const uint64_t* keys, double* cov9s);
+
 /* per-outer-iteration trace of the last gs_optimize: errors[n+1] (= chi2/2, [0] initial), lambdas[n], tries[n] */
 gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n);
 

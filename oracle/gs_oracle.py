@@ -317,6 +317,23 @@ def solve_damped(h, b, lam, diag=None):
     return lu.solve(-b.ravel()).reshape(-1, 3)
 
 
+def marginal_covariances(prob: Problem, poses, idx, mode=JAC_GTSAM_DEFAULT):
+    """gtsam::Marginals(graph, values).marginalCovariance(key) for each dense index in idx: the (key, key) 3x3 block
+    of the inverse of the Hessian J^T Omega J of the graph linearised at `poses` (tangent space of each pose).
+    The reference has the call commented out (src/graph/src/graph.cpp:120, 126-127).  Exact sparse LU."""
+    h, _, _ = prob.linearize(np.asarray(poses, dtype=np.float64), mode)
+    lu = spla.splu(h.tocsc(), permc_spec="MMD_AT_PLUS_A", diag_pivot_thresh=0.0, options=dict(SymmetricMode=True))
+    idx = np.atleast_1d(idx)
+    out = np.zeros((idx.shape[0], 3, 3))
+    for k, i in enumerate(idx):
+        rhs = np.zeros((h.shape[0], 3))
+        rhs[3 * i:3 * i + 3] = np.eye(3)
+        sol = lu.solve(rhs)
+        blk = sol[3 * i:3 * i + 3]
+        out[k] = 0.5 * (blk + blk.T)
+    return out
+
+
 def lm_optimize(prob: Problem, init, params: LMParams | None = None, solver=None):
     """LevenbergMarquardtOptimizer(graph, initial).optimize() restated (GTSAM 4.0.x
     NonlinearOptimizer::defaultOptimize + LevenbergMarquardtOptimizer::iterate/tryLambda).

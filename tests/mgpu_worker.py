@@ -29,6 +29,9 @@ def main():
     errors, lambdas, tries = G.trace()
     # warm-started second solve after appending nothing: exercises values staying on the devices
     st2 = G.optimize()
+    # marginals: the owner of each pose broadcasts its rows; same bits as one GPU (same PCG)
+    pick = np.array([g.keys[0], g.keys[n // 2], g.keys[-1]], dtype=np.uint64)
+    cov = G.marginal_covariances(pick)
     G.close()
     ok = True
     if rank == 0:
@@ -39,7 +42,8 @@ def main():
             _, x1 = G1.poses()
             e1, l1, t1 = G1.trace()
             st1b = G1.optimize()
-        ok = (chi0 == chi0_1 and np.array_equal(x, x1) and np.array_equal(errors, e1) and tries.tolist() == t1.tolist()
+            cov1 = G1.marginal_covariances(pick)
+        ok = (np.array_equal(cov, cov1) and chi0 == chi0_1 and np.array_equal(x, x1) and np.array_equal(errors, e1) and tries.tolist() == t1.tolist()
               and st["pcg_iterations_total"] == st1["pcg_iterations_total"] and st2["chi2_final"] == st1b["chi2_final"])
         print(f"[mgpu] world={dist.get_world_size()} N={g.n} iterations={st['iterations']} pcg={st['pcg_iterations_total']} "
               f"chi2 {st['chi2_initial']:.6g}->{st['chi2_final']:.6g} bitwise_equal_to_single_gpu={ok} "

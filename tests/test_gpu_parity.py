@@ -342,3 +342,34 @@ def test_g2o_load_is_all_or_nothing(tmp_path):
             G.load_g2o(f)
         assert e.value.status == _lib.GS_ENOKEY
         assert G.num_vertices == 0 and G.num_factors == 0
+
+
+def test_marginal_covariances_match_oracle():
+    """gtsam::Marginals (commented out at graph.cpp:120,126-127): blocks of (J^T Omega J)^-1 at the optimum."""
+    g = synth.config("C1", n=800, full_cov=True)
+    prob = O.Problem.from_graph(g)
+    with _load(g) as G:
+        G.optimize()
+        keys, x = G.poses()
+        pick = np.array([keys[0], keys[1], keys[len(keys) // 2], keys[-1]], dtype=np.uint64)
+        cov = G.marginal_covariances(pick)
+        chi2_before = G.chi2()
+        _, _, _, b_after, _ = G.system()                      # the borrowed gradient vector is back
+    idx = np.searchsorted(keys, pick)
+    ref = O.marginal_covariances(prob, x, idx)
+    for c, r in zip(cov, ref):
+        assert np.abs(c - r).max() <= 1e-8 * np.abs(r).max()
+        assert np.array_equal(c, c.T) and np.all(np.linalg.eigvalsh(c) > 0)
+    # uncertainty grows away from the anchored first pose
+    assert np.trace(cov[0]) < np.trace(cov[2])
+    _, ob, _ = prob.linearize(x)
+    assert np.abs(b_after - ob).max() <= 1e-9 * max(np.abs(ob).max(), 1.0)
+    assert chi2_before == pytest.approx(2 * prob.error(x), rel=1e-10)
+
+
+def test_marginal_covariance_unknown_key():
+    g = synth.config("C1", n=50)
+    with _load(g) as G:
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.marginal_covariances([10_000_000])
+        assert e.value.status == _lib.GS_ENOKEY

@@ -164,3 +164,23 @@ def test_generator_reproducible():
     i, j = g.dense_edges()
     loops = i > j
     assert loops.sum() == g.meta["n_loops"] and np.all(i[loops] - j[loops] >= 10)   # graph.cpp:15
+
+
+def test_marginal_covariances_equal_blocks_of_the_dense_inverse():
+    """gtsam::Marginals restated (oracle.marginal_covariances) against numpy's dense inverse of J^T Omega J."""
+    from graphslam_b200 import synth
+    g = synth.config("C1", n=80, full_cov=True)
+    prob = O.Problem.from_graph(g)
+    h, _, _ = prob.linearize(g.init)
+    inv = np.linalg.inv(h.toarray())
+    idx = [0, 7, 79]
+    m = O.marginal_covariances(prob, g.init, idx)
+    for k, i in enumerate(idx):
+        blk = inv[3 * i:3 * i + 3, 3 * i:3 * i + 3]
+        assert np.abs(m[k] - blk).max() <= 1e-10 * np.abs(blk).max()
+    # two poses and one prior with identity noise: Sigma_0 = I, Sigma_1 = I + Ad I Ad^T >= I
+    p = O.Problem(2, np.array([0]), np.array([1]), np.array([[1.0, 0.0, 0.0]]), np.eye(3).reshape(1, 9), 0,
+                  np.zeros(3), np.eye(3).reshape(9))
+    m = O.marginal_covariances(p, np.array([[0.0, 0, 0], [1.0, 0, 0]]), [0, 1])
+    assert np.allclose(m[0], np.eye(3), atol=1e-12)
+    assert np.all(np.linalg.eigvalsh(m[1] - np.eye(3)) > -1e-12)
