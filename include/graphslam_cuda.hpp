@@ -52,6 +52,13 @@ class PoseGraph {
     ck(gs_chi2(g_, &v));
     return v;
   }
+  void marginal_covariance(uint64_t key, double cov9[9]) { ck(gs_marginal_covariance(g_, key, cov9)); }     // :120,126-127
+  gs_g2o_counts load_g2o(const char* path) {               // g2o / TORO text; the reference has no persistence (:5-10)
+    gs_g2o_counts c;
+    ck(gs_load_g2o(g_, path, &c));
+    return c;
+  }
+  void save_g2o(const char* path) { ck(gs_save_g2o(g_, path)); }
   size_t num_vertices() const {
     size_t n = 0;
     gs_num_vertices(g_, &n);
