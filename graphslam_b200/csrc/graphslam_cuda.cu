@@ -117,8 +117,11 @@ struct gs_graph {
   int peer_generation[gs::kMaxRanks] = {0};
   unsigned int nbr_mask = 0;
   DevBuf<unsigned int> d_seq;             // [0] sequence base, [32] ticket (a line each)
+  int n_push_tiles = 0;                   // tiles that send halo rows
+  DevBuf<int4> d_hp_order;                 // CTA -> tile for k_dir_p2p (sending tiles first)
+  DevBuf<int> d_tile_halo;                // [tile] 1 when the tile's rows reference ghost columns
   DevBuf<gs::P2PWindow*> d_winptr;        // [rank] window pointers as the kernels see them
-  DevBuf<int> d_hp_tile, d_hp_row;
+  DevBuf<int> d_hp_row;
   DevBuf<double*> d_hp_dst;
   DevBuf<char> d_xchg;
   double* pvec = nullptr;                 // direction vector p (owned rows, then the NCCL path's ghost rows)
@@ -348,6 +351,7 @@ gs::P2PCtx p2p_ctx(gs_graph* g, unsigned int k_local) {
   x.k_local = k_local;
   x.ticket = g->d_seq.p + 32;   // its own 128-byte line
   x.spin_limit = 2000000000LL;
+  x.tile_halo = g->d_tile_halo.p;
   return x;
 }
 
@@ -363,9 +367,10 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
     } else {
       gs::HaloPush h;
-      h.tile_ptr = g->d_hp_tile.p;
       h.row = g->d_hp_row.p;
       h.dst = g->d_hp_dst.p;
+      h.n_push_tiles = g->n_push_tiles;
+      h.order = g->d_hp_order.p;
       gs::k_dir_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x, h);
     }
     return GS_OK;
@@ -518,9 +523,26 @@ gs_status prepare_p2p(gs_graph* g) {
     tile_ptr[ent[e].row / gs::kTile + 1]++;
   }
   for (int t = 0; t < nt; ++t) tile_ptr[t + 1] += tile_ptr[t];
-  if (gs_status s = upload(g, g->d_hp_tile, tile_ptr)) return s;
+  std::vector<int4> order;
+  order.reserve(nt);
+  for (int t = 0; t < nt; ++t)
+    if (tile_ptr[t + 1] > tile_ptr[t]) order.push_back(make_int4(t, tile_ptr[t], tile_ptr[t + 1], 0));
+  g->n_push_tiles = (int)order.size();
+  for (int t = 0; t < nt; ++t)
+    if (tile_ptr[t + 1] == tile_ptr[t]) order.push_back(make_int4(t, 0, 0, 0));
+  if (gs_status s = upload(g, g->d_hp_order, order)) return s;
   if (gs_status s = upload(g, g->d_hp_row, rows)) return s;
   if (gs_status s = upload(g, g->d_hp_dst, dsts)) return s;
+  std::vector<int> tile_halo(nt, 0);
+  for (int r = 0; r < g->n_own; ++r) {
+    const int w = S.rsell.width[r / gs::kSlice];
+    for (int k = 0; k < w; ++k)
+      if (S.r_col[S.rsell.pos(r, k)] >= g->n_own) {
+        tile_halo[r / gs::kTile] = 1;
+        break;
+      }
+  }
+  if (gs_status s = upload(g, g->d_tile_halo, tile_halo)) return s;
   std::vector<gs::P2PWindow*> wins(gs::kMaxRanks, nullptr);
   for (int q = 0; q < g->world; ++q) wins[q] = reinterpret_cast<gs::P2PWindow*>(q == g->rank ? g->win : g->peer_win[q]);
   if (gs_status s = upload(g, g->d_winptr, wins)) return s;

@@ -6,20 +6,25 @@
 // write into it directly (the owned part of p stays in ordinary memory: keeping the whole vector in
 // the exported allocation made every kernel that streams p several times slower):
 //
-//   k_spmv_p2p    waits until its neighbours have pushed the ghost rows of p for this iteration,
-//                 multiplies, and its last CTA stores this rank's p.Ap segment sums into EVERY
-//                 rank's window, fences, and raises a flag there.
-//   k_update_p2p  waits for all ranks' p.Ap flags, adds the 8 segment sums in the fixed global order
-//                 (so alpha has the same bits everywhere), updates x, r, z and pushes its r.z / r.r
-//                 segment sums the same way.
-//   k_dir_p2p     waits for all r.z / r.r flags, forms beta and the stopping test, updates p and
-//                 stores the rows its neighbours need straight into their ghost slots; the last CTA
-//                 raises the "p ready" flag at the neighbours.
+//   k_spmv_p2p    tiles that multiply ghost rows wait until the neighbours have pushed them for this
+//                 iteration (interior tiles start at once); the last CTA sends this rank's p.Ap segment
+//                 sums to EVERY rank's window as flagged words.
+//   k_update_p2p  one warp per CTA spins on the 16 flagged words of p.Ap, rebuilds the 8 segment sums and
+//                 adds them in the fixed global order (so alpha has the same bits everywhere); the CTA
+//                 updates x, r, z and the last CTA sends r.z / r.r the same way.
+//   k_dir_p2p     waits for the 32 words of r.z / r.r, forms beta and the stopping test, updates p and
+//                 stores the rows its neighbours need straight into their ghost slots; the last SENDING
+//                 tile raises the "p ready" flag at the neighbours (sending tiles are scheduled first).
 //
-// Flags carry the global iteration sequence number, which is a kernel argument (position inside the
-// captured batch) plus a device-resident base that only moves between batches, so no kernel reads a
-// word that another CTA of the same launch writes.  Every spin is bounded: after ~1 s a rank gives
-// up, marks the solve failed (done = 4) and every later kernel returns at once.
+// Stamps and flags carry the global iteration sequence number, which is a kernel argument (position inside
+// the captured batch) plus a device-resident base that only moves between batches, so no kernel reads a
+// word that another CTA of the same launch writes.  Every spin is bounded: after ~1 s a rank gives up,
+// marks the solve failed (done = 4) and every later kernel returns at once.
+//
+// Measured on 2 x B200, C3 (500k rows per rank), per iteration: 206 us with every thread reading the landed
+// sums -> 111 us (one warp per CTA reads them) -> 99 us (flagged words instead of data + system fence +
+// flag) -> 93 us (sending tiles first, only they take the ticket); the three kernels now cost what the
+// single-GPU kernels cost on a 500k-row graph, except the direction update (18 us against 10 us).
 #pragma once
 #include "kernels.cuh"
 
@@ -28,14 +33,16 @@ namespace gs {
 constexpr int kMaxRanks = kSegments;
 constexpr size_t kWindowHeaderBytes = 4096;   // flags + segment sums; the ghost rows of p start here
 
+// Segment sums travel as "flagged words" (the low-latency protocol NCCL calls LL): every double is split into
+// two 8-byte words {32 data bits, 32-bit iteration stamp}.  An aligned 8-byte store is delivered whole, so a
+// reader that sees the stamp has the data: no fence on the writer, no separate flag, one round trip on the reader.
+constexpr int kLLWordsPerQuantity = 2 * kSegments;   // 16
+
 struct P2PWindow {
   unsigned int halo_flag[kMaxRanks];   // [source rank] p pushed by that rank is valid for spmv number (value - 1)
-  unsigned int pap_flag[kMaxRanks];    // [source rank] its p.Ap segment sums of iteration (value - 1) have landed
-  unsigned int rz_flag[kMaxRanks];
-  unsigned int pad[kMaxRanks];
-  double seg_pap[2][kSegments];        // [iteration parity][global segment]
-  double seg_rz[2][kSegments];
-  double seg_rr[2][kSegments];
+  unsigned int pad[24];                // keeps the word arrays on their own 128-byte lines
+  unsigned long long ll_pap[2][kLLWordsPerQuantity];       // [iteration parity][2 * global segment + half]
+  unsigned long long ll_upd[2][2 * kLLWordsPerQuantity];   // r.z words, then r.r words
 };
 static_assert(sizeof(P2PWindow) <= kWindowHeaderBytes, "window header too small");
 
@@ -49,12 +56,16 @@ struct P2PCtx {
   unsigned int k_local;        // position of this iteration inside the batch
   unsigned int* ticket;        // last-CTA counter for the halo push
   long long spin_limit;        // clock64 ticks before a wait gives up
+  const int* tile_halo;        // per tile: 1 when some row of the tile multiplies a ghost row of p
 };
 
 struct HaloPush {
-  const int* tile_ptr;         // per tile: range of entries
   const int* row;              // local row to send
   double* const* dst;          // address of its 3 doubles in the peer's window
+  int n_push_tiles;            // tiles with at least one entry: the last of them to finish raises the flags
+  const int4* order;           // CTA -> (tile, first entry, end entry, -), sending tiles first: their remote stores and
+                               // system fences overlap the rest of the kernel instead of forming its tail (they are
+                               // the first and last tiles of the range)
 };
 
 // Flags and landing zones live in THIS GPU's memory and are written by peers over NVLink; remote stores
@@ -70,28 +81,30 @@ __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) 
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long ld_relaxed64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 // What one CTA learns at the top of a kernel: whether the wait succeeded, and the totals it waited for.
 struct WaitOut {
   int ok;
   double tot[2];
 };
 
-// Lane q of warp 0 spins until flags[q] >= target (q in mask); false on timeout (then sc->done = 4).
-// The same warp then reads the NT landed segment-sum arrays ONCE per CTA (lanes 0..7, one request)
-// and adds them in the fixed global order; everybody else takes the totals from shared memory.
-// (Letting every thread read the eight sums past L1 put ~10^5 requests per launch on a single L2
-// slice and made the three kernels 3-10x slower than their single-GPU forms.)
-template <int NT>
+// Halo flags: lane q of warp 0 spins until flags[q] >= target (q in mask); false on timeout (sc->done = 4).
 __device__ __forceinline__ bool wait_flags(const unsigned int* flags, unsigned int mask, unsigned int target, Scalars* sc,
-                                           long long limit, WaitOut* out, int which, const double* seg0,
-                                           const double* seg1) {
+                                           long long limit, WaitOut* out) {
   if (threadIdx.x < 32) {
     int ok = 1;
     const long long w0 = clock64();
     if (threadIdx.x < kMaxRanks && ((mask >> threadIdx.x) & 1u)) {
-      const long long t0 = clock64();
       while ((int)(ld_relaxed(flags + threadIdx.x) - target) < 0) {
-        if (clock64() - t0 > limit) {
+        if (clock64() - w0 > limit) {
           ok = 0;
           break;
         }
@@ -99,21 +112,55 @@ __device__ __forceinline__ bool wait_flags(const unsigned int* flags, unsigned i
     }
     ok = __all_sync(0xffffffffu, ok);
     __threadfence();
+    if (threadIdx.x == 0) {
+      if (!ok) sc->done = 4;
+      out->ok = ok;
+    }
+  }
+  __syncthreads();
+  return out->ok != 0;
+}
+
+// Segment sums: lane l of warp 0 spins on flagged word l until it carries `stamp`; the warp then rebuilds the
+// 8 doubles of each of the NQ quantities and adds them in the fixed global segment order.  Once per CTA: one
+// request for the 128/256 bytes (every thread reading them made ~10^5 requests per launch to one L2 slice).
+template <int NQ>
+__device__ __forceinline__ bool wait_sums(const unsigned long long* words, unsigned int stamp, Scalars* sc, long long limit,
+                                          WaitOut* out, int which) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    int ok = 1;
+    unsigned long long w = 0;
+    const long long w0 = clock64();
+    if (lane < NQ * kLLWordsPerQuantity) {
+      for (;;) {
+        w = ld_relaxed64(words + lane);
+        if ((unsigned int)(w >> 32) == stamp) break;
+        if (clock64() - w0 > limit) {
+          ok = 0;
+          break;
+        }
+      }
+    }
+    ok = __all_sync(0xffffffffu, ok);
+    const int half = (int)(unsigned int)(w & 0xffffffffull);
 #pragma unroll
-    for (int t = 0; t < NT; ++t) {
-      const double* seg = t == 0 ? seg0 : seg1;
-      const double v = threadIdx.x < kSegments ? __ldcg(seg + threadIdx.x) : 0.0;
+    for (int t = 0; t < NQ; ++t) {
       double acc = 0.0;
 #pragma unroll
-      for (int g = 0; g < kSegments; ++g) acc += __shfl_sync(0xffffffffu, v, g);
-      if (threadIdx.x == 0) out->tot[t] = acc;
+      for (int g = 0; g < kSegments; ++g) {
+        const int lo = __shfl_sync(0xffffffffu, half, t * kLLWordsPerQuantity + 2 * g);
+        const int hi = __shfl_sync(0xffffffffu, half, t * kLLWordsPerQuantity + 2 * g + 1);
+        acc += __hiloint2double(hi, lo);
+      }
+      if (lane == 0) out->tot[t] = acc;
     }
-    if (threadIdx.x == 0) {
+    if (lane == 0) {
       if (!ok) sc->done = 4;
       out->ok = ok;
       if (blockIdx.x == 0) {
         sc->spin[which] += clock64() - w0;
-        if (which == 0) sc->spin[3] += 1;
+        if (which == 1) sc->spin[3] += 1;
       }
     }
   }
@@ -121,11 +168,11 @@ __device__ __forceinline__ bool wait_flags(const unsigned int* flags, unsigned i
   return out->ok != 0;
 }
 
-// tile partials -> this rank's segment sums -> every rank's window, then the flag.  NQ quantities,
-// dst_of(window, q) gives the landing array of quantity q.
-template <int NQ, typename FlagOf, typename DstOf>
+// tile partials -> this rank's segment sums -> flagged words in every rank's window (no fence, no flag).
+// words_of(window) = the landing array of this reduction; quantity q occupies words [16 q, 16 q + 16) of a parity.
+template <int NQ, typename WordsOf>
 __device__ __forceinline__ void reduce_push(const ReduceCtx& c, const P2PCtx& x, const double (&v)[NQ], unsigned int par,
-                                            unsigned int stamp, FlagOf flag_of, DstOf dst_of, double* red, int* flag) {
+                                            unsigned int stamp, WordsOf words_of, double* red, int* flag) {
   __shared__ double mysegs[NQ > 1 ? NQ : 1][kSegments];
 #pragma unroll
   for (int q = 0; q < NQ; ++q) {
@@ -150,16 +197,17 @@ __device__ __forceinline__ void reduce_push(const ReduceCtx& c, const P2PCtx& x,
       }
     }
     __syncthreads();
-    // thread q serves rank q: data, system fence, flag
-    if ((int)threadIdx.x < x.world) {
-      P2PWindow* wq = x.win[threadIdx.x];
-#pragma unroll
-      for (int q = 0; q < NQ; ++q) {
-        double* dst = dst_of(wq, q) + (size_t)par * kSegments + (size_t)x.rank * x.spr;
-        for (int s = 0; s < x.spr; ++s) dst[s] = mysegs[q][s];
-      }
-      __threadfence_system();
-      st_release_sys(flag_of(wq) + x.rank, stamp);
+    // one thread per (destination rank, quantity, segment, half)
+    const int per_rank = NQ * x.spr * 2;
+    for (int t = threadIdx.x; t < x.world * per_rank; t += blockDim.x) {
+      const int d = t / per_rank, u = t - d * per_rank;
+      const int q = u / (x.spr * 2), sh = u - q * (x.spr * 2);
+      const int s = sh >> 1, h = sh & 1;
+      const double val = mysegs[q][s];
+      const unsigned int bits = (unsigned int)(h ? __double2hiint(val) : __double2loint(val));
+      unsigned long long* dst =
+          words_of(x.win[d]) + (size_t)par * (NQ * kLLWordsPerQuantity) + q * kLLWordsPerQuantity + 2 * (x.rank * x.spr + s) + h;
+      st_relaxed64(dst, ((unsigned long long)stamp << 32) | bits);
     }
     if (threadIdx.x == 0) *c.counter = 0u;
   }
@@ -173,24 +221,26 @@ __global__ void __launch_bounds__(kThreads) k_spmv_p2p(const SpmvView a, const d
   if (c.sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
   P2PWindow* me = x.me;
-  if (!wait_flags<0>(me->halo_flag, x.nbr_mask, S + 1, c.sc, x.spin_limit, &wo, 0, nullptr, nullptr)) return;
+  // only tiles that touch ghost rows wait for the neighbours' pushes: the interior tiles start at once and
+  // hide the arrival of the halo (the p.Ap flag below is raised after ALL tiles, so the iteration order holds)
+  if (x.tile_halo[blockIdx.x] && !wait_flags(me->halo_flag, x.nbr_mask, S + 1, c.sc, x.spin_limit, &wo)) return;
   const double lambda = c.sc->lambda;
   const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[1] = {0.0};
   if (r < a.n_own) v[0] = spmv_row(a, p, pg, y, r, lambda);
-  reduce_push<1>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return w->pap_flag; },
-                 [](P2PWindow* w, int) { return &w->seg_pap[0][0]; }, red, &flag);
+  reduce_push<1>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_pap[0][0]; }, red, &flag);
 }
 
 __global__ void __launch_bounds__(kThreads) k_update_p2p(const PcgView a, const ReduceCtx c, const P2PCtx x) {
   __shared__ double red[8];
   __shared__ int flag;
   __shared__ WaitOut wo;
+  // (loading the row's 18 operands before the wait was measured slower: 36-40 us against 31-37 us)
+  const int r = blockIdx.x * kThreads + threadIdx.x;
   if (c.sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
   P2PWindow* me = x.me;
-  if (!wait_flags<1>(me->pap_flag, (1u << x.world) - 1u, S + 1, c.sc, x.spin_limit, &wo, 1, me->seg_pap[S & 1u], nullptr))
-    return;
+  if (!wait_sums<1>(me->ll_pap[S & 1u], S + 1, c.sc, x.spin_limit, &wo, 1)) return;
   const double pAp = wo.tot[0];
   if (!(pAp > 0.0)) {  // breakdown: the same on every rank, nobody goes on
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -200,24 +250,31 @@ __global__ void __launch_bounds__(kThreads) k_update_p2p(const PcgView a, const 
     return;
   }
   const double alpha = c.sc->rzv[(S + 1u) & 1u] / pAp;   // r.z of the previous iterate
-  const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[2] = {0.0, 0.0};
   if (r < a.n_own) pcg_update_row(a, r, alpha, v[0], v[1]);
-  reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return w->rz_flag; },
-                 [](P2PWindow* w, int q) { return q == 0 ? &w->seg_rz[0][0] : &w->seg_rr[0][0]; }, red, &flag);
+  reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_upd[0][0]; }, red, &flag);
 }
 
-// p = z + beta p ; rows that neighbours need go straight into their ghost slots
+// p = z + beta p over the tile's 768 contiguous doubles; rows that neighbours need go straight into their ghost slots
 __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const ReduceCtx c, const P2PCtx x, const HaloPush h) {
   __shared__ int flag;
   __shared__ WaitOut wo;
   Scalars* sc = c.sc;
+  // operands first (they do not depend on beta), then the wait
+  const size_t n3 = 3 * (size_t)a.n_own;
+  const int4 job = ldg(h.order + blockIdx.x);
+  const size_t e0 = (size_t)job.x * (3 * kThreads) + threadIdx.x;
+  double zv[3], pv[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const size_t e = e0 + (size_t)k * kThreads;
+    zv[k] = e < n3 ? a.z[e] : 0.0;
+    pv[k] = e < n3 ? a.p[e] : 0.0;
+  }
   if (sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
   P2PWindow* me = x.me;
-  if (!wait_flags<2>(me->rz_flag, (1u << x.world) - 1u, S + 1, sc, x.spin_limit, &wo, 2, me->seg_rz[S & 1u],
-                     me->seg_rr[S & 1u]))
-    return;
+  if (!wait_sums<2>(me->ll_upd[S & 1u], S + 1, sc, x.spin_limit, &wo, 2)) return;
   const double rz = wo.tot[0];
   const double rr = wo.tot[1];
   const double rz_old = sc->rzv[(S + 1u) & 1u];
@@ -236,12 +293,16 @@ __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const Red
     if (done) sc->done = done;
   }
   if (done) return;
-  const int r = blockIdx.x * kThreads + threadIdx.x;
-  if (r < a.n_own) pcg_dir_row(a, r, beta);
-  __syncthreads();
-  const int e0 = h.tile_ptr[blockIdx.x], e1 = h.tile_ptr[blockIdx.x + 1];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const size_t e = e0 + (size_t)k * kThreads;
+    if (e < n3) a.p[e] = zv[k] + beta * pv[k];
+  }
+  const int h0 = job.y, h1 = job.z;
+  if (h1 == h0) return;   // nothing to send from this tile (uniform over the CTA)
+  __syncthreads();        // the tile's new p is visible to the CTA
   bool pushed = false;
-  for (int e = e0 + (int)threadIdx.x; e < e1; e += kThreads) {
+  for (int e = h0 + (int)threadIdx.x; e < h1; e += kThreads) {
     const double* src = a.p + 3 * (size_t)h.row[e];
     double* dst = h.dst[e];
     dst[0] = __ldcg(src);
@@ -253,10 +314,10 @@ __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const Red
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned int t = atomicAdd(x.ticket, 1u);
-    flag = (t == gridDim.x - 1);
+    flag = (t == (unsigned int)h.n_push_tiles - 1u);
   }
   __syncthreads();
-  if (flag) {
+  if (flag) {   // the last sending tile: every neighbour's rows are in place
     if ((int)threadIdx.x < x.world && ((x.nbr_mask >> threadIdx.x) & 1u))
       st_release_sys(&x.win[threadIdx.x]->halo_flag[x.rank], S + 2);
     if (threadIdx.x == 0) *x.ticket = 0u;

@@ -456,20 +456,42 @@ GS_HD void pcg_init_row(const PcgView& a, int v, double& rz, double& rr) {
 }
 
 // x += alpha p ; r -= alpha Ap ; z = Minv r ; out: r.z, r.r
-GS_HD void pcg_update_row(const PcgView& a, int v, double alpha, double& rz, double& rr) {
+// In two halves so that a kernel which has to wait for alpha (peer-memory path) can have the row's
+// loads in flight while it waits; pcg_update_row is the two halves back to back (same arithmetic).
+struct UpdateRow {
+  double p0, p1, p2, q0, q1, q2, x0, x1, x2, r0, r1, r2;
+  double m00, m01, m02, m11, m12, m22;
+};
+
+GS_HD void pcg_update_load(const PcgView& a, int v, UpdateRow& u) {
+  const size_t o = 3 * (size_t)v, n = (size_t)a.n_own, w = (size_t)v;
+  u.p0 = a.p[o]; u.p1 = a.p[o + 1]; u.p2 = a.p[o + 2];
+  u.q0 = a.Ap[o]; u.q1 = a.Ap[o + 1]; u.q2 = a.Ap[o + 2];
+  u.x0 = a.x[o]; u.x1 = a.x[o + 1]; u.x2 = a.x[o + 2];
+  u.r0 = a.r[o]; u.r1 = a.r[o + 1]; u.r2 = a.r[o + 2];
+  u.m00 = ldg(a.Minv + w); u.m01 = ldg(a.Minv + n + w); u.m02 = ldg(a.Minv + 2 * n + w);
+  u.m11 = ldg(a.Minv + 3 * n + w); u.m12 = ldg(a.Minv + 4 * n + w); u.m22 = ldg(a.Minv + 5 * n + w);
+}
+
+GS_HD void pcg_update_apply(const PcgView& a, int v, const UpdateRow& u, double alpha, double& rz, double& rr) {
   const size_t o = 3 * (size_t)v;
-  const double p0 = a.p[o], p1 = a.p[o + 1], p2 = a.p[o + 2];
-  const double q0 = a.Ap[o], q1 = a.Ap[o + 1], q2 = a.Ap[o + 2];
-  a.x[o] += alpha * p0;
-  a.x[o + 1] += alpha * p1;
-  a.x[o + 2] += alpha * p2;
-  const double r0 = a.r[o] - alpha * q0, r1 = a.r[o + 1] - alpha * q1, r2 = a.r[o + 2] - alpha * q2;
-  double z0, z1, z2;
-  apply_minv(a.Minv, (size_t)a.n_own, (size_t)v, r0, r1, r2, z0, z1, z2);
+  a.x[o] = u.x0 + alpha * u.p0;
+  a.x[o + 1] = u.x1 + alpha * u.p1;
+  a.x[o + 2] = u.x2 + alpha * u.p2;
+  const double r0 = u.r0 - alpha * u.q0, r1 = u.r1 - alpha * u.q1, r2 = u.r2 - alpha * u.q2;
+  const double z0 = (u.m00 * r0 + u.m01 * r1) + u.m02 * r2;
+  const double z1 = (u.m01 * r0 + u.m11 * r1) + u.m12 * r2;
+  const double z2 = (u.m02 * r0 + u.m12 * r1) + u.m22 * r2;
   a.r[o] = r0; a.r[o + 1] = r1; a.r[o + 2] = r2;
   a.z[o] = z0; a.z[o + 1] = z1; a.z[o + 2] = z2;
   rz = (r0 * z0 + r1 * z1) + r2 * z2;
   rr = (r0 * r0 + r1 * r1) + r2 * r2;
+}
+
+GS_HD void pcg_update_row(const PcgView& a, int v, double alpha, double& rz, double& rr) {
+  UpdateRow u;
+  pcg_update_load(a, v, u);
+  pcg_update_apply(a, v, u, alpha, rz, rr);
 }
 
 // p = z + beta p
