@@ -373,3 +373,17 @@ def test_marginal_covariance_unknown_key():
         with pytest.raises(graph.GraphSlamError) as e:
             G.marginal_covariances([10_000_000])
         assert e.value.status == _lib.GS_ENOKEY
+
+
+def test_deep_convergence_parity():
+    """SURVEY 8(c) P2: with the error tolerances switched off both sides run far past the reference's stopping point;
+    the accept/reject pattern is then rounding noise, but the minimum they sit in must be the same one."""
+    g = synth.config("C1", n=1500, full_cov=True)
+    prob = O.Problem.from_graph(g)
+    kw = dict(rel_error_tol=0.0, abs_error_tol=0.0, max_iterations=25)
+    ox, otr = O.lm_optimize(prob, g.init, O.LMParams(**kw))
+    with _load(g, **kw) as G:
+        st = G.optimize()
+        _, x = G.poses()
+    assert st["chi2_final"] == pytest.approx(2 * otr.errors[-1], rel=1e-12)
+    assert _pose_diff(x, ox) <= 1e-9
