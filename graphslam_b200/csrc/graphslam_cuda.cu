@@ -715,7 +715,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * nl3, g->stream));
   GS_CUDA(g, cudaMemsetAsync(g->pvec, 0, sizeof(double) * nl3, g->stream));
   g->grid_rows = std::max(S.ntiles, 1);
-  g->grid_flat3 = (int)((3 * (size_t)S.n_own + gs::kThreads - 1) / gs::kThreads);
+  g->grid_flat3 = (int)((3 * (size_t)S.n_own + gs::kThreads * gs::kDirPerThread - 1) / (gs::kThreads * gs::kDirPerThread));
   if (g->grid_flat3 < 1) g->grid_flat3 = 1;
   g->part_stride = g->grid_rows;
   GS_CUDA(g, g->d_part.alloc(2 * (size_t)g->part_stride));
