@@ -28,6 +28,7 @@
 #include "comm.hpp"
 #include "g2o.hpp"
 #include "kernels.cuh"
+#include "kernels_fused.cuh"
 #include "kernels_p2p.cuh"
 
 namespace {
@@ -36,6 +37,8 @@ using gs::LocalStructure;
 using gs::Scalars;
 
 constexpr int kPcgBatch = 32;  // PCG iterations per CUDA-graph launch
+constexpr int kFusedBatch = 128;  // PCG iterations per launch of the persistent small-graph kernel
+static_assert(kFusedBatch % 2 == 0, "an even batch leaves the latest direction in the graph's own p vector");
 
 double now_ms() {
   using namespace std::chrono;
@@ -106,6 +109,11 @@ struct gs_graph {
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
   bool use_graph = true;
+  bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
+  bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
+  int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
+  DevBuf<gs::GridBarrier> d_bar;
+  DevBuf<double> d_p_alt;                 // second direction buffer of the persistent kernel
   // peer-memory path (world > 1): collectives fused into the PCG kernels over NVLink
   bool p2p_wanted = true;                 // GS_P2P=0 keeps the NCCL-per-operation path
   bool p2p = false;                       // windows exchanged, peer-memory kernels in use
@@ -387,6 +395,23 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
 gs_status launch_pcg_iteration(gs_graph* g, unsigned int k_local) {
   for (int stage = 0; stage < 3; ++stage)
     if (gs_status s = launch_pcg_stage(g, stage, k_local)) return s;
+  return GS_OK;
+}
+
+// the persistent small-graph kernel: `n` iterations in one cooperative launch
+gs_status launch_pcg_fused(gs_graph* g, int n) {
+  gs::SpmvView sv = spmv_view(g);
+  gs::PcgView pv = pcg_view(g);
+  double* Ap = g->d_Ap.p;
+  double* p_alt = g->d_p_alt.p;
+  double* part = g->d_part.p;
+  int stride = g->part_stride;
+  const int* seg_tile = g->d_segtile.p;
+  Scalars* sc = g->d_sc.p;
+  gs::GridBarrier* bar = g->d_bar.p;
+  void* args[] = {&sv, &pv, &Ap, &p_alt, &part, &stride, &seg_tile, &sc, &bar, &n};
+  GS_CUDA(g, cudaLaunchCooperativeKernel((const void*)gs::k_pcg_fused, dim3((unsigned)g->grid_rows), dim3(gs::kThreads), args, 0,
+                                         g->stream));
   return GS_OK;
 }
 
@@ -718,7 +743,9 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->grid_flat3 = (int)((3 * (size_t)S.n_own + gs::kThreads * gs::kDirPerThread - 1) / (gs::kThreads * gs::kDirPerThread));
   if (g->grid_flat3 < 1) g->grid_flat3 = 1;
   g->part_stride = g->grid_rows;
-  GS_CUDA(g, g->d_part.alloc(2 * (size_t)g->part_stride));
+  GS_CUDA(g, g->d_part.alloc(3 * (size_t)g->part_stride));
+  g->fused = g->fused_wanted && g->world == 1 && g->fused_capacity > 0 && g->grid_rows <= g->fused_capacity;
+  if (g->fused) GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(g->n_own, 1)));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));  // staging vectors go out of scope
   g->topo_dirty = false;
   g->device_values_valid = false;
@@ -815,8 +842,12 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
   if (gs_status s = begin_p2p_solve(g)) return s;
   GS_CUDA(g, cudaGetLastError());
   const int64_t keep = g->launches;
+  int64_t fused_launches = 0;
   for (;;) {
-    if (g->pcg_exec) {
+    if (g->fused) {
+      if (gs_status s = launch_pcg_fused(g, kFusedBatch)) return s;
+      ++fused_launches;
+    } else if (g->pcg_exec) {
       GS_CUDA(g, cudaGraphLaunch(g->pcg_exec, g->stream));
     } else {
       if (gs_status s = launch_pcg_batch(g, kPcgBatch)) return s;
@@ -830,7 +861,7 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
                  h->spin[3]);
   if (h->done == 4) return g->fail(GS_ENCCL, "a peer rank did not answer within the wait limit (peer-memory PCG)");
   // kernels that did work (the no-op tail of the last batch is not counted)
-  g->launches = keep + launches_per_pcg_iteration(g) * (int64_t)h->iters;
+  g->launches = keep + (g->fused ? fused_launches : launches_per_pcg_iteration(g) * (int64_t)h->iters);
   if (iters_out) *iters_out = h->iters;
   if (relres_out) *relres_out = h->rr0 > 0.0 ? std::sqrt(h->rr / h->rr0) : 0.0;
   if (done_out) *done_out = h->done;
@@ -865,6 +896,19 @@ gs_status create_common(gs_graph* g) {
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   const char* env = std::getenv("GS_PCG_GRAPH");
   g->use_graph = !(env && env[0] == '0');
+  env = std::getenv("GS_PCG_FUSED");
+  g->fused_wanted = !(env && env[0] == '0');
+  {
+    int per_sm = 0, sms = 0, dev = 0, coop = 0;
+    GS_CUDA(g, cudaGetDevice(&dev));
+    GS_CUDA(g, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    GS_CUDA(g, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    GS_CUDA(g, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gs::k_pcg_fused, gs::kThreads, 0));
+    g->fused_capacity = coop ? per_sm * sms : 0;
+    if (const char* cap = std::getenv("GS_PCG_FUSED_MAX_TILES")) g->fused_capacity = std::min(g->fused_capacity, std::atoi(cap));
+  }
+  GS_CUDA(g, g->d_bar.alloc(1));
+  GS_CUDA(g, cudaMemsetAsync(g->d_bar.p, 0, sizeof(gs::GridBarrier), g->stream));
   env = std::getenv("GS_P2P");
   g->p2p_wanted = !(env && env[0] == '0');
   GS_CUDA(g, g->d_seq.alloc(64));

@@ -281,9 +281,11 @@ __global__ void __launch_bounds__(kThreads) k_pcg_dir(const double* __restrict__
     zb = *reinterpret_cast<const double2*>(z + j);
     pb = *reinterpret_cast<const double2*>(p + j);
   }
-  if (i < n2) *reinterpret_cast<double2*>(p + i) = make_double2(za.x + beta * pa.x, za.y + beta * pa.y);
-  if (j < n2) *reinterpret_cast<double2*>(p + j) = make_double2(zb.x + beta * pb.x, zb.y + beta * pb.y);
-  if ((n3 & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n3 - 1] = z[n3 - 1] + beta * p[n3 - 1];
+  if (i < n2)
+    *reinterpret_cast<double2*>(p + i) = make_double2(dir_value(za.x, beta, pa.x), dir_value(za.y, beta, pa.y));
+  if (j < n2)
+    *reinterpret_cast<double2*>(p + j) = make_double2(dir_value(zb.x, beta, pb.x), dir_value(zb.y, beta, pb.y));
+  if ((n3 & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n3 - 1] = dir_value(z[n3 - 1], beta, p[n3 - 1]);
 }
 
 __global__ void __launch_bounds__(kThreads) k_dot(const double* __restrict__ u, const double* __restrict__ w, int n_own,

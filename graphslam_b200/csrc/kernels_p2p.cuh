@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const Red
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     const size_t e = e0 + (size_t)k * kThreads;
-    if (e < n3) a.p[e] = zv[k] + beta * pv[k];
+    if (e < n3) a.p[e] = dir_value(zv[k], beta, pv[k]);
   }
   const int h0 = job.y, h1 = job.z;
   if (h1 == h0) return;   // nothing to send from this tile (uniform over the CTA)

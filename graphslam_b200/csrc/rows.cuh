@@ -365,8 +365,16 @@ GS_HD double spmv_finish(const double d[6], const double l[3], double px, double
   return (px * y0 + py * y1) + pz * y2;
 }
 
-// p: owned rows; pg: ghost rows (local column c >= n_own reads pg + 3 (c - n_own))
-GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, double* y, int r, double lambda) {
+// the PCG direction update, one component: p <- z + beta p.  One spelling for every kernel that forms it
+// (k_pcg_dir, k_dir_p2p, the fused small-graph kernel's on-the-fly form), so the rounding is the same everywhere.
+GS_HD double dir_value(double z, double beta, double p) { return fma(beta, p, z); }
+
+// p: owned rows; pg: ghost rows (local column c >= n_own reads pg + 3 (c - n_own)).
+// DIR: the direction is not stored yet: p(c) = z(c) + beta * pold(c) is formed on the fly for every column the
+// row touches (single rank, no ghosts), and the row's own new p goes to pnew.
+template <bool DIR>
+GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, const double* z, double beta, double* pnew,
+                        double* y, int r, double lambda) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
   double y0 = 0.0, y1 = 0.0, y2 = 0.0;
@@ -381,8 +389,19 @@ GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, doub
       double h[9];
 #pragma unroll
       for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * a.hstride);
-      const double* pc = ref.x < a.n_own ? p + 3 * (size_t)ref.x : pg + 3 * (size_t)(ref.x - a.n_own);
-      spmv_slot(h, pc[0], pc[1], pc[2], ref.y & 1, y0, y1, y2);
+      double px, py, pz;
+      if (DIR) {
+        const size_t o = 3 * (size_t)ref.x;
+        px = dir_value(z[o], beta, p[o]);
+        py = dir_value(z[o + 1], beta, p[o + 1]);
+        pz = dir_value(z[o + 2], beta, p[o + 2]);
+      } else {
+        const double* pc = ref.x < a.n_own ? p + 3 * (size_t)ref.x : pg + 3 * (size_t)(ref.x - a.n_own);
+        px = pc[0];
+        py = pc[1];
+        pz = pc[2];
+      }
+      spmv_slot(h, px, py, pz, ref.y & 1, y0, y1, y2);
     }
   }
   const size_t n = (size_t)a.n_own, rr = (size_t)r;
@@ -394,7 +413,20 @@ GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, doub
     l[1] *= a.dscale[3 * rr + 1];
     l[2] *= a.dscale[3 * rr + 2];
   }
-  return spmv_finish(d, l, p[3 * rr], p[3 * rr + 1], p[3 * rr + 2], y0, y1, y2, y, rr);
+  double q0 = p[3 * rr], q1 = p[3 * rr + 1], q2 = p[3 * rr + 2];
+  if (DIR) {
+    q0 = dir_value(z[3 * rr], beta, q0);
+    q1 = dir_value(z[3 * rr + 1], beta, q1);
+    q2 = dir_value(z[3 * rr + 2], beta, q2);
+    pnew[3 * rr] = q0;
+    pnew[3 * rr + 1] = q1;
+    pnew[3 * rr + 2] = q2;
+  }
+  return spmv_finish(d, l, q0, q1, q2, y0, y1, y2, y, rr);
+}
+
+GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, double* y, int r, double lambda) {
+  return spmv_row_t<false>(a, p, pg, nullptr, 0.0, nullptr, y, r, lambda);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -497,9 +529,9 @@ GS_HD void pcg_update_row(const PcgView& a, int v, double alpha, double& rz, dou
 // p = z + beta p
 GS_HD void pcg_dir_row(const PcgView& a, int v, double beta) {
   const size_t o = 3 * (size_t)v;
-  a.p[o] = a.z[o] + beta * a.p[o];
-  a.p[o + 1] = a.z[o + 1] + beta * a.p[o + 1];
-  a.p[o + 2] = a.z[o + 2] + beta * a.p[o + 2];
+  a.p[o] = dir_value(a.z[o], beta, a.p[o]);
+  a.p[o + 1] = dir_value(a.z[o + 1], beta, a.p[o + 1]);
+  a.p[o + 2] = dir_value(a.z[o + 2], beta, a.p[o + 2]);
 }
 
 GS_HD double dot_row(const double* u, const double* w, int v) {

@@ -387,3 +387,20 @@ def test_deep_convergence_parity():
         _, x = G.poses()
     assert st["chi2_final"] == pytest.approx(2 * otr.errors[-1], rel=1e-12)
     assert _pose_diff(x, ox) <= 1e-9
+
+
+@pytest.mark.parametrize("cid,n", [("C1", None), ("C5", 30000)])
+def test_fused_pcg_bitwise(cid, n, monkeypatch):
+    """Small graphs run the PCG iteration as one persistent kernel (grid barriers instead of launches); same per-row
+    code and reduction tree, so the result must equal the three-kernel path bit for bit."""
+    g = synth.config(cid, n=n)
+    out = {}
+    for fused in ("0", "1"):
+        monkeypatch.setenv("GS_PCG_FUSED", fused)
+        with _load(g) as G:
+            st = G.optimize()
+            _, x = G.poses()
+            out[fused] = (st["chi2_final"], st["pcg_iterations_total"], st["iterations"], x, st["gpu_launches"])
+    assert out["0"][:3] == out["1"][:3]
+    assert np.array_equal(out["0"][3], out["1"][3])
+    assert out["1"][4] < out["0"][4]          # and it really was the other path: far fewer launches
