@@ -7,6 +7,12 @@
 // boundary, and after each barrier EVERY CTA folds the tile partials itself (same fixed tree:
 // tile -> segment -> total) so no second barrier is needed to publish alpha / beta.
 //
+// Tried on top of this and dropped (B200, C5 12k / 36k poses, C2 100k; seconds per 3 LM steps):
+//   * taking a row's slots 2 or 4 at a time (more loads in flight per row): 0.129-0.133 against 0.133 / 0.244-
+//     0.253 against 0.254 — the phases are bounded by the barrier, not by the row's chain of loads;
+//   * making the barrier the reduction (every CTA publishes its partial as flagged words and polls everybody
+//     else's instead of arriving on a counter): 0.165 / 0.387 / C2 1.05 against 0.133 / 0.254 / 0.61 — N^2 polls.
+//
 // The arithmetic is the very same per-row code (rows.cuh) and the same reduction tree as the three-kernel
 // path, so the iterates are bit-identical to it (tests/test_gpu_parity.py::test_fused_pcg_bitwise).
 #pragma once
