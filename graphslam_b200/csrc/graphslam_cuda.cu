@@ -109,6 +109,8 @@ struct gs_graph {
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
   bool use_graph = true;
+  bool p2p_two = true;                    // peer-memory path with two kernels per iteration (GS_P2P_TWO=0: three)
+  int ghost_tile = -1;                    // tile that advances the ghost rows of p in k_spmvdir_p2p
   bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
@@ -366,6 +368,37 @@ gs::P2PCtx p2p_ctx(gs_graph* g, unsigned int k_local) {
 // one stage of a PCG iteration (0: SpMV + p.Ap, 1: x/r/z update + r.z, r.r, 2: direction);
 // k_local = the iteration's position in the batch (peer-memory path only)
 gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
+  if (g->p2p && g->p2p_two) {
+    const gs::P2PCtx x = p2p_ctx(g, k_local);
+    // iteration k reads the direction of iteration k-1 from buffer k&1 and writes its own into the other one
+    double* P[2] = {g->pvec, g->d_p_alt.p};
+    double* prev = P[k_local & 1u];
+    double* next = P[(k_local + 1u) & 1u];
+    const size_t own3 = 3 * (size_t)g->n_own;
+    gs::HaloPush h;
+    h.row = g->d_hp_row.p;
+    h.dst = g->d_hp_dst.p;
+    h.n_push_tiles = g->n_push_tiles;
+    h.order = g->d_hp_order.p;
+    if (stage == 0) {
+      gs::DirSpmvArgs d;
+      d.z = g->d_z.p;
+      d.zg = g->pghost;
+      d.p_prev = prev;
+      d.pg_prev = prev + own3;
+      d.p_next = next;
+      d.pg_next = next + own3;
+      d.y = g->d_Ap.p;
+      d.n_ghost = g->S.n_ghost;
+      d.ghost_tile = g->ghost_tile;
+      gs::k_spmvdir_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), d, reduce_ctx(g, 0), x);
+    } else if (stage == 1) {
+      gs::PcgView pv = pcg_view(g);
+      pv.p = next;
+      gs::k_updpush_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
+    }
+    return GS_OK;
+  }
   if (g->p2p) {
     const gs::P2PCtx x = p2p_ctx(g, k_local);
     if (stage == 0) {
@@ -558,6 +591,7 @@ gs_status prepare_p2p(gs_graph* g) {
   if (gs_status s = upload(g, g->d_hp_order, order)) return s;
   if (gs_status s = upload(g, g->d_hp_row, rows)) return s;
   if (gs_status s = upload(g, g->d_hp_dst, dsts)) return s;
+  GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(S.n_own + S.n_ghost, 1) + 3));
   std::vector<int> tile_halo(nt, 0);
   for (int r = 0; r < g->n_own; ++r) {
     const int w = S.rsell.width[r / gs::kSlice];
@@ -567,6 +601,9 @@ gs_status prepare_p2p(gs_graph* g) {
         break;
       }
   }
+  g->ghost_tile = -1;
+  for (int t = 0; t < nt && g->ghost_tile < 0; ++t)
+    if (tile_halo[t]) g->ghost_tile = t;
   if (gs_status s = upload(g, g->d_tile_halo, tile_halo)) return s;
   std::vector<gs::P2PWindow*> wins(gs::kMaxRanks, nullptr);
   for (int q = 0; q < g->world; ++q) wins[q] = reinterpret_cast<gs::P2PWindow*>(q == g->rank ? g->win : g->peer_win[q]);
@@ -818,13 +855,22 @@ void launch_pcg_setup(gs_graph* g) {
 // peer-memory path: ghost rows of p(0) by the ordinary halo exchange, then mark them valid
 gs_status begin_p2p_solve(gs_graph* g) {
   if (!g->p2p) return GS_OK;
-  if (gs_status s = halo_exchange(g, g->pvec, 3, g->pghost)) return s;
+  if (g->p2p_two) {
+    // the window's ghost rows carry z here (p = z at the start); both ghost copies of p must be finite
+    const size_t own3 = 3 * (size_t)g->n_own, gh = sizeof(double) * 3 * (size_t)std::max(g->S.n_ghost, 1);
+    GS_CUDA(g, cudaMemsetAsync(g->pvec + own3, 0, gh, g->stream));
+    GS_CUDA(g, cudaMemsetAsync(g->d_p_alt.p + own3, 0, gh, g->stream));
+    if (gs_status s = halo_exchange(g, g->d_z.p, 3, g->pghost)) return s;
+  } else if (gs_status s = halo_exchange(g, g->pvec, 3, g->pghost)) {
+    return s;
+  }
   gs::k_p2p_begin<<<1, 32, 0, g->stream>>>(reinterpret_cast<gs::P2PWindow*>(g->win), g->d_seq.p, g->d_sc.p);
   g->launches += 1;
   return GS_OK;
 }
 
 int64_t launches_per_pcg_iteration(const gs_graph* g) {
+  if (g->p2p && g->p2p_two) return 2;
   if (g->world == 1 || g->p2p) return 3;
   return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
 }
@@ -896,6 +942,8 @@ gs_status create_common(gs_graph* g) {
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   const char* env = std::getenv("GS_PCG_GRAPH");
   g->use_graph = !(env && env[0] == '0');
+  env = std::getenv("GS_P2P_TWO");
+  g->p2p_two = !(env && env[0] == '0');
   env = std::getenv("GS_PCG_FUSED");
   g->fused_wanted = !(env && env[0] == '0');
   {

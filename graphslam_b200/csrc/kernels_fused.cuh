@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_pcg_fused(const SpmvView sv, co
   for (int k = 0; k < batch; ++k) {
     // ---- A: p = z + beta p_prev (formed on the fly, own row stored to the other buffer), Ap = (H + lambda D) p, p.Ap
     {
-      const double v = live ? spmv_row_t<true>(sv, p_prev, nullptr, a.z, beta, p_next, Ap, r, lambda) : 0.0;
+      const double v = live ? spmv_row_t<true>(sv, p_prev, nullptr, a.z, nullptr, beta, p_next, Ap, r, lambda) : 0.0;
       const double s = block_sum(v, red);
       if (threadIdx.x == 0) part[2 * (size_t)part_stride + blockIdx.x] = s;
     }

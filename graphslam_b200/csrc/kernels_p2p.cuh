@@ -172,12 +172,13 @@ __device__ __forceinline__ bool wait_sums(const unsigned long long* words, unsig
 // words_of(window) = the landing array of this reduction; quantity q occupies words [16 q, 16 q + 16) of a parity.
 template <int NQ, typename WordsOf>
 __device__ __forceinline__ void reduce_push(const ReduceCtx& c, const P2PCtx& x, const double (&v)[NQ], unsigned int par,
-                                            unsigned int stamp, WordsOf words_of, double* red, int* flag) {
+                                            unsigned int stamp, WordsOf words_of, double* red, int* flag,
+                                            int tile = (int)blockIdx.x) {
   __shared__ double mysegs[NQ > 1 ? NQ : 1][kSegments];
 #pragma unroll
   for (int q = 0; q < NQ; ++q) {
     const double s = block_sum(v[q], red);
-    if (threadIdx.x == 0) c.part[(size_t)q * c.part_stride + blockIdx.x] = s;
+    if (threadIdx.x == 0) c.part[(size_t)q * c.part_stride + tile] = s;
   }
   if (last_block(c.counter, flag)) {
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
@@ -322,6 +323,121 @@ __global__ void __launch_bounds__(kThreads) k_dir_p2p(const PcgView a, const Red
       st_release_sys(&x.win[threadIdx.x]->halo_flag[x.rank], S + 2);
     if (threadIdx.x == 0) *x.ticket = 0u;
   }
+}
+
+// ---- two kernels per iteration -------------------------------------------------------------------------------
+// The direction update does not need a kernel (nor a cross-GPU signal) of its own: the product can form
+// p(c) = z(c) + beta p_prev(c) on the fly for every column it touches, as the single-GPU persistent kernel
+// does.  What neighbours then need from each other is z, which the update kernel has just computed:
+//
+//   k_spmvdir_p2p   waits for r.z / r.r of the previous iteration (beta, stopping test), tiles that touch ghost
+//                   columns also for the neighbours' z rows; stores its rows of the new p into the other p
+//                   buffer (one designated tile does the same for the ghost rows), multiplies, sends p.Ap.
+//   k_updpush_p2p   waits for p.Ap; updates x, r, z; sending tiles (scheduled first) store the z rows their
+//                   neighbours need into the neighbours' windows; sends r.z / r.r.
+//
+// Same arithmetic per row and per reduction as the three-kernel form, hence the same bits.
+struct DirSpmvArgs {
+  const double* z;        // owned rows
+  const double* zg;       // ghost rows of z: in this rank's window, written by the neighbours
+  const double* p_prev;   // previous direction, owned rows ...
+  const double* pg_prev;  // ... and ghost rows
+  double* p_next;
+  double* pg_next;
+  double* y;              // Ap
+  int n_ghost;
+  int ghost_tile;         // the tile that also advances the ghost rows of p (one that waits for the halo anyway)
+};
+
+__global__ void __launch_bounds__(kThreads) k_spmvdir_p2p(const SpmvView a, const DirSpmvArgs d, const ReduceCtx c,
+                                                           const P2PCtx x) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  __shared__ WaitOut wo;
+  Scalars* sc = c.sc;
+  if (sc->done) return;
+  const unsigned int S = *x.seq_base + x.k_local;
+  P2PWindow* me = x.me;
+  double beta = 0.0;
+  if (S != sc->seq0) {   // not the first iteration of the solve: close iteration S-1 (what k_dir_p2p did)
+    if (!wait_sums<2>(me->ll_upd[(S - 1u) & 1u], S, sc, x.spin_limit, &wo, 2)) return;
+    const double rz = wo.tot[0], rr = wo.tot[1];
+    const double rz_old = sc->rzv[S & 1u];
+    beta = rz / rz_old;
+    const int it = (int)(S - sc->seq0);
+    int done = 0;
+    if (rr <= sc->tol2 * sc->rr0) done = 1;
+    else if (!(rr == rr)) done = 2;
+    else if (it >= sc->max_iters) done = 3;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      sc->rzv[(S - 1u) & 1u] = rz;
+      sc->rz = rz;
+      sc->rr = rr;
+      sc->beta = beta;
+      sc->iters = it;
+      if (done) sc->done = done;
+    }
+    if (done) return;
+  }
+  const bool halo_tile = x.tile_halo[blockIdx.x] != 0;
+  if (halo_tile && !wait_flags(me->halo_flag, x.nbr_mask, S + 1, sc, x.spin_limit, &wo)) return;
+  if ((int)blockIdx.x == d.ghost_tile) {   // ghost rows of the new direction, for the next iteration's p_prev
+    for (int e = threadIdx.x; e < 3 * d.n_ghost; e += kThreads) d.pg_next[e] = dir_value(d.zg[e], beta, d.pg_prev[e]);
+  }
+  const double lambda = sc->lambda;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < a.n_own) v[0] = spmv_row_t<true>(a, d.p_prev, d.pg_prev, d.z, d.zg, beta, d.p_next, d.y, r, lambda);
+  reduce_push<1>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_pap[0][0]; }, red, &flag);
+}
+
+__global__ void __launch_bounds__(kThreads) k_updpush_p2p(const PcgView a, const ReduceCtx c, const P2PCtx x, const HaloPush h) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  __shared__ WaitOut wo;
+  if (c.sc->done) return;
+  const int4 job = ldg(h.order + blockIdx.x);   // (tile, first entry, end entry): sending tiles first
+  const unsigned int S = *x.seq_base + x.k_local;
+  P2PWindow* me = x.me;
+  if (!wait_sums<1>(me->ll_pap[S & 1u], S + 1, c.sc, x.spin_limit, &wo, 1)) return;
+  const double pAp = wo.tot[0];
+  if (!(pAp > 0.0)) {  // breakdown: the same on every rank, nobody goes on
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      c.sc->pAp = pAp;
+      c.sc->done = 2;
+    }
+    return;
+  }
+  const double alpha = c.sc->rzv[(S + 1u) & 1u] / pAp;   // r.z of the previous iterate
+  const int r = job.x * kThreads + threadIdx.x;
+  double v[2] = {0.0, 0.0};
+  if (r < a.n_own) pcg_update_row(a, r, alpha, v[0], v[1]);
+  if (job.z > job.y) {   // a sending tile (uniform over the CTA): its new z rows go to the neighbours' ghost slots
+    __syncthreads();
+    bool pushed = false;
+    for (int e = job.y + (int)threadIdx.x; e < job.z; e += kThreads) {
+      const double* src = a.z + 3 * (size_t)h.row[e];
+      double* dst = h.dst[e];
+      dst[0] = __ldcg(src);
+      dst[1] = __ldcg(src + 1);
+      dst[2] = __ldcg(src + 2);
+      pushed = true;
+    }
+    if (pushed) __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int t = atomicAdd(x.ticket, 1u);
+      flag = (t == (unsigned int)h.n_push_tiles - 1u);
+    }
+    __syncthreads();
+    if (flag) {
+      if ((int)threadIdx.x < x.world && ((x.nbr_mask >> threadIdx.x) & 1u))
+        st_release_sys(&x.win[threadIdx.x]->halo_flag[x.rank], S + 2);
+      if (threadIdx.x == 0) *x.ticket = 0u;
+    }
+    __syncthreads();
+  }
+  reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_upd[0][0]; }, red, &flag, job.x);
 }
 
 // start of a solve: the ghost rows of p(0) arrived by the ordinary halo exchange, so mark them

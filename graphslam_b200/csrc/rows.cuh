@@ -371,10 +371,10 @@ GS_HD double dir_value(double z, double beta, double p) { return fma(beta, p, z)
 
 // p: owned rows; pg: ghost rows (local column c >= n_own reads pg + 3 (c - n_own)).
 // DIR: the direction is not stored yet: p(c) = z(c) + beta * pold(c) is formed on the fly for every column the
-// row touches (single rank, no ghosts), and the row's own new p goes to pnew.
+// row touches (ghost columns from zg / pg), and the row's own new p goes to pnew.
 template <bool DIR>
-GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, const double* z, double beta, double* pnew,
-                        double* y, int r, double lambda) {
+GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, const double* z, const double* zg, double beta,
+                        double* pnew, double* y, int r, double lambda) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
   double y0 = 0.0, y1 = 0.0, y2 = 0.0;
@@ -391,10 +391,13 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
       for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * a.hstride);
       double px, py, pz;
       if (DIR) {
-        const size_t o = 3 * (size_t)ref.x;
-        px = dir_value(z[o], beta, p[o]);
-        py = dir_value(z[o + 1], beta, p[o + 1]);
-        pz = dir_value(z[o + 2], beta, p[o + 2]);
+        const bool ghost = ref.x >= a.n_own;
+        const size_t o = 3 * (size_t)(ghost ? ref.x - a.n_own : ref.x);
+        const double* zc = (ghost ? zg : z) + o;
+        const double* pc = (ghost ? pg : p) + o;
+        px = dir_value(zc[0], beta, pc[0]);
+        py = dir_value(zc[1], beta, pc[1]);
+        pz = dir_value(zc[2], beta, pc[2]);
       } else {
         const double* pc = ref.x < a.n_own ? p + 3 * (size_t)ref.x : pg + 3 * (size_t)(ref.x - a.n_own);
         px = pc[0];
@@ -426,7 +429,7 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
 }
 
 GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, double* y, int r, double lambda) {
-  return spmv_row_t<false>(a, p, pg, nullptr, 0.0, nullptr, y, r, lambda);
+  return spmv_row_t<false>(a, p, pg, nullptr, nullptr, 0.0, nullptr, y, r, lambda);
 }
 
 // ------------------------------------------------------------------------------------------------
