@@ -109,8 +109,9 @@ struct gs_graph {
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
   bool use_graph = true;
-  bool p2p_two = true;                    // peer-memory path with two kernels per iteration (GS_P2P_TWO=0: three)
-  int ghost_tile = -1;                    // tile that advances the ghost rows of p in k_spmvdir_p2p
+  bool p2p_two = true;                    // peer-memory path with two kernels per iteration (else three)
+  int p2p_two_env = -1;                   // GS_P2P_TWO: 0 / 1 force, unset = by rows per rank
+  int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
   bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
@@ -390,7 +391,7 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       d.pg_next = next + own3;
       d.y = g->d_Ap.p;
       d.n_ghost = g->S.n_ghost;
-      d.ghost_tile = g->ghost_tile;
+      d.ghost_chunk = g->ghost_chunk;
       gs::k_spmvdir_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), d, reduce_ctx(g, 0), x);
     } else if (stage == 1) {
       gs::PcgView pv = pcg_view(g);
@@ -591,6 +592,10 @@ gs_status prepare_p2p(gs_graph* g) {
   if (gs_status s = upload(g, g->d_hp_order, order)) return s;
   if (gs_status s = upload(g, g->d_hp_row, rows)) return s;
   if (gs_status s = upload(g, g->d_hp_dst, dsts)) return s;
+  // Two kernels per iteration pay a second gather per column in the product and save the direction kernel:
+  // measured on C3, 1.39 -> 1.31 s per step at 2 GPUs and 0.92 -> 0.87 s at 4, but 0.54 -> 0.6 s at 8 (125k rows
+  // per rank), so the choice goes by rows per rank (the same number on every rank).
+  g->p2p_two = g->p2p_two_env >= 0 ? g->p2p_two_env != 0 : (g->N / std::max(g->world, 1) >= 200000);
   GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(S.n_own + S.n_ghost, 1) + 3));
   std::vector<int> tile_halo(nt, 0);
   for (int r = 0; r < g->n_own; ++r) {
@@ -601,9 +606,10 @@ gs_status prepare_p2p(gs_graph* g) {
         break;
       }
   }
-  g->ghost_tile = -1;
-  for (int t = 0; t < nt && g->ghost_tile < 0; ++t)
-    if (tile_halo[t]) g->ghost_tile = t;
+  int n_halo_tiles = 0;
+  for (int t = 0; t < nt; ++t)
+    if (tile_halo[t]) tile_halo[t] = ++n_halo_tiles;   // ordinal: which share of the ghost rows the tile advances
+  g->ghost_chunk = n_halo_tiles ? (3 * S.n_ghost + n_halo_tiles - 1) / n_halo_tiles : 0;
   if (gs_status s = upload(g, g->d_tile_halo, tile_halo)) return s;
   std::vector<gs::P2PWindow*> wins(gs::kMaxRanks, nullptr);
   for (int q = 0; q < g->world; ++q) wins[q] = reinterpret_cast<gs::P2PWindow*>(q == g->rank ? g->win : g->peer_win[q]);
@@ -943,7 +949,7 @@ gs_status create_common(gs_graph* g) {
   const char* env = std::getenv("GS_PCG_GRAPH");
   g->use_graph = !(env && env[0] == '0');
   env = std::getenv("GS_P2P_TWO");
-  g->p2p_two = !(env && env[0] == '0');
+  g->p2p_two_env = env ? (env[0] != '0') : -1;
   env = std::getenv("GS_PCG_FUSED");
   g->fused_wanted = !(env && env[0] == '0');
   {

@@ -56,7 +56,7 @@ struct P2PCtx {
   unsigned int k_local;        // position of this iteration inside the batch
   unsigned int* ticket;        // last-CTA counter for the halo push
   long long spin_limit;        // clock64 ticks before a wait gives up
-  const int* tile_halo;        // per tile: 1 when some row of the tile multiplies a ghost row of p
+  const int* tile_halo;        // per tile: 0, or the 1-based ordinal among the tiles whose rows multiply ghost rows of p
 };
 
 struct HaloPush {
@@ -346,7 +346,9 @@ struct DirSpmvArgs {
   double* pg_next;
   double* y;              // Ap
   int n_ghost;
-  int ghost_tile;         // the tile that also advances the ghost rows of p (one that waits for the halo anyway)
+  int ghost_chunk;        // ghost doubles advanced by each halo tile: tile_halo[tile] = 1-based ordinal k takes
+                          // [(k-1) chunk, k chunk) — spread over the tiles that wait for the halo anyway (one tile
+                          // doing all of them put ~10 us on the 8-GPU critical path)
 };
 
 __global__ void __launch_bounds__(kThreads) k_spmvdir_p2p(const SpmvView a, const DirSpmvArgs d, const ReduceCtx c,
@@ -379,10 +381,11 @@ __global__ void __launch_bounds__(kThreads) k_spmvdir_p2p(const SpmvView a, cons
     }
     if (done) return;
   }
-  const bool halo_tile = x.tile_halo[blockIdx.x] != 0;
-  if (halo_tile && !wait_flags(me->halo_flag, x.nbr_mask, S + 1, sc, x.spin_limit, &wo)) return;
-  if ((int)blockIdx.x == d.ghost_tile) {   // ghost rows of the new direction, for the next iteration's p_prev
-    for (int e = threadIdx.x; e < 3 * d.n_ghost; e += kThreads) d.pg_next[e] = dir_value(d.zg[e], beta, d.pg_prev[e]);
+  const int halo_ord = x.tile_halo[blockIdx.x];
+  if (halo_ord && !wait_flags(me->halo_flag, x.nbr_mask, S + 1, sc, x.spin_limit, &wo)) return;
+  if (halo_ord) {   // this tile's share of the ghost rows of the new direction (the next iteration's p_prev)
+    const int e0 = (halo_ord - 1) * d.ghost_chunk, e1 = min(e0 + d.ghost_chunk, 3 * d.n_ghost);
+    for (int e = e0 + (int)threadIdx.x; e < e1; e += kThreads) d.pg_next[e] = dir_value(d.zg[e], beta, d.pg_prev[e]);
   }
   const double lambda = sc->lambda;
   const int r = blockIdx.x * kThreads + threadIdx.x;

@@ -26,14 +26,15 @@ def _free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("p2p", ["1", "0"], ids=["peer-memory", "nccl-per-op"])
+@pytest.mark.parametrize("p2p", ["1/1", "1/0", "0/0"], ids=["peer-memory-2-kernels", "peer-memory-3-kernels", "nccl-per-op"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_multi_gpu_path_bitwise_equals_single_gpu(world, p2p):
-    """p2p=1: halo rows and dot-product segment sums travel by stores into the peers' windows from inside the PCG
-    kernels; p2p=0: one NCCL call per exchange.  Both must reproduce the single-GPU bits."""
+    """peer memory: halo rows and dot-product segment sums travel by stores into the peers' windows from inside the PCG
+    kernels, with two (direction formed on the fly in the product) or three kernels per iteration; nccl-per-op: one
+    NCCL call per exchange.  All must reproduce the single-GPU bits."""
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
-    env = dict(os.environ, GS_P2P=p2p)
+    env = dict(os.environ, GS_P2P=p2p.split("/")[0], GS_P2P_TWO=p2p.split("/")[1])
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
            "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mgpu_worker.py"), "C3", "30000"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
