@@ -137,7 +137,7 @@ def run_reference(args):
     if rank != 0:
         return
     g = make_graph(args.config, args.n)
-    pcg_per_lm = args.pcg_per_lm or estimate_pcg_per_lm(g)
+    pcg_per_lm = args.pcg_per_lm or estimate_pcg_per_lm(g, args.warmup, args.steps)
     secs = []
     last = None
     for s in range(args.warmup + args.steps):
@@ -160,25 +160,30 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def estimate_pcg_per_lm(g):
-    """PCG iterations one LM iteration needs on this graph: measured on the GPU when one is present (same
-    algorithm, same tolerance), else a recorded figure, else the sample's own count."""
+def estimate_pcg_per_lm(g, warmup=0, steps=1):
+    """PCG iterations one LM iteration needs on this graph, averaged over the LM steps the GPU arm times (steps
+    warmup+1 .. warmup+steps of the warm-started sequence): from the recorded per-step counts
+    (profiles/pcg_iters.json, logged by the GPU arm: same algorithm, same tolerance, and the count is a property
+    of the problem, not of the machine), else measured on the GPU when one is present, else the sample's own count."""
     rec = os.path.join(ROOT, "profiles", "pcg_iters.json")
+    if os.path.exists(rec):
+        try:
+            per_step = json.load(open(rec)).get(f"{g.name}:{g.n}")
+        except Exception:
+            per_step = None
+        if per_step:
+            take = [per_step[min(k, len(per_step) - 1)] for k in range(warmup, warmup + max(steps, 1))]
+            return int(round(sum(take) / len(take)))
     try:
         import torch
         if torch.cuda.is_available():
             from graphslam_b200 import graph
             with graph.Graph(max_iterations=1, rel_error_tol=0.0, abs_error_tol=0.0, pcg_rel_tol=PCG_TOL) as G:
                 G.add_graph(g)
-                st = G.optimize()
-            return int(st["pcg_iterations_total"] / max(st["inner_iterations"], 1))
+                counts = [G.optimize() for _ in range(warmup + max(steps, 1))][warmup:]
+            return int(round(sum(c["pcg_iterations_total"] / max(c["inner_iterations"], 1) for c in counts) / len(counts)))
     except Exception as exc:  # no GPU for the reference arm is fine
         log(f"[bench/reference] no GPU estimate of PCG iterations ({exc})")
-    if os.path.exists(rec):
-        d = json.load(open(rec))
-        key = f"{g.name}:{g.n}"
-        if key in d:
-            return int(d[key])
     return None
 
 
@@ -250,6 +255,8 @@ def run_ours(args):
     dev_s = vmax(sum(s["ms_device"] for s in stats) * 1e-3)     # device time, max over ranks
     value = K / dev_s
     pcg_total = sum(s["pcg_iterations_total"] for s in stats)
+    log(f"[bench r{rank}] PCG iterations per step (after {W} warm-up steps): " +
+        json.dumps([int(s["pcg_iterations_total"]) for s in stats]))
     solves = sum(s["inner_iterations"] for s in stats)
     launches = vsum(float(sum(s["gpu_launches"] for s in stats)))
     ms_lin = vmax(sum(s["ms_linearize"] for s in stats))
@@ -283,7 +290,7 @@ def run_ours(args):
     G2.add_graph(g)
     G2.prepare()
     x = np.ascontiguousarray(g.init)
-    for _ in range(min(W, 1)):
+    for _ in range(W):                   # same warm-up as the resident leg: the timed steps start from the same state
         G2.set_poses(keys, x)
         G2.optimize()
         _, x = G2.poses()
