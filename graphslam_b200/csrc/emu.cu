@@ -153,8 +153,8 @@ extern "C" gs_status gs_host_partition(int32_t n, int32_t e, const int32_t* ei, 
   return GS_OK;
 }
 
-extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
-                                double pcg_rel_tol, gs_emu_result* out) {
+static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
+                         double pcg_rel_tol, int form, gs_emu_result* out) {
   if (!pb || !out || pb->n <= 0) return GS_EINVAL;
   if (!(world == 1 || world == 2 || world == 4 || world == 8)) return GS_EINVAL;
   const int N = pb->n, E = pb->e, P = pb->np;
@@ -211,7 +211,7 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
     me.Minv.assign(2 * n3, 0.0);
     me.b.assign(n3, 0.0);
     me.r.assign(n3, 0.0);
-    me.z.assign(n3, 0.0);
+    me.z.assign(nl3, 0.0);   // ghost room: the two-kernel form exchanges z
     me.Ap.assign(n3, 0.0);
     me.x.assign(nl3, 0.0);
     me.p.assign(nl3, 0.0);
@@ -278,7 +278,53 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
   rr = W.reduce([&](VRank& me, int r) { return gs::dot_row(me.r.data(), me.r.data(), r); });
   const double rr0 = rr;
   int it = 0, done = (rr == 0.0) ? 1 : 0;
-  while (!done && it < pcg_max_iters) {
+  if (form == 1) {
+    // the two-kernel form of the peer-memory path and of the persistent small-graph kernel: the direction is not
+    // stored before the product; p(c) = z(c) + beta p_prev(c) is formed on the fly (ghost columns from the exchanged
+    // z and the locally kept ghost p), the new p goes to a second buffer
+    std::vector<std::vector<double>> alt(W.R.size());
+    for (size_t q = 0; q < W.R.size(); ++q) alt[q].assign(W.R[q].p.size(), 0.0);
+    std::vector<double*> prev(W.R.size()), next(W.R.size());
+    for (size_t q = 0; q < W.R.size(); ++q) {
+      prev[q] = W.R[q].p.data();
+      next[q] = alt[q].data();
+      std::fill(W.R[q].p.begin() + 3 * (size_t)W.R[q].n_own, W.R[q].p.end(), 0.0);
+    }
+    double beta = 0.0;
+    while (!done && it < pcg_max_iters) {
+      W.halo([](VRank& v) { return v.z.data(); }, 3);
+      for (size_t q = 0; q < W.R.size(); ++q) {
+        VRank& me = W.R[q];
+        const size_t own3 = 3 * (size_t)me.n_own;
+        for (size_t e = own3; e < me.p.size(); ++e) next[q][e] = gs::dir_value(me.z[e], beta, prev[q][e]);
+      }
+      const double pAp = W.reduce([&](VRank& me, int r) {
+        const size_t q = (size_t)me.S.rank, own3 = 3 * (size_t)me.n_own;
+        return gs::spmv_row_t<true>(me.sv(), prev[q], prev[q] + own3, me.z.data(), me.z.data() + own3, beta, next[q],
+                                    me.Ap.data(), r, lambda);
+      });
+      for (size_t q = 0; q < W.R.size(); ++q) std::swap(prev[q], next[q]);
+      if (!(pAp > 0.0)) {
+        done = 2;
+        break;
+      }
+      const double alpha = rz / pAp;
+      const double nrz = W.reduce([&](VRank& me, int r) {
+        double a, b;
+        gs::PcgView v = me.pv();
+        v.p = prev[(size_t)me.S.rank];
+        gs::pcg_update_row(v, r, alpha, a, b);
+        return a;
+      });
+      rr = W.reduce([&](VRank& me, int r) { return gs::dot_row(me.r.data(), me.r.data(), r); });
+      beta = nrz / rz;
+      rz = nrz;
+      ++it;
+      if (rr <= pcg_rel_tol * pcg_rel_tol * rr0) done = 1;
+      else if (!(rr == rr)) done = 2;
+    }
+  }
+  while (form == 0 && !done && it < pcg_max_iters) {
     W.halo([](VRank& v) { return v.p.data(); }, 3);
     const double pAp = W.reduce([&](VRank& me, int r) { return gs::spmv_row(me.sv(), me.p.data(), me.p.data() + 3 * (size_t)me.n_own, me.Ap.data(), r, lambda); });
     if (!(pAp > 0.0)) {
@@ -340,4 +386,16 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
     out->n_block_copies += me.S.n_block_copies;
   }
   return GS_OK;
+}
+
+extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
+                                double pcg_rel_tol, gs_emu_result* out) {
+  return emu_run(pb, world, jacobian_mode, lambda, pcg_max_iters, pcg_rel_tol, 0, out);
+}
+
+// form 1: the PCG iteration with the direction formed on the fly (k_spmvdir_p2p / k_pcg_fused); same bits as form 0
+extern "C" gs_status gs_emu_run_form(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
+                                     double pcg_rel_tol, int form, gs_emu_result* out) {
+  if (form != 0 && form != 1) return GS_EINVAL;
+  return emu_run(pb, world, jacobian_mode, lambda, pcg_max_iters, pcg_rel_tol, form, out);
 }

@@ -15,7 +15,7 @@ def _upper6(om):
     return np.ascontiguousarray(np.stack([om[:, 0, 0], om[:, 0, 1], om[:, 0, 2], om[:, 1, 1], om[:, 1, 2], om[:, 2, 2]], 1))
 
 
-def emu_run(lib, prob, xyt, world=1, mode=0, lam=1e-5, max_iters=5000, tol=1e-12, want_blocks=True):
+def emu_run(lib, prob, xyt, world=1, mode=0, lam=1e-5, max_iters=5000, tol=1e-12, want_blocks=True, form=0):
     n, e = prob.n, len(prob.ei)
     ei = np.ascontiguousarray(prob.ei, np.int32)
     ej = np.ascontiguousarray(prob.ej, np.int32)
@@ -35,7 +35,7 @@ def emu_run(lib, prob, xyt, world=1, mode=0, lam=1e-5, max_iters=5000, tol=1e-12
     res = _lib.GsEmuResult()
     res.blocks = blocks.ctypes.data_as(dp) if want_blocks else None
     res.b, res.delta, res.xyt_new = b.ctypes.data_as(dp), delta.ctypes.data_as(dp), xnew.ctypes.data_as(dp)
-    rc = lib.gs_emu_run(C.byref(pb), world, mode, lam, max_iters, tol, C.byref(res))
+    rc = lib.gs_emu_run_form(C.byref(pb), world, mode, lam, max_iters, tol, form, C.byref(res))
     assert rc == 0, rc
     return dict(blocks=blocks, b=b, delta=delta, xyt_new=xnew, chi2=res.chi2, chi2_check=res.chi2_check,
                 chi2_new=res.chi2_new, dHd=res.dHd, db=res.db, rel_residual=res.rel_residual, pcg_iters=res.pcg_iters,
@@ -115,3 +115,16 @@ def test_emulated_hub_duplicates_and_tiny_graphs(lib):
     a = _check_against_oracle(lib, small, world=1)
     b = _check_against_oracle(lib, small, world=8)
     assert np.array_equal(a["delta"], b["delta"]) and a["chi2"] == b["chi2"]
+
+
+@pytest.mark.parametrize("world", [1, 2, 8])
+def test_direction_formed_on_the_fly_is_bitwise_the_same(lib, world):
+    """The two-kernel peer-memory iteration and the persistent small-graph kernel never store p before the product:
+    p(c) = z(c) + beta p_prev(c) is formed per touched column and z is what ranks exchange.  Same rounding, same bits."""
+    g = synth.config("C3", n=3000, full_cov=True)
+    prob = O.Problem.from_graph(g)
+    a = emu_run(lib, prob, g.init, world=world, want_blocks=False, form=0)
+    b = emu_run(lib, prob, g.init, world=world, want_blocks=False, form=1)
+    assert a["pcg_iters"] == b["pcg_iters"] and a["pcg_done"] == b["pcg_done"] == 1
+    assert np.array_equal(a["delta"], b["delta"]) and np.array_equal(a["xyt_new"], b["xyt_new"])
+    assert a["chi2_new"] == b["chi2_new"] and a["dHd"] == b["dHd"]
