@@ -171,6 +171,8 @@ def estimate_pcg_per_lm(g, warmup=0, steps=1):
             per_step = json.load(open(rec)).get(f"{g.name}:{g.n}")
         except Exception:
             per_step = None
+        if isinstance(per_step, (int, float)) and per_step > 0:     # older record: one average
+            return int(round(per_step))
         if per_step:
             take = [per_step[min(k, len(per_step) - 1)] for k in range(warmup, warmup + max(steps, 1))]
             return int(round(sum(take) / len(take)))
@@ -324,8 +326,15 @@ def run_ours(args):
             os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
             rec = os.path.join(ROOT, "profiles", "pcg_iters.json")
             d = json.load(open(rec)) if os.path.exists(rec) else {}
-            d[f"{g.name}:{g.n}"] = pcg_per_lm
-            json.dump(d, open(rec, "w"), indent=1, sort_keys=True)
+            key = f"{g.name}:{g.n}"
+            per_step = d.get(key) if isinstance(d.get(key), list) else []
+            per_step += [per_step[-1] if per_step else 0] * max(W + K - len(per_step), 0)
+            for k, s in enumerate(stats):          # LM steps W+1 .. W+K of the warm-started sequence
+                per_step[W + k] = int(round(s["pcg_iterations_total"] / max(s["inner_iterations"], 1)))
+            if W and not any(per_step[:W]):        # warm-up steps not recorded yet: best guess = the first timed one
+                per_step[:W] = [per_step[W]] * W
+            d[key] = per_step
+            json.dump(d, open(rec, "w"), sort_keys=True)
         except Exception:
             pass
 

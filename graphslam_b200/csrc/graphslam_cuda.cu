@@ -112,12 +112,14 @@ struct gs_graph {
   bool p2p_two = true;                    // peer-memory path with two kernels per iteration (else three)
   int p2p_two_env = -1;                   // GS_P2P_TWO: 0 / 1 force, unset = by rows per rank
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
-  // measured variants of the three-kernel PCG iteration (same bits; see kernels.cuh): GS_UPDATE_STAGED,
-  // GS_STREAM_LOADS, GS_SWEEP, GS_ASM_STREAM_STORES = 0 / 1
-  bool opt_staged = false;                // x/r/z update with full-width accesses through shared memory
-  bool opt_stream = false;                // evict-first loads of H, lists, M^-1 (and x, r in the staged update)
-  bool opt_sweep = false;                 // consecutive kernels sweep the rows in opposite directions
-  bool opt_asm_stream = false;            // assembly stores H with evict-first stores
+  // variants of the three-kernel PCG iteration, same bits whichever is on (see kernels.cuh; measured on C3 by
+  // tools/variant_probe.py, profiles/r1_v7_variant_probe.jsonl): GS_UPDATE_STAGED, GS_STREAM_LOADS, GS_SWEEP,
+  // GS_ASM_STREAM_STORES = 0 / 1
+  bool opt_staged = true;                 // x/r/z update with full-width accesses through shared memory: 51.5 -> 47.6 us
+  bool opt_stream = false;                // evict-first loads of H, lists, M^-1: SpMV 101 -> 112 us (the second
+                                          // reader of a shared block finds it evicted), kept off
+  bool opt_sweep = false;                 // consecutive kernels sweep the rows in opposite directions: no change
+  bool opt_asm_stream = false;            // assembly stores H with evict-first stores: no change
   bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once

@@ -404,3 +404,29 @@ def test_fused_pcg_bitwise(cid, n, monkeypatch):
     assert out["0"][:3] == out["1"][:3]
     assert np.array_equal(out["0"][3], out["1"][3])
     assert out["1"][4] < out["0"][4]          # and it really was the other path: far fewer launches
+
+
+@pytest.mark.parametrize("n", [4001, 60000])
+def test_pcg_kernel_variants_bitwise(n, monkeypatch):
+    """The three-kernel PCG iteration has switchable forms of its kernels (shared-memory staged x/r/z update — the
+    default —, evict-first loads, alternating sweep direction, evict-first H stores in assembly).  None changes a
+    row's arithmetic or the reduction tree, so a capped solve must give the same bits under every combination;
+    4001 rows leave an odd number of rows in the last tile."""
+    import ctypes as C
+    g = synth.config("C3", n=n)
+    monkeypatch.setenv("GS_PCG_FUSED", "0")
+    flags = ("GS_UPDATE_STAGED", "GS_STREAM_LOADS", "GS_SWEEP", "GS_ASM_STREAM_STORES")
+    combos = [(0, 0, 0, 0), (1, 0, 0, 0), (0, 1, 0, 0), (1, 1, 1, 0), (0, 0, 1, 0), (1, 0, 1, 1)]
+    out = []
+    for combo in combos:
+        for k, v in zip(flags, combo):
+            monkeypatch.setenv(k, str(v))
+        with _load(g, pcg_max_iters=96, pcg_rel_tol=1e-300) as G:
+            d = np.zeros((g.n, 3))
+            it, rr = C.c_int(), C.c_double()
+            st = G._lib.gs_solve_linear(G._h, 1e-5, d.ctypes.data_as(_lib.c_double_p), C.byref(it), C.byref(rr))
+            assert st in (_lib.GS_OK, _lib.GS_ENOTCONVERGED) and it.value == 96
+            out.append(d)
+    assert np.isfinite(out[0]).all() and np.abs(out[0]).max() > 0
+    for d in out[1:]:
+        assert np.array_equal(d, out[0])
