@@ -112,14 +112,7 @@ struct gs_graph {
   bool p2p_two = true;                    // peer-memory path with two kernels per iteration (else three)
   int p2p_two_env = -1;                   // GS_P2P_TWO: 0 / 1 force, unset = by rows per rank
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
-  // variants of the three-kernel PCG iteration, same bits whichever is on (see kernels.cuh; measured on C3 by
-  // tools/variant_probe.py, profiles/r1_v7_variant_probe.jsonl): GS_UPDATE_STAGED, GS_STREAM_LOADS, GS_SWEEP,
-  // GS_ASM_STREAM_STORES = 0 / 1
-  bool opt_staged = true;                 // x/r/z update with full-width accesses through shared memory: 51.5 -> 47.6 us
-  bool opt_stream = false;                // evict-first loads of H, lists, M^-1: SpMV 101 -> 112 us (the second
-                                          // reader of a shared block finds it evicted), kept off
-  bool opt_sweep = false;                 // consecutive kernels sweep the rows in opposite directions: no change
-  bool opt_asm_stream = false;            // assembly stores H with evict-first stores: no change
+  bool update_staged = true;              // GS_UPDATE_STAGED=0: k_pcg_update instead of k_pcg_update_staged (same bits)
   bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
@@ -342,17 +335,10 @@ gs_status finish_reduce(gs_graph* g, int nq, int op) {
   return GS_OK;
 }
 
-gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode, int rev = 0) {
+gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode) {
   if (gs_status s = halo_exchange(g, p, 3)) return s;
-  if (g->opt_stream)
-    gs::k_spmv_v<true><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, p + 3 * (size_t)g->n_own, y,
-                                                                     reduce_ctx(g, 0), mode, rev);
-  else if (rev)
-    gs::k_spmv_v<false><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, p + 3 * (size_t)g->n_own, y,
-                                                                      reduce_ctx(g, 0), mode, rev);
-  else
-    gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, p + 3 * (size_t)g->n_own, y, reduce_ctx(g, 0),
-                                                             mode);
+  gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), p, p + 3 * (size_t)g->n_own, y, reduce_ctx(g, 0),
+                                                           mode);
   return finish_reduce(g, 1, mode == 0 ? gs::OP_PAP : gs::OP_DOT);
 }
 
@@ -432,26 +418,15 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     }
     return GS_OK;
   }
-  // opt_sweep: consecutive kernels walk the rows in opposite directions (spmv and dir of iteration k forwards when
-  // k is even, the update between them backwards), so each starts on the rows the previous one left in L2
-  const int odd = g->opt_sweep ? (int)(k_local & 1u) : 0;
-  if (stage == 0) return launch_spmv(g, g->pvec, g->d_Ap.p, 0, odd);
+  if (stage == 0) return launch_spmv(g, g->pvec, g->d_Ap.p, 0);
   if (stage == 1) {
-    const int rev = g->opt_sweep ? 1 - odd : 0;
-    if (g->opt_staged && g->opt_stream)
-      gs::k_pcg_update_staged<true><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), rev);
-    else if (g->opt_staged)
-      gs::k_pcg_update_staged<false><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), rev);
-    else if (rev)
-      gs::k_pcg_update_v<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), rev);
+    if (g->update_staged)
+      gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
     else
       gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
     return finish_reduce(g, 2, gs::OP_UPDATE);
   }
-  if (g->opt_sweep)
-    gs::k_pcg_dir_tiles<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->pvec, g->d_sc.p, g->n_own, odd);
-  else
-    gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->pvec, g->d_sc.p, 3 * g->n_own);
+  gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->pvec, g->d_sc.p, 3 * g->n_own);
   return GS_OK;
 }
 
@@ -858,8 +833,6 @@ gs_status launch_assemble(gs_graph* g) {
   const gs::ReduceCtx rc = reduce_ctx(g, 2);
   if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT)
     gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
-  else if (g->opt_asm_stream)
-    gs::k_assemble<0, true><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
   else
     gs::k_assemble<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
   g->launches += 1;
@@ -983,14 +956,8 @@ gs_status create_common(gs_graph* g) {
   g->p2p_two_env = env ? (env[0] != '0') : -1;
   env = std::getenv("GS_PCG_FUSED");
   g->fused_wanted = !(env && env[0] == '0');
-  auto flag = [](const char* name, bool dflt) {
-    const char* v = std::getenv(name);
-    return v && v[0] ? v[0] != '0' : dflt;
-  };
-  g->opt_staged = flag("GS_UPDATE_STAGED", g->opt_staged);
-  g->opt_stream = flag("GS_STREAM_LOADS", g->opt_stream);
-  g->opt_sweep = flag("GS_SWEEP", g->opt_sweep);
-  g->opt_asm_stream = flag("GS_ASM_STREAM_STORES", g->opt_asm_stream);
+  env = std::getenv("GS_UPDATE_STAGED");
+  g->update_staged = !(env && env[0] == '0');
   {
     int per_sm = 0, sms = 0, dev = 0, coop = 0;
     GS_CUDA(g, cudaGetDevice(&dev));

@@ -143,15 +143,12 @@ __device__ __forceinline__ void apply_scalars(Scalars* sc, int op, double t0, do
 // tile partials -> (last CTA) segment sums -> (single rank) totals and scalar step.
 // In the last CTA warp w folds segment w: lane l adds partials l, l+32, ... in order, then the fixed
 // butterfly; all NQ quantities in one pass, no block barrier per segment.
-// `tile` = the 256-row tile this CTA worked on when it is not blockIdx.x (kernels that sweep the rows backwards).
 template <int NQ>
-__device__ __forceinline__ void reduce_finish(const ReduceCtx& c, const double (&v)[NQ], int op, double* red, int* flag,
-                                              int tile = -1) {
-  const int slot = tile < 0 ? (int)blockIdx.x : tile;
+__device__ __forceinline__ void reduce_finish(const ReduceCtx& c, const double (&v)[NQ], int op, double* red, int* flag) {
 #pragma unroll
   for (int q = 0; q < NQ; ++q) {
     const double s = block_sum(v[q], red);
-    if (threadIdx.x == 0) c.part[(size_t)q * c.part_stride + slot] = s;
+    if (threadIdx.x == 0) c.part[(size_t)q * c.part_stride + blockIdx.x] = s;
   }
   if (last_block(c.counter, flag)) {
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
@@ -193,13 +190,13 @@ __global__ void k_scalars(const double* segs, int nq, int spr, int op, Scalars* 
 }
 
 // ------------------------------------------------------------------------------------------------
-template <int MODE, bool ST = false>
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, 2) k_assemble(const AsmView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
   const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[1] = {0.0};
-  if (r < a.n_own) v[0] = assemble_row<MODE, ST>(a, r);
+  if (r < a.n_own) v[0] = assemble_row<MODE>(a, r);
   reduce_finish<1>(c, v, OP_CHI2, red, &flag);
 }
 
@@ -227,25 +224,6 @@ __global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const doubl
   double v[1] = {0.0};
   if (r < a.n_own) v[0] = spmv_row(a, p, pg, y, r, lambda);
   reduce_finish<1>(c, v, mode == 0 ? OP_PAP : OP_DOT, red, &flag);
-}
-
-// Measured variants of k_spmv (off unless asked for, see gs_graph::opt_* in graphslam_cuda.cu).  CS: H, its lists
-// and the diagonal planes are read with streaming (evict-first) loads; rev: the tiles are walked from the last
-// row to the first, so that a kernel starts on the rows its predecessor touched last.  Same bits either way: a
-// row's arithmetic does not depend on which CTA runs it, and partials are stored by tile.  (6 CTAs/SM as k_spmv.)
-template <bool CS>
-__global__ void __launch_bounds__(kThreads, 6) k_spmv_v(const SpmvView a, const double* __restrict__ p,
-                                                         const double* __restrict__ pg, double* __restrict__ y,
-                                                         const ReduceCtx c, int mode, int rev) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  if (mode == 0 && c.sc->done) return;
-  const double lambda = (mode == 0) ? c.sc->lambda : 0.0;
-  const int tile = rev ? (int)(gridDim.x - 1u - blockIdx.x) : (int)blockIdx.x;
-  const int r = tile * kThreads + threadIdx.x;
-  double v[1] = {0.0};
-  if (r < a.n_own) v[0] = spmv_row<CS>(a, p, pg, y, r, lambda);
-  reduce_finish<1>(c, v, mode == 0 ? OP_PAP : OP_DOT, red, &flag, rev ? (int)(gridDim.x - 1u - blockIdx.x) : (int)blockIdx.x);
 }
 
 __global__ void __launch_bounds__(kThreads) k_minv(const double* __restrict__ Hd, const double* __restrict__ dscale,
@@ -284,35 +262,22 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update(const PcgView a, const 
   reduce_finish<2>(c, v, OP_UPDATE, red, &flag);
 }
 
-// k_pcg_update walking the tiles backwards when `rev` (measured variant, see k_spmv_v)
-__global__ void __launch_bounds__(kThreads, 6) k_pcg_update_v(const PcgView a, const ReduceCtx c, int rev) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  if (c.sc->done) return;
-  const double alpha = c.sc->rz / c.sc->pAp;
-  const int tile = rev ? (int)(gridDim.x - 1u - blockIdx.x) : (int)blockIdx.x;
-  const int r = tile * kThreads + threadIdx.x;
-  double v[2] = {0.0, 0.0};
-  if (r < a.n_own) pcg_update_row(a, r, alpha, v[0], v[1]);
-  reduce_finish<2>(c, v, OP_UPDATE, red, &flag, tile);
-}
-
-// The same update with every global access a full-width one.  pcg_update_row reads and writes its vectors three
-// doubles per thread at a 24-byte stride: a warp's store instruction covers a third of each 32-byte sector it
-// touches, so the nine stores of a row reach L2 as three partial writes per sector, and the twelve loads as
-// three requests per line.  Here the tile's 768 doubles of x, p, r, Ap move as double2 (one or two per thread,
-// consecutive threads on consecutive 16 bytes); x and r are elementwise, the new r goes through shared memory to
-// the thread that owns the row for z = M^-1 r and the two dot products, and z goes back through shared memory to
-// be stored flat.  Same expressions per element and per row as pcg_update_apply, same reduction: same bits.
-template <bool CS>
-__global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a, const ReduceCtx c, int rev) {
+// k_pcg_update with every global access a full-width one (the default; GS_UPDATE_STAGED=0 keeps k_pcg_update).
+// pcg_update_row reads and writes its vectors three doubles per thread at a 24-byte stride: a warp's store
+// instruction covers a third of each 32-byte sector it touches, so the nine stores of a row reach L2 as three
+// partial writes per sector, and the twelve loads as three requests per line.  Here the tile's 768 doubles of
+// x, p, r, Ap move as double2 (one or two per thread, consecutive threads on consecutive 16 bytes); x and r are
+// elementwise, the new r goes through shared memory to the thread that owns the row for z = M^-1 r and the two
+// dot products, and z goes back through shared memory to be stored flat.  Same expressions per element and per
+// row as pcg_update_apply, same reduction tree: same bits (tests/test_gpu_parity.py::test_staged_update_bitwise).
+// C3: 51.5 -> 47.6 us per launch (profiles/r1_v7_variant_probe.jsonl).
+__global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
   __shared__ __align__(16) double sv[3 * kThreads];
   if (c.sc->done) return;
   const double alpha = c.sc->rz / c.sc->pAp;
-  const int tile = rev ? (int)(gridDim.x - 1u - blockIdx.x) : (int)blockIdx.x;
-  const int row0 = tile * kThreads;
+  const int row0 = blockIdx.x * kThreads;
   const int nrow = min(kThreads, a.n_own - row0);        // rows of this tile (the last one may be short)
   const size_t base = 3 * (size_t)row0;                  // 768 doubles per tile: 16-byte aligned
   const int nd = 3 * nrow, nd2 = nd >> 1;
@@ -322,18 +287,11 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a,
   double2* r2 = reinterpret_cast<double2*>(a.r + base);
   double2* s2 = reinterpret_cast<double2*>(sv);
   for (int i = threadIdx.x; i < nd2; i += kThreads) {   // at most two trips
-    const double2 pv = p2[i], qv = q2[i];
-    const double2 xv = CS ? __ldcs(x2 + i) : x2[i];
-    const double2 rv = CS ? __ldcs(r2 + i) : r2[i];
+    const double2 pv = p2[i], qv = q2[i], xv = x2[i], rv = r2[i];
     const double2 xn = make_double2(xv.x + alpha * pv.x, xv.y + alpha * pv.y);
     const double2 rn = make_double2(rv.x - alpha * qv.x, rv.y - alpha * qv.y);
-    if (CS) {
-      __stcs(x2 + i, xn);
-      __stcs(r2 + i, rn);
-    } else {
-      x2[i] = xn;
-      r2[i] = rn;
-    }
+    x2[i] = xn;
+    r2[i] = rn;
     s2[i] = rn;
   }
   if ((nd & 1) && threadIdx.x == 0) {                    // odd number of rows in a short last tile
@@ -349,12 +307,7 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a,
   const int t = threadIdx.x;
   if (t < nrow) {
     const double r0 = sv[3 * t], r1 = sv[3 * t + 1], r2v = sv[3 * t + 2];
-    const size_t n = (size_t)a.n_own, w = (size_t)(row0 + t);
-    const double m00 = ldx<CS>(a.Minv + w), m01 = ldx<CS>(a.Minv + n + w), m02 = ldx<CS>(a.Minv + 2 * n + w);
-    const double m11 = ldx<CS>(a.Minv + 3 * n + w), m12 = ldx<CS>(a.Minv + 4 * n + w), m22 = ldx<CS>(a.Minv + 5 * n + w);
-    z0 = (m00 * r0 + m01 * r1) + m02 * r2v;
-    z1 = (m01 * r0 + m11 * r1) + m12 * r2v;
-    z2 = (m02 * r0 + m12 * r1) + m22 * r2v;
+    apply_minv(a.Minv, (size_t)a.n_own, (size_t)(row0 + t), r0, r1, r2v, z0, z1, z2);
     v[0] = (r0 * z0 + r1 * z1) + r2v * z2;
     v[1] = (r0 * r0 + r1 * r1) + r2v * r2v;
   }
@@ -368,39 +321,7 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a,
   double2* z2p = reinterpret_cast<double2*>(a.z + base);
   for (int i = threadIdx.x; i < nd2; i += kThreads) z2p[i] = s2[i];
   if ((nd & 1) && threadIdx.x == 0) a.z[base + (size_t)nd - 1] = sv[nd - 1];
-  reduce_finish<2>(c, v, OP_UPDATE, red, &flag, tile);
-}
-
-// p = z + beta p, tile by tile (the 768 doubles of 256 rows per CTA, as double2), optionally from the last tile
-// to the first: the companion of the backward sweeps above (k_pcg_dir below splits the range in two halves a grid
-// apart, which has no direction).
-__global__ void __launch_bounds__(kThreads) k_pcg_dir_tiles(const double* __restrict__ z, double* __restrict__ p,
-                                                             const Scalars* sc, int n_own, int rev) {
-  if (sc->done) return;
-  const double beta = sc->beta;
-  const int tile = rev ? (int)(gridDim.x - 1u - blockIdx.x) : (int)blockIdx.x;
-  const int row0 = tile * kThreads;
-  const int nrow = min(kThreads, n_own - row0);
-  const size_t base = 3 * (size_t)row0;
-  const int nd = 3 * nrow, nd2 = nd >> 1;
-  const double2* zz = reinterpret_cast<const double2*>(z + base);
-  double2* pp = reinterpret_cast<double2*>(p + base);
-  const int i = threadIdx.x, j = threadIdx.x + kThreads;
-  double2 za = make_double2(0.0, 0.0), pa = za, zb = za, pb = za;
-  if (i < nd2) {
-    za = zz[i];
-    pa = pp[i];
-  }
-  if (j < nd2) {
-    zb = zz[j];
-    pb = pp[j];
-  }
-  if (i < nd2) pp[i] = make_double2(dir_value(za.x, beta, pa.x), dir_value(za.y, beta, pa.y));
-  if (j < nd2) pp[j] = make_double2(dir_value(zb.x, beta, pb.x), dir_value(zb.y, beta, pb.y));
-  if ((nd & 1) && threadIdx.x == 0) {
-    const size_t e = base + (size_t)nd - 1;
-    p[e] = dir_value(z[e], beta, p[e]);
-  }
+  reduce_finish<2>(c, v, OP_UPDATE, red, &flag);
 }
 
 // p = z + beta p over the flat owned range: four doubles per thread as two 16-byte accesses (one 8-byte

@@ -30,32 +30,6 @@ GS_HD double4 ldg(const double4* p) {
 #endif
 }
 
-// streaming forms for data a kernel touches once per launch (stored blocks of H, lists, M^-1): ld.global.cs /
-// st.global.cs allocate evict-first in L2, so the 24-MB PCG vectors (p, Ap, z) are what stays resident between
-// the kernels of an iteration instead of the 370 MB of H that streams past them.  Same values, same arithmetic.
-template <typename T>
-GS_HD T lds(const T* p) {
-#ifdef __CUDA_ARCH__
-  return __ldcs(p);
-#else
-  return *p;
-#endif
-}
-
-template <typename T>
-GS_HD void sts(T* p, T v) {
-#ifdef __CUDA_ARCH__
-  __stcs(p, v);
-#else
-  *p = v;
-#endif
-}
-
-template <bool CS, typename T>
-GS_HD T ldx(const T* p) {
-  return CS ? lds(p) : ldg(p);
-}
-
 struct SellView {
   const int* base;   // per slice
   const int* width;  // per slice
@@ -134,15 +108,9 @@ GS_HD void diag_pieces(const Sym3& O, const Mat3& Ar, const double e[3], double 
   for (int r = 0; r < 3; ++r) bv[r] = W[0 + r] * e[0] + W[3 + r] * e[1] + W[6 + r] * e[2];
 }
 
-// ST: evict-first stores — the block is next read by the first SpMV, after the rest of the assembly has streamed
-// through L2, so keeping it there only displaces the factor cells the other endpoint's row is about to read
-template <bool ST = false>
 GS_HD void store_block(double* Ho, size_t hstride, int pos, const double M[9]) {
 #pragma unroll
-  for (int k = 0; k < 9; ++k) {
-    if (ST) sts(Ho + (size_t)k * hstride + pos, M[k]);
-    else Ho[(size_t)k * hstride + pos] = M[k];
-  }
+  for (int k = 0; k < 9; ++k) Ho[(size_t)k * hstride + pos] = M[k];
 }
 
 // One factor side under GTSAM's default Jacobians (A_i = [[-c,-s,dt1],[s,-c,dt2],[0,0,-1]], A_j = I):
@@ -211,7 +179,7 @@ GS_HD void asm_begin(AsmAcc& A) {
 
 // one BetweenFactor side: code/cb are the contribution's words, prow/pcol the poses of the row's and the
 // other vertex, (zt, zr, o01, o23, o45) the factor
-template <int MODE, bool ST = false>
+template <int MODE>
 GS_HD void asm_between(AsmAcc& A, uint32_t code, int cb, const double4 prow, const double4 pcol, const double2 zt,
                        const double2 zr, const double2 o01, const double2 o23, const double2 o45, double* Ho,
                        size_t hstride) {
@@ -260,7 +228,7 @@ GS_HD void asm_between(AsmAcc& A, uint32_t code, int cb, const double4 prow, con
   }
   if (cb >= 0) {
     if (cb & 1) {
-      if (A.open >= 0) store_block<ST>(Ho, hstride, A.open, A.acc);
+      if (A.open >= 0) store_block(Ho, hstride, A.open, A.acc);
       A.open = cb >> 2;
 #pragma unroll
       for (int k = 0; k < 9; ++k) A.acc[k] = M[k];
@@ -285,21 +253,17 @@ GS_HD void asm_prior(AsmAcc& A, const double4 prow, const double4 pp, const doub
   for (int k = 0; k < 3; ++k) A.bv[k] += b3[k];
 }
 
-template <bool ST = false>
 GS_HD double asm_end(AsmAcc& A, const AsmView& a, int r) {
-  if (A.open >= 0) store_block<ST>(a.Ho, a.hstride, A.open, A.acc);
+  if (A.open >= 0) store_block(a.Ho, a.hstride, A.open, A.acc);
 #pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    if (ST) sts(a.Hd + (size_t)k * a.n_own + r, A.dg[k]);
-    else a.Hd[(size_t)k * a.n_own + r] = A.dg[k];
-  }
+  for (int k = 0; k < 6; ++k) a.Hd[(size_t)k * a.n_own + r] = A.dg[k];
 #pragma unroll
   for (int k = 0; k < 3; ++k) a.b[3 * (size_t)r + k] = A.bv[k];
   return A.chi2;
 }
 
 // returns the row's chi2 share (factors it is the counting side of, and its priors)
-template <int MODE, bool ST = false>
+template <int MODE>
 GS_HD double assemble_row(const AsmView& a, int r) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
@@ -319,12 +283,12 @@ GS_HD double assemble_row(const AsmView& a, int r) {
       const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
       const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
       const double4 pcol = ldg(a.pose + cur.z);
-      asm_between<MODE, ST>(A, code, cur.y, prow, pcol, zt, zr, o01, o23, o45, a.Ho, a.hstride);
+      asm_between<MODE>(A, code, cur.y, prow, pcol, zt, zr, o01, o23, o45, a.Ho, a.hstride);
     } else {
       asm_prior<MODE>(A, prow, ldg(a.pr.pose + idx), a.pr.om + 6 * idx);
     }
   }
-  return asm_end<ST>(A, a, r);
+  return asm_end(A, a, r);
 }
 
 // graph.error contribution of row r at `pose`: its priors, then the factors whose counting side is
@@ -408,7 +372,7 @@ GS_HD double dir_value(double z, double beta, double p) { return fma(beta, p, z)
 // p: owned rows; pg: ghost rows (local column c >= n_own reads pg + 3 (c - n_own)).
 // DIR: the direction is not stored yet: p(c) = z(c) + beta * pold(c) is formed on the fly for every column the
 // row touches (ghost columns from zg / pg), and the row's own new p goes to pnew.
-template <bool DIR, bool CS = false>
+template <bool DIR>
 GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, const double* z, const double* zg, double beta,
                         double* pnew, double* y, int r, double lambda) {
   const int sl = r / kSlice, lane = r % kSlice;
@@ -416,15 +380,15 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
   double y0 = 0.0, y1 = 0.0, y2 = 0.0;
   // w is uniform over the slice; the next slot's reference is fetched while this slot's block and
   // p are in flight, so a slot costs one dependent round trip
-  int2 nref = w > 0 ? ldx<CS>(a.refs + base) : make_int2(-1, 0);
+  int2 nref = w > 0 ? ldg(a.refs + base) : make_int2(-1, 0);
   for (int s = 0; s < w; ++s) {
     const int2 ref = nref;
-    if (s + 1 < w) nref = ldx<CS>(a.refs + base + (s + 1) * kSlice);
+    if (s + 1 < w) nref = ldg(a.refs + base + (s + 1) * kSlice);
     if (ref.x >= 0) {
       const double* hp = a.Ho + (ref.y >> 1);
       double h[9];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) h[k] = ldx<CS>(hp + (size_t)k * a.hstride);
+      for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * a.hstride);
       double px, py, pz;
       if (DIR) {
         const bool ghost = ref.x >= a.n_own;
@@ -446,7 +410,7 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
   const size_t n = (size_t)a.n_own, rr = (size_t)r;
   double d[6], l[3] = {lambda, lambda, lambda};
 #pragma unroll
-  for (int k = 0; k < 6; ++k) d[k] = ldx<CS>(a.Hd + (size_t)k * n + rr);
+  for (int k = 0; k < 6; ++k) d[k] = ldg(a.Hd + (size_t)k * n + rr);
   if (a.dscale) {
     l[0] *= a.dscale[3 * rr];
     l[1] *= a.dscale[3 * rr + 1];
@@ -464,9 +428,8 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
   return spmv_finish(d, l, q0, q1, q2, y0, y1, y2, y, rr);
 }
 
-template <bool CS = false>
 GS_HD double spmv_row(const SpmvView& a, const double* p, const double* pg, double* y, int r, double lambda) {
-  return spmv_row_t<false, CS>(a, p, pg, nullptr, nullptr, 0.0, nullptr, y, r, lambda);
+  return spmv_row_t<false>(a, p, pg, nullptr, nullptr, 0.0, nullptr, y, r, lambda);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -1,5 +1,7 @@
-"""One-shot GPU probe of the measured PCG / assembly variants (GS_UPDATE_STAGED, GS_STREAM_LOADS, GS_SWEEP,
-GS_ASM_STREAM_STORES — see gs_graph::opt_* in csrc/graphslam_cuda.cu).  For each combination, on config C3:
+"""Short GPU probe of switchable kernel variants (today: GS_UPDATE_STAGED, see csrc/kernels.cuh; the variants that
+lost — evict-first / no-L1 loads of H, alternating sweep direction, evict-first H stores and cp.async slot prefetch
+in assembly — are in git history (commits 2bad73e, 2a75c8b) and their numbers in profiles/r1_v7_variant_probe.jsonl).
+For each combination, on one config (default C3):
 
   * CUDA-event time of every kernel inside the real sequence (gs_profile_pcg / gs_profile_outer),
   * wall time per PCG iteration of a capped solve replayed from the captured CUDA graph (how gs_optimize runs it),
@@ -9,7 +11,7 @@ and the same bit check on a small ragged graph (odd number of rows in the last t
 Results are appended line by line to gpurun_out/variant_probe.jsonl, so a cut-off run still leaves what it
 measured.  No torch import: the library is driven through ctypes only.
 
-  python tools/variant_probe.py [n_poses] [capped_iters]
+  python tools/variant_probe.py [n_poses] [capped_iters] [only: comma-separated variant names] [config]
 """
 import ctypes as C
 import hashlib
@@ -24,15 +26,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from graphslam_b200 import _lib, graph, synth  # noqa: E402
 
-FLAGS = ("GS_UPDATE_STAGED", "GS_STREAM_LOADS", "GS_SWEEP", "GS_ASM_STREAM_STORES")
+FLAGS = ("GS_UPDATE_STAGED",)
 VARIANTS = [
     ("default", {}),
-    ("staged", {"GS_UPDATE_STAGED": "1"}),
-    ("stream", {"GS_STREAM_LOADS": "1"}),
-    ("staged+stream", {"GS_UPDATE_STAGED": "1", "GS_STREAM_LOADS": "1"}),
-    ("staged+stream+sweep", {"GS_UPDATE_STAGED": "1", "GS_STREAM_LOADS": "1", "GS_SWEEP": "1"}),
-    ("sweep", {"GS_SWEEP": "1"}),
-    ("staged+sweep+asm_stream", {"GS_UPDATE_STAGED": "1", "GS_SWEEP": "1", "GS_ASM_STREAM_STORES": "1"}),
+    ("unstaged", {"GS_UPDATE_STAGED": "0"}),
     ("default again", {}),
 ]
 OUT = os.path.join(ROOT, "gpurun_out", "variant_probe.jsonl")
@@ -87,16 +84,19 @@ def run(g, name, env, iters, extra_env=None, profile=True):
 
 
 def main():
-    n = int(sys.argv[1]) if len(sys.argv) > 1 else None
+    n = int(sys.argv[1]) if len(sys.argv) > 1 and int(sys.argv[1]) > 0 else None
     iters = int(sys.argv[2]) if len(sys.argv) > 2 else 640
+    only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
+    variants = [v for v in VARIANTS if only is None or v[0] in only]
     t0 = time.time()
     # small ragged graph first (cheap): 4001 rows = 15 full tiles + 161 rows; three-kernel path forced
     gs_ = synth.config("C3", n=4001)
-    small = [run(gs_, name, env, 96, {"GS_PCG_FUSED": "0"}, profile=False) for name, env in VARIANTS[:-1]]
+    small = [run(gs_, name, env, 96, {"GS_PCG_FUSED": "0"}, profile=False) for name, env in variants if name != "default again"]
     emit({"check": "small ragged graph bits", "equal": len({r["sha1"] for r in small}) == 1})
-    g = synth.config("C3", n=n)
+    cid = sys.argv[4] if len(sys.argv) > 4 else "C3"
+    g = synth.config(cid, n=n)
     emit({"generated": g.name, "n": int(g.n), "e": int(g.e), "s": round(time.time() - t0, 1)})
-    big = [run(g, name, env, iters) for name, env in VARIANTS]
+    big = [run(g, name, env, iters) for name, env in variants]
     emit({"check": "C3 bits", "equal": len({r["sha1"] for r in big}) == 1, "total_s": round(time.time() - t0, 1)})
 
 
