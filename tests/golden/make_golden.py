@@ -26,6 +26,29 @@ for k in range(a.shape[0]):
     out[k, 2] = math.fmod(a[k, 2] + b[k, 2] + math.pi, 2 * math.pi) - math.pi
 np.savez(os.path.join(HERE, "compose_reference.npz"), a=a, b=b, out=out)
 
+# the same function run as the REFERENCE'S OWN CODE: graph.hpp compiled from /root/reference by `make -C oracle ref`
+# (oracle/_ref/libgraph_hpp_ref.so).  2048 pairs incl. the theta wrap on both sides and large translations; this
+# table is what pins compose_reference on machines where the reference build is absent.
+from oracle import ref_graph_hpp as R      # noqa: E402
+if R.available():
+    assert all(np.array_equal(R.compose(x, y), w) for x, y, w in zip(a, b, out)), "python restatement != reference build"
+    rng2 = np.random.default_rng(30_43)
+    a2 = rng2.uniform(-50, 50, size=(2048, 3))
+    b2 = rng2.uniform(-50, 50, size=(2048, 3))
+    a2[:, 2] = rng2.uniform(-2 * math.pi, 2 * math.pi, size=2048)
+    b2[:, 2] = rng2.uniform(-2 * math.pi, 2 * math.pi, size=2048)
+    a2[:6, 2] = [math.pi, -math.pi, 3.0, -3.0, 0.0, math.pi / 2]
+    b2[:6, 2] = [0.0, 0.0, 0.2, -0.2, -math.pi, math.pi / 2]
+    out2 = np.array([R.compose(x, y) for x, y in zip(a2, b2)])
+    cov = rng2.uniform(-1, 1, size=(64, 9))
+    q = np.array([R.covariance_roundtrip(c)[0].reshape(9) for c in cov])
+    back = np.array([R.covariance_roundtrip(c)[1] for c in cov])
+    np.savez_compressed(os.path.join(HERE, "graph_hpp_reference_build.npz"), a=a2, b=b2, out=out2, cov=cov, q=q, back=back,
+                        source="reference src/graph/include/graph.hpp compiled by oracle/Makefile target ref "
+                               "(g++ -O2 -ffp-contract=off, stand-in headers oracle/ref_stubs)")
+else:
+    print("oracle/_ref/libgraph_hpp_ref.so absent: graph_hpp_reference_build.npz not regenerated")
+
 g = synth.config("C1")
 prob = O.Problem.from_graph(g)
 x, tr = O.lm_optimize(prob, g.init)

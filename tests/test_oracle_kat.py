@@ -33,6 +33,39 @@ def test_compose_reference_table():
         assert np.array_equal(O.compose_reference(a, b), want)
 
 
+def test_compose_reference_against_reference_build_vectors():
+    """graph_hpp_reference_build.npz was produced by the reference's own graph.hpp compiled here (oracle/Makefile
+    target `ref`): the oracle's compose_reference and the library's gs_compose_reference must reproduce every
+    vector bit for bit, and the covariance layout is row-major both ways (graph.hpp:45-68)."""
+    from graphslam_b200 import graph
+    tab = np.load(os.path.join(GOLDEN, "graph_hpp_reference_build.npz"))
+    for a, b, want in zip(tab["a"], tab["b"], tab["out"]):
+        assert np.array_equal(O.compose_reference(a, b), want)
+        assert np.array_equal(graph.compose_reference(a, b), want)
+    assert np.array_equal(tab["q"], tab["cov"]) and np.array_equal(tab["back"], tab["cov"])
+
+
+def test_compose_reference_against_live_reference_build():
+    """Where oracle/_ref/libgraph_hpp_ref.so exists (this container and any box the repo snapshot travels to), run the
+    reference's compiled compose beside ours on fresh random inputs."""
+    from graphslam_b200 import graph
+    from oracle import ref_graph_hpp as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libgraph_hpp_ref.so not built (needs /root/reference; `make -C oracle ref`)")
+    rng = np.random.default_rng(99)
+    A = rng.uniform(-20, 20, size=(4000, 3))
+    B = rng.uniform(-20, 20, size=(4000, 3))
+    for a, b in zip(A, B):
+        want = R.compose(a, b)
+        assert np.array_equal(O.compose_reference(a, b), want)
+        assert np.array_equal(graph.compose_reference(a, b), want)
+    tab = np.load(os.path.join(GOLDEN, "compose_reference.npz"))
+    for a, b, want in zip(tab["a"], tab["b"], tab["out"]):
+        assert np.array_equal(R.compose(a, b), want)
+    q, back = R.covariance_roundtrip(np.arange(9.0))
+    assert np.array_equal(q, np.arange(9.0).reshape(3, 3)) and np.array_equal(back, np.arange(9.0))
+
+
 def test_compose_correct():
     out = O.compose(np.array([1.0, 2.0, math.pi / 2]), np.array([1.0, 0.0, math.pi]))
     assert np.allclose(out, [1.0, 3.0, -math.pi / 2])
