@@ -31,14 +31,40 @@ class CpuStats(C.Structure):
 
 
 _lib = None
+HOST_TAG = os.path.join(HERE, "_build", "host.txt")
+
+
+def _host_tag() -> str:
+    """CPU model + ISA flags of this machine: the port is built -march=native, so a library built on another kind of
+    host (the repo snapshot travels to the GPU box with its built .so files) is rebuilt here rather than trusted."""
+    model, flags = "", ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name") and not model:
+                    model = line.split(":", 1)[1].strip()
+                elif line.startswith("flags") and not flags:
+                    flags = " ".join(sorted(line.split(":", 1)[1].split()))
+                if model and flags:
+                    break
+    except OSError:
+        pass
+    return model + "\n" + flags + "\n"
 
 
 def load():
     global _lib
     if _lib is None:
         src = os.path.join(HERE, "cpu_ref.c")
-        if not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src):
-            subprocess.run(["make", "-s", "-C", HERE], check=True)
+        tag = _host_tag()
+        try:
+            same_host = open(HOST_TAG).read() == tag
+        except OSError:
+            same_host = False
+        if not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src) or not same_host:
+            subprocess.run(["make", "-s", "-B", "-C", HERE, "_build/libgs_cpu_ref.so"], check=True)
+            with open(HOST_TAG, "w") as f:
+                f.write(tag)
         _lib = C.CDLL(LIB)
         _lib.gs_cpu_default_params.argtypes = [C.POINTER(CpuParams)]
         _lib.gs_cpu_threads.restype = C.c_int
