@@ -132,11 +132,7 @@ GS_HD void side_default(const double4 pi, const double4 pj, const double2 zt, co
   const double hy = -si * dx + ci * dy;
   double c = ci * cj + si * sj;
   double s = -si * cj + ci * sj;
-  {  // Rot2::atan2(s, c) normalises
-    const double inv = 1.0 / sqrt(c * c + s * s);
-    c *= inv;
-    s *= inv;
-  }
+  rot2_normalize(c, s);  // Rot2::atan2(s, c)
   const double cm = zr.x, sm = zr.y;
   const double rx = hx - zt.x, ry = hy - zt.y;
   S.e[0] = cm * rx + sm * ry;

@@ -15,6 +15,18 @@
 
 namespace gs {
 
+// gtsam::Rot2::normalize(): rescale (c, s) only when c^2 + s^2 is off 1 by more than 1e-10 — which the product of
+// two unit rotations never is, so in the kernels this is one compare and an untaken branch, not a sqrt and a
+// division in every factor's dependency chain (Rot2::atan2 / Rot2::fromCosSin both go through it).
+GS_HD void rot2_normalize(double& c, double& s) {
+  const double scale = c * c + s * s;
+  if (fabs(scale - 1.0) > 1e-10) {
+    const double inv = 1.0 / sqrt(scale);
+    c *= inv;
+    s *= inv;
+  }
+}
+
 struct Sym3 {  // symmetric 3x3: 00 01 02 11 12 22
   double a00, a01, a02, a11, a12, a22;
 };
@@ -37,11 +49,7 @@ GS_HD void between_linearize(const double4 pi, const double4 pj, const double2 z
   const double hy = -si * dx + ci * dy;
   double c = ci * cj + si * sj;
   double s = -si * cj + ci * sj;
-  {  // Rot2::atan2(s, c) normalises
-    const double inv = 1.0 / sqrt(c * c + s * s);
-    c *= inv;
-    s *= inv;
-  }
+  rot2_normalize(c, s);  // Rot2::atan2(s, c)
   const double cm = zr.x, sm = zr.y;
   const double rx = hx - zt.x, ry = hy - zt.y;
   L.e[0] = cm * rx + sm * ry;
@@ -78,9 +86,7 @@ GS_HD void between_error(const double4 pi, const double4 pj, const double2 zt, c
   const double hy = -si * dx + ci * dy;
   double c = ci * cj + si * sj;
   double s = -si * cj + ci * sj;
-  const double inv = 1.0 / sqrt(c * c + s * s);
-  c *= inv;
-  s *= inv;
+  rot2_normalize(c, s);
   const double cm = zr.x, sm = zr.y;
   const double rx = hx - zt.x, ry = hy - zt.y;
   e[0] = cm * rx + sm * ry;

@@ -98,8 +98,10 @@ static void lin_between(const double* pi, const double* pj, const double* z, con
   const double dx = pj[0] - pi[0], dy = pj[1] - pi[1];
   const double hx = ci * dx + si * dy, hy = -si * dx + ci * dy;
   double c = ci * cj + si * sj, s = -si * cj + ci * sj;
-  const double inv = 1.0 / sqrt(c * c + s * s);
-  c *= inv; s *= inv;
+  { /* gtsam::Rot2::normalize(): only when c^2 + s^2 is off 1 by more than 1e-10 */
+    const double scale = c * c + s * s;
+    if (fabs(scale - 1.0) > 1e-10) { const double inv = 1.0 / sqrt(scale); c *= inv; s *= inv; }
+  }
   const double cm = zcs[0], sm = zcs[1];
   const double rx = hx - z[0], ry = hy - z[1];
   e[0] = cm * rx + sm * ry;

@@ -138,8 +138,11 @@ def between_residual(pi, pj, z, jacobian_mode=JAC_GTSAM_DEFAULT):
     hy = -si * dx + ci * dy
     c = ci * cj + si * sj
     s = -si * cj + ci * sj
-    nrm = np.hypot(c, s)
-    c, s = c / nrm, s / nrm
+    scale = c * c + s * s                        # gtsam::Rot2::normalize(): only when off 1 by more than 1e-10
+    fix = np.abs(scale - 1.0) > 1e-10
+    if fix.any():
+        inv = np.where(fix, 1.0 / np.sqrt(np.where(fix, scale, 1.0)), 1.0)
+        c, s = c * inv, s * inv
     cm, sm = np.cos(z[:, 2]), np.sin(z[:, 2])
     rx, ry = hx - z[:, 0], hy - z[:, 1]
     e = np.empty((pi.shape[0], 3))
