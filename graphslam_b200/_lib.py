@@ -11,9 +11,9 @@ c_double_p = C.POINTER(C.c_double)
 c_u64_p = C.POINTER(C.c_uint64)
 c_i32_p = C.POINTER(C.c_int32)
 
-GS_OK, GS_EINVAL, GS_ENOTSPD, GS_EDUPKEY, GS_ENOKEY, GS_ECUDA, GS_ENCCL, GS_ENOTCONVERGED, GS_ENAN = range(9)
+GS_OK, GS_EINVAL, GS_ENOTSPD, GS_EDUPKEY, GS_ENOKEY, GS_ECUDA, GS_ENCCL, GS_ENOTCONVERGED, GS_ENAN, GS_ENOMEM = range(10)
 STATUS_NAMES = ["GS_OK", "GS_EINVAL", "GS_ENOTSPD", "GS_EDUPKEY", "GS_ENOKEY", "GS_ECUDA", "GS_ENCCL",
-                "GS_ENOTCONVERGED", "GS_ENAN"]
+                "GS_ENOTCONVERGED", "GS_ENAN", "GS_ENOMEM"]
 
 
 class GsParams(C.Structure):

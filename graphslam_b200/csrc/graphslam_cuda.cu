@@ -19,7 +19,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <limits>
+#include <new>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -979,6 +981,33 @@ gs_status create_common(gs_graph* g) {
 
 }  // namespace
 
+// No exception crosses the C ABI: every entry point is a function-try-block that ends here.  The host side
+// allocates (std::vector growth while adding factors, the structure build); std::bad_alloc and anything else a
+// standard container can throw become a status, with the message stored when that itself does not throw.
+static gs_status on_exception(gs_graph* g) noexcept {
+  gs_status code = GS_EINVAL;
+  const char* what = "unexpected C++ exception";
+  try {
+    throw;
+  } catch (const std::bad_alloc&) {
+    code = GS_ENOMEM;
+    what = "out of host memory";
+  } catch (const std::exception& e) {
+    what = e.what();
+    try {
+      if (g) g->fail(code, "C++ exception: %s", what);
+    } catch (...) {
+    }
+    return code;
+  } catch (...) {
+  }
+  try {
+    if (g) g->fail(code, "%s", what);
+  } catch (...) {
+  }
+  return code;
+}
+
 // =================================================================================================
 extern "C" {
 
@@ -1005,7 +1034,7 @@ void gs_default_params(gs_params* p) {
 
 int gs_version(void) { return GS_VERSION_MAJOR * 1000 + GS_VERSION_MINOR; }
 
-gs_status gs_create(gs_graph** out, const gs_params* params) {
+gs_status gs_create(gs_graph** out, const gs_params* params) try {
   if (!out) return GS_EINVAL;
   *out = nullptr;
   gs_graph* g = new (std::nothrow) gs_graph();
@@ -1016,9 +1045,11 @@ gs_status gs_create(gs_graph** out, const gs_params* params) {
   if (g->prm.world_size != 1 || g->prm.rank != 0)
     return g->fail(GS_EINVAL, "multi-rank graphs are created with gs_create_distributed");
   return create_common(g);
+} catch (...) {
+  return on_exception(nullptr);
 }
 
-gs_status gs_nccl_unique_id(void* out, size_t cap, size_t* n) {
+gs_status gs_nccl_unique_id(void* out, size_t cap, size_t* n) try {
   if (n) *n = sizeof(ncclUniqueId);
   if (!out) return GS_OK;
   if (cap < sizeof(ncclUniqueId)) return GS_EINVAL;
@@ -1027,9 +1058,11 @@ gs_status gs_nccl_unique_id(void* out, size_t cap, size_t* n) {
   if (gs::nccl().GetUniqueId(&id) != ncclSuccess) return GS_ENCCL;
   std::memcpy(out, &id, sizeof id);
   return GS_OK;
+} catch (...) {
+  return on_exception(nullptr);
 }
 
-gs_status gs_create_distributed(gs_graph** out, const gs_params* params, const void* nccl_id, size_t id_bytes) {
+gs_status gs_create_distributed(gs_graph** out, const gs_params* params, const void* nccl_id, size_t id_bytes) try {
   if (!out) return GS_EINVAL;
   *out = nullptr;
   gs_graph* g = new (std::nothrow) gs_graph();
@@ -1052,9 +1085,11 @@ gs_status gs_create_distributed(gs_graph** out, const gs_params* params, const v
     GS_NCCL(g, gs::nccl().CommInitRank(&g->comm, w, id, r));
   }
   return GS_OK;
+} catch (...) {
+  return on_exception(nullptr);
 }
 
-gs_status gs_destroy(gs_graph* g) {
+gs_status gs_destroy(gs_graph* g) try {
   if (!g) return GS_EINVAL;
   if (g->stream) cudaStreamSynchronize(g->stream);
   destroy_graph_exec(g);
@@ -1076,9 +1111,11 @@ gs_status gs_destroy(gs_graph* g) {
   if (g->stream) cudaStreamDestroy(g->stream);
   delete g;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_set_params(gs_graph* g, const gs_params* p) {
+gs_status gs_set_params(gs_graph* g, const gs_params* p) try {
   if (!g || !p) return GS_EINVAL;
   if (p->world_size != g->prm.world_size || p->rank != g->prm.rank || p->device != g->prm.device)
     return g->fail(GS_EINVAL, "device/rank/world_size are fixed at gs_create");
@@ -1086,9 +1123,11 @@ gs_status gs_set_params(gs_graph* g, const gs_params* p) {
   g->prm = *p;
   if (mode_changed) g->system_valid = false;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_add_vertex(gs_graph* g, uint64_t key, const double pose[3]) {
+gs_status gs_add_vertex(gs_graph* g, uint64_t key, const double pose[3]) try {
   if (!g || !pose) return GS_EINVAL;
   if (!(std::isfinite(pose[0]) && std::isfinite(pose[1]) && std::isfinite(pose[2])))
     return g->fail(GS_EINVAL, "non-finite pose for key %llu", (unsigned long long)key);
@@ -1105,9 +1144,11 @@ gs_status gs_add_vertex(gs_graph* g, uint64_t key, const double pose[3]) {
   g->xyt.insert(g->xyt.end(), pose, pose + 3);
   g->topo_dirty = true;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_add_prior(gs_graph* g, uint64_t key, const double pose[3], const double cov9[9]) {
+gs_status gs_add_prior(gs_graph* g, uint64_t key, const double pose[3], const double cov9[9]) try {
   if (!g || !pose || !cov9) return GS_EINVAL;
   const int v = g->find(key);
   if (v < 0) return g->fail(GS_ENOKEY, "prior on unknown key %llu", (unsigned long long)key);
@@ -1118,9 +1159,11 @@ gs_status gs_add_prior(gs_graph* g, uint64_t key, const double pose[3], const do
   g->pr_om.insert(g->pr_om.end(), om, om + 6);
   g->topo_dirty = true;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3], const double cov9[9]) {
+gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3], const double cov9[9]) try {
   if (!g || !d || !cov9) return GS_EINVAL;
   const int a = g->find(k1), b = g->find(k2);
   if (a < 0 || b < 0)
@@ -1136,10 +1179,12 @@ gs_status gs_add_between(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3
   g->eom.insert(g->eom.end(), om, om + 6);
   g->topo_dirty = true;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 // noiseModel::Gaussian::Information(I) forms of the two calls above (what a g2o file carries)
-gs_status gs_add_prior_information(gs_graph* g, uint64_t key, const double pose[3], const double info6[6]) {
+gs_status gs_add_prior_information(gs_graph* g, uint64_t key, const double pose[3], const double info6[6]) try {
   if (!g || !pose || !info6) return GS_EINVAL;
   const int v = g->find(key);
   if (v < 0) return g->fail(GS_ENOKEY, "prior on unknown key %llu", (unsigned long long)key);
@@ -1150,9 +1195,11 @@ gs_status gs_add_prior_information(gs_graph* g, uint64_t key, const double pose[
   g->pr_om.insert(g->pr_om.end(), info6, info6 + 6);
   g->topo_dirty = true;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_add_between_information(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3], const double info6[6]) {
+gs_status gs_add_between_information(gs_graph* g, uint64_t k1, uint64_t k2, const double d[3], const double info6[6]) try {
   if (!g || !d || !info6) return GS_EINVAL;
   const int a = g->find(k1), b = g->find(k2);
   if (a < 0 || b < 0)
@@ -1167,11 +1214,13 @@ gs_status gs_add_between_information(gs_graph* g, uint64_t k1, uint64_t k2, cons
   g->eom.insert(g->eom.end(), info6, info6 + 6);
   g->topo_dirty = true;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 // g2o / TORO text (csrc/g2o.hpp).  Loading appends to the graph: vertices first, then priors, then
 // edges, in file order; nothing is added when the file is malformed or names an unknown/duplicate key.
-gs_status gs_load_g2o(gs_graph* g, const char* path, gs_g2o_counts* counts) {
+gs_status gs_load_g2o(gs_graph* g, const char* path, gs_g2o_counts* counts) try {
   if (!g || !path) return GS_EINVAL;
   gs::G2oData d;
   const std::string err = gs::read_g2o(path, d);
@@ -1221,10 +1270,12 @@ gs_status gs_load_g2o(gs_graph* g, const char* path, gs_g2o_counts* counts) {
     counts->skipped_lines = d.skipped;
   }
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 // the whole graph with the CURRENT values (after gs_optimize: the optimum), loadable by gs_load_g2o
-gs_status gs_save_g2o(gs_graph* g, const char* path) {
+gs_status gs_save_g2o(gs_graph* g, const char* path) try {
   if (!g || !path) return GS_EINVAL;
   if (gs_status s = download_values(g)) return s;
   gs::G2oData d;
@@ -1245,10 +1296,12 @@ gs_status gs_save_g2o(gs_graph* g, const char* path) {
   const std::string err = gs::write_g2o(path, d);
   if (!err.empty()) return g->fail(GS_EINVAL, "%s", err.c_str());
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 gs_status gs_add_batch(gs_graph* g, size_t nv, const uint64_t* keys, const double* poses, size_t ne, const uint64_t* k1,
-                       const uint64_t* k2, const double* deltas, const double* cov9s) {
+                       const uint64_t* k2, const double* deltas, const double* cov9s) try {
   if (!g) return GS_EINVAL;
   if ((nv && (!keys || !poses)) || (ne && (!k1 || !k2 || !deltas || !cov9s))) return g->fail(GS_EINVAL, "null array");
   g->keys.reserve(g->keys.size() + nv);
@@ -1262,14 +1315,18 @@ gs_status gs_add_batch(gs_graph* g, size_t nv, const uint64_t* keys, const doubl
   for (size_t k = 0; k < ne; ++k)
     if (gs_status s = gs_add_between(g, k1[k], k2[k], deltas + 3 * k, cov9s + 9 * k)) return s;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_prepare(gs_graph* g) {
+gs_status gs_prepare(gs_graph* g) try {
   if (!g) return GS_EINVAL;
   return prepare(g, nullptr);
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_optimize(gs_graph* g, gs_stats* st) {
+gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   if (!g) return GS_EINVAL;
   const double t_begin = now_ms();
   gs_stats local;
@@ -1402,9 +1459,11 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) {
   local.d2h_bytes = g->d2h_bytes - d2h0;
   if (st) *st = local;
   return rc;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_get_pose(gs_graph* g, uint64_t key, double out[3]) {
+gs_status gs_get_pose(gs_graph* g, uint64_t key, double out[3]) try {
   if (!g || !out) return GS_EINVAL;
   const int v = g->find(key);
   if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)key);
@@ -1413,9 +1472,11 @@ gs_status gs_get_pose(gs_graph* g, uint64_t key, double out[3]) {
   out[1] = g->xyt[3 * v + 1];
   out[2] = std::atan2(std::sin(g->xyt[3 * v + 2]), std::cos(g->xyt[3 * v + 2]));
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* n) {
+gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* n) try {
   if (!g) return GS_EINVAL;
   const size_t nv = g->keys.size();
   if (n) *n = nv;
@@ -1433,9 +1494,11 @@ gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, siz
     }
   }
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt) {
+gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt) try {
   if (!g || (n && (!keys || !xyt))) return GS_EINVAL;
   if (gs_status s = download_values(g)) return s;
   for (size_t k = 0; k < n; ++k) {
@@ -1450,37 +1513,47 @@ gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double
   g->system_valid = false;
   if (!g->topo_dirty) return upload_values(g);
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_chi2(gs_graph* g, double* chi2) {
+gs_status gs_chi2(gs_graph* g, double* chi2) try {
   if (!g || !chi2) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;
   if (gs_status s = launch_chi2(g, g->d_pose.p)) return s;
   if (gs_status s = read_scalars(g)) return s;
   *chi2 = g->h_sc->chi2;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_num_vertices(const gs_graph* g, size_t* n) {
+gs_status gs_num_vertices(const gs_graph* g, size_t* n) try {
   if (!g || !n) return GS_EINVAL;
   *n = g->keys.size();
   return GS_OK;
+} catch (...) {
+  return on_exception(const_cast<gs_graph*>(g));
 }
 
-gs_status gs_num_factors(const gs_graph* g, size_t* n) {
+gs_status gs_num_factors(const gs_graph* g, size_t* n) try {
   if (!g || !n) return GS_EINVAL;
   *n = g->e1.size() + g->pr_v.size();
   return GS_OK;
+} catch (...) {
+  return on_exception(const_cast<gs_graph*>(g));
 }
 
-gs_status gs_get_transfer_bytes(const gs_graph* g, double* h2d, double* d2h) {
+gs_status gs_get_transfer_bytes(const gs_graph* g, double* h2d, double* d2h) try {
   if (!g) return GS_EINVAL;
   if (h2d) *h2d = g->h2d_bytes;
   if (d2h) *d2h = g->d2h_bytes;
   return GS_OK;
+} catch (...) {
+  return on_exception(const_cast<gs_graph*>(g));
 }
 
-gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* nnzb) {
+gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* nnzb) try {
   if (!g) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;
   std::vector<int32_t> rp, ci;
@@ -1489,9 +1562,11 @@ gs_status gs_get_pattern(gs_graph* g, int32_t* rowptr, int32_t* colidx, size_t* 
   if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
   if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) {
+gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) try {
   if (!g) return GS_EINVAL;
   if (g->world != 1) return g->fail(GS_EINVAL, "gs_get_system is a single-rank parity hook");
   if (gs_status s = prepare(g, nullptr)) return s;
@@ -1532,9 +1607,11 @@ gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) {
     }
   }
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual) {
+gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_iters, double* rel_residual) try {
   if (!g) return GS_EINVAL;
   if (g->world != 1 && delta) return g->fail(GS_EINVAL, "gs_solve_linear returns delta on a single rank only");
   if (gs_status s = prepare(g, nullptr)) return s;
@@ -1549,13 +1626,15 @@ gs_status gs_solve_linear(gs_graph* g, double lambda, double* delta, int* pcg_it
   if (done == 2) return g->fail(GS_ENAN, "PCG breakdown (p^T A p <= 0 or NaN)");
   if (done == 3) return g->fail(GS_ENOTCONVERGED, "PCG reached pcg_max_iters");
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 // Marginals(graph, values).marginalCovariance(key): the (key, key) 3x3 block of (J^T Omega J)^-1 at the
 // current values, in the tangent space of that pose (the reference has it commented out,
 // graph.cpp:120,126-127).  Three PCG solves with unit right-hand sides per pose, undamped, on the
 // assembled system; on several ranks the owner of the pose broadcasts the three rows.
-gs_status gs_marginal_covariances(gs_graph* g, size_t n, const uint64_t* keys, double* cov9s) {
+gs_status gs_marginal_covariances(gs_graph* g, size_t n, const uint64_t* keys, double* cov9s) try {
   if (!g || (n && (!keys || !cov9s))) return GS_EINVAL;
   for (size_t k = 0; k < n; ++k)
     if (g->find(keys[k]) < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[k]);
@@ -1611,13 +1690,17 @@ gs_status gs_marginal_covariances(gs_graph* g, size_t n, const uint64_t* keys, d
       cudaStreamSynchronize(g->stream) == cudaSuccess)
     g->system_valid = true;
   return rc;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_marginal_covariance(gs_graph* g, uint64_t key, double cov9[9]) {
+gs_status gs_marginal_covariance(gs_graph* g, uint64_t key, double cov9[9]) try {
   return gs_marginal_covariances(g, 1, &key, cov9);
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n) {
+gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas, int32_t* tries, size_t* n) try {
   if (!g) return GS_EINVAL;
   const size_t m = g->tr_tries.size();
   if (n) *n = m;
@@ -1630,9 +1713,11 @@ gs_status gs_get_trace(gs_graph* g, size_t cap, double* errors, double* lambdas,
   }
   if (tries) std::copy(g->tr_tries.begin(), g->tr_tries.end(), tries);
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], double bytes[3]) {
+gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], double bytes[3]) try {
   if (!g || !ms || iters <= 0) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;
   if (!g->system_valid)
@@ -1678,9 +1763,11 @@ gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], do
   }
   g->launches += launches_per_pcg_iteration(g) * (int64_t)(iters + 3) + 2;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
-gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3]) {
+gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3]) try {
   if (!g || !ms || reps <= 0) return GS_EINVAL;
   if (gs_status s = prepare(g, nullptr)) return s;
   GS_CUDA(g, cudaMemsetAsync(g->d_x.p, 0, sizeof(double) * 3 * std::max(g->n_loc, 1), g->stream));
@@ -1715,6 +1802,8 @@ gs_status gs_profile_outer(gs_graph* g, int reps, double ms[3], double bytes[3])
     bytes[2] = 80.0 * E;                                        // K5 chi2
   }
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 const char* gs_last_error(const gs_graph* g) { return g ? g->err.c_str() : "null graph"; }
@@ -1743,7 +1832,7 @@ void gs_compose(const double a[3], const double b[3], double out[3]) {
   out[2] = std::atan2(std::sin(th), std::cos(th));
 }
 
-gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist) {
+gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist) try {
   if (!g || !out_key || skip < 0) return GS_EINVAL;
   if (g->world != 1) return g->fail(GS_EINVAL, "gs_closest_keyframe runs on a single-rank graph");
   const int v = g->find(key);
@@ -1776,11 +1865,13 @@ gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out
   *out_key = g->keys[bi];
   if (out_dist) *out_dist = bd;
   return GS_OK;
+} catch (...) {
+  return on_exception(g);
 }
 
 // ---- host-only debug entries (no device needed): exercise the product's own host code on a CPU box
 gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,
-                          size_t* nnzb, int32_t* perm) {
+                          size_t* nnzb, int32_t* perm) try {
   if (n <= 0 || e < 0 || (e && (!ei || !ej))) return GS_EINVAL;
   std::vector<int32_t> rp, ci;
   gs::global_pattern(n, e, ei, ej, rp, ci);
@@ -1793,13 +1884,15 @@ gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t
     std::memcpy(perm, pm.data(), sizeof(int32_t) * e);
   }
   return GS_OK;
+} catch (...) {
+  return on_exception(nullptr);
 }
 
 // the g2o reader/writer the product uses, without a graph handle: parse `in_path`, report the counts
 // {vertices, edges, priors, fixed, skipped}, optionally copy the parsed arrays out and/or write the
 // parsed content back to `out_path`
 gs_status gs_host_g2o(const char* in_path, const char* out_path, size_t counts[5], uint64_t* vkey, double* vxyt,
-                      uint64_t* e1, uint64_t* e2, double* ez, double* einfo, uint64_t* pkey, double* pxyt, double* pinfo) {
+                      uint64_t* e1, uint64_t* e2, double* ez, double* einfo, uint64_t* pkey, double* pxyt, double* pinfo) try {
   if (!in_path) return GS_EINVAL;
   gs::G2oData d;
   if (!gs::read_g2o(in_path, d).empty()) return GS_EINVAL;
@@ -1824,12 +1917,14 @@ gs_status gs_host_g2o(const char* in_path, const char* out_path, size_t counts[5
   out(pinfo, d.pinfo);
   if (out_path && !gs::write_g2o(out_path, d).empty()) return GS_EINVAL;
   return GS_OK;
+} catch (...) {
+  return on_exception(nullptr);
 }
 
 // one factor, host evaluation of the same inline functions the kernels use
 gs_status gs_host_between(const double pi[3], const double pj[3], const double z[3], const double cov9[9], int mode,
                           double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],
-                          double bi[3], double bj[3]) {
+                          double bi[3], double bj[3]) try {
   double om[6];
   if (!spd_information(cov9, om)) return GS_ENOTSPD;
   const double4 a = make_double4(pi[0], pi[1], std::cos(pi[2]), std::sin(pi[2]));
@@ -1853,6 +1948,8 @@ gs_status gs_host_between(const double pi[3], const double pj[3], const double z
   std::memcpy(Ai, L.Ai.m, sizeof L.Ai.m);
   std::memcpy(Aj, L.Aj.m, sizeof L.Aj.m);
   return GS_OK;
+} catch (...) {
+  return on_exception(nullptr);
 }
 
 }  // extern "C"

@@ -42,7 +42,8 @@ typedef enum {
   GS_ECUDA = 5,         /* CUDA runtime failure, see gs_last_error */
   GS_ENCCL = 6,         /* NCCL failure (multi-GPU) */
   GS_ENOTCONVERGED = 7, /* PCG hit pcg_max_iters before pcg_rel_tol */
-  GS_ENAN = 8           /* non-finite chi2 */
+  GS_ENAN = 8,          /* non-finite chi2 */
+  GS_ENOMEM = 9         /* host allocation failed (std::bad_alloc caught at the boundary; no exception crosses the ABI) */
 } gs_status;
 
 enum { GS_JACOBIAN_GTSAM_DEFAULT = 0, GS_JACOBIAN_EXACT = 1 };
