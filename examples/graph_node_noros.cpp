@@ -1,7 +1,7 @@
 // graph.cpp with ROS stripped: replays a synthetic registration stream through the node's verbs
 // (prior_factor / new_factor / loop_factor / solve, reference src/graph/src/graph.cpp:27-132).
-//   g++ -std=c++17 -Iinclude examples/graph_node_noros.cpp -Lgraphslam_b200/lib -lgraphslam_cuda \
-//       -Wl,-rpath,$PWD/graphslam_b200/lib -o graph_node_noros && ./graph_node_noros 2000
+//   g++ -std=c++17 -Iinclude examples/graph_node_noros.cpp -Lgraphslam_b200/lib -lgraphslam_cuda
+//       -Wl,-rpath,$PWD/graphslam_b200/lib -o graph_node_noros   (one command line), then ./graph_node_noros 2000
 #include <cstdio>
 #include <cstdlib>
 #include <random>

@@ -4,6 +4,7 @@ functions (the same ones the kernels compile) agree with the oracle, and nothing
 import ctypes as C
 import os
 import re
+import subprocess
 
 import numpy as np
 import pytest
@@ -134,3 +135,30 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"(from|import)\s+oracle|oracle[/.]\w|libgs_oracle", src), f"{f} reaches into oracle/"
+
+
+def test_header_is_plain_c99(tmp_path):
+    """The boundary is a C ABI: include/graphslam_cuda.h (and the debug header) must compile as strict C99."""
+    src = tmp_path / "abi.c"
+    src.write_text('#include "graphslam_cuda.h"\n#include "graphslam_cuda_debug.h"\n'
+                   "int main(void) { gs_params p; gs_default_params(&p); return (int)GS_ENOMEM - 9 + p.max_iterations * 0; }\n")
+    inc = os.path.join(ROOT, "include")
+    res = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-fsyntax-only", "-I", inc, str(src)],
+                         capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+
+
+def test_cpp_shim_and_ros_free_example_build_against_the_library(lib, tmp_path):
+    """include/graphslam_cuda.hpp (the drop-in for graph.cpp's verbs) and examples/graph_node_noros.cpp compile and
+    link against the built .so — what a maintainer of the reference node would do."""
+    from graphslam_b200 import build
+    exe = tmp_path / "graph_node_noros"
+    res = subprocess.run(["g++", "-std=c++17", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                          os.path.join(ROOT, "examples", "graph_node_noros.cpp"), "-o", str(exe), build.LIB,
+                          "-Wl,-rpath," + os.path.dirname(build.LIB)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    # without a CUDA device the example must fail loudly (no CPU fallback), not crash
+    run = subprocess.run([str(exe)], capture_output=True, text=True)
+    if not _cuda_present():
+        assert run.returncode != 0 and run.returncode > 0, (run.returncode, run.stderr)
+        assert "CUDA" in (run.stderr + run.stdout)
