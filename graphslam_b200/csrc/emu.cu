@@ -218,8 +218,13 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
   }
 
   // ---- K1+K2
+  if (form & 2)
+    for (VRank& me : W.R)
+      if (me.S.n_merged != 0) return GS_EINVAL;   // a pair with two factors needs the run accumulator
   const double chi2 = W.reduce([&](VRank& me, int r) {
     const gs::AsmView a = me.av(me.pose.data());
+    if (form & 2)   // the form without run accumulator (k_assemble_nodup); only valid when no pair has two factors
+      return jacobian_mode ? gs::assemble_row<1, true>(a, r) : gs::assemble_row<0, true>(a, r);
     return jacobian_mode ? gs::assemble_row<1>(a, r) : gs::assemble_row<0>(a, r);
   });
   out->chi2 = chi2;
@@ -278,6 +283,7 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
   rr = W.reduce([&](VRank& me, int r) { return gs::dot_row(me.r.data(), me.r.data(), r); });
   const double rr0 = rr;
   int it = 0, done = (rr == 0.0) ? 1 : 0;
+  form &= 1;
   if (form == 1) {
     // the two-kernel form of the peer-memory path and of the persistent small-graph kernel: the direction is not
     // stored before the product; p(c) = z(c) + beta p_prev(c) is formed on the fly (ghost columns from the exchanged
@@ -396,6 +402,6 @@ extern "C" gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobia
 // form 1: the PCG iteration with the direction formed on the fly (k_spmvdir_p2p / k_pcg_fused); same bits as form 0
 extern "C" gs_status gs_emu_run_form(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
                                      double pcg_rel_tol, int form, gs_emu_result* out) {
-  if (form != 0 && form != 1) return GS_EINVAL;
+  if (form < 0 || form > 3) return GS_EINVAL;   // bit 0: PCG form, bit 1: assembly without run accumulator
   return emu_run(pb, world, jacobian_mode, lambda, pcg_max_iters, pcg_rel_tol, form, out);
 }

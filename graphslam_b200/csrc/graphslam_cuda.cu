@@ -114,6 +114,8 @@ struct gs_graph {
   bool p2p_two = true;                    // peer-memory path with two kernels per iteration (else three)
   int p2p_two_env = -1;                   // GS_P2P_TWO: 0 / 1 force, unset = by rows per rank
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
+  bool asm_nodup = false;                 // GS_ASM_NODUP=1: k_assemble_nodup on graphs without duplicate factors (round-2
+                                          // candidate: three CTAs per SM; same bits, not yet timed)
   bool update_staged = true;              // GS_UPDATE_STAGED=0: k_pcg_update instead of k_pcg_update_staged (same bits)
   bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
@@ -833,10 +835,14 @@ gs_status write_scalars(gs_graph* g) {
 gs_status launch_assemble(gs_graph* g) {
   const gs::AsmView av = asm_view(g, g->d_pose.p);
   const gs::ReduceCtx rc = reduce_ctx(g, 2);
-  if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT)
-    gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
-  else
-    gs::k_assemble<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+  const bool nodup = g->asm_nodup && g->S.n_merged == 0;
+  if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT) {
+    if (nodup) gs::k_assemble_nodup<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+    else gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+  } else {
+    if (nodup) gs::k_assemble_nodup<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+    else gs::k_assemble<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
+  }
   g->launches += 1;
   if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
   if (g->prm.diagonal_damping) {
@@ -958,6 +964,8 @@ gs_status create_common(gs_graph* g) {
   g->p2p_two_env = env ? (env[0] != '0') : -1;
   env = std::getenv("GS_PCG_FUSED");
   g->fused_wanted = !(env && env[0] == '0');
+  env = std::getenv("GS_ASM_NODUP");
+  g->asm_nodup = env && env[0] != '0';
   env = std::getenv("GS_UPDATE_STAGED");
   g->update_staged = !(env && env[0] == '0');
   {

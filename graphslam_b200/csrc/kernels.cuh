@@ -200,6 +200,20 @@ __global__ void __launch_bounds__(kThreads, 2) k_assemble(const AsmView a, const
   reduce_finish<1>(c, v, OP_CHI2, red, &flag);
 }
 
+// Candidate for round 2 (GS_ASM_NODUP=1, off by default, not yet timed on a B200): graphs without duplicate
+// factors need no run accumulator, and without it the row fits three CTAs per SM instead of two (k_assemble is
+// bound by its 4 warps per scheduler).  Same bits as k_assemble on such graphs
+// (tests/test_emulator_cpu.py::test_assemble_without_run_accumulator_is_bitwise_the_same).
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 3) k_assemble_nodup(const AsmView a, const ReduceCtx c) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < a.n_own) v[0] = assemble_row<MODE, true>(a, r);
+  reduce_finish<1>(c, v, OP_CHI2, red, &flag);
+}
+
 __global__ void __launch_bounds__(kThreads) k_chi2(const AsmView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;

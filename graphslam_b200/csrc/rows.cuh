@@ -175,7 +175,9 @@ GS_HD void asm_begin(AsmAcc& A) {
 
 // one BetweenFactor side: code/cb are the contribution's words, prow/pcol the poses of the row's and the
 // other vertex, (zt, zr, o01, o23, o45) the factor
-template <int MODE>
+// NODUP: the structure has no two factors between the same pair of vertices (LocalStructure::n_merged == 0), so
+// every run is one factor long and its block is stored as soon as it is formed: no run accumulator (18 registers)
+template <int MODE, bool NODUP = false>
 GS_HD void asm_between(AsmAcc& A, uint32_t code, int cb, const double4 prow, const double4 pcol, const double2 zt,
                        const double2 zr, const double2 o01, const double2 o23, const double2 o45, double* Ho,
                        size_t hstride) {
@@ -222,7 +224,9 @@ GS_HD void asm_between(AsmAcc& A, uint32_t code, int cb, const double4 prow, con
     if (code & 4u) A.chi2 += quad_form(O, L.e);
     if (cb >= 0) off_block(O, lo_is_i ? L.Ai : L.Aj, lo_is_i ? L.Aj : L.Ai, M);
   }
-  if (cb >= 0) {
+  if (NODUP) {
+    if (cb >= 0) store_block(Ho, hstride, cb >> 2, M);
+  } else if (cb >= 0) {
     if (cb & 1) {
       if (A.open >= 0) store_block(Ho, hstride, A.open, A.acc);
       A.open = cb >> 2;
@@ -249,8 +253,9 @@ GS_HD void asm_prior(AsmAcc& A, const double4 prow, const double4 pp, const doub
   for (int k = 0; k < 3; ++k) A.bv[k] += b3[k];
 }
 
+template <bool NODUP = false>
 GS_HD double asm_end(AsmAcc& A, const AsmView& a, int r) {
-  if (A.open >= 0) store_block(a.Ho, a.hstride, A.open, A.acc);
+  if (!NODUP && A.open >= 0) store_block(a.Ho, a.hstride, A.open, A.acc);
 #pragma unroll
   for (int k = 0; k < 6; ++k) a.Hd[(size_t)k * a.n_own + r] = A.dg[k];
 #pragma unroll
@@ -259,7 +264,7 @@ GS_HD double asm_end(AsmAcc& A, const AsmView& a, int r) {
 }
 
 // returns the row's chi2 share (factors it is the counting side of, and its priors)
-template <int MODE>
+template <int MODE, bool NODUP = false>
 GS_HD double assemble_row(const AsmView& a, int r) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
@@ -279,12 +284,12 @@ GS_HD double assemble_row(const AsmView& a, int r) {
       const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
       const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
       const double4 pcol = ldg(a.pose + cur.z);
-      asm_between<MODE>(A, code, cur.y, prow, pcol, zt, zr, o01, o23, o45, a.Ho, a.hstride);
+      asm_between<MODE, NODUP>(A, code, cur.y, prow, pcol, zt, zr, o01, o23, o45, a.Ho, a.hstride);
     } else {
       asm_prior<MODE>(A, prow, ldg(a.pr.pose + idx), a.pr.om + 6 * idx);
     }
   }
-  return asm_end(A, a, r);
+  return asm_end<NODUP>(A, a, r);
 }
 
 // graph.error contribution of row r at `pose`: its priors, then the factors whose counting side is

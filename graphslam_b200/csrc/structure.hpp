@@ -171,6 +171,8 @@ struct LocalStructure {
   int nnzo_own = 0;          // off-diagonal blocks of the owned rows of the full (non-symmetric) BSR
   int n_factor_copies = 0;   // factor cells that hold a copy (gather would not coalesce)
   int n_block_copies = 0;    // block cells that hold a transposed copy
+  int n_merged = 0;          // block contributions that continue a run (a second factor between the same pair); 0 =
+                             // every stored block comes from exactly one factor
   int ntiles = 0;
   int seg_tile[kSegments + 1] = {0};  // local tile ranges of the locally owned segments (first kSegments/P used)
   std::vector<int> ghosts;            // global index of ghost g (sorted)
@@ -434,6 +436,7 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   }
   // block words of the contributions whose row computes the pair's block into its own cell
   S.c_first.assign(std::max(n_own, 1), 0);
+  S.n_merged = 0;
   for (int row = 0; row < n_own; ++row) {
     const int g = v0 + row;
     int last = -1, s_ref = -1;
@@ -457,6 +460,7 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
       const int cell = S.rsell.pos(row, s_ref);
       if (rhome[cell] != cell) continue;  // the lo row's cell is shared
       S.c_blk[c] = (cell << 2) | ((g != lo) ? 2 : 0) | (head ? 1 : 0);
+      if (!head) S.n_merged++;
     }
   }
 

@@ -69,7 +69,8 @@ gs_status gs_emu_run(const gs_emu_problem* pb, int world, int jacobian_mode, dou
                      double pcg_rel_tol, gs_emu_result* out);
 
 /* the same with the PCG iteration in the form the two-kernel peer-memory path and the persistent small-graph kernel
- * use (form 1: direction formed on the fly inside the product, z exchanged instead of p); form 0 = gs_emu_run */
+ * use (form bit 0: direction formed on the fly inside the product, z exchanged instead of p; form bit 1: assembly
+ * without the run accumulator, GS_EINVAL when some vertex pair carries two factors); form 0 = gs_emu_run */
 gs_status gs_emu_run_form(const gs_emu_problem* pb, int world, int jacobian_mode, double lambda, int pcg_max_iters,
                           double pcg_rel_tol, int form, gs_emu_result* out);
 

@@ -128,3 +128,27 @@ def test_direction_formed_on_the_fly_is_bitwise_the_same(lib, world):
     assert a["pcg_iters"] == b["pcg_iters"] and a["pcg_done"] == b["pcg_done"] == 1
     assert np.array_equal(a["delta"], b["delta"]) and np.array_equal(a["xyt_new"], b["xyt_new"])
     assert a["chi2_new"] == b["chi2_new"] and a["dHd"] == b["dHd"]
+
+
+@pytest.mark.parametrize("cid,n,mode", [("C3", 3000, 0), ("C2", 5000, 0), ("C3", 1500, 1)])
+def test_assemble_without_run_accumulator_is_bitwise_the_same(lib, cid, n, mode):
+    """k_assemble_nodup's row code (no run accumulator: a block is stored as soon as it is formed) on graphs where
+    every vertex pair carries one factor: H, b, chi2 and the PCG solution equal the general form bit for bit; and the
+    form refuses a graph that has a duplicated factor."""
+    g = synth.config(cid, n=n)
+    prob = O.Problem.from_graph(g)
+    a = emu_run(lib, prob, g.init, mode=mode, form=0)
+    b = emu_run(lib, prob, g.init, mode=mode, form=2)
+    for k in a:
+        if isinstance(a[k], np.ndarray):
+            assert np.array_equal(a[k], b[k]), k
+        else:
+            assert a[k] == b[k], k
+    # a graph with a duplicated factor is refused (GS_EINVAL = 1): it needs the run accumulator
+    dup = synth.config("C3", n=600)
+    for name in ("k1", "k2"):
+        setattr(dup, name, np.concatenate([getattr(dup, name), getattr(dup, name)[-1:]]))
+    dup.z = np.concatenate([dup.z, dup.z[-1:]])
+    dup.cov = np.concatenate([dup.cov, dup.cov[-1:]])
+    with pytest.raises(AssertionError):
+        emu_run(lib, O.Problem.from_graph(dup), dup.init, form=2)
