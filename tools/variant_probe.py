@@ -26,10 +26,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from graphslam_b200 import _lib, graph, synth  # noqa: E402
 
-FLAGS = ("GS_UPDATE_STAGED",)
+FLAGS = ("GS_UPDATE_STAGED", "GS_ASM_NODUP")
 VARIANTS = [
     ("default", {}),
     ("unstaged", {"GS_UPDATE_STAGED": "0"}),
+    ("asm_nodup", {"GS_ASM_NODUP": "1"}),       # round-2 candidate: k_assemble_nodup, three CTAs per SM
     ("default again", {}),
 ]
 OUT = os.path.join(ROOT, "gpurun_out", "variant_probe.jsonl")
