@@ -114,6 +114,7 @@ struct gs_graph {
   bool p2p_two = true;                    // peer-memory path with two kernels per iteration (else three)
   int p2p_two_env = -1;                   // GS_P2P_TWO: 0 / 1 force, unset = by rows per rank
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
+  bool p2p_staged = false;                // GS_P2P_STAGED=1: k_update_p2p_staged / k_updpush_p2p_staged (round-2 candidates)
   bool asm_nodup = false;                 // GS_ASM_NODUP=1: k_assemble_nodup on graphs without duplicate factors (round-2
                                           // candidate: three CTAs per SM; same bits, not yet timed)
   bool update_staged = true;              // GS_UPDATE_STAGED=0: k_pcg_update instead of k_pcg_update_staged (same bits)
@@ -401,7 +402,10 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     } else if (stage == 1) {
       gs::PcgView pv = pcg_view(g);
       pv.p = next;
-      gs::k_updpush_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
+      if (g->p2p_staged)
+        gs::k_updpush_p2p_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
+      else
+        gs::k_updpush_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
     }
     return GS_OK;
   }
@@ -411,7 +415,10 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       gs::k_spmv_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->pvec, g->pghost, g->d_Ap.p,
                                                                    reduce_ctx(g, 0), x);
     } else if (stage == 1) {
-      gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
+      if (g->p2p_staged)
+        gs::k_update_p2p_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
+      else
+        gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
     } else {
       gs::HaloPush h;
       h.row = g->d_hp_row.p;
@@ -964,6 +971,8 @@ gs_status create_common(gs_graph* g) {
   g->p2p_two_env = env ? (env[0] != '0') : -1;
   env = std::getenv("GS_PCG_FUSED");
   g->fused_wanted = !(env && env[0] == '0');
+  env = std::getenv("GS_P2P_STAGED");
+  g->p2p_staged = env && env[0] != '0';
   env = std::getenv("GS_ASM_NODUP");
   g->asm_nodup = env && env[0] != '0';
   env = std::getenv("GS_UPDATE_STAGED");

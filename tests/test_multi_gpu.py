@@ -26,7 +26,14 @@ def _free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("p2p", ["1/1", "1/0", "0/0"], ids=["peer-memory-2-kernels", "peer-memory-3-kernels", "nccl-per-op"])
+# candidates not yet run on several GPUs are only exercised on request (GS_TEST_CANDIDATES=1): the staged x/r/z
+# update inside the peer-memory kernels (GS_P2P_STAGED=1, csrc/kernels_p2p.cuh)
+_FORMS = ["1/1/0", "1/0/0", "0/0/0"] + (["1/1/1", "1/0/1"] if os.environ.get("GS_TEST_CANDIDATES") == "1" else [])
+_IDS = ["peer-memory-2-kernels", "peer-memory-3-kernels", "nccl-per-op", "peer-memory-2-kernels-staged",
+        "peer-memory-3-kernels-staged"][:len(_FORMS)]
+
+
+@pytest.mark.parametrize("p2p", _FORMS, ids=_IDS)
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_multi_gpu_path_bitwise_equals_single_gpu(world, p2p):
     """peer memory: halo rows and dot-product segment sums travel by stores into the peers' windows from inside the PCG
@@ -34,7 +41,7 @@ def test_multi_gpu_path_bitwise_equals_single_gpu(world, p2p):
     NCCL call per exchange.  All must reproduce the single-GPU bits."""
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
-    env = dict(os.environ, GS_P2P=p2p.split("/")[0], GS_P2P_TWO=p2p.split("/")[1])
+    env = dict(os.environ, GS_P2P=p2p.split("/")[0], GS_P2P_TWO=p2p.split("/")[1], GS_P2P_STAGED=p2p.split("/")[2])
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
            "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mgpu_worker.py"), "C3", "30000"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
