@@ -11,6 +11,8 @@ c_double_p = C.POINTER(C.c_double)
 c_u64_p = C.POINTER(C.c_uint64)
 c_i32_p = C.POINTER(C.c_int32)
 
+GS_SOLVER_NO_CUDA_GRAPH, GS_SOLVER_NCCL_PER_OP, GS_SOLVER_NO_PERSISTENT, GS_SOLVER_DIR_KERNEL, GS_SOLVER_DIR_ON_THE_FLY = (
+    1, 2, 4, 8, 16)
 GS_OK, GS_EINVAL, GS_ENOTSPD, GS_EDUPKEY, GS_ENOKEY, GS_ECUDA, GS_ENCCL, GS_ENOTCONVERGED, GS_ENAN, GS_ENOMEM = range(10)
 STATUS_NAMES = ["GS_OK", "GS_EINVAL", "GS_ENOTSPD", "GS_EDUPKEY", "GS_ENOKEY", "GS_ECUDA", "GS_ENCCL",
                 "GS_ENOTCONVERGED", "GS_ENAN", "GS_ENOMEM"]
@@ -22,7 +24,7 @@ class GsParams(C.Structure):
                 ("lambda_upper", C.c_double), ("lambda_lower", C.c_double), ("min_model_fidelity", C.c_double),
                 ("diagonal_damping", C.c_int), ("jacobian_mode", C.c_int), ("pcg_rel_tol", C.c_double),
                 ("pcg_max_iters", C.c_int), ("device", C.c_int), ("rank", C.c_int), ("world_size", C.c_int),
-                ("reserved", C.c_int * 8)]
+                ("solver_flags", C.c_int), ("reserved", C.c_int * 7)]
 
 
 class GsStats(C.Structure):
@@ -32,10 +34,12 @@ class GsStats(C.Structure):
                 ("ms_linearize", C.c_double), ("ms_solve", C.c_double), ("ms_update", C.c_double),
                 ("ms_total", C.c_double), ("edges_per_sec", C.c_double), ("gn_iters_per_sec", C.c_double),
                 ("gpu_launches", C.c_double), ("ms_device", C.c_double), ("h2d_bytes", C.c_double),
-                ("d2h_bytes", C.c_double), ("reserved", C.c_double * 4)]
+                ("d2h_bytes", C.c_double), ("p2p_wait_ticks", C.c_double * 3), ("p2p_waits", C.c_double),
+                ("reserved", C.c_double * 4)]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("reserved", "p2p_wait_ticks")}
+        d["p2p_wait_ticks"] = list(self.p2p_wait_ticks)
         d["gpu_launches"] = int(self.gpu_launches)
         return d
 
@@ -116,10 +120,22 @@ DEBUG_SIGNATURES = {
 }
 
 _LIB = None
+_DEBUG_LIB = None
 
 
 def lib_path() -> str:
-    return _build.LIB
+    """The in-tree product library; GS_LIB (read here, in the Python test/bench harness, not by the library) points
+    the harness at a compile-time variant built by build.build_variant for A/B measurements."""
+    return os.environ.get("GS_LIB") or _build.LIB
+
+
+def _bind(path: str, signatures) -> C.CDLL:
+    lib = C.CDLL(path)
+    for name, (res, args) in signatures.items():
+        fn = getattr(lib, name)          # AttributeError = missing export = broken build
+        fn.restype = res
+        fn.argtypes = args
+    return lib
 
 
 def load(build_if_missing: bool = True) -> C.CDLL:
@@ -132,10 +148,19 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         if not build_if_missing:
             raise RuntimeError(f"{path} is missing: run `python -m graphslam_b200.build` (no CPU fallback exists)")
         _build.build()
-    lib = C.CDLL(path)
-    for name, (res, args) in {**SIGNATURES, **DEBUG_SIGNATURES}.items():
-        fn = getattr(lib, name)          # AttributeError = missing export = broken build
-        fn.restype = res
-        fn.argtypes = args
-    _LIB = lib
-    return lib
+    _LIB = _bind(path, SIGNATURES)
+    return _LIB
+
+
+def load_debug(build_if_missing: bool = True) -> C.CDLL:
+    """Load libgraphslam_cuda_debug.so (tests only: CPU emulator + host hooks of include/graphslam_cuda_debug.h)."""
+    global _DEBUG_LIB
+    if _DEBUG_LIB is not None:
+        return _DEBUG_LIB
+    path = os.environ.get("GS_DEBUG_LIB") or _build.DEBUG_LIB
+    if not os.path.exists(path):
+        if not build_if_missing:
+            raise RuntimeError(f"{path} is missing: run `python -m graphslam_b200.build`")
+        _build.build()
+    _DEBUG_LIB = _bind(path, DEBUG_SIGNATURES)
+    return _DEBUG_LIB

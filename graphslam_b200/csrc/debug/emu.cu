@@ -11,8 +11,8 @@
 #include <cstring>
 #include <vector>
 
-#include "../../include/graphslam_cuda_debug.h"
-#include "rows.cuh"
+#include "../../../include/graphslam_cuda_debug.h"
+#include "../rows.cuh"
 
 namespace {
 
@@ -21,9 +21,9 @@ using gs::LocalStructure;
 struct VRank {
   LocalStructure S;
   int n_own = 0, n_loc = 0;
-  std::vector<int2> eij, refs;
+  std::vector<int2> refs;
   std::vector<int4> cw;
-  std::vector<double2> zt, zr, o01, o23, o45;
+  gs::FactorStage fs;
   std::vector<double4> pr_pose, pose, pose_try;
   std::vector<double> pr_om, Ho, Hd, Minv, b, x, r, z, p, Ap, part;
   size_t hstride = 1;
@@ -33,12 +33,9 @@ struct VRank {
     a.cs.width = S.csell.width.data();
     a.c = cw.data();
     a.c_first = S.c_first.data();
-    a.f.ij = eij.data();
-    a.f.zt = zt.data();
-    a.f.zr = zr.data();
-    a.f.o01 = o01.data();
-    a.f.o23 = o23.data();
-    a.f.o45 = o45.data();
+    a.f.ij = fs.ij.data();
+    a.f.data = fs.data.data();
+    a.f.fstride = fs.fstride;
     a.pr.n = S.P_loc;
     a.pr.row = S.pr_row.data();
     a.pr.pose = pr_pose.data();
@@ -170,25 +167,15 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
     me.n_own = S.n_own;
     me.n_loc = S.n_own + S.n_ghost;
     const int FS = S.csell.slots;
-    me.eij.assign(FS, make_int2(-1, -1));
+    me.fs.init(FS);
     me.cw.resize(S.c_code.size());
     for (size_t c = 0; c < me.cw.size(); ++c) me.cw[c] = make_int4((int)S.c_code[c], S.c_blk[c], S.c_col[c], 0);
     me.refs.resize(S.r_col.size());
     for (size_t c = 0; c < me.refs.size(); ++c) me.refs[c] = make_int2(S.r_col[c], S.r_blk[c]);
-    me.zt.assign(FS, make_double2(0, 0));
-    me.zr.assign(FS, make_double2(1, 0));
-    me.o01.assign(FS, make_double2(0, 0));
-    me.o23.assign(FS, make_double2(0, 0));
-    me.o45.assign(FS, make_double2(0, 0));
     for (int s = 0; s < FS; ++s) {
       const int k = S.f_src[s];
       if (k < 0) continue;
-      me.eij[s] = make_int2(S.f_i[s] | (S.f_count[s] ? 0 : gs::kNoCountBit), S.f_j[s]);
-      me.zt[s] = make_double2(pb->z[3 * k], pb->z[3 * k + 1]);
-      me.zr[s] = make_double2(std::cos(pb->z[3 * k + 2]), std::sin(pb->z[3 * k + 2]));
-      me.o01[s] = make_double2(pb->om[6 * k], pb->om[6 * k + 1]);
-      me.o23[s] = make_double2(pb->om[6 * k + 2], pb->om[6 * k + 3]);
-      me.o45[s] = make_double2(pb->om[6 * k + 4], pb->om[6 * k + 5]);
+      me.fs.set(s, S.f_i[s] | (S.f_count[s] ? 0 : gs::kNoCountBit), S.f_j[s], pb->z + 3 * (size_t)k, pb->om + 6 * (size_t)k);
     }
     me.pr_pose.resize(std::max(S.P_loc, 1));
     me.pr_om.assign(6 * (size_t)std::max(S.P_loc, 1), 0.0);
@@ -204,7 +191,7 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
       const int d = me.global_of(l);
       me.pose[l] = make_double4(pb->xyt[3 * d], pb->xyt[3 * d + 1], std::cos(pb->xyt[3 * d + 2]), std::sin(pb->xyt[3 * d + 2]));
     }
-    me.hstride = (size_t)std::max(S.rsell.slots, 1);
+    me.hstride = (size_t)std::max(S.rsell.slots, gs::kSlice);
     me.Ho.assign(9 * me.hstride, 0.0);
     const size_t n3 = 3 * (size_t)std::max(me.n_own, 1), nl3 = 3 * (size_t)std::max(me.n_loc, 1);
     me.Hd.assign(2 * n3, 0.0);
@@ -262,7 +249,7 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
           const int word = S.r_blk[q], pos = word >> 1;
           const bool tr = word & 1;
           for (int a = 0; a < 3; ++a)
-            for (int c = 0; c < 3; ++c) out->blocks[9 * w + 3 * a + c] = me.Ho[(size_t)(tr ? 3 * c + a : 3 * a + c) * me.hstride + pos];
+            for (int c = 0; c < 3; ++c) out->blocks[9 * w + 3 * a + c] = gs::h_entry(me.Ho.data(), me.hstride, pos, a, c, tr);
           ++w;
         }
         if (!diag_done) put_diag();

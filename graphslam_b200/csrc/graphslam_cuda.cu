@@ -27,8 +27,10 @@
 #include <vector>
 
 #include "../../include/graphslam_cuda.h"
+#include "../../include/graphslam_cuda_debug.h"  // GS_X_* experiment bits only
 #include "comm.hpp"
 #include "g2o.hpp"
+#include "host_util.hpp"
 #include "kernels.cuh"
 #include "kernels_fused.cuh"
 #include "kernels_p2p.cuh"
@@ -37,6 +39,8 @@ namespace {
 
 using gs::LocalStructure;
 using gs::Scalars;
+using gs::spd_information;
+using gs::spd_upper;
 
 constexpr int kPcgBatch = 32;  // PCG iterations per CUDA-graph launch
 constexpr int kFusedBatch = 128;  // PCG iterations per launch of the persistent small-graph kernel
@@ -66,38 +70,6 @@ struct DevBuf {
   ~DevBuf() { release(); }
 };
 
-bool spd_information(const double* cov9, double* om6) {
-  // symmetrise, Cholesky test, invert via adjugate
-  const double a00 = cov9[0], a11 = cov9[4], a22 = cov9[8];
-  const double a01 = 0.5 * (cov9[1] + cov9[3]), a02 = 0.5 * (cov9[2] + cov9[6]), a12 = 0.5 * (cov9[5] + cov9[7]);
-  if (!(a00 > 0.0)) return false;
-  const double l00 = std::sqrt(a00), l10 = a01 / l00, l20 = a02 / l00;
-  const double d1 = a11 - l10 * l10;
-  if (!(d1 > 0.0)) return false;
-  const double l11 = std::sqrt(d1), l21 = (a12 - l20 * l10) / l11;
-  const double d2 = a22 - l20 * l20 - l21 * l21;
-  if (!(d2 > 0.0) || !std::isfinite(d2)) return false;
-  gs::Sym3 q{a00, a01, a02, a11, a12, a22};
-  const gs::Sym3 r = gs::inverse_spd(q);
-  om6[0] = r.a00; om6[1] = r.a01; om6[2] = r.a02; om6[3] = r.a11; om6[4] = r.a12; om6[5] = r.a22;
-  for (int k = 0; k < 6; ++k)
-    if (!std::isfinite(om6[k])) return false;
-  return true;
-}
-
-// information (inverse covariance) given directly, upper triangle I11 I12 I13 I22 I23 I33: SPD test only
-bool spd_upper(const double* o) {
-  for (int k = 0; k < 6; ++k)
-    if (!std::isfinite(o[k])) return false;
-  if (!(o[0] > 0.0)) return false;
-  const double l00 = std::sqrt(o[0]), l10 = o[1] / l00, l20 = o[2] / l00;
-  const double d1 = o[3] - l10 * l10;
-  if (!(d1 > 0.0)) return false;
-  const double l11 = std::sqrt(d1), l21 = (o[4] - l20 * l10) / l11;
-  const double d2 = o[5] - l20 * l20 - l21 * l21;
-  return d2 > 0.0;
-}
-
 }  // namespace
 
 struct gs_graph {
@@ -110,21 +82,21 @@ struct gs_graph {
   // ---- multi-GPU
   int world = 1, rank = 0;
   ncclComm_t comm = nullptr;
-  bool use_graph = true;
-  bool p2p_two = true;                    // peer-memory path with two kernels per iteration (else three)
-  int p2p_two_env = -1;                   // GS_P2P_TWO: 0 / 1 force, unset = by rows per rank
+  // execution-path choices: gs_params.solver_flags (fixed at gs_create), never the environment
+  bool use_graph = true;                  // !GS_SOLVER_NO_CUDA_GRAPH
+  bool dir_otf = false;                   // direction formed on the fly inside the product: two kernels per iteration
+                                          // (k_spmvdir[_p2p] + update) instead of three; decided in prepare()
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
-  bool p2p_staged = false;                // GS_P2P_STAGED=1: k_update_p2p_staged / k_updpush_p2p_staged (round-2 candidates)
-  bool asm_nodup = false;                 // GS_ASM_NODUP=1: k_assemble_nodup on graphs without duplicate factors (round-2
-                                          // candidate: three CTAs per SM; same bits, not yet timed)
-  bool update_staged = true;              // GS_UPDATE_STAGED=0: k_pcg_update instead of k_pcg_update_staged (same bits)
-  bool fused_wanted = true;               // GS_PCG_FUSED=0 keeps the three-kernel iteration on small graphs too
+  bool p2p_staged = false;                // GS_X_P2P_STAGED (experiment): k_update_p2p_staged / k_updpush_p2p_staged
+  bool asm_nodup = false;                 // GS_X_ASM_NODUP (experiment): k_assemble_nodup on graphs without duplicate factors
+  bool update_staged = true;              // !GS_X_UPDATE_UNSTAGED (experiment)
+  bool fused_wanted = true;               // !GS_SOLVER_NO_PERSISTENT
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
   DevBuf<gs::GridBarrier> d_bar;
   DevBuf<double> d_p_alt;                 // second direction buffer of the persistent kernel
   // peer-memory path (world > 1): collectives fused into the PCG kernels over NVLink
-  bool p2p_wanted = true;                 // GS_P2P=0 keeps the NCCL-per-operation path
+  bool p2p_wanted = true;                 // !GS_SOLVER_NCCL_PER_OP
   bool p2p = false;                       // windows exchanged, peer-memory kernels in use
   char* win = nullptr;                    // this rank's exported window: header + p
   size_t win_bytes = 0;
@@ -174,7 +146,8 @@ struct gs_graph {
   DevBuf<double4> d_pose, d_pose_try, d_pr_pose, d_pose_all;
   DevBuf<int2> d_eij, d_refs;
   DevBuf<int4> d_cw;
-  DevBuf<double2> d_zt, d_zr, d_o01, d_o23, d_o45;
+  DevBuf<double2> d_fdata;   // factor cells, five double2 components each (layout: rows.cuh, GS_F_LAYOUT)
+  size_t fstride = gs::kSlice;
   DevBuf<int> d_pr_row, d_cbase, d_cwidth, d_rbase, d_rwidth, d_segtile, d_send_rows, d_cfirst;
   DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part, d_segs, d_sendbuf;
   DevBuf<Scalars> d_sc;
@@ -190,6 +163,7 @@ struct gs_graph {
   std::vector<double> tr_err, tr_lambda;
   std::vector<int32_t> tr_tries;
   int64_t launches = 0;
+  double p2p_wait[4] = {0, 0, 0, 0};  // peer-memory path: clock ticks CTA 0 waited in spmv / update / dir, waits counted
 
   gs_status fail(gs_status s, const char* fmt, ...) {
     char buf[512];
@@ -256,11 +230,8 @@ gs::AsmView asm_view(gs_graph* g, const double4* pose) {
   a.c = g->d_cw.p;
   a.c_first = g->d_cfirst.p;
   a.f.ij = g->d_eij.p;
-  a.f.zt = g->d_zt.p;
-  a.f.zr = g->d_zr.p;
-  a.f.o01 = g->d_o01.p;
-  a.f.o23 = g->d_o23.p;
-  a.f.o45 = g->d_o45.p;
+  a.f.data = g->d_fdata.p;
+  a.f.fstride = g->fstride;
   a.pr.n = g->S.P_loc;
   a.pr.row = g->d_pr_row.p;
   a.pr.pose = g->d_pr_pose.p;
@@ -375,7 +346,7 @@ gs::P2PCtx p2p_ctx(gs_graph* g, unsigned int k_local) {
 // one stage of a PCG iteration (0: SpMV + p.Ap, 1: x/r/z update + r.z, r.r, 2: direction);
 // k_local = the iteration's position in the batch (peer-memory path only)
 gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
-  if (g->p2p && g->p2p_two) {
+  if (g->p2p && g->dir_otf) {
     const gs::P2PCtx x = p2p_ctx(g, k_local);
     // iteration k reads the direction of iteration k-1 from buffer k&1 and writes its own into the other one
     double* P[2] = {g->pvec, g->d_p_alt.p};
@@ -426,6 +397,21 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       h.n_push_tiles = g->n_push_tiles;
       h.order = g->d_hp_order.p;
       gs::k_dir_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x, h);
+    }
+    return GS_OK;
+  }
+  if (g->dir_otf && g->world == 1) {
+    // single GPU, two kernels per iteration: iteration k reads the direction of iteration k-1 from buffer k&1 and
+    // writes its own into the other one (an even batch leaves the latest direction in pvec)
+    double* P[2] = {g->pvec, g->d_p_alt.p};
+    double* prev = P[k_local & 1u];
+    double* next = P[(k_local + 1u) & 1u];
+    if (stage == 0) {
+      gs::k_spmvdir<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->d_z.p, prev, next, g->d_Ap.p, reduce_ctx(g, 0));
+    } else if (stage == 1) {
+      gs::PcgView pv = pcg_view(g);
+      pv.p = next;
+      gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1));
     }
     return GS_OK;
   }
@@ -610,7 +596,6 @@ gs_status prepare_p2p(gs_graph* g) {
   // Two kernels per iteration pay a second gather per column in the product and save the direction kernel:
   // measured on C3, 1.39 -> 1.31 s per step at 2 GPUs and 0.92 -> 0.87 s at 4, but 0.54 -> 0.6 s at 8 (125k rows
   // per rank), so the choice goes by rows per rank (the same number on every rank).
-  g->p2p_two = g->p2p_two_env >= 0 ? g->p2p_two_env != 0 : (g->N / std::max(g->world, 1) >= 200000);
   GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(S.n_own + S.n_ghost, 1) + 3));
   std::vector<int> tile_halo(nt, 0);
   for (int r = 0; r < g->n_own; ++r) {
@@ -727,19 +712,14 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->n_loc = S.n_own + S.n_ghost;
   // factor arrays in storage (SELL) order; padding slots are never referenced
   const int FS = S.csell.slots;
-  std::vector<int2> eij(FS, make_int2(-1, -1));
-  std::vector<double2> zt(FS, make_double2(0, 0)), zr(FS, make_double2(1, 0)), o01(FS, make_double2(0, 0)),
-      o23(FS, make_double2(0, 0)), o45(FS, make_double2(0, 0));
+  gs::FactorStage fst;
+  fst.init(FS);
   for (int q = 0; q < FS; ++q) {
     const int s = S.f_src[q];
     if (s < 0) continue;
-    eij[q] = make_int2(S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q]);
-    zt[q] = make_double2(g->ez[3 * s], g->ez[3 * s + 1]);
-    zr[q] = make_double2(std::cos(g->ez[3 * s + 2]), std::sin(g->ez[3 * s + 2]));
-    o01[q] = make_double2(g->eom[6 * s], g->eom[6 * s + 1]);
-    o23[q] = make_double2(g->eom[6 * s + 2], g->eom[6 * s + 3]);
-    o45[q] = make_double2(g->eom[6 * s + 4], g->eom[6 * s + 5]);
+    fst.set(q, S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q], &g->ez[3 * (size_t)s], &g->eom[6 * (size_t)s]);
   }
+  g->fstride = fst.fstride;
   g->e_count = 0;
   for (uint32_t code : S.c_code)
     if (code != gs::kPadCode && (code & 4u) && (code & 3u) < 2) g->e_count++;
@@ -751,12 +731,8 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     for (int m = 0; m < 6; ++m) prom[6 * (size_t)k + m] = g->pr_om[6 * (size_t)s + m];
   }
   std::vector<int> segtile(S.seg_tile, S.seg_tile + gs::kSegments + 1);
-  if (gs_status s = upload(g, g->d_eij, eij)) return s;
-  if (gs_status s = upload(g, g->d_zt, zt)) return s;
-  if (gs_status s = upload(g, g->d_zr, zr)) return s;
-  if (gs_status s = upload(g, g->d_o01, o01)) return s;
-  if (gs_status s = upload(g, g->d_o23, o23)) return s;
-  if (gs_status s = upload(g, g->d_o45, o45)) return s;
+  if (gs_status s = upload(g, g->d_eij, fst.ij)) return s;
+  if (gs_status s = upload(g, g->d_fdata, fst.data)) return s;
   if (gs_status s = upload(g, g->d_pr_row, S.pr_row)) return s;
   if (gs_status s = upload(g, g->d_pr_pose, prp)) return s;
   if (gs_status s = upload(g, g->d_pr_om, prom)) return s;
@@ -777,7 +753,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = upload(g, g->d_cfirst, S.c_first)) return s;
   if (gs_status s = upload(g, g->d_send_rows, S.send_rows)) return s;
   const size_t n3 = 3 * (size_t)std::max(S.n_own, 1), nl3 = 3 * (size_t)std::max(g->n_loc, 1);
-  g->hstride = (size_t)std::max(S.rsell.slots, 1);
+  g->hstride = (size_t)std::max(S.rsell.slots, gs::kSlice);
   GS_CUDA(g, g->d_pose.alloc(std::max(g->n_loc, 1)));
   GS_CUDA(g, g->d_pose_try.alloc(std::max(g->n_loc, 1)));
   if (g->world > 1) GS_CUDA(g, g->d_pose_all.alloc(N));
@@ -803,7 +779,18 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->part_stride = g->grid_rows;
   GS_CUDA(g, g->d_part.alloc(3 * (size_t)g->part_stride));
   g->fused = g->fused_wanted && g->world == 1 && g->fused_capacity > 0 && g->grid_rows <= g->fused_capacity;
-  if (g->fused) GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(g->n_own, 1)));
+  {
+    // direction on the fly (two kernels per iteration) or as a kernel of its own (three)?  Forming it inside the
+    // product pays a second gather per column and saves a kernel plus, on several GPUs, a cross-GPU signal: measured
+    // on C3, 1.39 -> 1.31 s per step at 2 GPUs and 0.92 -> 0.87 s at 4, but 0.54 -> 0.6 s at 8 (125k rows per rank),
+    // so the choice goes by rows per rank (the same number on every rank).  The NCCL-per-exchange path keeps three.
+    const int f = g->prm.solver_flags;
+    const bool can = g->world == 1 ? !g->fused : g->p2p_wanted;
+    if (!can || (f & GS_SOLVER_DIR_KERNEL)) g->dir_otf = false;
+    else if (f & GS_SOLVER_DIR_ON_THE_FLY) g->dir_otf = true;
+    else g->dir_otf = g->world > 1 ? (N / g->world >= 200000) : false;
+  }
+  if (g->fused || (g->dir_otf && g->world == 1)) GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(g->n_own, 1) + 3));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));  // staging vectors go out of scope
   g->topo_dirty = false;
   g->device_values_valid = false;
@@ -880,7 +867,7 @@ void launch_pcg_setup(gs_graph* g) {
 // peer-memory path: ghost rows of p(0) by the ordinary halo exchange, then mark them valid
 gs_status begin_p2p_solve(gs_graph* g) {
   if (!g->p2p) return GS_OK;
-  if (g->p2p_two) {
+  if (g->dir_otf) {
     // the window's ghost rows carry z here (p = z at the start); both ghost copies of p must be finite
     const size_t own3 = 3 * (size_t)g->n_own, gh = sizeof(double) * 3 * (size_t)std::max(g->S.n_ghost, 1);
     GS_CUDA(g, cudaMemsetAsync(g->pvec + own3, 0, gh, g->stream));
@@ -895,7 +882,7 @@ gs_status begin_p2p_solve(gs_graph* g) {
 }
 
 int64_t launches_per_pcg_iteration(const gs_graph* g) {
-  if (g->p2p && g->p2p_two) return 2;
+  if (g->dir_otf && (g->p2p || g->world == 1)) return 2;
   if (g->world == 1 || g->p2p) return 3;
   return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
 }
@@ -926,10 +913,8 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
     if (gs_status s = read_scalars(g)) return s;
     if (h->done) break;
   }
-  if (g->p2p && std::getenv("GS_P2P_DEBUG") && h->spin[3] > 0)
-    std::fprintf(stderr, "[gs r%d] p2p waits of CTA 0 per iteration (clock ticks): spmv %.0f update %.0f dir %.0f over %lld iterations\n",
-                 g->rank, (double)h->spin[0] / h->spin[3], (double)h->spin[1] / h->spin[3], (double)h->spin[2] / h->spin[3],
-                 h->spin[3]);
+  if (g->p2p)
+    for (int k = 0; k < 4; ++k) g->p2p_wait[k] += (double)h->spin[k];
   if (h->done == 4) return g->fail(GS_ENCCL, "a peer rank did not answer within the wait limit (peer-memory PCG)");
   // kernels that did work (the no-op tail of the last batch is not counted)
   g->launches = keep + (g->fused ? fused_launches : launches_per_pcg_iteration(g) * (int64_t)h->iters);
@@ -965,18 +950,13 @@ gs_status create_common(gs_graph* g) {
   GS_CUDA(g, cudaMemsetAsync(g->d_segs.p, 0, 2 * gs::kSegments * sizeof(double), g->stream));
   GS_CUDA(g, cudaMallocHost(&g->h_sc, sizeof(Scalars)));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
-  const char* env = std::getenv("GS_PCG_GRAPH");
-  g->use_graph = !(env && env[0] == '0');
-  env = std::getenv("GS_P2P_TWO");
-  g->p2p_two_env = env ? (env[0] != '0') : -1;
-  env = std::getenv("GS_PCG_FUSED");
-  g->fused_wanted = !(env && env[0] == '0');
-  env = std::getenv("GS_P2P_STAGED");
-  g->p2p_staged = env && env[0] != '0';
-  env = std::getenv("GS_ASM_NODUP");
-  g->asm_nodup = env && env[0] != '0';
-  env = std::getenv("GS_UPDATE_STAGED");
-  g->update_staged = !(env && env[0] == '0');
+  const int flags = g->prm.solver_flags;
+  g->use_graph = !(flags & GS_SOLVER_NO_CUDA_GRAPH);
+  g->fused_wanted = !(flags & GS_SOLVER_NO_PERSISTENT);
+  g->p2p_wanted = !(flags & GS_SOLVER_NCCL_PER_OP);
+  g->p2p_staged = (flags & GS_X_P2P_STAGED) != 0;
+  g->asm_nodup = (flags & GS_X_ASM_NODUP) != 0;
+  g->update_staged = !(flags & GS_X_UPDATE_UNSTAGED);
   {
     int per_sm = 0, sms = 0, dev = 0, coop = 0;
     GS_CUDA(g, cudaGetDevice(&dev));
@@ -984,12 +964,9 @@ gs_status create_common(gs_graph* g) {
     GS_CUDA(g, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
     GS_CUDA(g, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gs::k_pcg_fused, gs::kThreads, 0));
     g->fused_capacity = coop ? per_sm * sms : 0;
-    if (const char* cap = std::getenv("GS_PCG_FUSED_MAX_TILES")) g->fused_capacity = std::min(g->fused_capacity, std::atoi(cap));
   }
   GS_CUDA(g, g->d_bar.alloc(1));
   GS_CUDA(g, cudaMemsetAsync(g->d_bar.p, 0, sizeof(gs::GridBarrier), g->stream));
-  env = std::getenv("GS_P2P");
-  g->p2p_wanted = !(env && env[0] == '0');
   GS_CUDA(g, g->d_seq.alloc(64));
   GS_CUDA(g, cudaMemsetAsync(g->d_seq.p, 0, 64 * sizeof(unsigned int), g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
@@ -1134,11 +1111,16 @@ gs_status gs_destroy(gs_graph* g) try {
 
 gs_status gs_set_params(gs_graph* g, const gs_params* p) try {
   if (!g || !p) return GS_EINVAL;
-  if (p->world_size != g->prm.world_size || p->rank != g->prm.rank || p->device != g->prm.device)
-    return g->fail(GS_EINVAL, "device/rank/world_size are fixed at gs_create");
+  if (p->world_size != g->prm.world_size || p->rank != g->prm.rank || p->device != g->prm.device ||
+      p->solver_flags != g->prm.solver_flags)
+    return g->fail(GS_EINVAL, "device/rank/world_size/solver_flags are fixed at gs_create");
   const bool mode_changed = p->jacobian_mode != g->prm.jacobian_mode || p->diagonal_damping != g->prm.diagonal_damping;
+  const bool damping_changed = p->diagonal_damping != g->prm.diagonal_damping;
   g->prm = *p;
   if (mode_changed) g->system_valid = false;
+  // the product's dscale pointer (lambda*I or lambda*diag(H)) is an argument captured in the PCG graph
+  if (damping_changed && g->pcg_exec)
+    if (gs_status s = capture_pcg_graph(g)) return s;
   return GS_OK;
 } catch (...) {
   return on_exception(g);
@@ -1359,6 +1341,7 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   g->tr_lambda.clear();
   g->tr_tries.clear();
   g->launches = 0;
+  for (double& w : g->p2p_wait) w = 0.0;
 
   // error at the initial values
   if (gs_status s = launch_chi2(g, g->d_pose.p)) return s;
@@ -1474,6 +1457,8 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   }
   local.h2d_bytes = g->h2d_bytes - h2d0;
   local.d2h_bytes = g->d2h_bytes - d2h0;
+  for (int k = 0; k < 3; ++k) local.p2p_wait_ticks[k] = g->p2p_wait[k];
+  local.p2p_waits = g->p2p_wait[3];
   if (st) *st = local;
   return rc;
 } catch (...) {
@@ -1607,7 +1592,7 @@ gs_status gs_get_system(gs_graph* g, double* blocks, double* b, double* chi2) tr
       const int pos = word >> 1;
       const bool tr = word & 1;
       for (int r = 0; r < 3; ++r)
-        for (int c = 0; c < 3; ++c) blocks[9 * w + 3 * r + c] = ho[(size_t)(tr ? 3 * c + r : 3 * r + c) * hs + pos];
+        for (int c = 0; c < 3; ++c) blocks[9 * w + 3 * r + c] = gs::h_entry(ho.data(), hs, pos, r, c, tr);
       ++w;
     };
     for (int r = 0; r < N; ++r) {
@@ -1895,89 +1880,6 @@ gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out
   return GS_OK;
 } catch (...) {
   return on_exception(g);
-}
-
-// ---- host-only debug entries (no device needed): exercise the product's own host code on a CPU box
-gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,
-                          size_t* nnzb, int32_t* perm) try {
-  if (n <= 0 || e < 0 || (e && (!ei || !ej))) return GS_EINVAL;
-  std::vector<int32_t> rp, ci;
-  gs::global_pattern(n, e, ei, ej, rp, ci);
-  if (nnzb) *nnzb = ci.size();
-  if (rowptr) std::memcpy(rowptr, rp.data(), sizeof(int32_t) * rp.size());
-  if (colidx) std::memcpy(colidx, ci.data(), sizeof(int32_t) * ci.size());
-  if (perm) {
-    std::vector<int> pm;
-    gs::canonical_order(n, e, ei, ej, pm);
-    std::memcpy(perm, pm.data(), sizeof(int32_t) * e);
-  }
-  return GS_OK;
-} catch (...) {
-  return on_exception(nullptr);
-}
-
-// the g2o reader/writer the product uses, without a graph handle: parse `in_path`, report the counts
-// {vertices, edges, priors, fixed, skipped}, optionally copy the parsed arrays out and/or write the
-// parsed content back to `out_path`
-gs_status gs_host_g2o(const char* in_path, const char* out_path, size_t counts[5], uint64_t* vkey, double* vxyt,
-                      uint64_t* e1, uint64_t* e2, double* ez, double* einfo, uint64_t* pkey, double* pxyt, double* pinfo) try {
-  if (!in_path) return GS_EINVAL;
-  gs::G2oData d;
-  if (!gs::read_g2o(in_path, d).empty()) return GS_EINVAL;
-  if (counts) {
-    counts[0] = d.vkey.size();
-    counts[1] = d.e1.size();
-    counts[2] = d.pkey.size();
-    counts[3] = d.fixed.size();
-    counts[4] = d.skipped;
-  }
-  auto out = [](auto* dst, const auto& v) {
-    if (dst && !v.empty()) std::memcpy(dst, v.data(), sizeof(v[0]) * v.size());
-  };
-  out(vkey, d.vkey);
-  out(vxyt, d.vxyt);
-  out(e1, d.e1);
-  out(e2, d.e2);
-  out(ez, d.ez);
-  out(einfo, d.einfo);
-  out(pkey, d.pkey);
-  out(pxyt, d.pxyt);
-  out(pinfo, d.pinfo);
-  if (out_path && !gs::write_g2o(out_path, d).empty()) return GS_EINVAL;
-  return GS_OK;
-} catch (...) {
-  return on_exception(nullptr);
-}
-
-// one factor, host evaluation of the same inline functions the kernels use
-gs_status gs_host_between(const double pi[3], const double pj[3], const double z[3], const double cov9[9], int mode,
-                          double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],
-                          double bi[3], double bj[3]) try {
-  double om[6];
-  if (!spd_information(cov9, om)) return GS_ENOTSPD;
-  const double4 a = make_double4(pi[0], pi[1], std::cos(pi[2]), std::sin(pi[2]));
-  const double4 b = make_double4(pj[0], pj[1], std::cos(pj[2]), std::sin(pj[2]));
-  const double2 zt = make_double2(z[0], z[1]), zr = make_double2(std::cos(z[2]), std::sin(z[2]));
-  gs::BetweenLin L;
-  if (mode == 0) gs::between_linearize<0>(a, b, zt, zr, L);
-  else gs::between_linearize<1>(a, b, zt, zr, L);
-  gs::Sym3 O{om[0], om[1], om[2], om[3], om[4], om[5]};
-  double dg[6], bv[3];
-  gs::diag_pieces(O, L.Ai, L.e, dg, bv);
-  const double fi[9] = {dg[0], dg[1], dg[2], dg[1], dg[3], dg[4], dg[2], dg[4], dg[5]};
-  std::memcpy(Hii, fi, sizeof fi);
-  std::memcpy(bi, bv, sizeof bv);
-  gs::off_block(O, L.Ai, L.Aj, Hij);
-  gs::diag_pieces(O, L.Aj, L.e, dg, bv);
-  const double fj[9] = {dg[0], dg[1], dg[2], dg[1], dg[3], dg[4], dg[2], dg[4], dg[5]};
-  std::memcpy(Hjj, fj, sizeof fj);
-  std::memcpy(bj, bv, sizeof bv);
-  std::memcpy(e, L.e, sizeof L.e);
-  std::memcpy(Ai, L.Ai.m, sizeof L.Ai.m);
-  std::memcpy(Aj, L.Aj.m, sizeof L.Aj.m);
-  return GS_OK;
-} catch (...) {
-  return on_exception(nullptr);
 }
 
 }  // extern "C"

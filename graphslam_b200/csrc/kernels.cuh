@@ -119,6 +119,7 @@ __device__ __forceinline__ void apply_scalars(Scalars* sc, int op, double t0, do
       sc->rzv[1] = t0;
       sc->rr = t1;
       sc->rr0 = t1;
+      sc->beta = 0.0;
       sc->iters = 0;
       sc->done = (t1 == 0.0) ? 1 : 0;
       break;
@@ -238,6 +239,22 @@ __global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const doubl
   double v[1] = {0.0};
   if (r < a.n_own) v[0] = spmv_row(a, p, pg, y, r, lambda);
   reduce_finish<1>(c, v, mode == 0 ? OP_PAP : OP_DOT, red, &flag);
+}
+
+// The product with the direction update folded in (two kernels per iteration): p(c) = z(c) + beta p_prev(c) is formed
+// on the fly for every column the row touches and the row's own new p goes to the other direction buffer.  beta is
+// 0 in the first iteration of a solve (p_prev = z there).  Same expressions as k_pcg_dir + k_spmv: same bits.
+__global__ void __launch_bounds__(kThreads) k_spmvdir(const SpmvView a, const double* __restrict__ z,
+                                                       const double* __restrict__ p_prev, double* __restrict__ p_next,
+                                                       double* __restrict__ y, const ReduceCtx c) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  if (c.sc->done) return;
+  const double lambda = c.sc->lambda, beta = c.sc->beta;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  double v[1] = {0.0};
+  if (r < a.n_own) v[0] = spmv_row_t<true>(a, p_prev, nullptr, z, nullptr, beta, p_next, y, r, lambda);
+  reduce_finish<1>(c, v, OP_PAP, red, &flag);
 }
 
 __global__ void __launch_bounds__(kThreads) k_minv(const double* __restrict__ Hd, const double* __restrict__ dscale,

@@ -4,7 +4,9 @@
 // one fixed order.  The functions are __host__ __device__: the kernels in kernels.cuh call them per
 // thread, and the test-only emulator (emu.cu) calls the very same code per row on the CPU.
 #pragma once
+#include <cmath>
 #include <cstdint>
+#include <vector>
 #include "se2.cuh"
 #include "structure.hpp"
 
@@ -35,17 +37,108 @@ struct SellView {
   const int* width;  // per slice
 };
 
+// ---- storage layouts of the two big per-cell arrays (compile-time; results do not depend on them) -------------
+// GS_H_LAYOUT  0: nine planes of hstride doubles (entry k of block cell q at k*hstride + q)
+//              1: slice-major: the nine entries of the 32 cells of one (slice, slot) are adjacent, 9 x 256 B
+// GS_F_LAYOUT  0: five planes of fstride double2 (component c of factor cell q at c*fstride + q)
+//              1: slice-major: the five components of the 32 cells of one (slice, slot) are adjacent, 5 x 512 B
+// Cells come in groups of 32 (SELL-32 lists), so both strides are multiples of 32.
+#ifndef GS_H_LAYOUT
+#define GS_H_LAYOUT 0
+#endif
+#ifndef GS_F_LAYOUT
+#define GS_F_LAYOUT 0
+#endif
+
+// offset of entry 0 of block cell q, and the distance between consecutive entries of one block
+GS_HD size_t h_base(int q) {
+#if GS_H_LAYOUT == 1
+  return (size_t)(q >> 5) * (9 * kSlice) + (size_t)(q & 31);
+#else
+  return (size_t)q;
+#endif
+}
+GS_HD size_t h_step(size_t hstride) {
+#if GS_H_LAYOUT == 1
+  (void)hstride;
+  return kSlice;
+#else
+  return hstride;
+#endif
+}
+// offset of component 0 of factor cell q, and the distance between consecutive components
+GS_HD size_t f_base(int q) {
+#if GS_F_LAYOUT == 1
+  return (size_t)(q >> 5) * (5 * kSlice) + (size_t)(q & 31);
+#else
+  return (size_t)q;
+#endif
+}
+GS_HD size_t f_step(size_t fstride) {
+#if GS_F_LAYOUT == 1
+  (void)fstride;
+  return kSlice;
+#else
+  return fstride;
+#endif
+}
+
 constexpr int kNoCountBit = 1 << 30;   // set in ij.x of a stored factor whose chi2 another rank counts
 constexpr int kIdxMask = kNoCountBit - 1;
 
 struct FactorView {
   const int2* ij;       // per factor cell: local indices of id_1 (| kNoCountBit), id_2 ; (-1,-1) = no data
-  const double2* zt;    // measured translation
-  const double2* zr;    // (cos, sin) of the measured rotation
-  const double2* o01;   // information, upper triangle 00 01 | 02 11 | 12 22
-  const double2* o23;
-  const double2* o45;
+  const double2* data;  // five double2 components per cell, at f_base(cell) + c * f_step(fstride):
+                        //   0 measured translation, 1 (cos, sin) of the measured rotation,
+                        //   2..4 information, upper triangle 00 01 | 02 11 | 12 22
+  size_t fstride;
 };
+
+struct FactorData {
+  double2 zt, zr, o01, o23, o45;
+};
+
+GS_HD FactorData load_factor(const FactorView& f, int cell) {
+  const double2* p = f.data + f_base(cell);
+  const size_t st = f_step(f.fstride);
+  FactorData d;
+  d.zt = ldg(p);
+  d.zr = ldg(p + st);
+  d.o01 = ldg(p + 2 * st);
+  d.o23 = ldg(p + 3 * st);
+  d.o45 = ldg(p + 4 * st);
+  return d;
+}
+
+// host staging of the factor cells in the device layout (the structure build's f_src / f_i / f_j / f_count say
+// which cells hold data); `cells` = csell.slots, a multiple of 32
+struct FactorStage {
+  std::vector<int2> ij;
+  std::vector<double2> data;
+  size_t fstride = kSlice;
+  void init(int cells) {
+    fstride = (size_t)((std::max(cells, 1) + kSlice - 1) / kSlice) * kSlice;
+    ij.assign(fstride, make_int2(-1, -1));
+    data.assign(5 * fstride, make_double2(0.0, 0.0));
+    for (size_t q = 0; q < fstride; ++q) data[f_base((int)q) + f_step(fstride)] = make_double2(1.0, 0.0);  // unit rotation
+  }
+  // z = (dx, dy, dtheta), om = information upper triangle (6)
+  void set(int q, int i, int j, const double* z, const double* om) {
+    ij[q] = make_int2(i, j);
+    double2* p = data.data() + f_base(q);
+    const size_t st = f_step(fstride);
+    p[0] = make_double2(z[0], z[1]);
+    p[st] = make_double2(std::cos(z[2]), std::sin(z[2]));
+    p[2 * st] = make_double2(om[0], om[1]);
+    p[3 * st] = make_double2(om[2], om[3]);
+    p[4 * st] = make_double2(om[4], om[5]);
+  }
+};
+
+// entry (r, c) of the stored block cell `pos` of a host copy of Ho, optionally transposed
+inline double h_entry(const double* Ho, size_t hstride, int pos, int r, int c, bool tr) {
+  return Ho[h_base(pos) + (size_t)(tr ? 3 * c + r : 3 * r + c) * h_step(hstride)];
+}
 
 struct PriorView {
   int n;                 // priors on this rank's rows
@@ -109,8 +202,10 @@ GS_HD void diag_pieces(const Sym3& O, const Mat3& Ar, const double e[3], double 
 }
 
 GS_HD void store_block(double* Ho, size_t hstride, int pos, const double M[9]) {
+  double* hp = Ho + h_base(pos);
+  const size_t st = h_step(hstride);
 #pragma unroll
-  for (int k = 0; k < 9; ++k) Ho[(size_t)k * hstride + pos] = M[k];
+  for (int k = 0; k < 9; ++k) hp[(size_t)k * st] = M[k];
 }
 
 // One factor side under GTSAM's default Jacobians (A_i = [[-c,-s,dt1],[s,-c,dt2],[0,0,-1]], A_j = I):
@@ -281,10 +376,9 @@ GS_HD double assemble_row(const AsmView& a, int r) {
     if (code == kPadCode) continue;
     const int idx = (int)(code >> 3);
     if ((code & 3u) < 2) {
-      const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
-      const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
+      const FactorData fd = load_factor(a.f, idx);
       const double4 pcol = ldg(a.pose + cur.z);
-      asm_between<MODE, NODUP>(A, code, cur.y, prow, pcol, zt, zr, o01, o23, o45, a.Ho, a.hstride);
+      asm_between<MODE, NODUP>(A, code, cur.y, prow, pcol, fd.zt, fd.zr, fd.o01, fd.o23, fd.o45, a.Ho, a.hstride);
     } else {
       asm_prior<MODE>(A, prow, ldg(a.pr.pose + idx), a.pr.om + 6 * idx);
     }
@@ -321,11 +415,10 @@ GS_HD double chi2_row(const AsmView& a, int r) {
     const int idx = base + s * kSlice;
     const int2 ij = s >= first ? ldg(a.f.ij + idx) : make_int2(-1, -1);
     if (ij.x >= 0 && !(ij.x & kNoCountBit)) {
-      const double2 zt = ldg(a.f.zt + idx), zr = ldg(a.f.zr + idx);
-      const double2 o01 = ldg(a.f.o01 + idx), o23 = ldg(a.f.o23 + idx), o45 = ldg(a.f.o45 + idx);
+      const FactorData fd = load_factor(a.f, idx);
       double e[3];
-      between_error(ldg(a.pose + ij.x), ldg(a.pose + ij.y), zt, zr, e);
-      const Sym3 O{o01.x, o01.y, o23.x, o23.y, o45.x, o45.y};
+      between_error(ldg(a.pose + ij.x), ldg(a.pose + ij.y), fd.zt, fd.zr, e);
+      const Sym3 O{fd.o01.x, fd.o01.y, fd.o23.x, fd.o23.y, fd.o45.x, fd.o45.y};
       chi2 += quad_form(O, e);
     }
   }
@@ -386,10 +479,11 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
     const int2 ref = nref;
     if (s + 1 < w) nref = ldg(a.refs + base + (s + 1) * kSlice);
     if (ref.x >= 0) {
-      const double* hp = a.Ho + (ref.y >> 1);
+      const double* hp = a.Ho + h_base(ref.y >> 1);
+      const size_t hst = h_step(a.hstride);
       double h[9];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * a.hstride);
+      for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * hst);
       double px, py, pz;
       if (DIR) {
         const bool ghost = ref.x >= a.n_own;

@@ -48,6 +48,17 @@ typedef enum {
 
 enum { GS_JACOBIAN_GTSAM_DEFAULT = 0, GS_JACOBIAN_EXACT = 1 };
 
+/* gs_params.solver_flags: the few real choices of execution path (all give the same bits; the defaults are the
+ * measured winners).  Fixed at gs_create; nothing in the library reads the environment. */
+enum {
+  GS_SOLVER_NO_CUDA_GRAPH = 1 << 0,  /* launch the PCG kernels one by one instead of replaying the captured batch */
+  GS_SOLVER_NCCL_PER_OP = 1 << 1,    /* multi-GPU: ncclSend/Recv + all-gather per exchange instead of stores into peer memory */
+  GS_SOLVER_NO_PERSISTENT = 1 << 2,  /* small graphs: per-kernel iteration instead of the cooperative persistent kernel */
+  GS_SOLVER_DIR_KERNEL = 1 << 3,     /* keep the direction update p = z + beta p as a kernel of its own (three kernels per
+                                        iteration); default: formed on the fly inside the product where that is faster */
+  GS_SOLVER_DIR_ON_THE_FLY = 1 << 4  /* force the on-the-fly form (two kernels per iteration) */
+};
+
 /* Defaults == gtsam::LevenbergMarquardtParams defaults, i.e. what graph.cpp:119 runs with. */
 typedef struct gs_params {
   int max_iterations;        /* 100   */
@@ -66,7 +77,8 @@ typedef struct gs_params {
   int device;                /* CUDA device ordinal, -1 = current */
   int rank;                  /* multi-GPU: this process's rank (0)      */
   int world_size;            /* multi-GPU: number of ranks (1)          */
-  int reserved[8];
+  int solver_flags;          /* GS_SOLVER_* bits (0)                    */
+  int reserved[7];
 } gs_params;
 
 typedef struct gs_stats {
@@ -89,6 +101,8 @@ typedef struct gs_stats {
   double ms_device;          /* CUDA-event time on the graph's stream, first to last kernel   */
   double h2d_bytes;          /* host->device bytes copied by this call                        */
   double d2h_bytes;          /* device->host bytes copied by this call                        */
+  double p2p_wait_ticks[3];  /* peer-memory path: SM clock ticks CTA 0 spent waiting for other GPUs in the product /  */
+  double p2p_waits;          /*   update / direction kernels during this call, and the iterations they cover        */
   double reserved[4];
 } gs_stats;
 

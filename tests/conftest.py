@@ -18,3 +18,11 @@ def lib():
     from graphslam_b200 import _lib, build
     build.build()
     return _lib.load()
+
+
+@pytest.fixture(scope="session")
+def dbg():
+    """libgraphslam_cuda_debug.so: the test-only CPU emulator and host hooks (never part of the product library)."""
+    from graphslam_b200 import _lib, build
+    build.build()
+    return _lib.load_debug()

@@ -17,11 +17,12 @@ from graphslam_b200 import graph, synth  # noqa: E402
 def main():
     cid = sys.argv[1] if len(sys.argv) > 1 else "C3"
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 30000
+    flags = int(sys.argv[3]) if len(sys.argv) > 3 else 0     # gs_params.solver_flags of the multi-GPU graph
     rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     g = synth.config(cid, n=n, full_cov=True)
-    G = graph.distributed_graph()
+    G = graph.distributed_graph(solver_flags=flags)
     G.add_graph(g)
     chi0 = G.chi2()
     st = G.optimize()

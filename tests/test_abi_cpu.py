@@ -23,7 +23,7 @@ def _cuda_present():
         return False
 
 
-def test_header_symbols_all_exported(lib):
+def test_header_symbols_all_exported(lib, dbg):
     hdr = open(os.path.join(ROOT, "include", "graphslam_cuda.h")).read()
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
     declared = set(re.findall(r"\b(gs_[a-z0-9_]+)\s*\(", hdr))
@@ -33,12 +33,15 @@ def test_header_symbols_all_exported(lib):
         assert hasattr(lib, name), f"{name} not exported"
     assert lib.gs_version() == 1
     # the test-only header too
-    dbg = open(os.path.join(ROOT, "include", "graphslam_cuda_debug.h")).read()
-    dbg = re.sub(r"/\*.*?\*/", "", dbg, flags=re.S)
-    declared_dbg = set(re.findall(r"\b(gs_[a-z0-9_]+)\s*\(", dbg))
+    dhdr = open(os.path.join(ROOT, "include", "graphslam_cuda_debug.h")).read()
+    dhdr = re.sub(r"/\*.*?\*/", "", dhdr, flags=re.S)
+    declared_dbg = set(re.findall(r"\b(gs_[a-z0-9_]+)\s*\(", dhdr))
     assert declared_dbg == set(_lib.DEBUG_SIGNATURES), declared_dbg ^ set(_lib.DEBUG_SIGNATURES)
     for name in declared_dbg:
-        assert hasattr(lib, name), f"{name} not exported"
+        assert hasattr(dbg, name), f"{name} not exported by the debug library"
+    # the product library carries no test scaffolding (emulator, host hooks)
+    for name in declared_dbg:
+        assert not hasattr(lib, name), f"{name} leaked into libgraphslam_cuda.so"
 
 
 def test_default_params_are_gtsam_defaults(lib):
@@ -65,17 +68,17 @@ def _host_pattern(lib, n, ei, ej):
 
 
 @pytest.mark.parametrize("cid,n", [("C1", None), ("C2", 20000), ("C3", 50000), ("C4", 4000)])
-def test_structure_bit_exact_vs_oracle(lib, cid, n):
+def test_structure_bit_exact_vs_oracle(dbg, cid, n):
     g = synth.config(cid, n=n)
     prob = O.Problem.from_graph(g)
-    rp, ci, perm = _host_pattern(lib, g.n, prob.ei, prob.ej)
+    rp, ci, perm = _host_pattern(dbg, g.n, prob.ei, prob.ej)
     orp, oci = prob.pattern()
     assert rp.dtype == orp.dtype == np.int32
     assert np.array_equal(rp, orp) and np.array_equal(ci, oci)
     assert sorted(perm.tolist()) == list(range(g.e))
 
 
-def test_structure_duplicates_isolated_and_hub(lib):
+def test_structure_duplicates_isolated_and_hub(dbg):
     rng = np.random.default_rng(5)
     n = 300
     ei = np.r_[rng.integers(0, n - 10, 900), np.zeros(600, np.int64)]        # vertex 0 is a hub (600 edges)
@@ -84,17 +87,17 @@ def test_structure_duplicates_isolated_and_hub(lib):
     ei, ej = ei[m], ej[m]
     prob = O.Problem(n, ei, ej, np.zeros((len(ei), 3)), np.tile(np.eye(3).reshape(9), (len(ei), 1)), [0],
                      np.zeros((1, 3)), np.eye(3).reshape(1, 9))
-    rp, ci, _ = _host_pattern(lib, n, ei, ej)
+    rp, ci, _ = _host_pattern(dbg, n, ei, ej)
     orp, oci = prob.pattern()
     assert np.array_equal(rp, orp) and np.array_equal(ci, oci)
     # canonical order does not depend on the insertion order of the factors
     sh = rng.permutation(len(ei))
-    rp2, ci2, _ = _host_pattern(lib, n, ei[sh], ej[sh])
+    rp2, ci2, _ = _host_pattern(dbg, n, ei[sh], ej[sh])
     assert np.array_equal(rp, rp2) and np.array_equal(ci, ci2)
 
 
 @pytest.mark.parametrize("mode", [0, 1])
-def test_host_between_matches_oracle(lib, mode):
+def test_host_between_matches_oracle(dbg, mode):
     g = synth.config("C1", full_cov=True)
     prob = O.Problem.from_graph(g)
     t = prob.edge_terms(g.init, mode)
@@ -102,7 +105,7 @@ def test_host_between_matches_oracle(lib, mode):
     for k in rng.integers(0, g.e, 300):
         outs = [np.zeros(3), np.zeros(9), np.zeros(9), np.zeros(9), np.zeros(9), np.zeros(9), np.zeros(3), np.zeros(3)]
         args = [np.ascontiguousarray(a) for a in (g.init[prob.ei[k]], g.init[prob.ej[k]], g.z[k], g.cov[k])]
-        st = lib.gs_host_between(*[graph._dp(a) for a in args], mode, *[graph._dp(o) for o in outs])
+        st = dbg.gs_host_between(*[graph._dp(a) for a in args], mode, *[graph._dp(o) for o in outs])
         assert st == 0
         ref = [t["e"][k], t["a_i"][k].ravel(), t["a_j"][k].ravel(), t["h_ii"][k].ravel(), t["h_ij"][k].ravel(),
                t["h_jj"][k].ravel(), t["b_i"][k], t["b_j"][k]]

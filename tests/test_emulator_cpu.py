@@ -11,6 +11,11 @@ from graphslam_b200 import _lib, synth
 from oracle import gs_oracle as O
 
 
+@pytest.fixture(scope="module")
+def lib(dbg):
+    return dbg   # every entry point used here lives in the test-only debug library
+
+
 def _upper6(om):
     return np.ascontiguousarray(np.stack([om[:, 0, 0], om[:, 0, 1], om[:, 0, 2], om[:, 1, 1], om[:, 1, 2], om[:, 2, 2]], 1))
 

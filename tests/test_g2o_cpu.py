@@ -11,7 +11,7 @@ from graphslam_b200._lib import c_double_p, c_u64_p
 
 @pytest.fixture(scope="module")
 def lib():
-    return _lib.load()
+    return _lib.load_debug()
 
 
 def _parse(lib, path, out_path=None):

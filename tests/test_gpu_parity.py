@@ -390,14 +390,13 @@ def test_deep_convergence_parity():
 
 
 @pytest.mark.parametrize("cid,n", [("C1", None), ("C5", 30000)])
-def test_fused_pcg_bitwise(cid, n, monkeypatch):
+def test_fused_pcg_bitwise(cid, n):
     """Small graphs run the PCG iteration as one persistent kernel (grid barriers instead of launches); same per-row
     code and reduction tree, so the result must equal the three-kernel path bit for bit."""
     g = synth.config(cid, n=n)
     out = {}
     for fused in ("0", "1"):
-        monkeypatch.setenv("GS_PCG_FUSED", fused)
-        with _load(g) as G:
+        with _load(g, solver_flags=0 if fused == "1" else _lib.GS_SOLVER_NO_PERSISTENT) as G:
             st = G.optimize()
             _, x = G.poses()
             out[fused] = (st["chi2_final"], st["pcg_iterations_total"], st["iterations"], x, st["gpu_launches"])
@@ -407,22 +406,24 @@ def test_fused_pcg_bitwise(cid, n, monkeypatch):
 
 
 @pytest.mark.parametrize("n", [4001, 60000])
-def test_staged_update_bitwise(n, monkeypatch):
-    """k_pcg_update_staged (the default: x, r, z moved as full-width double2 through shared memory) against
-    k_pcg_update (GS_UPDATE_STAGED=0): same expressions per element and per row, same reduction tree, so a capped
-    solve must give the same bits.  4001 rows leave an odd number of rows in the last tile; the three-kernel
-    iteration is forced (small graphs would otherwise take the persistent kernel)."""
+def test_pcg_iteration_forms_bitwise(n):
+    """The forms of the PCG iteration on one GPU must give the same bits on a capped solve: the three-kernel iteration
+    (k_spmv, k_pcg_update_staged, k_pcg_dir), the two-kernel one with the direction formed on the fly inside the
+    product (k_spmvdir), the same replayed from the captured CUDA graph or launched kernel by kernel, and the
+    persistent cooperative kernel small graphs take by default.  Same expressions per element and per row, same
+    reduction tree.  4001 rows leave an odd number of rows in the last tile."""
     import ctypes as C
     g = synth.config("C3", n=n)
-    monkeypatch.setenv("GS_PCG_FUSED", "0")
+    NP, F = _lib.GS_SOLVER_NO_PERSISTENT, _lib
     out = []
-    for staged in ("0", "1"):
-        monkeypatch.setenv("GS_UPDATE_STAGED", staged)
-        with _load(g, pcg_max_iters=96, pcg_rel_tol=1e-300) as G:
+    for flags in (NP | F.GS_SOLVER_DIR_KERNEL, NP | F.GS_SOLVER_DIR_ON_THE_FLY, NP | F.GS_SOLVER_DIR_ON_THE_FLY | F.GS_SOLVER_NO_CUDA_GRAPH,
+                  NP | F.GS_SOLVER_DIR_KERNEL | F.GS_SOLVER_NO_CUDA_GRAPH, 0):
+        with _load(g, pcg_max_iters=96, pcg_rel_tol=1e-300, solver_flags=flags) as G:
             d = np.zeros((g.n, 3))
             it, rr = C.c_int(), C.c_double()
             st = G._lib.gs_solve_linear(G._h, 1e-5, d.ctypes.data_as(_lib.c_double_p), C.byref(it), C.byref(rr))
             assert st in (_lib.GS_OK, _lib.GS_ENOTCONVERGED) and it.value == 96
             out.append(d)
     assert np.isfinite(out[0]).all() and np.abs(out[0]).max() > 0
-    assert np.array_equal(out[0], out[1])
+    for d in out[1:]:
+        assert np.array_equal(out[0], d)

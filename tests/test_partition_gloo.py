@@ -27,7 +27,7 @@ def _worker(rank, world, port, q):
         import torch.distributed as dist
         from graphslam_b200 import _lib, graph, synth
         dist.init_process_group("gloo", rank=rank, world_size=world)
-        lib = _lib.load()
+        lib = _lib.load_debug()
         g = synth.config("C3", n=6000)
         ei, ej = g.dense_edges()
         ip = _lib.c_i32_p
