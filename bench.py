@@ -17,6 +17,7 @@ from the synthetic initial guess.  One JSON line on stdout (rank 0); everything 
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import statistics
@@ -109,100 +110,156 @@ def workload_name(g):
 
 
 # ----------------------------------------------------------------------------------------- CPU arm
-def cpu_sample(g, pcg_cap, pcg_per_lm=None):
-    """One LM iteration of the C/OpenMP port on the full graph with PCG capped at `pcg_cap` iterations.
-    Returns seconds per LM iteration, scaled to `pcg_per_lm` PCG iterations when the cap was hit."""
+def config_dict(g):
+    """The workload both arms run; printed unchanged by both (run-specific details go under "run")."""
+    return {"workload": workload_name(g), "n_poses": int(g.n), "n_factors": int(g.e), "pcg_rel_tol": PCG_TOL,
+            "step": "one outer LM iteration (linearise, damped solve, retract, chi2, accept/reject), warm-started, lambda reset"}
+
+
+def pose_digest(x):
+    """SHA-256 of the pose array's bytes (float64, sorted-key order): equal digests = bitwise equal results."""
+    return hashlib.sha256(np.ascontiguousarray(x, dtype=np.float64).tobytes()).hexdigest()
+
+
+def cpu_threads():
+    """Set the OpenMP thread count of the CPU port explicitly to the host's cores (torchrun exports OMP_NUM_THREADS=1
+    to its children) and fail loudly if that did not take."""
     from oracle import cpu_ref
+    want = cpu_ref.host_cores()
+    got = cpu_ref.set_threads(want)
+    if want > 1 and got <= 1:
+        raise SystemExit(f"bench.py: the CPU arm would run on {got} thread of {want} cores")
+    return got
+
+
+def cpu_warm():
     global _CPU_WARM
     if not _CPU_WARM:   # spin up the OpenMP thread pool outside the measurement
         from graphslam_b200 import synth
+        from oracle import cpu_ref
         cpu_ref.optimize(synth.config("C3", n=20000), max_iterations=1, pcg_iter_cap_total=20)
         _CPU_WARM = True
-    x, st, errs, tries = cpu_ref.optimize(g, max_iterations=1, rel_error_tol=0.0, abs_error_tol=0.0,
-                                          pcg_rel_tol=PCG_TOL, pcg_iter_cap_total=pcg_cap)
+
+
+def cpu_step(g, x, solver, **kw):
+    """One real LM iteration of the C/OpenMP port from values x (lambda reset, like gs_optimize(max_iterations=1)).
+    Time = the call minus its one-off structure build and ordering, which the GPU arm also keeps out of a step."""
+    from oracle import cpu_ref
+    x1, st, errs, _ = cpu_ref.optimize(g, init=x, max_iterations=1, rel_error_tol=0.0, abs_error_tol=0.0,
+                                       pcg_rel_tol=PCG_TOL, solver=solver, **kw)
+    st["sec"] = (st["ms_total"] - st["ms_structure"] - st["ms_analyze"]) * 1e-3
+    return x1, st
+
+
+def cpu_pcg_sample(g, x, cap_iters, time_cap_s, pcg_per_lm=None):
+    """The CPU PCG variant on one LM iteration: run to the tolerance unless it exceeds `time_cap_s` (or `cap_iters`
+    iterations when no time cap is given); then the measured ms per PCG iteration is reported, and scaled to
+    `pcg_per_lm` iterations only as a labelled extrapolation."""
+    kw = dict(pcg_time_cap_ms=time_cap_s * 1e3) if time_cap_s else dict(pcg_iter_cap_total=cap_iters)
+    _, st = cpu_step(g, x, 0, **kw)
     its = max(int(st["pcg_iterations_total"]), 1)
-    per_pcg = st["ms_solve"] / its
+    per = st["ms_solve"] / its
     fixed = st["ms_linearize"] + st["ms_update"]
-    capped = its >= pcg_cap
-    n_pcg = pcg_per_lm if (capped and pcg_per_lm) else its
-    sec = (fixed + per_pcg * n_pcg) * 1e-3
-    return dict(sec_per_lm=sec, ms_per_pcg=per_pcg, ms_fixed=fixed, pcg_run=its, pcg_scaled_to=n_pcg,
-                threads=int(st["threads"]), capped=capped, edges_per_sec=g.e / max(st["ms_linearize"] * 1e-3, 1e-12))
+    finished = not st["capped"]
+    out = {"ms_per_pcg_iteration": per, "pcg_iterations_run": its, "finished": bool(finished),
+           "ms_linearize_update": fixed, "edges_linearized_per_sec": g.e / max(st["ms_linearize"] * 1e-3, 1e-12)}
+    if finished:
+        out["sec_per_step"] = st["sec"]
+    elif pcg_per_lm:
+        out["sec_per_step_extrapolated"] = (fixed + per * pcg_per_lm) * 1e-3
+        out["extrapolated_to_pcg_iterations"] = int(pcg_per_lm)
+    else:
+        out["sec_per_step_lower_bound"] = st["sec"]
+    return out
+
+
+def superlu_sample(n=100_000):
+    """Informational third figure: wall time of the numpy/SuperLU oracle's damped solve on a bounded
+    sample of the workload (the same generator cut to `n` poses)."""
+    from graphslam_b200 import synth
+    from oracle import gs_oracle as O
+    g = synth.config("C3", n=n)
+    prob = O.Problem.from_graph(g)
+    h, b, _ = prob.linearize(g.init, 0)
+    t = time.time()
+    prob.solve_damped(h, b, 1e-5)
+    return {"sec_per_solve": time.time() - t, "sample": f"one damped solve (scipy splu, 1 thread) on C3 cut to {n} poses"}
 
 
 def run_reference(args):
-    """--impl reference: the CPU implementation of the path on the host cores (oracle port; the reference's own
-    optimiser is an absent third-party library).  Each step = one bounded sample."""
+    """--impl reference: the reference's algorithm for the path on the host cores.  What graph.cpp:119 runs is GTSAM's
+    LM with a multifrontal Cholesky; GTSAM is absent (unpinned third-party dependency), so this is the oracle's C
+    restatement: every step is a REAL, un-capped LM iteration of oracle/cpu_ref.c with its sparse multifrontal
+    Cholesky (oracle/cpu_chol.c), warm-started like the GPU arm's steps.  The CPU PCG variant (the CUDA path's own
+    algorithm) is timed beside it on one step, capped by wall time; `value` is the faster variant's."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    threads = cpu_threads()
     g = make_graph(args.config, args.n)
-    pcg_per_lm = args.pcg_per_lm or estimate_pcg_per_lm(g, args.warmup, args.steps)
-    cap = args.cpu_pcg_cap
-    if pcg_per_lm is None and g.n <= 250_000:
-        cap = 2_000_000_000      # no iteration count on record and the graph is small enough: solve to the tolerance
-    secs = []
-    last = None
-    for s in range(args.warmup + args.steps):
-        last = cpu_sample(g, cap, pcg_per_lm)
-        if s >= args.warmup:
-            secs.append(last["sec_per_lm"])
-        log(f"[bench/reference] step {s}: {last['sec_per_lm']:.2f} s per LM iteration "
-            f"({last['ms_per_pcg']:.2f} ms per PCG iteration x {last['pcg_scaled_to']})")
-    sec = statistics.mean(secs)
+    cpu_warm()
+    K, W = args.steps, args.warmup
+    x = np.ascontiguousarray(g.init)
+    secs, chi2 = [], None
+    t_begin = time.time()
+    skipped = 0
+    for s in range(W + K):
+        if time.time() - t_begin > args.ref_budget_s and len(secs) >= 2:
+            skipped = W + K - s
+            break
+        x, st = cpu_step(g, x, 1)
+        chi2 = st["chi2_final"]
+        if s >= W:
+            secs.append(st["sec"])
+        log(f"[bench/reference] step {s}: {st['sec']:.2f} s (factor {st['ms_factor'] * 1e-3:.2f} s, "
+            f"solve {(st['ms_solve'] - st['ms_factor']) * 1e-3:.2f} s, linearise {st['ms_linearize'] * 1e-3:.2f} s; ordering "
+            f"{st['ms_analyze'] * 1e-3:.2f} s not counted) chi2 {st['chi2_initial']:.6g} -> {st['chi2_final']:.6g}")
+    if not secs:      # budget hit during warm-up: the steps so far are what there is
+        secs = [st["sec"]]
+    sec_chol = statistics.mean(secs)
+    pcg = None
+    if not args.no_cpu_pcg:
+        pcg = cpu_pcg_sample(g, np.ascontiguousarray(g.init), args.cpu_pcg_cap, args.cpu_pcg_time_cap_s, args.pcg_per_lm)
+        log(f"[bench/reference] CPU PCG variant: {json.dumps(pcg)}")
+    sec_pcg = (pcg or {}).get("sec_per_step") or (pcg or {}).get("sec_per_step_lower_bound")
+    variant = "cholesky" if (sec_pcg is None or sec_chol <= sec_pcg) else "pcg"
+    sec = sec_chol if variant == "cholesky" else sec_pcg
     value = 1.0 / sec
-    if last["capped"] and pcg_per_lm:
-        sample = (f"1 LM iteration on the full graph, PCG capped at {cap} iterations and scaled to "
-                  f"{pcg_per_lm} iterations/LM-iteration (count the same algorithm needs at tol {PCG_TOL:g})")
-    elif last["capped"]:
-        sample = (f"1 LM iteration on the full graph, PCG capped at {cap} iterations and NOT scaled (no iteration count "
-                  f"on record for this graph): an upper bound on the CPU rate")
-    else:
-        sample = f"1 LM iteration on the full graph, PCG to tol {PCG_TOL:g} ({last['pcg_run']} iterations)"
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(g), "n_poses": g.n, "n_factors": g.e, "pcg_rel_tol": PCG_TOL},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["threads"], "kind": "port", "sample": sample},
+    sample = (f"{len(secs)} real LM iterations of oracle/cpu_ref.c on the full graph, sparse multifrontal Cholesky "
+              f"(nnz(L) {st['chol_nnz']:.3g}, {st['chol_flops']:.3g} flop per factorisation), {threads} threads; "
+              f"structure build and ordering not counted" + (f"; {skipped} step(s) skipped at the {args.ref_budget_s}-s budget" if skipped else ""))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K,
+            "warmup": W, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(g),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "variant": variant,
+                             "sample": sample, "cholesky": {"sec_per_step": sec_chol, "steps_measured": len(secs)},
+                             "pcg": pcg},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "steps_measured": len(secs), "chi2_final": repr(float(chi2)),
+            "pose_sha256": pose_digest(x)}
     print(json.dumps(line), flush=True)
 
 
-def estimate_pcg_per_lm(g, warmup=0, steps=1):
-    """PCG iterations one LM iteration needs on this graph, averaged over the LM steps the GPU arm times (steps
-    warmup+1 .. warmup+steps of the warm-started sequence): from the recorded per-step counts
-    (profiles/pcg_iters.json, logged by the GPU arm: same algorithm, same tolerance, and the count is a property
-    of the problem, not of the machine), else measured on the GPU when one is present, else the sample's own count."""
-    rec = os.path.join(ROOT, "profiles", "pcg_iters.json")
-    if os.path.exists(rec):
-        try:
-            per_step = json.load(open(rec)).get(f"{g.name}:{g.n}")
-        except Exception:
-            per_step = None
-        if isinstance(per_step, (int, float)) and per_step > 0:     # older record: one average
-            return int(round(per_step))
-        if per_step:
-            take = [per_step[min(k, len(per_step) - 1)] for k in range(warmup, warmup + max(steps, 1))]
-            return int(round(sum(take) / len(take)))
-    try:
-        import torch
-        if torch.cuda.is_available():
-            from graphslam_b200 import graph
-            with graph.Graph(max_iterations=1, rel_error_tol=0.0, abs_error_tol=0.0, pcg_rel_tol=PCG_TOL) as G:
-                G.add_graph(g)
-                counts = [G.optimize() for _ in range(warmup + max(steps, 1))][warmup:]
-            return int(round(sum(c["pcg_iterations_total"] / max(c["inner_iterations"], 1) for c in counts) / len(counts)))
-    except Exception as exc:  # no GPU for the reference arm is fine
-        log(f"[bench/reference] no GPU estimate of PCG iterations ({exc})")
-    return None
-
-
 # ----------------------------------------------------------------------------------------- our arm
+def kernel_table(prof, peak):
+    return {name: {"ms": round(ms, 5), "algorithmic_MB": round(by / 1e6, 2), "GBps": round(by / (ms * 1e-3) / 1e9, 1),
+                   "frac": round(by / (ms * 1e-3) / 1e9 / peak, 4)} for name, (ms, by) in prof.items() if ms > 0}
+
+
+def roofline_pass(graph_mod, g, device, peak, iters):
+    """Per-kernel CUDA-event timings of one config inside the real kernel sequence (gs_profile_pcg / gs_profile_outer)."""
+    with graph_mod.Graph(device=device) as G:
+        G.add_graph(g)
+        G.prepare()
+        prof = G.profile_pcg(1e-5, iters)
+        outer = G.profile_outer(3)
+    return kernel_table({**prof, **outer}, peak)
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from graphslam_b200 import graph
+    from graphslam_b200 import graph, synth
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -273,18 +330,22 @@ def run_ours(args):
     ms_lin = vmax(sum(s["ms_linearize"] for s in stats))
     ms_solve = vmax(sum(s["ms_solve"] for s in stats))
     ms_upd = vmax(sum(s["ms_update"] for s in stats))
+    waits = None
+    if world > 1:   # peer-memory path: what CTA 0 of this rank spent waiting for other GPUs, per PCG iteration (SM clock ticks)
+        n_w = max(sum(s["p2p_waits"] for s in stats), 1.0)
+        waits = {k: sum(s["p2p_wait_ticks"][i] for s in stats) / n_w for i, k in enumerate(("spmv", "update", "dir"))}
+    _, x_res = G.poses()            # collective on several ranks; every rank receives all poses
+    chi2_final = stats[-1]["chi2_final"]
+    digest = pose_digest(x_res)
     log(f"[bench r{rank}] resident: {K} steps in {dev_s:.3f}s device ({wall:.3f}s wall), {pcg_total} PCG iterations, "
-        f"chi2 {stats[0]['chi2_initial']:.6g} -> {stats[-1]['chi2_final']:.6g}")
+        f"chi2 {stats[0]['chi2_initial']:.17g} -> {chi2_final:.17g}, poses sha256 {digest[:16]}")
 
     # ---- roofline of the dominant kernel, CUDA events around every launch on the library's stream
     prof = G.profile_pcg(1e-5, args.profile_iters)
     outer = G.profile_outer(3)
     spmv_ms, spmv_bytes = prof["spmv"]
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
-    kernels = {}
-    for name, (ms, by) in {**prof, **outer}.items():
-        kernels[name] = {"ms": round(ms, 5), "algorithmic_MB": round(by / 1e6, 2), "GBps": round(by / (ms * 1e-3) / 1e9, 1),
-                         "frac": round(by / (ms * 1e-3) / 1e9 / peak, 4)}
+    kernels = kernel_table({**prof, **outer}, peak)
     log(f"[bench r{rank}] kernels: " + json.dumps(kernels))
     traffic = None
     tf = os.path.join(ROOT, "profiles", "spmv_traffic.json")
@@ -311,7 +372,7 @@ def run_ours(args):
     for _ in range(K):
         G2.set_poses(keys, x)            # host -> device (this rank's rows + halo, (x,y,cos,sin) doubles)
         G2.optimize()
-        _, x = G2.poses()                # device -> host (all N poses on every rank)
+        _, x = G2.poses()                # device -> host
     barrier()
     e2e_s = vmax(time.time() - t0)
     e2e = K / e2e_s
@@ -320,50 +381,75 @@ def run_ours(args):
     h2d_step = vsum(h2d1 - h2d0) / K
     d2h_step = vsum(d2h1 - d2h0) / K
 
-    # ---- CPU baseline on a bounded sample (rank 0, N = 1)
-    pcg_per_lm = int(round(pcg_total / max(solves, 1)))
+    extra = {}
     cpu = None
-    if not args.no_cpu_baseline and world == 1:
-        c = cpu_sample(g, args.cpu_pcg_cap, pcg_per_lm)
-        cpu = {"value": 1.0 / c["sec_per_lm"], "unit": UNIT, "cores": c["threads"], "kind": "port",
-               "sample": (f"1 LM iteration of oracle/cpu_ref.c (C+OpenMP) on the full graph, PCG capped at {c['pcg_run']} "
-                          f"iterations ({c['ms_per_pcg']:.2f} ms each) and scaled to the {pcg_per_lm} iterations per solve "
-                          f"the same algorithm needed on the GPU; linearise+update {c['ms_fixed']:.0f} ms"),
-               "edges_linearized_per_sec": c["edges_per_sec"]}
-    if rank == 0:
+    if world == 1 and rank == 0 and not args.no_extras:
+        # ---- the north-star gate names C4 as well: per-kernel roofline of the dense loop-closure graph
         try:
-            os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
-            rec = os.path.join(ROOT, "profiles", "pcg_iters.json")
-            d = json.load(open(rec)) if os.path.exists(rec) else {}
-            key = f"{g.name}:{g.n}"
-            per_step = d.get(key) if isinstance(d.get(key), list) else []
-            per_step += [per_step[-1] if per_step else 0] * max(W + K - len(per_step), 0)
-            for k, s in enumerate(stats):          # LM steps W+1 .. W+K of the warm-started sequence
-                per_step[W + k] = int(round(s["pcg_iterations_total"] / max(s["inner_iterations"], 1)))
-            if W and not any(per_step[:W]):        # warm-up steps not recorded yet: best guess = the first timed one
-                per_step[:W] = [per_step[W]] * W
-            d[key] = per_step
-            json.dump(d, open(rec, "w"), sort_keys=True)
-        except Exception:
-            pass
+            t0 = time.time()
+            g4 = synth.config("C4")
+            extra["roofline_c4"] = {"workload": f"{g4.name}: {g4.n} poses / {g4.e} factors", "peak": peak, "unit": "GB/s",
+                                    "kernels": roofline_pass(graph, g4, local_rank, peak, args.profile_iters)}
+            log(f"[bench] C4 roofline pass {time.time() - t0:.1f}s: " + json.dumps(extra["roofline_c4"]["kernels"]))
+        except Exception as exc:
+            extra["roofline_c4"] = {"error": str(exc)[:300]}
+        # ---- BASELINE config C5: latency per incremental update (bounded sample: the last updates of the sequence)
+        try:
+            from tools import bench_incremental
+            t0 = time.time()
+            extra["incremental_c5"] = bench_incremental.run(n0=50_000 - 100 * args.c5_updates, updates=args.c5_updates,
+                                                            cpu_updates=0 if args.no_cpu_baseline else 1)
+            log(f"[bench] C5 incremental sample {time.time() - t0:.1f}s: p50 {extra['incremental_c5']['p50']:.1f} ms")
+        except Exception as exc:
+            extra["incremental_c5"] = {"error": str(exc)[:300]}
 
+    # ---- CPU baseline on a bounded sample (rank 0, N = 1): both CPU variants + the SuperLU oracle's time
+    pcg_per_lm = int(round(pcg_total / max(solves, 1)))
+    if not args.no_cpu_baseline and world == 1:
+        threads = cpu_threads()
+        cpu_warm()
+        x0 = np.ascontiguousarray(g.init)
+        _, st = cpu_step(g, x0, 1)
+        chol = {"sec_per_step": st["sec"], "sec_factor": st["ms_factor"] * 1e-3, "sec_ordering_not_counted": st["ms_analyze"] * 1e-3,
+                "nnz_L": st["chol_nnz"], "flop_per_factorisation": st["chol_flops"]}
+        pcg = cpu_pcg_sample(g, x0, args.cpu_pcg_cap, 0, pcg_per_lm)
+        sec_pcg = pcg.get("sec_per_step") or pcg.get("sec_per_step_extrapolated")
+        variant = "cholesky" if (sec_pcg is None or chol["sec_per_step"] <= sec_pcg) else "pcg"
+        sec = chol["sec_per_step"] if variant == "cholesky" else sec_pcg
+        try:
+            slu = superlu_sample()
+        except Exception as exc:
+            slu = {"error": str(exc)[:200]}
+        cpu = {"value": 1.0 / sec, "unit": UNIT, "cores": threads, "kind": "port", "variant": variant,
+               "sample": ("1 real LM iteration of oracle/cpu_ref.c from the initial values on the full graph with the sparse "
+                          "multifrontal Cholesky (what the reference's GTSAM call does), and the CPU PCG variant capped at "
+                          f"{pcg['pcg_iterations_run']} iterations ({pcg['ms_per_pcg_iteration']:.2f} ms each; scaled to the "
+                          f"{pcg_per_lm} iterations per solve the GPU needed, as a labelled extrapolation); value = the faster"),
+               "cholesky": chol, "pcg": pcg, "superlu_oracle": slu,
+               "edges_linearized_per_sec": pcg["edges_linearized_per_sec"]}
+
+    run = {"partition": (f"vertex ranges over {world} ranks; halo rows and dot-product segment sums travel by stores into peer "
+                         f"memory (NVLink) from inside the PCG kernels; NCCL only for setup and the final pose gather")
+           if world > 1 else "single GPU",
+           "l2": "inputs larger than L2 (H alone is %.0f MB per PCG iteration on this rank)" % (spmv_bytes / 1e6),
+           "pcg_iters_per_step": pcg_total / K, "us_per_pcg_iteration": dev_s / max(pcg_total, 1) * 1e6,
+           "structure_build_s": round(t_prep, 3), "host_add_s": round(t_add, 3), "wall_s_timed_region": round(wall, 3),
+           "p2p_wait_ticks_per_iteration_rank0": waits}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dev_s / K * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(g), "n_poses": g.n, "n_factors": g.e, "pcg_rel_tol": PCG_TOL,
-                       "partition": f"vertex ranges over {world} rank(s), NCCL halo exchange + segment-sum all-gathers"
-                       if world > 1 else "single GPU",
-                       "l2": "inputs larger than L2 (H alone is %.0f MB per PCG iteration on this rank)" % (spmv_bytes / 1e6),
-                       "pcg_iters_per_step": pcg_total / K, "structure_build_s": round(t_prep, 3),
-                       "host_add_s": round(t_add, 3), "wall_s_timed_region": round(wall, 3)},
+            "dtype": "f64", "data": "synthetic", "config": config_dict(g), "run": run,
+            "chi2_final": repr(float(chi2_final)), "pose_sha256": digest,
             "edges_linearized_per_sec": g.e * len(stats) / (ms_lin * 1e-3),
             "roofline": {"bound": "hbm", "kernel": "k_spmv", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernels": kernels,
+                         "frac": achieved / peak, "traffic": traffic,
+                         "traffic_source": "ncu --set full capture committed under profiles/ (not measured by this run)",
+                         "peak_source": peak_src, "kernels": kernels,
                          "note": "rank 0's kernels on its own rows" if world > 1 else "whole graph"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step},
             "gpu_launches": int(launches), "clocks": clocks,
             "breakdown_ms_per_step": {"linearize_assemble": ms_lin / K, "pcg": ms_solve / K, "update": ms_upd / K}}
+    line.update(extra)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -379,11 +465,20 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C3")
     ap.add_argument("--n", type=int, default=None, help="override the pose count (default: the config's full size)")
-    ap.add_argument("--cpu-pcg-cap", type=int, default=120, help="PCG iterations in the bounded CPU sample")
+    ap.add_argument("--cpu-pcg-cap", type=int, default=120, help="PCG iterations in the GPU arm's bounded CPU PCG sample")
+    ap.add_argument("--cpu-pcg-time-cap-s", type=float, default=60.0,
+                    help="reference arm: wall-time cap of the CPU PCG variant's one LM iteration")
     ap.add_argument("--pcg-per-lm", type=int, default=None)
     ap.add_argument("--profile-iters", type=int, default=40)
+    ap.add_argument("--ref-budget-s", type=float, default=900.0, help="reference arm: stop starting new steps after this")
+    ap.add_argument("--c5-updates", type=int, default=30, help="incremental (C5) updates sampled by the default line")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-pcg", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C4 roofline pass and the C5 incremental sample")
     args = ap.parse_args()
+    if args.config == "C5":
+        from tools import bench_incremental
+        return bench_incremental.main_from_bench(args)
     if args.impl == "reference":
         run_reference(args)
     else:

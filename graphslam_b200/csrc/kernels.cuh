@@ -21,6 +21,24 @@ namespace gs {
 
 constexpr int kThreads = kTile;
 
+// Minimum resident CTAs per SM of the product kernels = their register budget.  Left to itself ptxas compiles the
+// slot loop to 40 registers and gets there by reusing the registers of the first loaded entries for the next ones:
+// the twelve loads of a slot then go out in FOUR dependent groups (profiles/r2_spmv_sass.md), four memory round
+// trips per slot in a kernel that is latency-bound (75 % long-scoreboard stalls at 48 % DRAM utilisation).  With
+// 48 registers (five CTAs) all twelve are requested before the first use.
+#ifndef GS_SPMV_MINB
+#define GS_SPMV_MINB 5
+#endif
+#ifndef GS_SPMVDIR_MINB
+#define GS_SPMVDIR_MINB 4
+#endif
+#ifndef GS_UPD_HOIST
+#define GS_UPD_HOIST 1   // k_pcg_update_staged: request the row's M^-1 block together with the tile's vectors
+#endif
+#ifndef GS_UPD_MINB
+#define GS_UPD_MINB 1
+#endif
+
 // Device-resident scalars: PCG coefficients never visit the host.
 struct Scalars {
   double rz;        // r^T z of the current iterate
@@ -229,7 +247,7 @@ __global__ void __launch_bounds__(kThreads) k_chi2(const AsmView a, const Reduce
 // (A variant that staged several slots per thread through shared memory with cp.async was measured
 //  slower on C3 — 123-165 us against 101 us — because the staging buffers cost occupancy and L1; see
 //  DESIGN.md "What did not help".)
-__global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const double* __restrict__ p, const double* __restrict__ pg,
+__global__ void __launch_bounds__(kThreads, GS_SPMV_MINB) k_spmv(const SpmvView a, const double* __restrict__ p, const double* __restrict__ pg,
                                                     double* __restrict__ y, const ReduceCtx c, int mode) {
   __shared__ double red[8];
   __shared__ int flag;
@@ -244,7 +262,7 @@ __global__ void __launch_bounds__(kThreads) k_spmv(const SpmvView a, const doubl
 // The product with the direction update folded in (two kernels per iteration): p(c) = z(c) + beta p_prev(c) is formed
 // on the fly for every column the row touches and the row's own new p goes to the other direction buffer.  beta is
 // 0 in the first iteration of a solve (p_prev = z there).  Same expressions as k_pcg_dir + k_spmv: same bits.
-__global__ void __launch_bounds__(kThreads) k_spmvdir(const SpmvView a, const double* __restrict__ z,
+__global__ void __launch_bounds__(kThreads, GS_SPMVDIR_MINB) k_spmvdir(const SpmvView a, const double* __restrict__ z,
                                                        const double* __restrict__ p_prev, double* __restrict__ p_next,
                                                        double* __restrict__ y, const ReduceCtx c) {
   __shared__ double red[8];
@@ -302,7 +320,7 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update(const PcgView a, const 
 // dot products, and z goes back through shared memory to be stored flat.  Same expressions per element and per
 // row as pcg_update_apply, same reduction tree: same bits (tests/test_gpu_parity.py::test_staged_update_bitwise).
 // C3: 51.5 -> 47.6 us per launch (profiles/r1_v7_variant_probe.jsonl).
-__global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a, const ReduceCtx c) {
+__global__ void __launch_bounds__(kThreads, GS_UPD_MINB) k_pcg_update_staged(const PcgView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
   __shared__ __align__(16) double sv[3 * kThreads];
@@ -317,6 +335,17 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a,
   double2* x2 = reinterpret_cast<double2*>(a.x + base);
   double2* r2 = reinterpret_cast<double2*>(a.r + base);
   double2* s2 = reinterpret_cast<double2*>(sv);
+  // the row's preconditioner block is requested together with the tile's vectors, not after the barrier below
+  // (one memory round trip per CTA instead of two)
+  const int t = threadIdx.x;
+  double m00 = 0.0, m01 = 0.0, m02 = 0.0, m11 = 0.0, m12 = 0.0, m22 = 0.0;
+#if GS_UPD_HOIST
+  if (t < nrow) {
+    const size_t n = (size_t)a.n_own, w = (size_t)(row0 + t);
+    m00 = ldg(a.Minv + w); m01 = ldg(a.Minv + n + w); m02 = ldg(a.Minv + 2 * n + w);
+    m11 = ldg(a.Minv + 3 * n + w); m12 = ldg(a.Minv + 4 * n + w); m22 = ldg(a.Minv + 5 * n + w);
+  }
+#endif
   for (int i = threadIdx.x; i < nd2; i += kThreads) {   // at most two trips
     const double2 pv = p2[i], qv = q2[i], xv = x2[i], rv = r2[i];
     const double2 xn = make_double2(xv.x + alpha * pv.x, xv.y + alpha * pv.y);
@@ -335,10 +364,16 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a,
   __syncthreads();
   double v[2] = {0.0, 0.0};
   double z0 = 0.0, z1 = 0.0, z2 = 0.0;
-  const int t = threadIdx.x;
   if (t < nrow) {
+#if !GS_UPD_HOIST
+    const size_t n = (size_t)a.n_own, w = (size_t)(row0 + t);
+    m00 = ldg(a.Minv + w); m01 = ldg(a.Minv + n + w); m02 = ldg(a.Minv + 2 * n + w);
+    m11 = ldg(a.Minv + 3 * n + w); m12 = ldg(a.Minv + 4 * n + w); m22 = ldg(a.Minv + 5 * n + w);
+#endif
     const double r0 = sv[3 * t], r1 = sv[3 * t + 1], r2v = sv[3 * t + 2];
-    apply_minv(a.Minv, (size_t)a.n_own, (size_t)(row0 + t), r0, r1, r2v, z0, z1, z2);
+    z0 = (m00 * r0 + m01 * r1) + m02 * r2v;   // apply_minv's expressions
+    z1 = (m01 * r0 + m11 * r1) + m12 * r2v;
+    z2 = (m02 * r0 + m12 * r1) + m22 * r2v;
     v[0] = (r0 * z0 + r1 * z1) + r2v * z2;
     v[1] = (r0 * r0 + r1 * r1) + r2v * r2v;
   }

@@ -214,7 +214,7 @@ __device__ __forceinline__ void reduce_push(const ReduceCtx& c, const P2PCtx& x,
   }
 }
 
-__global__ void __launch_bounds__(kThreads) k_spmv_p2p(const SpmvView a, const double* __restrict__ p, const double* __restrict__ pg,
+__global__ void __launch_bounds__(kThreads, GS_SPMV_MINB) k_spmv_p2p(const SpmvView a, const double* __restrict__ p, const double* __restrict__ pg,
                                                         double* __restrict__ y, const ReduceCtx c, const P2PCtx x) {
   __shared__ double red[8];
   __shared__ int flag;
@@ -351,7 +351,7 @@ struct DirSpmvArgs {
                           // doing all of them put ~10 us on the 8-GPU critical path)
 };
 
-__global__ void __launch_bounds__(kThreads) k_spmvdir_p2p(const SpmvView a, const DirSpmvArgs d, const ReduceCtx c,
+__global__ void __launch_bounds__(kThreads, GS_SPMVDIR_MINB) k_spmvdir_p2p(const SpmvView a, const DirSpmvArgs d, const ReduceCtx c,
                                                            const P2PCtx x) {
   __shared__ double red[8];
   __shared__ int flag;

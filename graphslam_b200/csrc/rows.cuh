@@ -40,26 +40,31 @@ struct SellView {
 // ---- storage layouts of the two big per-cell arrays (compile-time; results do not depend on them) -------------
 // GS_H_LAYOUT  0: nine planes of hstride doubles (entry k of block cell q at k*hstride + q)
 //              1: slice-major: the nine entries of the 32 cells of one (slice, slot) are adjacent, 9 x 256 B
+//              2: slice-major in pairs: entries (0,1) (2,3) (4,5) (6,7) of a cell are adjacent (16-byte accesses,
+//                 4 x 512 B per group), entry 8 follows (256 B): five accesses per block instead of nine
 // GS_F_LAYOUT  0: five planes of fstride double2 (component c of factor cell q at c*fstride + q)
 //              1: slice-major: the five components of the 32 cells of one (slice, slot) are adjacent, 5 x 512 B
 // Cells come in groups of 32 (SELL-32 lists), so both strides are multiples of 32.
 #ifndef GS_H_LAYOUT
-#define GS_H_LAYOUT 0
+#define GS_H_LAYOUT 1   // measured on C3 / C4 (B200): k_spmv 100.5 -> 94.5 us / 144.8 -> 134.5 us against layout 0
 #endif
 #ifndef GS_F_LAYOUT
-#define GS_F_LAYOUT 0
+#define GS_F_LAYOUT 1   // k_assemble 179.8 -> 177 us on C3, 319.8 -> 312.9 us on C4
+#endif
+#ifndef GS_SPMV_PRELOAD
+#define GS_SPMV_PRELOAD 0   // 1: the row's diagonal block and own p are requested before the slot loop
 #endif
 
 // offset of entry 0 of block cell q, and the distance between consecutive entries of one block
 GS_HD size_t h_base(int q) {
-#if GS_H_LAYOUT == 1
+#if GS_H_LAYOUT >= 1
   return (size_t)(q >> 5) * (9 * kSlice) + (size_t)(q & 31);
 #else
   return (size_t)q;
 #endif
 }
 GS_HD size_t h_step(size_t hstride) {
-#if GS_H_LAYOUT == 1
+#if GS_H_LAYOUT >= 1
   (void)hstride;
   return kSlice;
 #else
@@ -135,11 +140,6 @@ struct FactorStage {
   }
 };
 
-// entry (r, c) of the stored block cell `pos` of a host copy of Ho, optionally transposed
-inline double h_entry(const double* Ho, size_t hstride, int pos, int r, int c, bool tr) {
-  return Ho[h_base(pos) + (size_t)(tr ? 3 * c + r : 3 * r + c) * h_step(hstride)];
-}
-
 struct PriorView {
   int n;                 // priors on this rank's rows
   const int* row;        // local row, ascending
@@ -202,10 +202,78 @@ GS_HD void diag_pieces(const Sym3& O, const Mat3& Ar, const double e[3], double 
 }
 
 GS_HD void store_block(double* Ho, size_t hstride, int pos, const double M[9]) {
+#if GS_H_LAYOUT == 2
+  (void)hstride;
+  double* g = Ho + (size_t)(pos >> 5) * (9 * kSlice);
+  const int l = pos & 31;
+  double2* g2 = reinterpret_cast<double2*>(g);
+#pragma unroll
+  for (int m = 0; m < 4; ++m) g2[m * kSlice + l] = make_double2(M[2 * m], M[2 * m + 1]);
+  g[8 * kSlice + l] = M[8];
+#else
   double* hp = Ho + h_base(pos);
   const size_t st = h_step(hstride);
 #pragma unroll
   for (int k = 0; k < 9; ++k) hp[(size_t)k * st] = M[k];
+#endif
+}
+
+GS_HD void load_block(const double* Ho, size_t hstride, int pos, double h[9]) {
+#if GS_H_LAYOUT == 2
+  (void)hstride;
+  const double* g = Ho + (size_t)(pos >> 5) * (9 * kSlice);
+  const int l = pos & 31;
+  const double2* g2 = reinterpret_cast<const double2*>(g);
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    const double2 v = ldg(g2 + m * kSlice + l);
+    h[2 * m] = v.x;
+    h[2 * m + 1] = v.y;
+  }
+  h[8] = ldg(g + 8 * kSlice + l);
+#else
+  const double* hp = Ho + h_base(pos);
+  const size_t st = h_step(hstride);
+#pragma unroll
+  for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * st);
+#endif
+}
+
+// The same block as the row that uses it needs it: transposed when `tr` (the hi row of the pair reads the lo row's
+// canonical block).  The transposition is taken in the ADDRESSES (entries 1<->3, 2<->6, 5<->7 swap), not by selecting
+// between loaded values: the nine loads are independent of each other and of the arithmetic, so they all go out
+// before the first use instead of in four dependent groups (the selects forced register reuse between groups).
+GS_HD void load_block_as(const double* Ho, size_t hstride, int pos, bool tr, double a[9]) {
+#if GS_H_LAYOUT == 2
+  double h[9];
+  load_block(Ho, hstride, pos, h);
+  a[0] = h[0]; a[4] = h[4]; a[8] = h[8];
+  a[1] = tr ? h[3] : h[1]; a[3] = tr ? h[1] : h[3];
+  a[2] = tr ? h[6] : h[2]; a[6] = tr ? h[2] : h[6];
+  a[5] = tr ? h[7] : h[5]; a[7] = tr ? h[5] : h[7];
+#else
+  const double* hp = Ho + h_base(pos);
+  const size_t st = h_step(hstride);
+  const size_t s1 = tr ? 3 * st : st, s3 = tr ? st : 3 * st;
+  const size_t s2 = tr ? 6 * st : 2 * st, s6 = tr ? 2 * st : 6 * st;
+  const size_t s5 = tr ? 7 * st : 5 * st, s7 = tr ? 5 * st : 7 * st;
+  a[0] = ldg(hp);
+  a[1] = ldg(hp + s1);
+  a[2] = ldg(hp + s2);
+  a[3] = ldg(hp + s3);
+  a[4] = ldg(hp + 4 * st);
+  a[5] = ldg(hp + s5);
+  a[6] = ldg(hp + s6);
+  a[7] = ldg(hp + s7);
+  a[8] = ldg(hp + 8 * st);
+#endif
+}
+
+// entry (r, c) of the stored block cell `pos` of a host copy of Ho, optionally transposed
+inline double h_entry(const double* Ho, size_t hstride, int pos, int r, int c, bool tr) {
+  double h[9];
+  load_block(Ho, hstride, pos, h);
+  return h[tr ? 3 * c + r : 3 * r + c];
 }
 
 // One factor side under GTSAM's default Jacobians (A_i = [[-c,-s,dt1],[s,-c,dt2],[0,0,-1]], A_j = I):
@@ -438,13 +506,11 @@ struct SpmvView {
   int n_own;
 };
 
-// one neighbour block: y += H_rc p_c, with the stored block used transposed when `tr`
-GS_HD void spmv_slot(const double h[9], double px, double py, double pz, bool tr, double& y0, double& y1, double& y2) {
-  const double a01 = tr ? h[3] : h[1], a02 = tr ? h[6] : h[2], a10 = tr ? h[1] : h[3];
-  const double a12 = tr ? h[7] : h[5], a20 = tr ? h[2] : h[6], a21 = tr ? h[5] : h[7];
-  y0 += (h[0] * px + a01 * py) + a02 * pz;
-  y1 += (a10 * px + h[4] * py) + a12 * pz;
-  y2 += (a20 * px + a21 * py) + h[8] * pz;
+// one neighbour block: y += A p_c, A = the block as this row uses it (load_block_as), row-major
+GS_HD void spmv_slot(const double a[9], double px, double py, double pz, double& y0, double& y1, double& y2) {
+  y0 += (a[0] * px + a[1] * py) + a[2] * pz;
+  y1 += (a[3] * px + a[4] * py) + a[5] * pz;
+  y2 += (a[6] * px + a[7] * py) + a[8] * pz;
 }
 
 // diagonal block, damping, store, and the row's share of p.y ; d = (00 01 02 11 12 22), l = damping per component
@@ -472,6 +538,12 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
   double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+  const size_t n = (size_t)a.n_own, rr = (size_t)r;
+  double d[6], l[3] = {lambda, lambda, lambda};
+#if GS_SPMV_PRELOAD
+#pragma unroll
+  for (int k = 0; k < 6; ++k) d[k] = ldg(a.Hd + (size_t)k * n + rr);
+#endif
   // w is uniform over the slice; the next slot's reference is fetched while this slot's block and
   // p are in flight, so a slot costs one dependent round trip
   int2 nref = w > 0 ? ldg(a.refs + base) : make_int2(-1, 0);
@@ -479,11 +551,8 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
     const int2 ref = nref;
     if (s + 1 < w) nref = ldg(a.refs + base + (s + 1) * kSlice);
     if (ref.x >= 0) {
-      const double* hp = a.Ho + h_base(ref.y >> 1);
-      const size_t hst = h_step(a.hstride);
       double h[9];
-#pragma unroll
-      for (int k = 0; k < 9; ++k) h[k] = ldg(hp + (size_t)k * hst);
+      load_block_as(a.Ho, a.hstride, ref.y >> 1, ref.y & 1, h);
       double px, py, pz;
       if (DIR) {
         const bool ghost = ref.x >= a.n_own;
@@ -499,13 +568,13 @@ GS_HD double spmv_row_t(const SpmvView& a, const double* p, const double* pg, co
         py = pc[1];
         pz = pc[2];
       }
-      spmv_slot(h, px, py, pz, ref.y & 1, y0, y1, y2);
+      spmv_slot(h, px, py, pz, y0, y1, y2);
     }
   }
-  const size_t n = (size_t)a.n_own, rr = (size_t)r;
-  double d[6], l[3] = {lambda, lambda, lambda};
+#if !GS_SPMV_PRELOAD
 #pragma unroll
   for (int k = 0; k < 6; ++k) d[k] = ldg(a.Hd + (size_t)k * n + rr);
+#endif
   if (a.dscale) {
     l[0] *= a.dscale[3 * rr];
     l[1] *= a.dscale[3 * rr + 1];

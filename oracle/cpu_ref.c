@@ -14,9 +14,11 @@
  *   graph.cpp:119           LevenbergMarquardtOptimizer(graph, initial).optimize()   gs_cpu_optimize()
  *   graph.cpp:122-125       x(), y(), theta()             theta = atan2(s, c)
  *
- * Linear solve: block-Jacobi PCG on the 3x3-block CSR normal equations (the same algorithm the CUDA
- * path runs, so iteration counts are comparable), all host threads via OpenMP.  GTSAM itself uses a
- * multifrontal Cholesky; gs_oracle.py plays that role (exact solve) for parity.
+ * Linear solve, two variants (cpu_params.solver):
+ *   0  block-Jacobi PCG on the 3x3-block CSR normal equations (the same algorithm the CUDA path runs, so iteration
+ *      counts are comparable), all host threads via OpenMP;
+ *   1  sparse multifrontal Cholesky with a nested-dissection ordering (oracle/cpu_chol.c): what GTSAM's default
+ *      MULTIFRONTAL_CHOLESKY does behind graph.cpp:119, and an exact solve written independently of gs_oracle.py.
  */
 #include <math.h>
 #include <stdint.h>
@@ -26,6 +28,7 @@
 #ifdef _OPENMP
 #include <omp.h>
 #endif
+#include "cpu_chol.h"
 
 typedef struct {
   int max_iterations;
@@ -35,6 +38,9 @@ typedef struct {
   double pcg_rel_tol;
   int pcg_max_iters;
   int pcg_iter_cap_total; /* >0: stop after this many PCG iterations in total (bounded timing sample) */
+  double pcg_time_cap_ms; /* >0: a PCG solve gives up after this much wall time (bounded timing sample) */
+  int solver;             /* 0: block-Jacobi PCG (the CUDA path's algorithm); 1: sparse multifrontal Cholesky (what the
+                             reference's GTSAM call does, graph.cpp:119; oracle/cpu_chol.c) */
 } cpu_params;
 
 typedef struct {
@@ -43,6 +49,9 @@ typedef struct {
   int64_t pcg_iterations_total;
   double ms_structure, ms_linearize, ms_solve, ms_update, ms_total;
   int threads;
+  double ms_analyze, ms_factor;     /* solver 1: ordering + symbolic (once), numeric factorisations (summed) */
+  double chol_nnz, chol_flops;      /* solver 1: entries of L, flops of one factorisation */
+  int capped;                       /* 1: a PCG cap (iterations or time) ended the run before the tolerance */
 } cpu_stats;
 
 static double now_ms(void) {
@@ -71,6 +80,15 @@ int gs_cpu_threads(void) {
   return omp_get_max_threads();
 #else
   return 1;
+#endif
+}
+
+/* explicit thread count (torchrun exports OMP_NUM_THREADS=1 to its children; a timed baseline must not inherit that) */
+void gs_cpu_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
 #endif
 }
 
@@ -330,8 +348,9 @@ static void build_minv(const problem* P, double lambda, const double* dscale, do
 
 /* block-Jacobi PCG for (H + lambda D) x = -b ; returns iterations, -1 on breakdown */
 static int pcg(const problem* P, double lambda, const double* dscale, const double* M, double* x, double* r, double* z,
-               double* p, double* Ap, double tol, int max_iters, double* relres) {
+               double* p, double* Ap, double tol, int max_iters, double time_cap_ms, double* relres) {
   const int n = P->n;
+  const double t_start = now_ms();
   double rz = 0, rr0 = 0;
 #pragma omp parallel for reduction(+ : rz, rr0) schedule(static)
   for (int v = 0; v < n; ++v) {
@@ -369,6 +388,7 @@ static int pcg(const problem* P, double lambda, const double* dscale, const doub
     }
     ++it;
     if (rr <= tol * tol * rr0) break;
+    if (time_cap_ms > 0.0 && (it & 15) == 0 && now_ms() - t_start > time_cap_ms) break;
     const double beta = rzn / rz;
     rz = rzn;
 #pragma omp parallel for schedule(static)
@@ -412,6 +432,13 @@ int gs_cpu_optimize(int n, int e, const int* ei, const int* ej, const double* z,
   memset(&S, 0, sizeof S);
   S.threads = gs_cpu_threads();
   S.ms_structure = now_ms() - t_begin;
+  chol* CH = 0;
+  if (p->solver == 1) {
+    const double ta = now_ms();
+    CH = chol_analyze(n, G.rowptr, G.colidx);
+    S.ms_analyze = now_ms() - ta;
+    chol_info(CH, &S.chol_nnz, &S.chol_flops, 0, 0);
+  }
   const size_t n3 = 3 * (size_t)n;
   double* pose = (double*)malloc(sizeof(double) * 4 * (size_t)n);
   double* cand = (double*)malloc(sizeof(double) * 4 * (size_t)n);
@@ -448,14 +475,27 @@ int gs_cpu_optimize(int n, int e, const int* ei, const int* ej, const double* z,
       ++tries;
       S.inner_iterations++;
       t0 = now_ms();
-      build_minv(&G, lambda, ds, M);
-      double relres;
-      int max_it = p->pcg_max_iters;
-      if (p->pcg_iter_cap_total > 0) {
-        const int64_t left = (int64_t)p->pcg_iter_cap_total - S.pcg_iterations_total;
-        if (left < max_it) max_it = (int)(left > 0 ? left : 0);
+      double relres = 0.0;
+      int it;
+      if (CH) {   /* exact solve: (H + lambda D) x = -b */
+        const int bad = chol_factor(CH, G.H, G.diag, lambda, ds);
+        S.ms_factor += now_ms() - t0;
+        if (!bad) {
+#pragma omp parallel for schedule(static)
+          for (size_t i = 0; i < n3; ++i) r[i] = -G.b[i];
+          chol_solve(CH, r, x);
+        }
+        it = bad ? -1 : 0;
+      } else {
+        build_minv(&G, lambda, ds, M);
+        int max_it = p->pcg_max_iters;
+        if (p->pcg_iter_cap_total > 0) {
+          const int64_t left = (int64_t)p->pcg_iter_cap_total - S.pcg_iterations_total;
+          if (left < max_it) max_it = (int)(left > 0 ? left : 0);
+        }
+        it = pcg(&G, lambda, ds, M, x, r, zv, pv, Ap, p->pcg_rel_tol, max_it, p->pcg_time_cap_ms, &relres);
+        if (p->pcg_time_cap_ms > 0.0 && relres > p->pcg_rel_tol) capped = 1;
       }
-      int it = pcg(&G, lambda, ds, M, x, r, zv, pv, Ap, p->pcg_rel_tol, max_it, &relres);
       S.ms_solve += now_ms() - t0;
       const int solved = it >= 0;
       if (it < 0) it = 0;
@@ -522,11 +562,13 @@ int gs_cpu_optimize(int n, int e, const int* ei, const int* ej, const double* z,
     poses_xyt[3 * (size_t)v + 2] = atan2(pose[4 * (size_t)v + 3], pose[4 * (size_t)v + 2]);
   }
   S.iterations = iterations;
+  S.capped = capped;
   S.chi2_final = 2 * error;
   S.lambda_final = lambda;
   S.ms_total = now_ms() - t_begin;
   if (st) *st = S;
   free(pose); free(cand); free(buf);
+  chol_free(CH);
   destroy(&G);
   return rc;
 }

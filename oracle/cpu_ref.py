@@ -17,14 +17,18 @@ class CpuParams(C.Structure):
                 ("error_tol", C.c_double), ("lambda_initial", C.c_double), ("lambda_factor", C.c_double),
                 ("lambda_upper", C.c_double), ("lambda_lower", C.c_double), ("min_model_fidelity", C.c_double),
                 ("diagonal_damping", C.c_int), ("jacobian_mode", C.c_int), ("pcg_rel_tol", C.c_double),
-                ("pcg_max_iters", C.c_int), ("pcg_iter_cap_total", C.c_int)]
+                ("pcg_max_iters", C.c_int), ("pcg_iter_cap_total", C.c_int), ("pcg_time_cap_ms", C.c_double),
+                ("solver", C.c_int)]
+
+SOLVER_PCG, SOLVER_CHOLESKY = 0, 1
 
 
 class CpuStats(C.Structure):
     _fields_ = [("iterations", C.c_int), ("outer_loops", C.c_int), ("inner_iterations", C.c_int), ("converged", C.c_int),
                 ("chi2_initial", C.c_double), ("chi2_final", C.c_double), ("lambda_final", C.c_double),
                 ("pcg_iterations_total", C.c_int64), ("ms_structure", C.c_double), ("ms_linearize", C.c_double),
-                ("ms_solve", C.c_double), ("ms_update", C.c_double), ("ms_total", C.c_double), ("threads", C.c_int)]
+                ("ms_solve", C.c_double), ("ms_update", C.c_double), ("ms_total", C.c_double), ("threads", C.c_int),
+                ("ms_analyze", C.c_double), ("ms_factor", C.c_double), ("chol_nnz", C.c_double), ("chol_flops", C.c_double), ("capped", C.c_int)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -55,24 +59,40 @@ def _host_tag() -> str:
 def load():
     global _lib
     if _lib is None:
-        src = os.path.join(HERE, "cpu_ref.c")
+        srcs = [os.path.join(HERE, f) for f in ("cpu_ref.c", "cpu_chol.c", "cpu_chol.h")]
         tag = _host_tag()
         try:
             same_host = open(HOST_TAG).read() == tag
         except OSError:
             same_host = False
-        if not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src) or not same_host:
+        if not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(f) for f in srcs) or not same_host:
             subprocess.run(["make", "-s", "-B", "-C", HERE, "_build/libgs_cpu_ref.so"], check=True)
             with open(HOST_TAG, "w") as f:
                 f.write(tag)
         _lib = C.CDLL(LIB)
         _lib.gs_cpu_default_params.argtypes = [C.POINTER(CpuParams)]
         _lib.gs_cpu_threads.restype = C.c_int
+        _lib.gs_cpu_set_threads.argtypes = [C.c_int]
         dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
         _lib.gs_cpu_optimize.restype = C.c_int
         _lib.gs_cpu_optimize.argtypes = [C.c_int, C.c_int, ip, ip, dp, dp, C.c_int, ip, dp, dp, dp, C.POINTER(CpuParams),
                                          C.POINTER(CpuStats), dp, ip, C.c_int]
     return _lib
+
+
+def host_cores() -> int:
+    """Cores this process may run on (what a timed CPU baseline should use)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def set_threads(n: int | None = None) -> int:
+    """Set the OpenMP thread count explicitly (torchrun exports OMP_NUM_THREADS=1 to its children); returns it."""
+    lib = load()
+    lib.gs_cpu_set_threads(int(n or host_cores()))
+    return int(lib.gs_cpu_threads())
 
 
 def optimize(g, init=None, **overrides):

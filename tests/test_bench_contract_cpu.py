@@ -27,6 +27,10 @@ def test_reference_arm_prints_one_json_line_with_the_contract_keys():
     assert "workload" in d["config"] and "model" not in d["config"]
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    # both CPU variants are there: real Cholesky steps and the PCG variant beside them; the line's value is the faster one's
+    assert cb["variant"] in ("cholesky", "pcg") and cb["cholesky"]["sec_per_step"] > 0 and cb["pcg"]["ms_per_pcg_iteration"] > 0
+    assert d["steps_measured"] == 1 and len(d["pose_sha256"]) == 64 and float(d["chi2_final"]) > 0
+    assert set(d["config"]) == {"workload", "n_poses", "n_factors", "pcg_rel_tol", "step"}
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 
@@ -35,12 +39,12 @@ def test_reference_arm_other_ranks_exit_quietly():
     assert res.returncode == 0 and res.stdout.strip() == ""
 
 
-def test_recorded_iteration_counts_cover_the_benchmark_steps():
-    """The reference arm scales its bounded sample to the PCG iteration counts recorded for the very LM steps our arm
-    times (default --warmup 3 --steps 3 on C3): the record must hold them."""
-    rec = json.load(open(os.path.join(ROOT, "profiles", "pcg_iters.json")))
-    per_step = rec["C3-grid1M:1000000"]
-    assert isinstance(per_step, list) and len(per_step) >= 6 and all(isinstance(v, int) and v > 1000 for v in per_step)
+def test_reference_arm_sets_its_thread_count_itself():
+    """torchrun exports OMP_NUM_THREADS=1 to its children; the CPU arm must not inherit that."""
+    res = _run("--impl", "reference", "--steps", "1", "--warmup", "0", "--n", "6000", "--no-cpu-pcg", env={"OMP_NUM_THREADS": "1"})
+    assert res.returncode == 0, res.stderr[-2000:]
+    d = json.loads(res.stdout.strip().splitlines()[-1])
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
 
 
 def test_our_arm_needs_a_cuda_device():

@@ -35,41 +35,39 @@ def dead_reckon(last_pose, z_odo):
     return out
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--n0", type=int, default=10_000)
-    ap.add_argument("--batch", type=int, default=100)
-    ap.add_argument("--updates", type=int, default=400)
-    ap.add_argument("--cpu-updates", type=int, default=3, help="updates re-run on the CPU port (0 = skip)")
-    args = ap.parse_args()
-
+def run(n0=10_000, batch=100, updates=400, cpu_updates=3, verbose=True):
+    """The C5 sequence from n0 poses on; returns the result dict (see the module docstring)."""
     g = synth.config("C5")
-    n_final = args.n0 + args.batch * args.updates
+    n_final = n0 + batch * updates
     assert n_final <= g.n, "C5 has 50,000 poses"
     k1, k2 = g.k1.astype(np.int64), g.k2.astype(np.int64)
     arrival = np.maximum(k1, k2)
     is_odo = (k2 == k1 + 1)
 
     G = graph.Graph()
-    G.add_graph(g.prefix(args.n0))
+    G.add_graph(g.prefix(n0))
     t0 = time.perf_counter()
     st0 = G.optimize()
     t_first = time.perf_counter() - t0
-    print(f"[c5] initial solve of {args.n0} poses: {t_first * 1e3:.1f} ms, {st0['iterations']} LM iterations, "
-          f"{st0['pcg_iterations_total']} PCG iterations, chi2 {st0['chi2_initial']:.5g} -> {st0['chi2_final']:.5g}",
-          file=sys.stderr, flush=True)
+    if verbose:
+        print(f"[c5] initial solve of {n0} poses: {t_first * 1e3:.1f} ms, {st0['iterations']} LM iterations, "
+              f"{st0['pcg_iterations_total']} PCG iterations, chi2 {st0['chi2_initial']:.5g} -> {st0['chi2_final']:.5g}",
+              file=sys.stderr, flush=True)
 
     lat, ms_struct, ms_solve, lm_its, pcg_its, chi2 = [], [], [], [], [], []
     cpu_cases = []
-    cpu_at = set(np.linspace(0, args.updates - 1, args.cpu_updates).astype(int).tolist()) if args.cpu_updates else set()
-    for u in range(args.updates):
-        lo, hi = args.n0 + u * args.batch, args.n0 + (u + 1) * args.batch
+    cpu_at = set(np.linspace(0, updates - 1, cpu_updates).astype(int).tolist()) if cpu_updates else set()
+    for u in range(updates):
+        lo, hi = n0 + u * batch, n0 + (u + 1) * batch
         m = (arrival > lo) & (arrival <= hi)
         # odometry measurement into each new keyframe (first one in arrival order)
-        zo = np.zeros((args.batch, 3))
+        zo = np.zeros((batch, 3))
         mo = np.flatnonzero(m & is_odo)
         zo[k2[mo] - lo - 1] = g.z[mo]
         keys = g.keys[lo:hi]
+        x_before = None
+        if u in cpu_at:
+            _, x_before = G.poses()
         t0 = time.perf_counter()
         last = G.pose(int(g.keys[lo - 1]))
         poses = dead_reckon(last, zo)
@@ -84,10 +82,9 @@ def main():
         pcg_its.append(st["pcg_iterations_total"])
         chi2.append(st["chi2_final"])
         if u in cpu_at:
-            _, x_now = G.poses()
-            cpu_cases.append((hi, x_now.copy(), poses.copy(), lo))
-        if (u + 1) % 50 == 0:
-            print(f"[c5] update {u + 1}/{args.updates}: N={hi} latency {dt * 1e3:.1f} ms ({st['iterations']} LM, "
+            cpu_cases.append((hi, x_before.copy(), poses.copy(), lo))
+        if verbose and (u + 1) % 50 == 0:
+            print(f"[c5] update {u + 1}/{updates}: N={hi} latency {dt * 1e3:.1f} ms ({st['iterations']} LM, "
                   f"{st['pcg_iterations_total']} PCG, structure {st['ms_structure']:.1f} ms) newest pose {newest}",
                   file=sys.stderr, flush=True)
     G.close()
@@ -95,32 +92,51 @@ def main():
     cpu = None
     if cpu_cases:
         from oracle import cpu_ref   # the checker / CPU baseline, never on the product path
+        threads = cpu_ref.set_threads()
         cpu_ref.optimize(synth.config("C3", n=20000), max_iterations=1, pcg_iter_cap_total=20)   # thread pool warm-up
-        ms = []
-        for hi, x_after, poses_new, lo in cpu_cases:
+        res = {"cholesky": [], "pcg": []}
+        for hi, x_before, poses_new, lo in cpu_cases:
             sub = g.prefix(hi)
-            # warm start as the GPU run had it: previous optimum for the old poses is approximated by the
-            # optimum after the update (the CPU gets an easier start than the GPU did), new poses dead-reckoned
-            init = x_after.copy()
+            init = np.zeros((hi, 3))           # the same start the GPU update had: previous optimum + dead-reckoned batch
+            init[:lo] = x_before[:lo]
             init[lo:hi] = poses_new
-            t0 = time.perf_counter()
-            _, st, _, _ = cpu_ref.optimize(sub, init=init, pcg_rel_tol=1e-12)
-            ms.append((time.perf_counter() - t0) * 1e3)
-            threads = int(st["threads"])
-        cpu = dict(kind="port", cores=threads, updates=len(ms), sizes=[c[0] for c in cpu_cases], latency_ms=ms,
-                   mean_ms=float(np.mean(ms)))
+            for name, solver in (("cholesky", 1), ("pcg", 0)):
+                t0 = time.perf_counter()
+                cpu_ref.optimize(sub, init=init, pcg_rel_tol=1e-12, solver=solver)
+                res[name].append((time.perf_counter() - t0) * 1e3)
+        cpu = dict(kind="port", cores=threads, updates=len(cpu_cases), sizes=[c[0] for c in cpu_cases],
+                   latency_ms_cholesky=res["cholesky"], latency_ms_pcg=res["pcg"],
+                   mean_ms=float(min(np.mean(res["cholesky"]), np.mean(res["pcg"]))),
+                   variant="cholesky" if np.mean(res["cholesky"]) <= np.mean(res["pcg"]) else "pcg",
+                   note="full solve() of the same update (structure, ordering and LM to GTSAM's stopping rule) from the "
+                        "same start the GPU update had")
 
     lat = np.array(lat)
-    out = dict(metric="incremental_update_latency", unit="ms", higher_is_better=False,
-               config=dict(workload="C5-incremental: 224-wide lawn-mower SE(2) graph growing %d -> %d poses in %d batches of "
-                                    "%d keyframes, full re-optimisation per batch, warm start" %
-                                    (args.n0, n_final, args.updates, args.batch)),
-               p50=float(np.percentile(lat, 50)), p99=float(np.percentile(lat, 99)), mean=float(lat.mean()),
-               max=float(lat.max()), first_solve_ms=t_first * 1e3,
-               mean_structure_ms=float(np.mean(ms_struct)), mean_solve_ms=float(np.mean(ms_solve)),
-               mean_lm_iterations=float(np.mean(lm_its)), mean_pcg_iterations=float(np.mean(pcg_its)),
-               final_chi2=chi2[-1], n_final=n_final, cpu_baseline=cpu, dtype="f64", data="synthetic")
-    print(json.dumps(out))
+    return dict(metric="incremental_update_latency", unit="ms", higher_is_better=False,
+                config=dict(workload="C5-incremental: 224-wide lawn-mower SE(2) graph growing %d -> %d poses in %d batches of "
+                                     "%d keyframes, full re-optimisation per batch, warm start" %
+                                     (n0, n_final, updates, batch)),
+                p50=float(np.percentile(lat, 50)), p99=float(np.percentile(lat, 99)), mean=float(lat.mean()),
+                max=float(lat.max()), first_solve_ms=t_first * 1e3,
+                mean_structure_ms=float(np.mean(ms_struct)), mean_solve_ms=float(np.mean(ms_solve)),
+                mean_lm_iterations=float(np.mean(lm_its)), mean_pcg_iterations=float(np.mean(pcg_its)),
+                final_chi2=chi2[-1], n_final=n_final, cpu_baseline=cpu, dtype="f64", data="synthetic")
+
+
+def main_from_bench(args):
+    """`python bench.py --config C5`: the full C5 sequence (400 updates) as one JSON line."""
+    out = run(updates=400, cpu_updates=0 if args.no_cpu_baseline else 3)
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n0", type=int, default=10_000)
+    ap.add_argument("--batch", type=int, default=100)
+    ap.add_argument("--updates", type=int, default=400)
+    ap.add_argument("--cpu-updates", type=int, default=3, help="updates re-run on the CPU port (0 = skip)")
+    args = ap.parse_args()
+    print(json.dumps(run(args.n0, args.batch, args.updates, args.cpu_updates)))
 
 
 if __name__ == "__main__":

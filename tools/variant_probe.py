@@ -1,22 +1,24 @@
-"""Short GPU probe of switchable kernel variants (today: GS_UPDATE_STAGED, see csrc/kernels.cuh; the variants that
-lost — evict-first / no-L1 loads of H, alternating sweep direction, evict-first H stores and cp.async slot prefetch
-in assembly — are in git history (commits 2bad73e, 2a75c8b) and their numbers in profiles/r1_v7_variant_probe.jsonl).
-For each combination, on one config (default C3):
+"""Short GPU probe of kernel variants: compile-time variants of the library (storage layouts, built by
+graphslam_b200.build.build_variant into lib/variants/) x run-time execution paths (gs_params.solver_flags, including
+the GS_X_* experiment bits of include/graphslam_cuda_debug.h).  For each combination, on one config:
 
   * CUDA-event time of every kernel inside the real sequence (gs_profile_pcg / gs_profile_outer),
   * wall time per PCG iteration of a capped solve replayed from the captured CUDA graph (how gs_optimize runs it),
   * SHA-1 of the solve's delta: every variant must reproduce the default path's bits,
 
-and the same bit check on a small ragged graph (odd number of rows in the last tile, three-kernel path forced).
-Results are appended line by line to gpurun_out/variant_probe.jsonl, so a cut-off run still leaves what it
-measured.  No torch import: the library is driven through ctypes only.
+and the same bit check on a small ragged graph (odd number of rows in the last tile, persistent kernel off).
+Each library variant runs in its own child process (the ctypes handle is per process; GS_LIB points the Python
+harness at the variant).  Results are appended line by line to gpurun_out/variant_probe.jsonl, so a cut-off run
+still leaves what it measured.  No torch import: the library is driven through ctypes only.
 
-  python tools/variant_probe.py [n_poses] [capped_iters] [only: comma-separated variant names] [config]
+  python tools/variant_probe.py build                       # here (no GPU): compile the variant libraries
+  python tools/variant_probe.py run [config] [n_poses] [capped_iters] [libs: a,b,..] [flagsets: x,y,..]
 """
 import ctypes as C
 import hashlib
 import json
 import os
+import subprocess
 import sys
 import time
 
@@ -24,15 +26,26 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from graphslam_b200 import _lib, graph, synth  # noqa: E402
 
-FLAGS = ("GS_UPDATE_STAGED", "GS_ASM_NODUP")
-VARIANTS = [
-    ("default", {}),
-    ("unstaged", {"GS_UPDATE_STAGED": "0"}),
-    ("asm_nodup", {"GS_ASM_NODUP": "1"}),       # round-2 candidate: k_assemble_nodup, three CTAs per SM
-    ("default again", {}),
-]
+LIBS = {                       # name -> -D switches ([] = the in-tree default library)
+    "default": [],
+    "spmv_minb4": ["GS_SPMV_MINB=4"],
+    "spmv_minb6": ["GS_SPMV_MINB=6"],
+    "pre_minb4": ["GS_SPMV_PRELOAD=1", "GS_SPMV_MINB=4"],
+    "pre_minb5": ["GS_SPMV_PRELOAD=1", "GS_SPMV_MINB=5"],
+    "upd_nohoist": ["GS_UPD_HOIST=0"],
+    "upd_minb5": ["GS_UPD_MINB=5"],
+    "h2": ["GS_H_LAYOUT=2"],
+    "dir_minb5": ["GS_SPMVDIR_MINB=5"],
+    "dir_minb3": ["GS_SPMVDIR_MINB=3"],
+}
+NP, DIRK, OTF = 4, 8, 16
+X_NODUP, X_UNSTAGED = 1 << 16, 1 << 18
+FLAGSETS = {                   # name -> solver_flags (persistent kernel off everywhere: the probe is about the big-graph path)
+    "three": NP | DIRK,
+    "otf": NP | OTF,
+    "nodup": NP | DIRK | X_NODUP,
+}
 OUT = os.path.join(ROOT, "gpurun_out", "variant_probe.jsonl")
 
 
@@ -43,14 +56,14 @@ def emit(rec):
     print(json.dumps(rec), flush=True)
 
 
-def set_env(env):
-    for k in FLAGS:
-        os.environ.pop(k, None)
-    os.environ.update(env)
+def lib_file(name):
+    from graphslam_b200 import build
+    return build.LIB if not LIBS[name] else os.path.join(build.LIBDIR, "variants", f"libgraphslam_cuda_{name}.so")
 
 
 def capped_solve(G, lam):
     """gs_solve_linear with the iteration cap hit on purpose: (delta, iterations, seconds)."""
+    from graphslam_b200 import _lib
     lib = _lib.load()
     d = np.zeros((G.num_vertices, 3))
     it, rr = C.c_int(), C.c_double()
@@ -62,11 +75,10 @@ def capped_solve(G, lam):
     return d, it.value, dt
 
 
-def run(g, name, env, iters, extra_env=None, profile=True):
-    set_env(env)
-    os.environ.update(extra_env or {})
-    rec = {"variant": name, "n": int(g.n), "env": env}
-    with graph.Graph(pcg_max_iters=iters, pcg_rel_tol=1e-300) as G:
+def run(g, libname, fname, iters, profile=True):
+    from graphslam_b200 import graph
+    rec = {"lib": libname, "flags": fname, "graph": g.name, "n": int(g.n)}
+    with graph.Graph(pcg_max_iters=iters, pcg_rel_tol=1e-300, solver_flags=FLAGSETS[fname]) as G:
         G.add_graph(g)
         G.prepare()
         if profile:
@@ -78,27 +90,58 @@ def run(g, name, env, iters, extra_env=None, profile=True):
         d, it, dt = capped_solve(G, 1e-5)
         rec["capped_solve"] = {"iterations": it, "us_per_iteration_wall": round(dt / max(it, 1) * 1e6, 2)}
         rec["sha1"] = hashlib.sha1(d.tobytes()).hexdigest()
-    for k in (extra_env or {}):
-        os.environ.pop(k, None)
+        _, _, blocks, b, chi2 = G.system() if g.n <= 50000 else (0, 0, np.zeros(1), np.zeros(1), 0.0)
+        rec["sha1_system"] = hashlib.sha1(blocks.tobytes() + b.tobytes()).hexdigest()
     emit(rec)
     return rec
 
 
-def main():
-    n = int(sys.argv[1]) if len(sys.argv) > 1 and int(sys.argv[1]) > 0 else None
-    iters = int(sys.argv[2]) if len(sys.argv) > 2 else 640
-    only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
-    variants = [v for v in VARIANTS if only is None or v[0] in only]
+def child(cid, n, iters, libname, fnames):
+    from graphslam_b200 import synth
     t0 = time.time()
-    # small ragged graph first (cheap): 4001 rows = 15 full tiles + 161 rows; three-kernel path forced
-    gs_ = synth.config("C3", n=4001)
-    small = [run(gs_, name, env, 96, {"GS_PCG_FUSED": "0"}, profile=False) for name, env in variants if name != "default again"]
-    emit({"check": "small ragged graph bits", "equal": len({r["sha1"] for r in small}) == 1})
-    cid = sys.argv[4] if len(sys.argv) > 4 else "C3"
+    small = synth.config("C3", n=4001)              # 15 full tiles + 161 rows
+    for f in fnames:
+        run(small, libname, f, 96, profile=False)
     g = synth.config(cid, n=n)
-    emit({"generated": g.name, "n": int(g.n), "e": int(g.e), "s": round(time.time() - t0, 1)})
-    big = [run(g, name, env, iters) for name, env in variants]
-    emit({"check": "C3 bits", "equal": len({r["sha1"] for r in big}) == 1, "total_s": round(time.time() - t0, 1)})
+    emit({"lib": libname, "generated": g.name, "n": int(g.n), "e": int(g.e), "s": round(time.time() - t0, 1)})
+    for f in fnames:
+        run(g, libname, f, iters)
+
+
+def main():
+    mode = sys.argv[1] if len(sys.argv) > 1 else "run"
+    if mode == "build":
+        from graphslam_b200 import build
+        build.build()
+        for name, defs in LIBS.items():
+            if defs:
+                print(build.build_variant(name, defs), flush=True)
+        return
+    if mode == "child":
+        cid, n, iters, libname = sys.argv[2], int(sys.argv[3]) or None, int(sys.argv[4]), sys.argv[5]
+        child(cid, n, iters, libname, sys.argv[6].split(","))
+        return
+    cid = sys.argv[2] if len(sys.argv) > 2 else "C3"
+    n = sys.argv[3] if len(sys.argv) > 3 else "0"
+    iters = sys.argv[4] if len(sys.argv) > 4 else "320"
+    libs = sys.argv[5].split(",") if len(sys.argv) > 5 else list(LIBS)
+    fsets = sys.argv[6] if len(sys.argv) > 6 else ",".join(FLAGSETS)
+    for name in libs:
+        path = lib_file(name)
+        if not os.path.exists(path):
+            emit({"lib": name, "error": f"{path} missing: run `python tools/variant_probe.py build` first"})
+            continue
+        env = dict(os.environ, GS_LIB=path)
+        res = subprocess.run([sys.executable, os.path.abspath(__file__), "child", cid, n, iters, name, fsets], env=env,
+                             capture_output=True, text=True, timeout=600)
+        if res.returncode != 0:
+            emit({"lib": name, "error": res.stderr[-1500:]})
+    # bit checks over everything recorded for this config in this run
+    recs = [json.loads(l) for l in open(OUT)] if os.path.exists(OUT) else []
+    for key in sorted({(r["graph"], r["n"]) for r in recs if "sha1" in r}):
+        rs = [r for r in recs if (r.get("graph"), r.get("n")) == key and "sha1" in r]
+        emit({"check": f"bits on {key[0]} n={key[1]}", "variants": len(rs), "solve_equal": len({r["sha1"] for r in rs}) == 1,
+              "system_equal": len({r["sha1_system"] for r in rs}) == 1})
 
 
 if __name__ == "__main__":
