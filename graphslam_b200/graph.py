@@ -336,8 +336,10 @@ class GraphNode:
     def new_factor(self, registration):
         self.keyframe_ids += 1                                    # graph.cpp:68
         f = registration["factor_new"]
-        last = self.keyframes[-1]
-        pose_new = self._compose(last["pose_opti"], f["delta"])   # graph.cpp:71
+        # graph.cpp:72 composes from input.keyframe_last.pose_opti — what the scanner obtained from the last_keyframe
+        # service (graph.cpp:134-144) before publishing; a message without it falls back to the node's own last keyframe
+        last = registration.get("keyframe_last") or self.keyframes[-1]
+        pose_new = self._compose(last["pose_opti"], f["delta"])   # graph.cpp:72
         self.keyframes.append(dict(id=self.keyframe_ids, pose_opti=pose_new.copy()))
         self.graph.add_vertex(self.keyframe_ids, pose_new)        # graph.cpp:86
         self.graph.add_between(f["id_1"], self.keyframe_ids, f["delta"], f["covariance"])   # graph.cpp:87-92
@@ -367,6 +369,11 @@ class GraphNode:
 
     def last_keyframe(self):
         return self.keyframes[-1] if self.keyframes else None     # graph.cpp:134-144
+
+    def publish_keyframes(self):
+        """common/Keyframes as the node publishes it (graph.cpp:18-25): (ids, poses) of every keyframe."""
+        return (np.array([kf["id"] for kf in self.keyframes], dtype=np.uint64),
+                np.array([kf["pose_opti"] for kf in self.keyframes], dtype=np.float64).reshape(-1, 3))
 
     def closest_keyframe(self, key: int):
         """graph.cpp:146-178 on the device copy of the values."""

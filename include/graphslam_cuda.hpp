@@ -5,6 +5,9 @@
 #pragma once
 #include <array>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -97,11 +100,75 @@ struct Keyframe {                       // Keyframe.msg without the point cloud
   uint64_t id = 0;
   Pose2DWithCovariance pose_opti;
 };
+struct Keyframes {                      // Keyframes.msg: what publish_keyframes sends (graph.cpp:18-25)
+  std::vector<Keyframe> keyframes;
+};
 struct Registration {                   // Registration.msg
   bool first_frame_flag = false, keyframe_flag = false, loop_closure_flag = false;
   Keyframe keyframe_new, keyframe_last;
   Factor factor_new, factor_loop;
 };
+
+// One entry of a recorded registration stream (graphslam_b200/regstream.py writes the same text format):
+//   REG <first> <keyframe> <loop> [NEW id_1 dx dy dtheta c0..c8] [LOOP id_1 id_2 dx dy dtheta c0..c8]
+//   SOLVE        where the node's solve() runs (the call the reference has commented out, graph.cpp:195)
+struct StreamEvent {
+  bool solve = false;
+  Registration reg;
+};
+
+inline std::vector<StreamEvent> read_registration_stream(const char* path) {
+  std::vector<StreamEvent> out;
+  std::FILE* f = std::fopen(path, "r");
+  if (!f) throw Error(GS_EINVAL, std::string("cannot open ") + path);
+  std::vector<char> buf(1 << 16);
+  int lineno = 0;
+  auto bad = [&](const char* why) {
+    std::fclose(f);
+    throw Error(GS_EINVAL, std::string(path) + ":" + std::to_string(lineno) + ": " + why);
+  };
+  while (std::fgets(buf.data(), (int)buf.size(), f)) {
+    ++lineno;
+    if (char* hash = std::strchr(buf.data(), '#')) *hash = 0;
+    std::vector<std::string> t;
+    for (char* tok = std::strtok(buf.data(), " \t\r\n"); tok; tok = std::strtok(nullptr, " \t\r\n")) t.emplace_back(tok);
+    if (t.empty()) continue;
+    StreamEvent ev;
+    if (t[0] == "SOLVE") {
+      ev.solve = true;
+      out.push_back(ev);
+      continue;
+    }
+    if (t[0] != "REG" || t.size() < 4) bad("not a registration line");
+    ev.reg.first_frame_flag = t[1] == "1";
+    ev.reg.keyframe_flag = t[2] == "1";
+    ev.reg.loop_closure_flag = t[3] == "1";
+    auto pose = [&](size_t k, Pose2DWithCovariance& d) {   // 12 numbers from token k
+      d.x = std::strtod(t[k].c_str(), nullptr);
+      d.y = std::strtod(t[k + 1].c_str(), nullptr);
+      d.theta = std::strtod(t[k + 2].c_str(), nullptr);
+      for (int q = 0; q < 9; ++q) d.covariance[q] = std::strtod(t[k + 3 + q].c_str(), nullptr);
+    };
+    size_t k = 4;
+    while (k < t.size()) {
+      if (t[k] == "NEW" && k + 14 <= t.size()) {
+        ev.reg.factor_new.id_1 = std::strtoull(t[k + 1].c_str(), nullptr, 10);
+        pose(k + 2, ev.reg.factor_new.delta);
+        k += 14;
+      } else if (t[k] == "LOOP" && k + 15 <= t.size()) {
+        ev.reg.factor_loop.id_1 = std::strtoull(t[k + 1].c_str(), nullptr, 10);
+        ev.reg.factor_loop.id_2 = std::strtoull(t[k + 2].c_str(), nullptr, 10);
+        pose(k + 3, ev.reg.factor_loop.delta);
+        k += 15;
+      } else {
+        bad("unknown or truncated field");
+      }
+    }
+    out.push_back(ev);
+  }
+  std::fclose(f);
+  return out;
+}
 
 class GraphNode {
  public:
@@ -124,7 +191,9 @@ class GraphNode {
   }
   void new_factor(Registration input) {                // graph.cpp:63-95
     ++keyframe_ids_;
-    const Pose2DWithCovariance& last = keyframes.back().pose_opti;
+    // graph.cpp:72 composes from input.keyframe_last.pose_opti: what the scanner got from the last_keyframe service
+    // (graph.cpp:134-144) before it published.  A message without it (id 0) falls back to the node's own last keyframe.
+    const Pose2DWithCovariance& last = input.keyframe_last.id ? input.keyframe_last.pose_opti : keyframes.back().pose_opti;
     const double a[3] = {last.x, last.y, last.theta};
     const double d[3] = {input.factor_new.delta.x, input.factor_new.delta.y, input.factor_new.delta.theta};
     double pn[3];
@@ -153,6 +222,31 @@ class GraphNode {
       kf.pose_opti.theta = p[2];
     }
     return st;  // warm start: the library keeps the optimum as the next initial values (graph.cpp:130)
+  }
+  bool last_keyframe(Keyframe* out) const {            // LastKeyframe service, graph.cpp:134-144
+    if (keyframes.empty()) return false;
+    *out = keyframes.back();
+    return true;
+  }
+  Keyframes publish_keyframes() const {                // graph.cpp:18-25 (the message, not the transport)
+    Keyframes out;
+    out.keyframes = keyframes;
+    return out;
+  }
+  // replay of a recorded stream: every REG goes through registration_callback with keyframe_last filled from the
+  // last_keyframe service, as the scanner does; SOLVE runs solve().  Returns the stats of the last solve.
+  gs_stats replay(const std::vector<StreamEvent>& events) {
+    gs_stats st{};
+    for (const StreamEvent& ev : events) {
+      if (ev.solve) {
+        st = solve();
+        continue;
+      }
+      Registration reg = ev.reg;
+      if (reg.keyframe_flag) last_keyframe(&reg.keyframe_last);
+      registration_callback(reg, false);
+    }
+    return st;
   }
   void registration_callback(const Registration& input, bool do_solve) {   // graph.cpp:180-200
     if (input.first_frame_flag) {

@@ -63,3 +63,17 @@ for name, graph, mode in (("c3_small", synth.config("C3", n=2500, full_cov=True)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), n=graph.n, e=graph.e, iterations=tr.iterations,
                         tries=np.array(tr.tries), errors=np.array(tr.errors), poses=x, mode=mode)
 print("golden written")
+
+# a recorded registration stream (common/Registration messages, graphslam_b200/regstream.py format) and the Keyframes
+# message the ORACLE's replay of it ends with (oracle/replay.py): the fixture of the ROS-free replay driver
+# (examples/graph_node_noros.cpp, graph.GraphNode) — solve() after every 100 keyframes and at the end
+from graphslam_b200 import regstream      # noqa: E402
+from oracle import replay as oreplay       # noqa: E402
+gm = synth.manhattan(400, seed=5, target_edges=560)
+msgs = regstream.from_graph(gm, solve_every=100)
+regstream.write(os.path.join(HERE, "registration_stream_manhattan400.reg"), msgs)
+ids, kposes, traces = oreplay.replay(regstream.read(os.path.join(HERE, "registration_stream_manhattan400.reg")))
+np.savez_compressed(os.path.join(HERE, "registration_stream_manhattan400_keyframes.npz"), ids=ids, poses=kposes,
+                    iterations=np.array([t.iterations for t in traces]), final_errors=np.array([t.errors[-1] for t in traces]))
+print("registration stream written:", len(msgs), "events,", len(ids), "keyframes, LM iterations per solve",
+      [t.iterations for t in traces])

@@ -161,7 +161,8 @@ def test_cpp_shim_and_ros_free_example_build_against_the_library(lib, tmp_path):
                           "-Wl,-rpath," + os.path.dirname(build.LIB)], capture_output=True, text=True)
     assert res.returncode == 0, res.stderr
     # without a CUDA device the example must fail loudly (no CPU fallback), not crash
-    run = subprocess.run([str(exe)], capture_output=True, text=True)
+    stream = os.path.join(ROOT, "tests", "golden", "registration_stream_manhattan400.reg")
+    run = subprocess.run([str(exe), stream], capture_output=True, text=True)
     if not _cuda_present():
         assert run.returncode != 0 and run.returncode > 0, (run.returncode, run.stderr)
         assert "CUDA" in (run.stderr + run.stdout)

@@ -1,0 +1,77 @@
+"""Parity at the sizes BASELINE.json names (SURVEY.md 8(d) configs C2-C5 at full size), through the C ABI.
+
+The numpy oracle's exact solve (SuperLU) needs a minute per damped solve at these sizes, so the exact-solve arbiter
+here is the C port's LM with the sparse multifrontal Cholesky (oracle/cpu_chol.c), which tests/test_cpu_port.py pins
+to the numpy oracle (same iterations, same accept/reject sequence, chi2 1e-9, poses 1e-6) on C1 and on cut-down
+C2/C3/C4.  Integer structure and the linearisation are compared with the vectorised numpy oracle directly.
+
+Tolerances are the north_star's: integers bit-exact; H and b within 1e-11 of the block scale; final chi2 within 1e-9
+relative; poses within 1e-6 (theta modulo 2 pi); intermediate chi2_k within 1e-6 (see DESIGN.md "Parity protocol").
+"""
+import numpy as np
+import pytest
+
+from graphslam_b200 import graph, synth
+from oracle import cpu_ref
+from oracle import gs_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+CHI2_RTOL = 1e-9
+POSE_ATOL = 1e-6
+TRACE_RTOL = 1e-6
+
+
+def _pose_diff(a, b):
+    return max(np.abs(a[:, :2] - b[:, :2]).max(), np.abs(O.wrap_pi(a[:, 2] - b[:, 2])).max())
+
+
+def _full_size_parity(g, lm_against_port=True):
+    prob = O.Problem.from_graph(g)
+    with graph.Graph() as G:
+        G.add_graph(g)
+        # ---- integers: bit-exact
+        rowptr, colidx, blocks, b, chi2 = G.system()
+        orp, oci = prob.pattern()
+        assert np.array_equal(rowptr, orp) and np.array_equal(colidx, oci)
+        # ---- linearisation at the initial values
+        h, ob, ochi2 = prob.linearize(g.init, 0)
+        _, _, oblocks = prob.bsr(h)
+        assert np.abs(blocks - oblocks).max() <= 1e-11 * np.abs(oblocks).max()
+        assert np.abs(b - ob).max() <= 1e-11 * np.abs(ob).max()
+        assert chi2 == pytest.approx(ochi2, rel=1e-12)
+        del blocks, oblocks, h
+        # ---- LM to GTSAM's stopping rule
+        st = G.optimize()
+        errors, lambdas, tries = G.trace()
+        _, x = G.poses()
+    assert st["converged"] == 1 and np.all(np.diff(errors) <= 0)
+    # the oracle re-evaluates the returned poses
+    assert prob.chi2(x) == pytest.approx(st["chi2_final"], rel=1e-12)
+    if lm_against_port:
+        cpu_ref.set_threads()
+        cx, cst, cerrs, ctries = cpu_ref.optimize(g, solver=cpu_ref.SOLVER_CHOLESKY)
+        assert cst["status"] == 0
+        assert st["iterations"] == cst["iterations"] and tries.tolist() == ctries.tolist()   # same accept/reject sequence
+        rel = np.abs(errors - cerrs) / cerrs
+        assert rel.max() <= TRACE_RTOL and rel[-1] <= CHI2_RTOL, rel
+        assert _pose_diff(x, cx) <= POSE_ATOL
+    return st
+
+
+def test_c3_one_million_poses():
+    """The headline graph: 1,000,000 poses / 2,996,001 factors."""
+    st = _full_size_parity(synth.config("C3"))
+    assert st["pcg_iterations_total"] > 0 and st["gpu_launches"] > 0
+
+
+def test_c4_dense_200k():
+    _full_size_parity(synth.config("C4"))
+
+
+def test_c2_100k():
+    _full_size_parity(synth.config("C2"))
+
+
+def test_c5_50k():
+    _full_size_parity(synth.config("C5"))
