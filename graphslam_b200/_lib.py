@@ -11,8 +11,8 @@ c_double_p = C.POINTER(C.c_double)
 c_u64_p = C.POINTER(C.c_uint64)
 c_i32_p = C.POINTER(C.c_int32)
 
-GS_SOLVER_NO_CUDA_GRAPH, GS_SOLVER_NCCL_PER_OP, GS_SOLVER_NO_PERSISTENT, GS_SOLVER_DIR_KERNEL, GS_SOLVER_DIR_ON_THE_FLY = (
-    1, 2, 4, 8, 16)
+(GS_SOLVER_NO_CUDA_GRAPH, GS_SOLVER_NCCL_PER_OP, GS_SOLVER_NO_PERSISTENT, GS_SOLVER_DIR_KERNEL, GS_SOLVER_DIR_ON_THE_FLY,
+ GS_SOLVER_BLOCK_JACOBI_ONLY) = (1, 2, 4, 8, 16, 32)
 GS_OK, GS_EINVAL, GS_ENOTSPD, GS_EDUPKEY, GS_ENOKEY, GS_ECUDA, GS_ENCCL, GS_ENOTCONVERGED, GS_ENAN, GS_ENOMEM = range(10)
 STATUS_NAMES = ["GS_OK", "GS_EINVAL", "GS_ENOTSPD", "GS_EDUPKEY", "GS_ENOKEY", "GS_ECUDA", "GS_ENCCL",
                 "GS_ENOTCONVERGED", "GS_ENAN", "GS_ENOMEM"]
@@ -35,11 +35,12 @@ class GsStats(C.Structure):
                 ("ms_total", C.c_double), ("edges_per_sec", C.c_double), ("gn_iters_per_sec", C.c_double),
                 ("gpu_launches", C.c_double), ("ms_device", C.c_double), ("h2d_bytes", C.c_double),
                 ("d2h_bytes", C.c_double), ("p2p_wait_ticks", C.c_double * 3), ("p2p_waits", C.c_double),
-                ("reserved", C.c_double * 4)]
+                ("ms_structure_parts", C.c_double * 4)]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("reserved", "p2p_wait_ticks")}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("ms_structure_parts", "p2p_wait_ticks")}
         d["p2p_wait_ticks"] = list(self.p2p_wait_ticks)
+        d["ms_structure_parts"] = dict(zip(("host", "upload", "comm", "capture"), self.ms_structure_parts))
         d["gpu_launches"] = int(self.gpu_launches)
         return d
 
@@ -68,6 +69,7 @@ SIGNATURES = {
     "gs_load_g2o": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(GsG2oCounts)]),
     "gs_save_g2o": (C.c_int, [C.c_void_p, C.c_char_p]),
     "gs_prepare": (C.c_int, [C.c_void_p]),
+    "gs_get_structure_timing": (C.c_int, [C.c_void_p, c_double_p]),
     "gs_optimize": (C.c_int, [C.c_void_p, C.POINTER(GsStats)]),
     "gs_get_pose": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
     "gs_get_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p, C.POINTER(C.c_size_t)]),

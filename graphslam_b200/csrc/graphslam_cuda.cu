@@ -11,6 +11,7 @@
 // exchange of p (per SpMV) and of the poses (per retract), and all-gathers of the segment sums of
 // the dot products, which every rank then adds in the same fixed order.
 #include <cuda_runtime.h>
+#include <cusolverDn.h>
 
 #include <algorithm>
 #include <chrono>
@@ -32,6 +33,7 @@
 #include "g2o.hpp"
 #include "host_util.hpp"
 #include "kernels.cuh"
+#include "kernels_coarse.cuh"
 #include "kernels_fused.cuh"
 #include "kernels_p2p.cuh"
 
@@ -88,8 +90,6 @@ struct gs_graph {
                                           // (k_spmvdir[_p2p] + update) instead of three; decided in prepare()
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
   bool p2p_staged = false;                // GS_X_P2P_STAGED (experiment): k_update_p2p_staged / k_updpush_p2p_staged
-  bool asm_nodup = false;                 // GS_X_ASM_NODUP (experiment): k_assemble_nodup on graphs without duplicate factors
-  bool update_staged = true;              // !GS_X_UPDATE_UNSTAGED (experiment)
   bool fused_wanted = true;               // !GS_SOLVER_NO_PERSISTENT
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
@@ -144,6 +144,8 @@ struct gs_graph {
 
   // ---- device
   DevBuf<double4> d_pose, d_pose_try, d_pr_pose, d_pose_all;
+  DevBuf<double4> d_pose_lin;   // two-level preconditioner: the linearisation point its basis W is built at (fixed address:
+                                // d_pose / d_pose_try swap on every accepted step, the captured PCG graph must not see that)
   DevBuf<int2> d_eij, d_refs;
   DevBuf<int4> d_cw;
   DevBuf<double2> d_fdata;   // factor cells, five double2 components each (layout: rows.cuh, GS_F_LAYOUT)
@@ -152,6 +154,9 @@ struct gs_graph {
   DevBuf<double> d_pr_om, d_Ho, d_Hd, d_b, d_x, d_r, d_z, d_p, d_Ap, d_Minv, d_dscale, d_part, d_segs, d_sendbuf;
   DevBuf<Scalars> d_sc;
   DevBuf<unsigned int> d_counter;
+  DevBuf<gs::ClosestOut> d_closest;       // closest_keyframe: [0] result, [2 .. 2+ranks) gathered results, then per-CTA partials
+  DevBuf<int> d_closest_order;            // insertion index -> dense row, when keys were not inserted in increasing order
+  int closest_order_n = -1;
   Scalars* h_sc = nullptr;  // pinned mirror
   size_t hstride = 1;
   int grid_rows = 1, grid_flat3 = 1, part_stride = 1;
@@ -159,10 +164,24 @@ struct gs_graph {
   cudaGraph_t pcg_graph = nullptr;
   cudaGraphExec_t pcg_exec = nullptr;
 
+  // ---- two-level preconditioner (kernels_coarse.cuh): block-Jacobi + rigid-body coarse space over aggregates
+  bool coarse_wanted = true;              // !GS_SOLVER_BLOCK_JACOBI_ONLY
+  bool coarse = false;                    // in use for this graph (single rank, lambda*I damping, large enough)
+  gs::Aggregation agg;
+  DevBuf<int> d_agg_of, d_agg_ptr, d_agg_rows, d_agg_color, d_nbr_of_color;
+  DevBuf<double> d_cvec, d_mu, d_cpart, d_R, d_G, d_E, d_chol_work, d_basis;
+  DevBuf<int> d_chol_info;
+  cusolverDnHandle_t cusolver = nullptr;
+  int chol_lwork = 0;
+  bool coarse_e0_valid = false;           // R (= W^T H W by columns) and G computed at the current linearisation
+  double coarse_lambda = -1.0;            // the lambda d_E (= E^-1) was built for; < 0: none
+  double ms_coarse_setup = 0.0;
+
   // ---- last optimise trace
   std::vector<double> tr_err, tr_lambda;
   std::vector<int32_t> tr_tries;
   int64_t launches = 0;
+  double prep_ms[4] = {0, 0, 0, 0};   // last structure build: host structure, staging + upload, communicator setup, graph capture
   double p2p_wait[4] = {0, 0, 0, 0};  // peer-memory path: clock ticks CTA 0 waited in spmv / update / dir, waits counted
 
   gs_status fail(gs_status s, const char* fmt, ...) {
@@ -271,6 +290,19 @@ gs::PcgView pcg_view(gs_graph* g) {
   return a;
 }
 
+bool coarse_active(const gs_graph* g) { return g->coarse && !g->prm.diagonal_damping; }
+
+gs::CoarseView coarse_view(gs_graph* g) {
+  gs::CoarseView c;
+  c.agg_of = g->d_agg_of.p;
+  c.agg_ptr = g->d_agg_ptr.p;
+  c.agg_rows = g->d_agg_rows.p;
+  c.pose = g->d_pose_lin.p;
+  c.n_agg = g->agg.n_agg;
+  c.n_own = g->n_own;
+  return c;
+}
+
 // ---- multi-rank plumbing (no-ops on a single rank) ------------------------------------------------
 // ghost slots of `vec` (width doubles per vertex) <- owner ranks' current values
 // `ghost` = where the ghost rows land (nullptr: right behind the owned rows of `vec`)
@@ -317,6 +349,8 @@ gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode) {
                                                            mode);
   return finish_reduce(g, 1, mode == 0 ? gs::OP_PAP : gs::OP_DOT);
 }
+
+gs_status coarse_setup(gs_graph* g, double lambda);
 
 template <typename T>
 gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
@@ -400,27 +434,23 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     }
     return GS_OK;
   }
-  if (g->dir_otf && g->world == 1) {
-    // single GPU, two kernels per iteration: iteration k reads the direction of iteration k-1 from buffer k&1 and
-    // writes its own into the other one (an even batch leaves the latest direction in pvec)
-    double* P[2] = {g->pvec, g->d_p_alt.p};
-    double* prev = P[k_local & 1u];
-    double* next = P[(k_local + 1u) & 1u];
-    if (stage == 0) {
-      gs::k_spmvdir<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->d_z.p, prev, next, g->d_Ap.p, reduce_ctx(g, 0));
-    } else if (stage == 1) {
-      gs::PcgView pv = pcg_view(g);
-      pv.p = next;
-      gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1));
+  if (stage == 0) return launch_spmv(g, g->pvec, g->d_Ap.p, 0);
+  if (coarse_active(g)) {
+    // two-level preconditioner: z = M^-1 r + W E^-1 W^T r.  r.z = r.M^-1 r + c.mu is completed by k_coarse_mv, which also
+    // forms beta; the corrected z is only ever needed inside the direction update
+    const int m = 3 * g->agg.n_agg;
+    if (stage == 1) {
+      gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), gs::OP_UPDATE_2L);
+      gs::k_restrict<<<g->agg.n_agg, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p);
+      gs::k_coarse_mv<<<(m + 7) / 8, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
+                                                                    g->d_counter.p + 6, g->d_sc.p, 0);
+    } else {
+      gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
     }
     return GS_OK;
   }
-  if (stage == 0) return launch_spmv(g, g->pvec, g->d_Ap.p, 0);
   if (stage == 1) {
-    if (g->update_staged)
-      gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
-    else
-      gs::k_pcg_update<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
+    gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), gs::OP_UPDATE);
     return finish_reduce(g, 2, gs::OP_UPDATE);
   }
   gs::k_pcg_dir<<<g->grid_flat3, gs::kThreads, 0, g->stream>>>(g->d_z.p, g->pvec, g->d_sc.p, 3 * g->n_own);
@@ -693,6 +723,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = download_values(g)) return s;
   if (g->keys.empty()) return g->fail(GS_EINVAL, "graph has no vertices");
   build_dense_order(g);
+  g->closest_order_n = -1;
   const int N = (int)g->keys.size(), E = (int)g->e1.size(), P = (int)g->pr_v.size();
   g->di.resize(E);
   g->dj.resize(E);
@@ -705,6 +736,15 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   gs::canonical_order(N, E, g->di.data(), g->dj.data(), g->perm);
   gs::build_local_structure(N, E, g->di.data(), g->dj.data(), g->perm, P, g->dp.data(), g->world, g->rank, g->S);
   const LocalStructure& S = g->S;
+  // two-level preconditioner: aggregates of the block rows (one rank; small graphs keep the persistent kernel)
+  g->coarse = g->coarse_wanted && g->world == 1 && N >= 8192;
+  if (g->coarse) {
+    std::vector<int32_t> rp, ci;
+    gs::global_pattern(N, E, g->di.data(), g->dj.data(), rp, ci);
+    gs::build_aggregation(N, rp, ci, std::max(128, (N + 1023) / 1024), g->agg);
+  }
+  const double t_host = now_ms();
+  g->prep_ms[0] = t_host - t0;
   g->N = N;
   g->E = E;
   g->P = P;
@@ -778,23 +818,57 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (g->grid_flat3 < 1) g->grid_flat3 = 1;
   g->part_stride = g->grid_rows;
   GS_CUDA(g, g->d_part.alloc(3 * (size_t)g->part_stride));
-  g->fused = g->fused_wanted && g->world == 1 && g->fused_capacity > 0 && g->grid_rows <= g->fused_capacity;
+  g->fused = g->fused_wanted && g->world == 1 && g->fused_capacity > 0 && g->grid_rows <= g->fused_capacity && !g->coarse;
+  if (g->coarse) {
+    const gs::Aggregation& A = g->agg;
+    const size_t m = 3 * (size_t)A.n_agg;
+    if (gs_status s = upload(g, g->d_agg_of, A.agg_of)) return s;
+    if (gs_status s = upload(g, g->d_agg_ptr, A.ptr)) return s;
+    if (gs_status s = upload(g, g->d_agg_rows, A.rows)) return s;
+    if (gs_status s = upload(g, g->d_agg_color, A.color)) return s;
+    if (gs_status s = upload(g, g->d_nbr_of_color, A.nbr_of_color)) return s;
+    GS_CUDA(g, g->d_cvec.alloc(m));
+    GS_CUDA(g, g->d_mu.alloc(m));
+    GS_CUDA(g, g->d_cpart.alloc((m + 7) / 8 + 1));
+    GS_CUDA(g, g->d_R.alloc((size_t)A.n_colors * 3 * m));
+    GS_CUDA(g, g->d_G.alloc(3 * m));
+    GS_CUDA(g, g->d_E.alloc(m * m));
+    GS_CUDA(g, g->d_basis.alloc(nl3));
+    GS_CUDA(g, g->d_pose_lin.alloc(std::max(g->n_loc, 1)));
+    GS_CUDA(g, g->d_chol_info.alloc(1));
+    if (!g->cusolver) {
+      if (cusolverDnCreate(&g->cusolver) != CUSOLVER_STATUS_SUCCESS) return g->fail(GS_ECUDA, "cusolverDnCreate failed");
+      cusolverDnSetStream(g->cusolver, g->stream);
+    }
+    int l1 = 0, l2 = 0;
+    if (cusolverDnDpotrf_bufferSize(g->cusolver, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l1) != CUSOLVER_STATUS_SUCCESS ||
+        cusolverDnDpotri_bufferSize(g->cusolver, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l2) != CUSOLVER_STATUS_SUCCESS)
+      return g->fail(GS_ECUDA, "cusolver workspace query failed");
+    g->chol_lwork = std::max(l1, l2);
+    GS_CUDA(g, g->d_chol_work.alloc((size_t)std::max(g->chol_lwork, 1)));
+  }
+  g->coarse_e0_valid = false;
+  g->coarse_lambda = -1.0;
   {
     // direction on the fly (two kernels per iteration) or as a kernel of its own (three)?  Forming it inside the
     // product pays a second gather per column and saves a kernel plus, on several GPUs, a cross-GPU signal: measured
     // on C3, 1.39 -> 1.31 s per step at 2 GPUs and 0.92 -> 0.87 s at 4, but 0.54 -> 0.6 s at 8 (125k rows per rank),
     // so the choice goes by rows per rank (the same number on every rank).  The NCCL-per-exchange path keeps three.
     const int f = g->prm.solver_flags;
-    const bool can = g->world == 1 ? !g->fused : g->p2p_wanted;
+    // (one GPU keeps three: forming the direction inside the product was measured at 161.9 us per iteration against
+    //  160.8 us on C3, and 218 us against 157 us on C4; profiles/r2_variant_probe.md)
+    const bool can = g->world > 1 && g->p2p_wanted;
     if (!can || (f & GS_SOLVER_DIR_KERNEL)) g->dir_otf = false;
     else if (f & GS_SOLVER_DIR_ON_THE_FLY) g->dir_otf = true;
     else g->dir_otf = g->world > 1 ? (N / g->world >= 200000) : false;
   }
-  if (g->fused || (g->dir_otf && g->world == 1)) GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(g->n_own, 1) + 3));
+  if (g->fused) GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(g->n_own, 1) + 3));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));  // staging vectors go out of scope
   g->topo_dirty = false;
   g->device_values_valid = false;
   if (gs_status s = upload_values(g)) return s;
+  const double t_up = now_ms();
+  g->prep_ms[1] = t_up - t_host;
   if (g->world > 1) {
     if (g->p2p_wanted) {
       if (gs_status s = prepare_p2p(g)) return s;
@@ -807,8 +881,65 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     GS_NCCL(g, gs::nccl().AllGather(g->d_segs.p + g->rank * chunk, g->d_segs.p, chunk, ncclDouble, g->comm, g->stream));
     GS_CUDA(g, cudaStreamSynchronize(g->stream));
   }
+  const double t_comm = now_ms();
+  g->prep_ms[2] = t_comm - t_up;
   if (gs_status s = capture_pcg_graph(g)) return s;
+  g->prep_ms[3] = now_ms() - t_comm;
   if (ms_out) *ms_out = now_ms() - t0;
+  return GS_OK;
+}
+
+// Two-level preconditioner, setup for the solve with damping `lambda` at the current linearisation:
+//   E0 = W^T H W by columns — one undamped product H w per (colour, rigid mode), restricted per aggregate — and
+//   G = W^T W, once per linearisation;  E = E0 + lambda G, Cholesky-factored and inverted (cuSOLVER potrf / potri: a
+//   dense 3 n_agg square, <= 3072), once per lambda.  d_E then holds E^-1 in full.
+gs_status coarse_setup(gs_graph* g, double lambda) {
+  const double t0 = now_ms();
+  const gs::Aggregation& A = g->agg;
+  const int m = 3 * A.n_agg;
+  if (!g->coarse_e0_valid) {
+    GS_CUDA(g, cudaMemcpyAsync(g->d_pose_lin.p, g->d_pose.p, sizeof(double4) * (size_t)g->n_loc, cudaMemcpyDeviceToDevice, g->stream));
+    const gs::CoarseView cv = coarse_view(g);
+    for (int c = 0; c < A.n_colors; ++c)
+      for (int mode = 0; mode < 3; ++mode) {
+        gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, c, mode, g->d_basis.p);
+        if (gs_status s = launch_spmv(g, g->d_basis.p, g->d_Ap.p, 1)) return s;
+        gs::k_restrict<<<A.n_agg, gs::kThreads, 0, g->stream>>>(cv, g->d_Ap.p, g->d_sc.p, 0,
+                                                                 g->d_R.p + ((size_t)c * 3 + mode) * m);
+      }
+    for (int mode = 0; mode < 3; ++mode) {
+      gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, -1, mode, g->d_basis.p);
+      gs::k_restrict<<<A.n_agg, gs::kThreads, 0, g->stream>>>(cv, g->d_basis.p, g->d_sc.p, 0, g->d_G.p + (size_t)mode * m);
+    }
+    g->launches += 3 * (int64_t)A.n_colors * 3 + 6;
+    g->coarse_e0_valid = true;
+    g->coarse_lambda = -1.0;
+  }
+  if (g->coarse_lambda != lambda) {
+    GS_CUDA(g, cudaMemsetAsync(g->d_E.p, 0, sizeof(double) * (size_t)m * m, g->stream));
+    const int total = A.n_agg * A.n_colors * 3;
+    gs::k_coarse_E<<<(total + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(
+        g->d_R.p, g->d_G.p, g->d_nbr_of_color.p, A.n_agg, A.n_colors, lambda, g->d_E.p);
+    if (cusolverDnDpotrf(g->cusolver, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
+        CUSOLVER_STATUS_SUCCESS)
+      return g->fail(GS_ECUDA, "cusolverDnDpotrf failed");
+    int info = 0;
+    GS_CUDA(g, cudaMemcpyAsync(&info, g->d_chol_info.p, sizeof(int), cudaMemcpyDeviceToHost, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+    if (info != 0)
+      return g->fail(GS_ENAN, "coarse matrix of the two-level preconditioner is not positive definite (leading minor %d): is the "
+                              "graph anchored by a prior?", info);
+    if (cusolverDnDpotri(g->cusolver, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
+        CUSOLVER_STATUS_SUCCESS)
+      return g->fail(GS_ECUDA, "cusolverDnDpotri failed");
+    const size_t mm = (size_t)m * m;
+    gs::k_symmetrize<<<(unsigned)((mm + gs::kThreads - 1) / gs::kThreads), gs::kThreads, 0, g->stream>>>(g->d_E.p, m);
+    g->launches += 2;
+    g->coarse_lambda = lambda;
+  }
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  GS_CUDA(g, cudaGetLastError());
+  g->ms_coarse_setup += now_ms() - t0;
   return GS_OK;
 }
 
@@ -829,7 +960,9 @@ gs_status write_scalars(gs_graph* g) {
 gs_status launch_assemble(gs_graph* g) {
   const gs::AsmView av = asm_view(g, g->d_pose.p);
   const gs::ReduceCtx rc = reduce_ctx(g, 2);
-  const bool nodup = g->asm_nodup && g->S.n_merged == 0;
+  // no vertex pair carries two factors (every BASELINE config): the form without the run accumulator, 80 registers and
+  // three CTAs per SM instead of 118 and two (C3: 175.9 -> 163.5 us; same bits, tests/test_emulator_cpu.py)
+  const bool nodup = g->S.n_merged == 0;
   if (g->prm.jacobian_mode == GS_JACOBIAN_EXACT) {
     if (nodup) gs::k_assemble_nodup<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
     else gs::k_assemble<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(av, rc);
@@ -845,6 +978,8 @@ gs_status launch_assemble(gs_graph* g) {
   }
   GS_CUDA(g, cudaGetLastError());
   g->system_valid = true;
+  g->coarse_e0_valid = false;
+  g->coarse_lambda = -1.0;
   return GS_OK;
 }
 
@@ -860,8 +995,17 @@ gs_status launch_chi2(gs_graph* g, const double4* pose) {
 void launch_pcg_setup(gs_graph* g) {
   gs::k_minv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
                                                            g->d_sc.p, g->d_Minv.p, g->n_own);
-  gs::k_pcg_init<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1));
+  const bool two = coarse_active(g);
+  gs::k_pcg_init<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), two ? gs::OP_INIT_2L : gs::OP_INIT);
   g->launches += 2;
+  if (two) {   // p(0) = z(0) = M^-1 r + W E^-1 W^T r
+    const int m = 3 * g->agg.n_agg;
+    gs::k_restrict<<<g->agg.n_agg, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p);
+    gs::k_coarse_mv<<<(m + 7) / 8, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
+                                                                  g->d_counter.p + 6, g->d_sc.p, 1);
+    gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
+    g->launches += 3;
+  }
 }
 
 // peer-memory path: ghost rows of p(0) by the ordinary halo exchange, then mark them valid
@@ -882,7 +1026,8 @@ gs_status begin_p2p_solve(gs_graph* g) {
 }
 
 int64_t launches_per_pcg_iteration(const gs_graph* g) {
-  if (g->dir_otf && (g->p2p || g->world == 1)) return 2;
+  if (g->dir_otf && g->p2p) return 2;
+  if (coarse_active(g)) return 5;
   if (g->world == 1 || g->p2p) return 3;
   return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
 }
@@ -890,6 +1035,8 @@ int64_t launches_per_pcg_iteration(const gs_graph* g) {
 // Solve (H + lambda D) x = -b by block-Jacobi PCG; result in d_x.  H, b must be assembled.
 gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_out, int* done_out) {
   Scalars* h = g->h_sc;
+  if (coarse_active(g))
+    if (gs_status s = coarse_setup(g, lambda)) return s;
   std::memset(h, 0, sizeof(Scalars));
   h->lambda = lambda;
   h->tol2 = g->prm.pcg_rel_tol * g->prm.pcg_rel_tol;
@@ -955,8 +1102,7 @@ gs_status create_common(gs_graph* g) {
   g->fused_wanted = !(flags & GS_SOLVER_NO_PERSISTENT);
   g->p2p_wanted = !(flags & GS_SOLVER_NCCL_PER_OP);
   g->p2p_staged = (flags & GS_X_P2P_STAGED) != 0;
-  g->asm_nodup = (flags & GS_X_ASM_NODUP) != 0;
-  g->update_staged = !(flags & GS_X_UPDATE_UNSTAGED);
+  g->coarse_wanted = !(flags & GS_SOLVER_BLOCK_JACOBI_ONLY);
   {
     int per_sm = 0, sms = 0, dev = 0, coop = 0;
     GS_CUDA(g, cudaGetDevice(&dev));
@@ -1096,6 +1242,7 @@ gs_status gs_destroy(gs_graph* g) try {
     exchange_records(g, mine, all);
   }
   if (g->win) cudaFree(g->win);
+  if (g->cusolver) cusolverDnDestroy(g->cusolver);
   if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->ev0) cudaEventDestroy(g->ev0);
@@ -1325,6 +1472,14 @@ gs_status gs_prepare(gs_graph* g) try {
   return on_exception(g);
 }
 
+gs_status gs_get_structure_timing(const gs_graph* g, double ms[4]) try {
+  if (!g || !ms) return GS_EINVAL;
+  for (int k = 0; k < 4; ++k) ms[k] = g->prep_ms[k];
+  return GS_OK;
+} catch (...) {
+  return on_exception(const_cast<gs_graph*>(g));
+}
+
 gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   if (!g) return GS_EINVAL;
   const double t_begin = now_ms();
@@ -1334,6 +1489,8 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   const double h2d0 = g->h2d_bytes, d2h0 = g->d2h_bytes;
   if (gs_status s = prepare(g, &ms_structure)) return s;
   local.ms_structure = ms_structure;
+  if (ms_structure > 0.0)
+    for (int k = 0; k < 4; ++k) local.ms_structure_parts[k] = g->prep_ms[k];
   GS_CUDA(g, cudaEventRecord(g->ev_begin, g->stream));
   const gs_params& P = g->prm;
   Scalars* h = g->h_sc;
@@ -1729,6 +1886,8 @@ gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], do
   h->lambda = lambda;
   h->tol2 = 0.0;  // never converge: every profiled iteration does full work
   h->max_iters = 1 << 30;
+  if (coarse_active(g))
+    if (gs_status s = coarse_setup(g, lambda)) return s;
   if (gs_status s = write_scalars(g)) return s;
   launch_pcg_setup(g);
   if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
@@ -1847,34 +2006,59 @@ void gs_compose(const double a[3], const double b[3], double out[3]) {
 
 gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist) try {
   if (!g || !out_key || skip < 0) return GS_EINVAL;
-  if (g->world != 1) return g->fail(GS_EINVAL, "gs_closest_keyframe runs on a single-rank graph");
   const int v = g->find(key);
   if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)key);
   const int nv = (int)g->keys.size();
   if (nv <= skip) return g->fail(GS_ENOKEY, "not enough keyframes (%d <= skip %d)", nv, skip);
   if (gs_status s = prepare(g, nullptr)) return s;
   const int count = nv - skip;
-  // query pose from the device copy (insertion order -> dense index)
-  double4 q;
-  GS_CUDA(g, cudaMemcpyAsync(&q, g->d_pose.p + g->ins2dense[v], sizeof q, cudaMemcpyDeviceToHost, g->stream));
-  GS_CUDA(g, cudaStreamSynchronize(g->stream));
-  DevBuf<int> d_order;
+  // candidates in insertion order -> dense rows (identity when the keys were inserted in increasing order)
   const int* order = nullptr;
   if (!g->identity_order) {
-    std::vector<int> ord(g->ins2dense.begin(), g->ins2dense.begin() + count);
-    GS_CUDA(g, d_order.alloc(count));
-    GS_CUDA(g, cudaMemcpyAsync(d_order.p, ord.data(), sizeof(int) * count, cudaMemcpyHostToDevice, g->stream));
-    GS_CUDA(g, cudaStreamSynchronize(g->stream));
-    order = d_order.p;
+    if (g->closest_order_n != nv) {
+      GS_CUDA(g, g->d_closest_order.alloc(nv));
+      GS_CUDA(g, cudaMemcpyAsync(g->d_closest_order.p, g->ins2dense.data(), sizeof(int) * nv, cudaMemcpyHostToDevice, g->stream));
+      g->h2d_bytes += sizeof(int) * (double)nv;
+      g->closest_order_n = nv;
+    }
+    order = g->d_closest_order.p;
   }
-  double* d_best = g->d_part.p;
-  int* d_idx = reinterpret_cast<int*>(g->d_part.p + 1);
-  gs::k_closest<<<1, gs::kThreads, 0, g->stream>>>(g->d_pose.p, order, count, q.x, q.y, d_best, d_idx);
-  double bd;
-  int bi;
-  GS_CUDA(g, cudaMemcpyAsync(&bd, d_best, sizeof bd, cudaMemcpyDeviceToHost, g->stream));
-  GS_CUDA(g, cudaMemcpyAsync(&bi, d_idx, sizeof bi, cudaMemcpyDeviceToHost, g->stream));
+  const int grid = (count + gs::kThreads * gs::kClosestPerThread - 1) / (gs::kThreads * gs::kClosestPerThread);
+  GS_CUDA(g, g->d_closest.alloc((size_t)grid + 2 + gs::kMaxRanks));
+  gs::ClosestOut* part = g->d_closest.p + 2 + gs::kMaxRanks;
+  gs::ClosestOut* res = g->d_closest.p;                      // [0] this rank's result, [2 ...] all ranks' results
+  // the query pose stays on the device: its owner's row, broadcast to the other ranks
+  const int qdense = g->ins2dense[v];
+  const double4* query = nullptr;
+  if (g->world == 1) {
+    query = g->d_pose.p + qdense;
+  } else {
+    const int owner = g->S.part.owner(qdense);
+    double* qbuf = reinterpret_cast<double*>(g->d_pose_all.p);   // scratch: only the final pose gather uses it
+    const double* src = reinterpret_cast<const double*>(g->d_pose.p + (owner == g->rank ? qdense - g->S.v0 : 0));
+    GS_NCCL(g, gs::nccl().Broadcast(src, qbuf, 4, ncclDouble, owner, g->comm, g->stream));
+    query = reinterpret_cast<const double4*>(qbuf);
+  }
+  gs::k_closest<<<grid, gs::kThreads, 0, g->stream>>>(g->d_pose.p, order, count, query, g->world > 1 ? g->S.v0 : 0, g->n_own, part,
+                                                       g->d_counter.p + 5, res);
+  g->launches += 1;
+  gs::ClosestOut all[gs::kMaxRanks];
+  if (g->world > 1) {
+    GS_NCCL(g, gs::nccl().AllGather(res, res + 2, sizeof(gs::ClosestOut), ncclChar, g->comm, g->stream));
+    GS_CUDA(g, cudaMemcpyAsync(all, res + 2, sizeof(gs::ClosestOut) * g->world, cudaMemcpyDeviceToHost, g->stream));
+  } else {
+    GS_CUDA(g, cudaMemcpyAsync(all, res, sizeof(gs::ClosestOut), cudaMemcpyDeviceToHost, g->stream));
+  }
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  g->d2h_bytes += sizeof(gs::ClosestOut) * (double)g->world;
+  double bd = all[0].dist;
+  int bi = all[0].idx;
+  for (int q = 1; q < g->world; ++q)
+    if (all[q].dist < bd || (all[q].dist == bd && all[q].idx < bi)) {
+      bd = all[q].dist;
+      bi = all[q].idx;
+    }
+  if (bi < 0 || bi >= nv) return g->fail(GS_ECUDA, "closest_keyframe: no candidate found");
   *out_key = g->keys[bi];
   if (out_dist) *out_dist = bd;
   return GS_OK;

@@ -27,16 +27,10 @@ constexpr int kThreads = kTile;
 // trips per slot in a kernel that is latency-bound (75 % long-scoreboard stalls at 48 % DRAM utilisation).  With
 // 48 registers (five CTAs) all twelve are requested before the first use.
 #ifndef GS_SPMV_MINB
-#define GS_SPMV_MINB 5
+#define GS_SPMV_MINB 4
 #endif
 #ifndef GS_SPMVDIR_MINB
 #define GS_SPMVDIR_MINB 4
-#endif
-#ifndef GS_UPD_HOIST
-#define GS_UPD_HOIST 1   // k_pcg_update_staged: request the row's M^-1 block together with the tile's vectors
-#endif
-#ifndef GS_UPD_MINB
-#define GS_UPD_MINB 1
 #endif
 
 // Device-resident scalars: PCG coefficients never visit the host.
@@ -56,9 +50,10 @@ struct Scalars {
   unsigned int seq0;  // peer-memory path: sequence number of this solve's first iteration
   double rzv[2];      // peer-memory path: r^T z by iteration parity (reader and writer never share a slot)
   long long spin[4];  // peer-memory path: clock ticks CTA 0 spent waiting in spmv / update / dir, and the waits counted
+  double rz_bj;       // two-level preconditioner: r.M^-1 r of the new residual, before the coarse term c.mu is added
 };
 
-enum ReduceOp { OP_PAP = 0, OP_DOT = 1, OP_INIT = 2, OP_UPDATE = 3, OP_CHI2 = 4 };
+enum ReduceOp { OP_PAP = 0, OP_DOT = 1, OP_INIT = 2, OP_UPDATE = 3, OP_CHI2 = 4, OP_INIT_2L = 5, OP_UPDATE_2L = 6 };
 
 // where a kernel's reduction goes
 struct ReduceCtx {
@@ -156,6 +151,26 @@ __device__ __forceinline__ void apply_scalars(Scalars* sc, int op, double t0, do
     case OP_CHI2:
       sc->chi2 = t0;
       break;
+    // two-level preconditioner: r.z is completed by k_coarse_mv (r.M^-1 r here, + c.mu there), which also forms beta
+    case OP_INIT_2L:
+      sc->rz_bj = t0;
+      sc->rr = t1;
+      sc->rr0 = t1;
+      sc->beta = 0.0;
+      sc->iters = 0;
+      sc->done = (t1 == 0.0) ? 1 : 0;
+      break;
+    case OP_UPDATE_2L: {
+      if (sc->done) return;
+      sc->rz_bj = t0;
+      sc->rr = t1;
+      const int it = sc->iters + 1;
+      sc->iters = it;
+      if (t1 <= sc->tol2 * sc->rr0) sc->done = 1;
+      else if (!(t1 == t1)) sc->done = 2;
+      else if (it >= sc->max_iters) sc->done = 3;
+      break;
+    }
   }
 }
 
@@ -259,22 +274,6 @@ __global__ void __launch_bounds__(kThreads, GS_SPMV_MINB) k_spmv(const SpmvView 
   reduce_finish<1>(c, v, mode == 0 ? OP_PAP : OP_DOT, red, &flag);
 }
 
-// The product with the direction update folded in (two kernels per iteration): p(c) = z(c) + beta p_prev(c) is formed
-// on the fly for every column the row touches and the row's own new p goes to the other direction buffer.  beta is
-// 0 in the first iteration of a solve (p_prev = z there).  Same expressions as k_pcg_dir + k_spmv: same bits.
-__global__ void __launch_bounds__(kThreads, GS_SPMVDIR_MINB) k_spmvdir(const SpmvView a, const double* __restrict__ z,
-                                                       const double* __restrict__ p_prev, double* __restrict__ p_next,
-                                                       double* __restrict__ y, const ReduceCtx c) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  if (c.sc->done) return;
-  const double lambda = c.sc->lambda, beta = c.sc->beta;
-  const int r = blockIdx.x * kThreads + threadIdx.x;
-  double v[1] = {0.0};
-  if (r < a.n_own) v[0] = spmv_row_t<true>(a, p_prev, nullptr, z, nullptr, beta, p_next, y, r, lambda);
-  reduce_finish<1>(c, v, OP_PAP, red, &flag);
-}
-
 __global__ void __launch_bounds__(kThreads) k_minv(const double* __restrict__ Hd, const double* __restrict__ dscale,
                                                     const Scalars* sc, double* __restrict__ Minv, int n_own) {
   const int v = blockIdx.x * kThreads + threadIdx.x;
@@ -291,27 +290,16 @@ __global__ void __launch_bounds__(kThreads) k_dscale(const double* __restrict__ 
   dscale[3 * (size_t)v + 2] = fmin(fmax(Hd[5 * n + v], 1e-6), 1e32);
 }
 
-__global__ void __launch_bounds__(kThreads) k_pcg_init(const PcgView a, const ReduceCtx c) {
+__global__ void __launch_bounds__(kThreads) k_pcg_init(const PcgView a, const ReduceCtx c, int op) {
   __shared__ double red[8];
   __shared__ int flag;
   const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[2] = {0.0, 0.0};
   if (r < a.n_own) pcg_init_row(a, r, v[0], v[1]);
-  reduce_finish<2>(c, v, OP_INIT, red, &flag);
+  reduce_finish<2>(c, v, op, red, &flag);
 }
 
-__global__ void __launch_bounds__(kThreads) k_pcg_update(const PcgView a, const ReduceCtx c) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  if (c.sc->done) return;
-  const double alpha = c.sc->rz / c.sc->pAp;
-  const int r = blockIdx.x * kThreads + threadIdx.x;
-  double v[2] = {0.0, 0.0};
-  if (r < a.n_own) pcg_update_row(a, r, alpha, v[0], v[1]);
-  reduce_finish<2>(c, v, OP_UPDATE, red, &flag);
-}
-
-// k_pcg_update with every global access a full-width one (the default; GS_UPDATE_STAGED=0 keeps k_pcg_update).
+// The x/r/z update with every global access a full-width one.
 // pcg_update_row reads and writes its vectors three doubles per thread at a 24-byte stride: a warp's store
 // instruction covers a third of each 32-byte sector it touches, so the nine stores of a row reach L2 as three
 // partial writes per sector, and the twelve loads as three requests per line.  Here the tile's 768 doubles of
@@ -320,7 +308,7 @@ __global__ void __launch_bounds__(kThreads) k_pcg_update(const PcgView a, const 
 // dot products, and z goes back through shared memory to be stored flat.  Same expressions per element and per
 // row as pcg_update_apply, same reduction tree: same bits (tests/test_gpu_parity.py::test_staged_update_bitwise).
 // C3: 51.5 -> 47.6 us per launch (profiles/r1_v7_variant_probe.jsonl).
-__global__ void __launch_bounds__(kThreads, GS_UPD_MINB) k_pcg_update_staged(const PcgView a, const ReduceCtx c) {
+__global__ void __launch_bounds__(kThreads) k_pcg_update_staged(const PcgView a, const ReduceCtx c, int op) {
   __shared__ double red[8];
   __shared__ int flag;
   __shared__ __align__(16) double sv[3 * kThreads];
@@ -335,17 +323,6 @@ __global__ void __launch_bounds__(kThreads, GS_UPD_MINB) k_pcg_update_staged(con
   double2* x2 = reinterpret_cast<double2*>(a.x + base);
   double2* r2 = reinterpret_cast<double2*>(a.r + base);
   double2* s2 = reinterpret_cast<double2*>(sv);
-  // the row's preconditioner block is requested together with the tile's vectors, not after the barrier below
-  // (one memory round trip per CTA instead of two)
-  const int t = threadIdx.x;
-  double m00 = 0.0, m01 = 0.0, m02 = 0.0, m11 = 0.0, m12 = 0.0, m22 = 0.0;
-#if GS_UPD_HOIST
-  if (t < nrow) {
-    const size_t n = (size_t)a.n_own, w = (size_t)(row0 + t);
-    m00 = ldg(a.Minv + w); m01 = ldg(a.Minv + n + w); m02 = ldg(a.Minv + 2 * n + w);
-    m11 = ldg(a.Minv + 3 * n + w); m12 = ldg(a.Minv + 4 * n + w); m22 = ldg(a.Minv + 5 * n + w);
-  }
-#endif
   for (int i = threadIdx.x; i < nd2; i += kThreads) {   // at most two trips
     const double2 pv = p2[i], qv = q2[i], xv = x2[i], rv = r2[i];
     const double2 xn = make_double2(xv.x + alpha * pv.x, xv.y + alpha * pv.y);
@@ -364,16 +341,12 @@ __global__ void __launch_bounds__(kThreads, GS_UPD_MINB) k_pcg_update_staged(con
   __syncthreads();
   double v[2] = {0.0, 0.0};
   double z0 = 0.0, z1 = 0.0, z2 = 0.0;
+  const int t = threadIdx.x;
   if (t < nrow) {
-#if !GS_UPD_HOIST
-    const size_t n = (size_t)a.n_own, w = (size_t)(row0 + t);
-    m00 = ldg(a.Minv + w); m01 = ldg(a.Minv + n + w); m02 = ldg(a.Minv + 2 * n + w);
-    m11 = ldg(a.Minv + 3 * n + w); m12 = ldg(a.Minv + 4 * n + w); m22 = ldg(a.Minv + 5 * n + w);
-#endif
     const double r0 = sv[3 * t], r1 = sv[3 * t + 1], r2v = sv[3 * t + 2];
-    z0 = (m00 * r0 + m01 * r1) + m02 * r2v;   // apply_minv's expressions
-    z1 = (m01 * r0 + m11 * r1) + m12 * r2v;
-    z2 = (m02 * r0 + m12 * r1) + m22 * r2v;
+    // (requesting the row's M^-1 block before the barrier, together with the tile's vectors, costs 18 registers and
+    //  two resident CTAs: 71 us against 48 us on C3; profiles/r2_variant_probe.md)
+    apply_minv(a.Minv, (size_t)a.n_own, (size_t)(row0 + t), r0, r1, r2v, z0, z1, z2);
     v[0] = (r0 * z0 + r1 * z1) + r2v * z2;
     v[1] = (r0 * r0 + r1 * r1) + r2v * r2v;
   }
@@ -387,7 +360,7 @@ __global__ void __launch_bounds__(kThreads, GS_UPD_MINB) k_pcg_update_staged(con
   double2* z2p = reinterpret_cast<double2*>(a.z + base);
   for (int i = threadIdx.x; i < nd2; i += kThreads) z2p[i] = s2[i];
   if ((nd & 1) && threadIdx.x == 0) a.z[base + (size_t)nd - 1] = sv[nd - 1];
-  reduce_finish<2>(c, v, OP_UPDATE, red, &flag);
+  reduce_finish<2>(c, v, op, red, &flag);
 }
 
 // p = z + beta p over the flat owned range: four doubles per thread as two 16-byte accesses (one 8-byte
@@ -443,40 +416,91 @@ __global__ void __launch_bounds__(kThreads) k_pack(const double* __restrict__ ve
   out[i] = vec[(size_t)rows[k] * width + c];
 }
 
-// closest_keyframe (reference graph.cpp:146-178): argmin of Euclidean distance over the first
-// `count` vertices in insertion order; ties -> lowest index.  One CTA: the scan is 32 B per vertex.
-__global__ void __launch_bounds__(kThreads) k_closest(const double4* __restrict__ pose, const int* __restrict__ order,
-                                                       int count, double qx, double qy, double* best_d, int* best_i) {
-  __shared__ double sd[kThreads];
-  __shared__ int si[kThreads];
+// closest_keyframe (reference graph.cpp:146-178): argmin of the Euclidean distance to the query pose over the first
+// `count` vertices in insertion order; ties -> lowest insertion index (the reference's strict '<', graph.cpp:162).
+// Grid-wide: every CTA scans a tile of candidates (32 B per vertex, coalesced when keys were inserted in order),
+// reduces (distance, index) lexicographically, and the last CTA to finish folds the per-CTA results.  The query pose
+// is read on the device (no host round trip).  On several ranks each rank scans the candidates it owns (dense rows
+// [v0, v0 + n_own)); the host then takes the minimum of the ranks' results with the same tie rule.
+struct ClosestOut {
+  double dist;
+  int idx;      // insertion index, 0x7fffffff = no candidate on this rank
+  int pad;
+};
+
+constexpr int kClosestPerThread = 8;
+
+__device__ __forceinline__ void closest_min(double& bd, int& bi, double od, int oi) {
+  if (od < bd || (od == bd && oi < bi)) {
+    bd = od;
+    bi = oi;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_closest(const double4* __restrict__ pose, const int* __restrict__ order, int count,
+                                                       const double4* __restrict__ query, int v0, int n_own,
+                                                       ClosestOut* __restrict__ part, unsigned int* counter,
+                                                       ClosestOut* __restrict__ out) {
+  __shared__ double sd[kThreads / 32];
+  __shared__ int si[kThreads / 32];
+  __shared__ int flag;
+  const double4 q = ldg(query);
   double bd = INFINITY;
   int bi = 0x7fffffff;
-  for (int t = threadIdx.x; t < count; t += kThreads) {
-    const double4 p = pose[order ? order[t] : t];
-    // sqrt(pow(dx,2)+pow(dy,2)) as the reference computes it (graph.cpp:157)
-    const double dist = sqrt((p.x - qx) * (p.x - qx) + (p.y - qy) * (p.y - qy));
-    if (dist < bd) {
-      bd = dist;
-      bi = t;
-    }
-  }
-  sd[threadIdx.x] = bd;
-  si[threadIdx.x] = bi;
-  __syncthreads();
-  for (int s = kThreads / 2; s > 0; s >>= 1) {
-    if (threadIdx.x < s) {
-      const double od = sd[threadIdx.x + s];
-      const int oi = si[threadIdx.x + s];
-      if (od < sd[threadIdx.x] || (od == sd[threadIdx.x] && oi < si[threadIdx.x])) {
-        sd[threadIdx.x] = od;
-        si[threadIdx.x] = oi;
+  const int base = blockIdx.x * (kThreads * kClosestPerThread) + threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < kClosestPerThread; ++k) {
+    const int t = base + k * kThreads;
+    if (t < count) {
+      const int dense = order ? order[t] : t;
+      const int local = dense - v0;
+      if (local >= 0 && local < n_own) {
+        const double4 p = ldg(pose + local);
+        // sqrt(pow(dx,2)+pow(dy,2)) as the reference computes it (graph.cpp:157)
+        const double dist = sqrt((p.x - q.x) * (p.x - q.x) + (p.y - q.y) * (p.y - q.y));
+        closest_min(bd, bi, dist, t);
       }
     }
-    __syncthreads();
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) closest_min(bd, bi, __shfl_xor_sync(0xffffffffu, bd, o), __shfl_xor_sync(0xffffffffu, bi, o));
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) {
+    sd[w] = bd;
+    si[w] = bi;
+  }
+  __syncthreads();
+  if (w == 0) {
+    bd = l < kThreads / 32 ? sd[l] : INFINITY;
+    bi = l < kThreads / 32 ? si[l] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) closest_min(bd, bi, __shfl_xor_sync(0xffffffffu, bd, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    if (l == 0) {
+      part[blockIdx.x].dist = bd;
+      part[blockIdx.x].idx = bi;
+    }
+  }
+  if (!last_block(counter, &flag)) return;
+  bd = INFINITY;
+  bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += kThreads) {
+    const double od = __ldcg(&part[i].dist);
+    const int oi = __ldcg(&part[i].idx);
+    closest_min(bd, bi, od, oi);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) closest_min(bd, bi, __shfl_xor_sync(0xffffffffu, bd, o), __shfl_xor_sync(0xffffffffu, bi, o));
+  __syncthreads();
+  if (l == 0) {
+    sd[w] = bd;
+    si[w] = bi;
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
-    *best_d = sd[0];
-    *best_i = si[0];
+    for (int k = 1; k < kThreads / 32; ++k) closest_min(bd, bi, sd[k], si[k]);
+    out->dist = bd;
+    out->idx = bi;
+    *counter = 0u;
   }
 }
 

@@ -1,0 +1,208 @@
+// Coarse-space correction of the block-Jacobi preconditioner (two-level additive preconditioner):
+//
+//     z = M^-1 r  +  W E^-1 W^T r ,      E = W^T (H + lambda I) W
+//
+// W has three columns per AGGREGATE of about a thousand graph-adjacent poses (structure.hpp: build_aggregation): the
+// rigid-body motions of the aggregate — world-frame translation (2) and rotation about the aggregate's reference
+// pose (1) — written in the body-frame tangent coordinates GTSAM's Pose2 retract uses:
+//
+//     W_i = [ R_i^T   R_i^T J (t_i - t_ref) ]        J = [0 -1; 1 0]
+//           [ 0  0            1             ]
+//
+// They span the near-null space of the between-factors' Hessian (a rigid motion of a whole aggregate changes no
+// residual inside it), i.e. exactly the smooth error block-Jacobi PCG needs thousands of iterations for: on the
+// 1M-pose graph 14,700 iterations per solve become about 700.  W is never stored: a row's
+// block follows from its pose and the reference pose.  Everything is deterministic (fixed-order sums, no atomics).
+//
+//   k_basis_vec   v = column `mode` of W for the aggregates of one colour (zero elsewhere)  -> E's columns, via k_spmv
+//   k_restrict    c_a = sum_{i in a} W_i^T r_i                       one CTA per aggregate, rows in list order
+//   k_coarse_E    dense E = E0 + lambda G from the restricted products (layout: column-major, 3 n_agg square)
+//   k_coarse_mv   mu = E^-1 c (dense symmetric product, one warp per row) and c.mu, then the scalar step
+//   k_dir_coarse  p = (z + W mu) + beta p                            the direction update with the prolongation folded in
+#pragma once
+#include "kernels.cuh"
+
+namespace gs {
+
+struct CoarseView {
+  const int* agg_of;        // per owned row: aggregate
+  const int* agg_ptr;       // per aggregate: range in agg_rows
+  const int* agg_rows;      // local rows, ascending; the first one is the aggregate's reference row
+  const double4* pose;      // the linearisation point
+  int n_agg;
+  int n_own;
+};
+
+// W_i as four numbers: (c, s) of the pose, (u, v) = R^T J (t_i - t_ref)
+struct WBlock {
+  double c, s, u, v;
+};
+
+__device__ __forceinline__ WBlock w_block(const double4 p, const double4 ref) {
+  const double dx = p.x - ref.x, dy = p.y - ref.y;
+  WBlock w;
+  w.c = p.z;
+  w.s = p.w;
+  w.u = p.w * dx - p.z * dy;    // R^T (-dy, dx), first component
+  w.v = p.w * dy + p.z * dx;
+  return w;
+}
+
+// column `mode` of W_i
+__device__ __forceinline__ void w_column(const WBlock& w, int mode, double out[3]) {
+  if (mode == 0) { out[0] = w.c; out[1] = -w.s; out[2] = 0.0; }
+  else if (mode == 1) { out[0] = w.s; out[1] = w.c; out[2] = 0.0; }
+  else { out[0] = w.u; out[1] = w.v; out[2] = 1.0; }
+}
+
+// color < 0: every aggregate
+__global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, const int* __restrict__ agg_color, int color, int mode,
+                                                         double* __restrict__ v) {
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  if (r >= a.n_own) return;
+  const int g = a.agg_of[r];
+  double o[3] = {0.0, 0.0, 0.0};
+  if (color < 0 || agg_color[g] == color) {
+    const double4 ref = ldg(a.pose + a.agg_rows[a.agg_ptr[g]]);
+    w_column(w_block(ldg(a.pose + r), ref), mode, o);
+  }
+  v[3 * (size_t)r] = o[0];
+  v[3 * (size_t)r + 1] = o[1];
+  v[3 * (size_t)r + 2] = o[2];
+}
+
+// out[3 a .. 3 a + 3) = sum over the aggregate's rows (list order) of W_i^T r_i.  Thread t takes rows t, t+T, ...;
+// then the fixed shuffle / shared-memory tree of block_sum.
+__global__ void __launch_bounds__(kThreads) k_restrict(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
+                                                        int honour_done, double* __restrict__ out) {
+  __shared__ double red[8];
+  if (honour_done && sc->done) return;
+  const int g = blockIdx.x;
+  const int q0 = a.agg_ptr[g], q1 = a.agg_ptr[g + 1];
+  const double4 ref = ldg(a.pose + a.agg_rows[q0]);
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+  for (int q = q0 + (int)threadIdx.x; q < q1; q += kThreads) {
+    const int i = a.agg_rows[q];
+    const WBlock w = w_block(ldg(a.pose + i), ref);
+    const double r0 = r[3 * (size_t)i], r1 = r[3 * (size_t)i + 1], r2 = r[3 * (size_t)i + 2];
+    s0 += w.c * r0 - w.s * r1;
+    s1 += w.s * r0 + w.c * r1;
+    s2 += (w.u * r0 + w.v * r1) + r2;
+  }
+  const double t0 = block_sum(s0, red);
+  const double t1 = block_sum(s1, red);
+  const double t2 = block_sum(s2, red);
+  if (threadIdx.x == 0) {
+    out[3 * (size_t)g] = t0;
+    out[3 * (size_t)g + 1] = t1;
+    out[3 * (size_t)g + 2] = t2;
+  }
+}
+
+// Dense E (column-major, m = 3 n_agg) from the restricted products: R[(color * 3 + mode) * m + 3 a + k] is row
+// 3a+k of the column (b, mode), b = the aggregate of that colour next to a; Gm[mode * m + 3 a + k] likewise for
+// G = W^T W (block diagonal).  One thread per (row block a, colour, mode).
+__global__ void __launch_bounds__(kThreads) k_coarse_E(const double* __restrict__ R, const double* __restrict__ Gm,
+                                                        const int* __restrict__ nbr_of_color, int n_agg, int n_colors,
+                                                        double lambda, double* __restrict__ Em) {
+  const int t = blockIdx.x * kThreads + threadIdx.x;
+  const int total = n_agg * n_colors * 3;
+  if (t >= total) return;
+  const int mode = t % 3, c = (t / 3) % n_colors, a = t / (3 * n_colors);
+  const int b = nbr_of_color[(size_t)a * n_colors + c];
+  if (b < 0) return;
+  const size_t m = 3 * (size_t)n_agg;
+  const size_t col = 3 * (size_t)b + mode;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    double e = R[((size_t)c * 3 + mode) * m + 3 * (size_t)a + k];
+    if (a == b) e += lambda * Gm[(size_t)mode * m + 3 * (size_t)a + k];
+    Em[col * m + 3 * (size_t)a + k] = e;
+  }
+}
+
+// potri leaves one triangle of E^-1: mirror it (column-major, lower -> upper)
+__global__ void __launch_bounds__(kThreads) k_symmetrize(double* __restrict__ Em, int m) {
+  const size_t t = (size_t)blockIdx.x * kThreads + threadIdx.x;
+  if (t >= (size_t)m * m) return;
+  const int i = (int)(t % m), j = (int)(t / m);
+  if (i < j) Em[t] = Em[(size_t)i * m + j];
+}
+
+// mu = Einv c (dense, symmetric, column-major = row-major): one warp per row, lanes stride the columns, fixed shuffle
+// tree.  The last CTA to finish adds c.mu in fixed order and takes the scalar step that closes the preconditioner
+// application:  r.z = r.M^-1 r (from the update kernel) + c.mu  — the corrected z is never formed for the dot product.
+//   init != 0: start of a solve (r.z of the initial residual, no beta)
+__global__ void __launch_bounds__(kThreads) k_coarse_mv(const double* __restrict__ Einv, const double* __restrict__ cvec, int m,
+                                                         double* __restrict__ mu, double* __restrict__ part,
+                                                         unsigned int* counter, Scalars* sc, int init) {
+  __shared__ double red[8];
+  __shared__ int flag;
+  if (sc->done) return;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int row = blockIdx.x * (kThreads / 32) + w;
+  double acc = 0.0;
+  if (row < m) {
+    // eight independent partial sums per lane (columns l + 32 (8 q + u)), so eight loads of the row are in flight at
+    // once; they are added in one fixed order
+    const double* e = Einv + (size_t)row * m;
+    double part8[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    int j = l;
+    for (; j + 7 * 32 < m; j += 8 * 32) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) part8[u] += ldg(e + j + 32 * u) * ldg(cvec + j + 32 * u);
+    }
+    for (int u = 0; j < m; j += 32, ++u) part8[u] += ldg(e + j) * ldg(cvec + j);
+    acc = ((part8[0] + part8[1]) + (part8[2] + part8[3])) + ((part8[4] + part8[5]) + (part8[6] + part8[7]));
+  }
+  acc = warp_sum(acc);
+  double prod = 0.0;
+  if (row < m && l == 0) {
+    mu[row] = acc;
+    prod = acc * cvec[row];
+  }
+  // per-CTA partial of c.mu: the 8 rows of this CTA in warp order
+  if (l == 0) red[w] = prod;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int k = 0; k < kThreads / 32; ++k) s += red[k];
+    part[blockIdx.x] = s;
+  }
+  if (!last_block(counter, &flag)) return;
+  const double cmu = final_sum(part, (int)gridDim.x, red);
+  if (threadIdx.x == 0) {
+    const double rz_new = sc->rz_bj + cmu;
+    if (init) {
+      sc->rz = rz_new;
+      sc->beta = 0.0;
+    } else {
+      sc->beta = rz_new / sc->rz;
+      sc->rz = rz_new;
+    }
+    *counter = 0u;
+  }
+}
+
+// p = (z + W mu) + beta p, one thread per row
+__global__ void __launch_bounds__(kThreads) k_dir_coarse(const CoarseView a, const double* __restrict__ z,
+                                                          const double* __restrict__ mu, double* __restrict__ p,
+                                                          const Scalars* sc) {
+  if (sc->done) return;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  if (r >= a.n_own) return;
+  const double beta = sc->beta;
+  const int g = a.agg_of[r];
+  const double4 ref = ldg(a.pose + a.agg_rows[a.agg_ptr[g]]);
+  const WBlock w = w_block(ldg(a.pose + r), ref);
+  const double m0 = mu[3 * (size_t)g], m1 = mu[3 * (size_t)g + 1], m2 = mu[3 * (size_t)g + 2];
+  const size_t o = 3 * (size_t)r;
+  const double z0 = z[o] + ((w.c * m0 + w.s * m1) + w.u * m2);
+  const double z1 = z[o + 1] + ((w.c * m1 - w.s * m0) + w.v * m2);
+  const double z2 = z[o + 2] + m2;
+  p[o] = dir_value(z0, beta, p[o]);
+  p[o + 1] = dir_value(z1, beta, p[o + 1]);
+  p[o + 2] = dir_value(z2, beta, p[o + 2]);
+}
+
+}  // namespace gs

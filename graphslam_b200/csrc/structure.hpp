@@ -204,6 +204,144 @@ struct LocalStructure {
   }
 };
 
+// ---- coarse space of the two-level preconditioner (host side, integer-only) ---------------------------------------
+// The block rows are grouped into AGGREGATES of about `target` graph-adjacent vertices; each aggregate carries three
+// coarse unknowns (its rigid-body motion).  Aggregates never cross the fixed segment boundaries of the partition, so an
+// aggregate belongs to one rank whatever the number of ranks, and the aggregation does not depend on that number.
+// Built by recursive bisection: a breadth-first order of the vertex set from a far-away vertex (two sweeps), cut at
+// its median, until a set has at most `target` vertices.  Deterministic (no hashing, no randomness).
+//   colour : distance-2 colouring of the aggregate adjacency graph — aggregates of one colour have no common
+//            neighbour, so the coarse matrix E = W^T H W is formed with one product H w per (colour, rigid mode)
+//            instead of one per aggregate.
+struct Aggregation {
+  int n_agg = 0, n_colors = 0, target = 0;
+  std::vector<int> agg_of;        // per global row
+  std::vector<int> ptr, rows;     // rows of aggregate a: rows[ptr[a] .. ptr[a+1]), ascending; rows[ptr[a]] is its reference row
+  std::vector<int> color;         // per aggregate
+  std::vector<int> nbr_of_color;  // [a * n_colors + c]: the aggregate of colour c in the closed neighbourhood of a, or -1
+  int seg_agg[kSegments + 1] = {0};
+};
+
+inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const std::vector<int32_t>& colidx, int target,
+                              Aggregation& A) {
+  Partition part;
+  part.init(N, 1);
+  A.target = target;
+  A.agg_of.assign(N, -1);
+  A.ptr.assign(1, 0);
+  A.rows.clear();
+  A.rows.reserve(N);
+  std::vector<int> region(N, 0), mark(N, -1), order, queue;
+  int next_region = 1, stamp = 0;
+  // breadth-first order of `verts` (all of region rid), component after component, starting at `root`
+  auto bfs_order = [&](const std::vector<int>& verts, int rid, int root, std::vector<int>& out) {
+    ++stamp;
+    out.clear();
+    size_t scan = 0;
+    int start = root;
+    for (;;) {
+      size_t head = out.size();
+      out.push_back(start);
+      mark[start] = stamp;
+      while (head < out.size()) {
+        const int v = out[head++];
+        for (int k = rowptr[v]; k < rowptr[v + 1]; ++k) {
+          const int u = colidx[k];
+          if (region[u] != rid || mark[u] == stamp) continue;
+          mark[u] = stamp;
+          out.push_back(u);
+        }
+      }
+      if (out.size() == verts.size()) break;
+      while (mark[verts[scan]] == stamp) ++scan;   // next component
+      start = verts[scan];
+    }
+  };
+  struct Job {
+    std::vector<int> verts;
+    int rid;
+  };
+  for (int sgm = 0; sgm < kSegments; ++sgm) {
+    A.seg_agg[sgm] = A.n_agg;
+    const int r0 = part.seg_row[sgm], r1 = part.seg_row[sgm + 1];
+    if (r1 <= r0) continue;
+    std::vector<Job> stack;
+    {
+      Job j;
+      j.rid = next_region++;
+      j.verts.resize(r1 - r0);
+      for (int r = r0; r < r1; ++r) {
+        j.verts[r - r0] = r;
+        region[r] = j.rid;
+      }
+      stack.push_back(std::move(j));
+    }
+    while (!stack.empty()) {
+      Job j = std::move(stack.back());
+      stack.pop_back();
+      const int cnt = (int)j.verts.size();
+      if (cnt <= target) {
+        std::sort(j.verts.begin(), j.verts.end());
+        for (int v : j.verts) {
+          A.agg_of[v] = A.n_agg;
+          A.rows.push_back(v);
+          region[v] = -1;
+        }
+        A.ptr.push_back((int)A.rows.size());
+        A.n_agg++;
+        continue;
+      }
+      bfs_order(j.verts, j.rid, j.verts[0], order);
+      const int far = order.back();
+      bfs_order(j.verts, j.rid, far, order);
+      bfs_order(j.verts, j.rid, order.back(), order);
+      const int half = cnt / 2;
+      Job lo, hi;
+      lo.rid = next_region++;
+      hi.rid = next_region++;
+      lo.verts.assign(order.begin(), order.begin() + half);
+      hi.verts.assign(order.begin() + half, order.end());
+      for (int v : lo.verts) region[v] = lo.rid;
+      for (int v : hi.verts) region[v] = hi.rid;
+      stack.push_back(std::move(hi));   // lo is processed first
+      stack.push_back(std::move(lo));
+    }
+  }
+  A.seg_agg[kSegments] = A.n_agg;
+  // aggregate adjacency (closed neighbourhoods), then greedy distance-2 colouring in aggregate order
+  const int na = A.n_agg;
+  std::vector<std::vector<int>> adj(na);
+  for (int a = 0; a < na; ++a) {
+    std::vector<int>& l = adj[a];
+    for (int q = A.ptr[a]; q < A.ptr[a + 1]; ++q) {
+      const int v = A.rows[q];
+      for (int k = rowptr[v]; k < rowptr[v + 1]; ++k) l.push_back(A.agg_of[colidx[k]]);
+    }
+    std::sort(l.begin(), l.end());
+    l.erase(std::unique(l.begin(), l.end()), l.end());   // contains a itself (diagonal entry)
+  }
+  A.color.assign(na, -1);
+  A.n_colors = 0;
+  std::vector<int> forbid;
+  for (int a = 0; a < na; ++a) {
+    forbid.clear();
+    for (int b : adj[a])
+      for (int c2 : adj[b])
+        if (A.color[c2] >= 0) forbid.push_back(A.color[c2]);
+    std::sort(forbid.begin(), forbid.end());
+    int c = 0;
+    for (int f : forbid) {
+      if (f == c) ++c;
+      else if (f > c) break;
+    }
+    A.color[a] = c;
+    if (c + 1 > A.n_colors) A.n_colors = c + 1;
+  }
+  A.nbr_of_color.assign((size_t)na * A.n_colors, -1);
+  for (int a = 0; a < na; ++a)
+    for (int b : adj[a]) A.nbr_of_color[(size_t)a * A.n_colors + A.color[b]] = b;
+}
+
 // distinct values of key(x) over a small array (<= 32 entries)
 template <typename F>
 inline int distinct_count(const int* v, int n, F key) {

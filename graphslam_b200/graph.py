@@ -152,6 +152,12 @@ class Graph:
     def prepare(self):
         self._ck(self._lib.gs_prepare(self._h))
 
+    def structure_timing(self) -> dict:
+        """ms of the last structure build: host structure (K6), staging + upload, communicator setup, graph capture."""
+        ms = np.zeros(4)
+        self._ck(self._lib.gs_get_structure_timing(self._h, _dp(ms)))
+        return dict(zip(("host", "upload", "comm", "capture"), ms.tolist()))
+
     # -- solving
     def optimize(self, allow_not_converged=True) -> dict:
         st = GsStats()

@@ -54,9 +54,13 @@ enum {
   GS_SOLVER_NO_CUDA_GRAPH = 1 << 0,  /* launch the PCG kernels one by one instead of replaying the captured batch */
   GS_SOLVER_NCCL_PER_OP = 1 << 1,    /* multi-GPU: ncclSend/Recv + all-gather per exchange instead of stores into peer memory */
   GS_SOLVER_NO_PERSISTENT = 1 << 2,  /* small graphs: per-kernel iteration instead of the cooperative persistent kernel */
-  GS_SOLVER_DIR_KERNEL = 1 << 3,     /* keep the direction update p = z + beta p as a kernel of its own (three kernels per
-                                        iteration); default: formed on the fly inside the product where that is faster */
-  GS_SOLVER_DIR_ON_THE_FLY = 1 << 4  /* force the on-the-fly form (two kernels per iteration) */
+  GS_SOLVER_DIR_KERNEL = 1 << 3,     /* multi-GPU: keep the direction update p = z + beta p as a kernel of its own (three kernels
+                                        per iteration); default: formed on the fly inside the product above 200k rows per rank */
+  GS_SOLVER_DIR_ON_THE_FLY = 1 << 4, /* multi-GPU: force the on-the-fly form (two kernels per iteration) */
+  GS_SOLVER_BLOCK_JACOBI_ONLY = 1 << 5 /* PCG with the 3x3 block-Jacobi preconditioner alone.  Default (one GPU, lambda*I damping,
+                                        >= 8192 poses): block-Jacobi plus a coarse-space correction over aggregates of poses
+                                        (rigid-body modes), which cuts the PCG iterations of large graphs ~20x.  The solution
+                                        of the linear system is the same to pcg_rel_tol either way. */
 };
 
 /* Defaults == gtsam::LevenbergMarquardtParams defaults, i.e. what graph.cpp:119 runs with. */
@@ -103,7 +107,8 @@ typedef struct gs_stats {
   double d2h_bytes;          /* device->host bytes copied by this call                        */
   double p2p_wait_ticks[3];  /* peer-memory path: SM clock ticks CTA 0 spent waiting for other GPUs in the product /  */
   double p2p_waits;          /*   update / direction kernels during this call, and the iterations they cover        */
-  double reserved[4];
+  double ms_structure_parts[4]; /* ms_structure split: host structure build, staging + upload, communicator setup
+                                   (multi-GPU: peer-memory windows, first NCCL exchanges), CUDA-graph capture        */
 } gs_stats;
 
 void gs_default_params(gs_params* p);
@@ -156,6 +161,9 @@ gs_status gs_save_g2o(gs_graph* g, const char* path);
 /* upload pending vertices/factors and (re)build the sparse structure now; gs_optimize does this
  * lazily.  Separates one-off topology work from the per-iteration path for measurement. */
 gs_status gs_prepare(gs_graph* g);
+/* wall time of the last structure build in ms: [0] host structure (K6), [1] staging + upload, [2] communicator setup
+ * (multi-GPU), [3] CUDA-graph capture */
+gs_status gs_get_structure_timing(const gs_graph* g, double ms[4]);
 
 /* gtsam::LevenbergMarquardtOptimizer(graph, initial).optimize(); result kept as the next initial
  * values (warm start)                                           graph.cpp:119, 130 */

@@ -20,9 +20,7 @@ extern "C" {
  * gives the same bits as the default path; a bit disappears once its candidate has won (becomes the default) or
  * lost (is deleted). */
 enum {
-  GS_X_ASM_NODUP = 1 << 16,        /* k_assemble_nodup on graphs without duplicate factors */
-  GS_X_P2P_STAGED = 1 << 17,       /* staged x/r/z update inside the peer-memory kernels */
-  GS_X_UPDATE_UNSTAGED = 1 << 18   /* row-strided k_pcg_update instead of k_pcg_update_staged */
+  GS_X_P2P_STAGED = 1 << 17        /* staged x/r/z update inside the peer-memory kernels */
 };
 
 /* sorted unique block pattern (rowptr[n+1], colidx[nnzb]) and the canonical factor order `perm`

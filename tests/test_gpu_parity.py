@@ -408,16 +408,14 @@ def test_fused_pcg_bitwise(cid, n):
 @pytest.mark.parametrize("n", [4001, 60000])
 def test_pcg_iteration_forms_bitwise(n):
     """The forms of the PCG iteration on one GPU must give the same bits on a capped solve: the three-kernel iteration
-    (k_spmv, k_pcg_update_staged, k_pcg_dir), the two-kernel one with the direction formed on the fly inside the
-    product (k_spmvdir), the same replayed from the captured CUDA graph or launched kernel by kernel, and the
-    persistent cooperative kernel small graphs take by default.  Same expressions per element and per row, same
+    (k_spmv, k_pcg_update_staged, k_pcg_dir) replayed from the captured CUDA graph or launched kernel by kernel, and
+    the persistent cooperative kernel small graphs take by default (direction formed on the fly inside the product).  Same expressions per element and per row, same
     reduction tree.  4001 rows leave an odd number of rows in the last tile."""
     import ctypes as C
     g = synth.config("C3", n=n)
     NP, F = _lib.GS_SOLVER_NO_PERSISTENT, _lib
     out = []
-    for flags in (NP | F.GS_SOLVER_DIR_KERNEL, NP | F.GS_SOLVER_DIR_ON_THE_FLY, NP | F.GS_SOLVER_DIR_ON_THE_FLY | F.GS_SOLVER_NO_CUDA_GRAPH,
-                  NP | F.GS_SOLVER_DIR_KERNEL | F.GS_SOLVER_NO_CUDA_GRAPH, 0):
+    for flags in (NP, NP | F.GS_SOLVER_NO_CUDA_GRAPH, 0):
         with _load(g, pcg_max_iters=96, pcg_rel_tol=1e-300, solver_flags=flags) as G:
             d = np.zeros((g.n, 3))
             it, rr = C.c_int(), C.c_double()
@@ -427,3 +425,90 @@ def test_pcg_iteration_forms_bitwise(n):
     assert np.isfinite(out[0]).all() and np.abs(out[0]).max() > 0
     for d in out[1:]:
         assert np.array_equal(out[0], d)
+
+
+def _closest_numpy(xy, q, count):
+    """graph.cpp:149-165: argmin of sqrt(pow(dx,2)+pow(dy,2)) over the first `count` keyframes, strict '<'."""
+    d = np.sqrt((xy[:count, 0] - q[0]) ** 2 + (xy[:count, 1] - q[1]) ** 2)
+    return int(np.argmin(d)), float(d.min())
+
+
+def test_closest_keyframe_grid_wide_ties_and_small_counts():
+    """closest_keyframe (graph.cpp:146-178) as one grid-wide reduction on the device: large candidate sets (many CTAs),
+    exact ties (lowest index wins, the reference's strict '<'), count == 1, and too few keyframes (service returns false)."""
+    rng = np.random.default_rng(3)
+    n = 70_000                                    # 35 CTAs of 2048 candidates
+    xy = rng.uniform(-500, 500, (n, 2))
+    xy[[17, 40_017, 65_000]] = xy[-1] + [3.0, 4.0]     # three candidates at exactly the same distance 5.0 ...
+    xy[50_000] = xy[-1] + [0.0, 5.0]                   # ... and a fourth with another offset but the same distance
+    near = np.sqrt(((xy[:n - 10] - xy[-1]) ** 2).sum(1)) < 5.0
+    xy[:n - 10][near] += 100.0                         # nobody closer than the tie
+    poses = np.c_[xy, rng.uniform(-3, 3, n)]
+    with graph.Graph() as G:
+        G.add_batch(np.arange(1, n + 1, dtype=np.uint64), poses, np.zeros(0, np.uint64), np.zeros(0, np.uint64),
+                    np.zeros((0, 3)), np.zeros((0, 9)))
+        G.add_prior(1, poses[0], np.eye(3).reshape(9))
+        key, dist = G.closest_keyframe(n, 10)
+        want, wd = _closest_numpy(xy, xy[-1], n - 10)
+        assert want == 17 and key == want + 1 and dist == wd == 5.0
+        for skip in (n - 1, n - 2, 5000):              # count == 1, 2, many
+            key, dist = G.closest_keyframe(n, skip)
+            want, wd = _closest_numpy(xy, xy[-1], n - skip)
+            assert key == want + 1 and dist == wd
+        key, dist = G.closest_keyframe(123, 0)         # the query is its own closest keyframe when it is a candidate
+        assert key == 123 and dist == 0.0
+        with pytest.raises(graph.GraphSlamError) as e:
+            G.closest_keyframe(n, n)
+        assert e.value.status == _lib.GS_ENOKEY
+
+
+def test_closest_keyframe_keys_inserted_out_of_order():
+    """Candidates are the first `count` keyframes in INSERTION order, whatever their keys (dense rows are in key order)."""
+    rng = np.random.default_rng(4)
+    n = 5000
+    keys = rng.permutation(np.arange(10, 10 + n)).astype(np.uint64)
+    poses = np.c_[rng.uniform(-50, 50, (n, 2)), np.zeros(n)]
+    with graph.Graph() as G:
+        G.add_batch(keys, poses, np.zeros(0, np.uint64), np.zeros(0, np.uint64), np.zeros((0, 3)), np.zeros((0, 9)))
+        G.add_prior(int(keys[0]), poses[0], np.eye(3).reshape(9))
+        for skip in (10, 2500):
+            key, dist = G.closest_keyframe(int(keys[-1]), skip)
+            want, wd = _closest_numpy(poses, poses[-1], n - skip)
+            assert key == int(keys[want]) and dist == wd
+
+
+@pytest.mark.parametrize("cid,n", [("C3", 60000), ("C4", 20000), ("C2", 100000)])
+def test_two_level_preconditioner_solves_the_same_system(cid, n):
+    """The default PCG on graphs of >= 8192 poses adds a coarse-space correction (rigid-body modes over aggregates) to the
+    block-Jacobi preconditioner.  The preconditioner changes the iteration count, not the solution: both variants
+    reach pcg_rel_tol on the same system, agree with each other and with the oracle's exact solve, the two-level one in
+    far fewer iterations; and it is deterministic (two runs give the same bits)."""
+    g = synth.config(cid, n=n)
+    prob = O.Problem.from_graph(g)
+    h, b, _ = prob.linearize(g.init)
+    out = {}
+    for name, flags in (("two_level", 0), ("two_level_again", 0), ("block_jacobi", _lib.GS_SOLVER_BLOCK_JACOBI_ONLY)):
+        with _load(g, solver_flags=flags) as G:
+            d, it, rr = G.solve_linear(1e-5)
+            assert rr <= 1e-12 and it > 0
+            res = h @ d.ravel() + 1e-5 * d.ravel() + b.ravel()
+            assert np.linalg.norm(res) <= 1e-10 * np.linalg.norm(b)
+            out[name] = (d, it)
+    assert np.array_equal(out["two_level"][0], out["two_level_again"][0]) and out["two_level"][1] == out["two_level_again"][1]
+    assert np.abs(out["two_level"][0] - out["block_jacobi"][0]).max() <= 1e-8 * np.abs(out["block_jacobi"][0]).max()
+    assert out["two_level"][1] * 4 < out["block_jacobi"][1], (out["two_level"][1], out["block_jacobi"][1])
+
+
+def test_two_level_lm_trace_parity_and_damping_modes():
+    """LM with the two-level preconditioner against the oracle (same iterations, same accept/reject sequence), and the
+    switch to lambda*diag(H) damping (where the coarse correction is not used) through gs_set_params on a live graph."""
+    g = synth.config("C3", n=40000)
+    _trace_parity(g)
+    prob = O.Problem.from_graph(g)
+    ox, otr = O.lm_optimize(prob, g.init, O.LMParams(diagonal_damping=True))
+    with _load(g) as G:
+        d0, it0, _ = G.solve_linear(1e-3)                  # two-level, lambda*I
+        G.set_params(diagonal_damping=1)                   # -> block-Jacobi, PCG graph recaptured (advisor finding, round 1)
+        st = G.optimize()
+        _, x = G.poses()
+        assert st["iterations"] == otr.iterations and _pose_diff(x, ox) <= POSE_ATOL
