@@ -22,6 +22,7 @@
 #include <cstring>
 #include <exception>
 #include <limits>
+#include <mutex>
 #include <new>
 #include <string>
 #include <unordered_map>
@@ -171,7 +172,7 @@ struct gs_graph {
   DevBuf<int> d_agg_of, d_agg_ptr, d_agg_rows, d_agg_color, d_nbr_of_color;
   DevBuf<double> d_cvec, d_mu, d_cpart, d_R, d_G, d_E, d_chol_work, d_basis;
   DevBuf<int> d_chol_info;
-  cusolverDnHandle_t cusolver = nullptr;
+  DevBuf<double2> d_agg_ref;
   int chol_lwork = 0;
   bool coarse_e0_valid = false;           // R (= W^T H W by columns) and G computed at the current linearisation
   double coarse_lambda = -1.0;            // the lambda d_E (= E^-1) was built for; < 0: none
@@ -292,12 +293,31 @@ gs::PcgView pcg_view(gs_graph* g) {
 
 bool coarse_active(const gs_graph* g) { return g->coarse && !g->prm.diagonal_damping; }
 
+// cuSOLVER handles are expensive to create (~0.5 s with the libraries' own initialisation): one per device for the
+// process, used under a lock with the calling graph's stream
+struct SolverPool {
+  std::mutex mu;
+  cusolverDnHandle_t h[64] = {nullptr};
+};
+SolverPool& solver_pool() {
+  static SolverPool p;
+  return p;
+}
+cusolverDnHandle_t device_cusolver() {   // call with solver_pool().mu held
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  SolverPool& p = solver_pool();
+  if (!p.h[dev] && cusolverDnCreate(&p.h[dev]) != CUSOLVER_STATUS_SUCCESS) p.h[dev] = nullptr;
+  return p.h[dev];
+}
+
 gs::CoarseView coarse_view(gs_graph* g) {
   gs::CoarseView c;
   c.agg_of = g->d_agg_of.p;
   c.agg_ptr = g->d_agg_ptr.p;
   c.agg_rows = g->d_agg_rows.p;
   c.pose = g->d_pose_lin.p;
+  c.ref = g->d_agg_ref.p;
   c.n_agg = g->agg.n_agg;
   c.n_own = g->n_own;
   return c;
@@ -442,7 +462,7 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     if (stage == 1) {
       gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), gs::OP_UPDATE_2L);
       gs::k_restrict<<<g->agg.n_agg, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p);
-      gs::k_coarse_mv<<<(m + 7) / 8, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
+      gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
                                                                     g->d_counter.p + 6, g->d_sc.p, 0);
     } else {
       gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
@@ -741,7 +761,12 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (g->coarse) {
     std::vector<int32_t> rp, ci;
     gs::global_pattern(N, E, g->di.data(), g->dj.data(), rp, ci);
-    gs::build_aggregation(N, rp, ci, std::max(128, (N + 1023) / 1024), g->agg);
+    // about sqrt(N) aggregates of about sqrt(N) poses: the dense coarse product (9 n_agg^2 doubles per PCG iteration)
+    // stays a fraction of the fine-level traffic (~600 N bytes) at every size; at most 1024 aggregates
+    int target = g->prm.coarse_aggregate_size > 0 ? g->prm.coarse_aggregate_size
+                                                  : std::max(128, (int)std::ceil(std::sqrt((double)N)));
+    target = std::max(target, (N + 4095) / 4096);   // the dense coarse inverse is (3 n_agg)^2 doubles: at most 1.2 GB
+    gs::build_aggregation(N, rp, ci, target, g->agg);
   }
   const double t_host = now_ms();
   g->prep_ms[0] = t_host - t0;
@@ -829,20 +854,20 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     if (gs_status s = upload(g, g->d_nbr_of_color, A.nbr_of_color)) return s;
     GS_CUDA(g, g->d_cvec.alloc(m));
     GS_CUDA(g, g->d_mu.alloc(m));
-    GS_CUDA(g, g->d_cpart.alloc((m + 7) / 8 + 1));
+    GS_CUDA(g, g->d_cpart.alloc(m / gs::kCoarseRows + 2));
     GS_CUDA(g, g->d_R.alloc((size_t)A.n_colors * 3 * m));
     GS_CUDA(g, g->d_G.alloc(3 * m));
     GS_CUDA(g, g->d_E.alloc(m * m));
     GS_CUDA(g, g->d_basis.alloc(nl3));
     GS_CUDA(g, g->d_pose_lin.alloc(std::max(g->n_loc, 1)));
     GS_CUDA(g, g->d_chol_info.alloc(1));
-    if (!g->cusolver) {
-      if (cusolverDnCreate(&g->cusolver) != CUSOLVER_STATUS_SUCCESS) return g->fail(GS_ECUDA, "cusolverDnCreate failed");
-      cusolverDnSetStream(g->cusolver, g->stream);
-    }
+    GS_CUDA(g, g->d_agg_ref.alloc((size_t)A.n_agg));
+    std::lock_guard<std::mutex> lock(solver_pool().mu);
+    cusolverDnHandle_t hs = device_cusolver();
+    if (!hs) return g->fail(GS_ECUDA, "cusolverDnCreate failed");
     int l1 = 0, l2 = 0;
-    if (cusolverDnDpotrf_bufferSize(g->cusolver, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l1) != CUSOLVER_STATUS_SUCCESS ||
-        cusolverDnDpotri_bufferSize(g->cusolver, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l2) != CUSOLVER_STATUS_SUCCESS)
+    if (cusolverDnDpotrf_bufferSize(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l1) != CUSOLVER_STATUS_SUCCESS ||
+        cusolverDnDpotri_bufferSize(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l2) != CUSOLVER_STATUS_SUCCESS)
       return g->fail(GS_ECUDA, "cusolver workspace query failed");
     g->chol_lwork = std::max(l1, l2);
     GS_CUDA(g, g->d_chol_work.alloc((size_t)std::max(g->chol_lwork, 1)));
@@ -900,6 +925,8 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
   if (!g->coarse_e0_valid) {
     GS_CUDA(g, cudaMemcpyAsync(g->d_pose_lin.p, g->d_pose.p, sizeof(double4) * (size_t)g->n_loc, cudaMemcpyDeviceToDevice, g->stream));
     const gs::CoarseView cv = coarse_view(g);
+    gs::k_agg_ref<<<(A.n_agg + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(g->d_agg_ptr.p, g->d_agg_rows.p,
+                                                                                             g->d_pose_lin.p, A.n_agg, g->d_agg_ref.p);
     for (int c = 0; c < A.n_colors; ++c)
       for (int mode = 0; mode < 3; ++mode) {
         gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, c, mode, g->d_basis.p);
@@ -920,7 +947,10 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
     const int total = A.n_agg * A.n_colors * 3;
     gs::k_coarse_E<<<(total + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(
         g->d_R.p, g->d_G.p, g->d_nbr_of_color.p, A.n_agg, A.n_colors, lambda, g->d_E.p);
-    if (cusolverDnDpotrf(g->cusolver, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
+    std::lock_guard<std::mutex> lock(solver_pool().mu);
+    cusolverDnHandle_t hs = device_cusolver();
+    if (!hs || cusolverDnSetStream(hs, g->stream) != CUSOLVER_STATUS_SUCCESS) return g->fail(GS_ECUDA, "cuSOLVER handle unavailable");
+    if (cusolverDnDpotrf(hs, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
         CUSOLVER_STATUS_SUCCESS)
       return g->fail(GS_ECUDA, "cusolverDnDpotrf failed");
     int info = 0;
@@ -929,7 +959,7 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
     if (info != 0)
       return g->fail(GS_ENAN, "coarse matrix of the two-level preconditioner is not positive definite (leading minor %d): is the "
                               "graph anchored by a prior?", info);
-    if (cusolverDnDpotri(g->cusolver, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
+    if (cusolverDnDpotri(hs, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
         CUSOLVER_STATUS_SUCCESS)
       return g->fail(GS_ECUDA, "cusolverDnDpotri failed");
     const size_t mm = (size_t)m * m;
@@ -1001,7 +1031,7 @@ void launch_pcg_setup(gs_graph* g) {
   if (two) {   // p(0) = z(0) = M^-1 r + W E^-1 W^T r
     const int m = 3 * g->agg.n_agg;
     gs::k_restrict<<<g->agg.n_agg, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p);
-    gs::k_coarse_mv<<<(m + 7) / 8, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
+    gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
                                                                   g->d_counter.p + 6, g->d_sc.p, 1);
     gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
     g->launches += 3;
@@ -1242,7 +1272,6 @@ gs_status gs_destroy(gs_graph* g) try {
     exchange_records(g, mine, all);
   }
   if (g->win) cudaFree(g->win);
-  if (g->cusolver) cusolverDnDestroy(g->cusolver);
   if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->ev0) cudaEventDestroy(g->ev0);

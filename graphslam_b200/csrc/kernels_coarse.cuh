@@ -29,6 +29,7 @@ struct CoarseView {
   const int* agg_ptr;       // per aggregate: range in agg_rows
   const int* agg_rows;      // local rows, ascending; the first one is the aggregate's reference row
   const double4* pose;      // the linearisation point
+  const double2* ref;       // per aggregate: position of its reference row at the linearisation point (k_agg_ref)
   int n_agg;
   int n_own;
 };
@@ -38,7 +39,7 @@ struct WBlock {
   double c, s, u, v;
 };
 
-__device__ __forceinline__ WBlock w_block(const double4 p, const double4 ref) {
+__device__ __forceinline__ WBlock w_block(const double4 p, const double2 ref) {
   const double dx = p.x - ref.x, dy = p.y - ref.y;
   WBlock w;
   w.c = p.z;
@@ -55,6 +56,15 @@ __device__ __forceinline__ void w_column(const WBlock& w, int mode, double out[3
   else { out[0] = w.u; out[1] = w.v; out[2] = 1.0; }
 }
 
+// reference position of every aggregate = its first row's
+__global__ void __launch_bounds__(kThreads) k_agg_ref(const int* __restrict__ agg_ptr, const int* __restrict__ agg_rows,
+                                                       const double4* __restrict__ pose, int n_agg, double2* __restrict__ ref) {
+  const int g = blockIdx.x * kThreads + threadIdx.x;
+  if (g >= n_agg) return;
+  const double4 p = ldg(pose + agg_rows[agg_ptr[g]]);
+  ref[g] = make_double2(p.x, p.y);
+}
+
 // color < 0: every aggregate
 __global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, const int* __restrict__ agg_color, int color, int mode,
                                                          double* __restrict__ v) {
@@ -63,8 +73,7 @@ __global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, cons
   const int g = a.agg_of[r];
   double o[3] = {0.0, 0.0, 0.0};
   if (color < 0 || agg_color[g] == color) {
-    const double4 ref = ldg(a.pose + a.agg_rows[a.agg_ptr[g]]);
-    w_column(w_block(ldg(a.pose + r), ref), mode, o);
+    w_column(w_block(ldg(a.pose + r), ldg(a.ref + g)), mode, o);
   }
   v[3 * (size_t)r] = o[0];
   v[3 * (size_t)r + 1] = o[1];
@@ -73,21 +82,38 @@ __global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, cons
 
 // out[3 a .. 3 a + 3) = sum over the aggregate's rows (list order) of W_i^T r_i.  Thread t takes rows t, t+T, ...;
 // then the fixed shuffle / shared-memory tree of block_sum.
-__global__ void __launch_bounds__(kThreads) k_restrict(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
+__global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
                                                         int honour_done, double* __restrict__ out) {
   __shared__ double red[8];
   if (honour_done && sc->done) return;
   const int g = blockIdx.x;
   const int q0 = a.agg_ptr[g], q1 = a.agg_ptr[g + 1];
-  const double4 ref = ldg(a.pose + a.agg_rows[q0]);
+  const double2 ref = ldg(a.ref + g);
   double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-  for (int q = q0 + (int)threadIdx.x; q < q1; q += kThreads) {
-    const int i = a.agg_rows[q];
-    const WBlock w = w_block(ldg(a.pose + i), ref);
-    const double r0 = r[3 * (size_t)i], r1 = r[3 * (size_t)i + 1], r2 = r[3 * (size_t)i + 2];
-    s0 += w.c * r0 - w.s * r1;
-    s1 += w.s * r0 + w.c * r1;
-    s2 += (w.u * r0 + w.v * r1) + r2;
+  // four rows per thread and trip: the four row indices, then their poses and residuals, are requested together;
+  // the sums run over the thread's rows in list order
+  for (int q = q0 + (int)threadIdx.x; q < q1; q += 4 * kThreads) {
+    int idx[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) idx[u] = (q + u * kThreads < q1) ? ldg(a.agg_rows + q + u * kThreads) : -1;
+    double4 ps[4];
+    double rv[4][3];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = idx[u] < 0 ? 0 : idx[u];
+      ps[u] = ldg(a.pose + i);
+      rv[u][0] = r[3 * (size_t)i];
+      rv[u][1] = r[3 * (size_t)i + 1];
+      rv[u][2] = r[3 * (size_t)i + 2];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (idx[u] < 0) continue;
+      const WBlock w = w_block(ps[u], ref);
+      s0 += w.c * rv[u][0] - w.s * rv[u][1];
+      s1 += w.s * rv[u][0] + w.c * rv[u][1];
+      s2 += (w.u * rv[u][0] + w.v * rv[u][1]) + rv[u][2];
+    }
   }
   const double t0 = block_sum(s0, red);
   const double t1 = block_sum(s1, red);
@@ -129,44 +155,60 @@ __global__ void __launch_bounds__(kThreads) k_symmetrize(double* __restrict__ Em
   if (i < j) Em[t] = Em[(size_t)i * m + j];
 }
 
-// mu = Einv c (dense, symmetric, column-major = row-major): one warp per row, lanes stride the columns, fixed shuffle
-// tree.  The last CTA to finish adds c.mu in fixed order and takes the scalar step that closes the preconditioner
-// application:  r.z = r.M^-1 r (from the update kernel) + c.mu  — the corrected z is never formed for the dot product.
+// mu = Einv c (dense, symmetric, column-major = row-major): kCoarseRows rows per CTA, kThreads / kCoarseRows threads
+// per row, every thread eight columns at a time (eight loads in flight), all sums in one fixed order.  The last CTA
+// to finish adds c.mu in fixed order and takes the scalar step that closes the preconditioner application:
+//     r.z = r.M^-1 r (from the update kernel) + c.mu      — the corrected z is never formed for the dot product.
 //   init != 0: start of a solve (r.z of the initial residual, no beta)
-__global__ void __launch_bounds__(kThreads) k_coarse_mv(const double* __restrict__ Einv, const double* __restrict__ cvec, int m,
+constexpr int kCoarseRows = 2;
+__global__ void __launch_bounds__(kThreads, 4) k_coarse_mv(const double* __restrict__ Einv, const double* __restrict__ cvec, int m,
                                                          double* __restrict__ mu, double* __restrict__ part,
                                                          unsigned int* counter, Scalars* sc, int init) {
   __shared__ double red[8];
   __shared__ int flag;
   if (sc->done) return;
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  const int row = blockIdx.x * (kThreads / 32) + w;
+  constexpr int kPerRow = kThreads / kCoarseRows;        // threads per row
+  const int w = threadIdx.x >> 5;
+  const int sub = threadIdx.x / kPerRow, t = threadIdx.x % kPerRow;
+  const int row = blockIdx.x * kCoarseRows + sub;
   double acc = 0.0;
   if (row < m) {
-    // eight independent partial sums per lane (columns l + 32 (8 q + u)), so eight loads of the row are in flight at
-    // once; they are added in one fixed order
     const double* e = Einv + (size_t)row * m;
-    double part8[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    int j = l;
-    for (; j + 7 * 32 < m; j += 8 * 32) {
+    double p8[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int j = t; j < m; j += 8 * kPerRow) {      // the tail is predicated, not a second loop: p8 stays in registers
+      double ev[8], cv[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) part8[u] += ldg(e + j + 32 * u) * ldg(cvec + j + 32 * u);
+      for (int u = 0; u < 8; ++u) {
+        const int col = j + kPerRow * u;
+        const bool in = col < m;
+        ev[u] = in ? ldg(e + col) : 0.0;
+        cv[u] = in ? ldg(cvec + col) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) p8[u] += ev[u] * cv[u];
     }
-    for (int u = 0; j < m; j += 32, ++u) part8[u] += ldg(e + j) * ldg(cvec + j);
-    acc = ((part8[0] + part8[1]) + (part8[2] + part8[3])) + ((part8[4] + part8[5]) + (part8[6] + part8[7]));
+    acc = ((p8[0] + p8[1]) + (p8[2] + p8[3])) + ((p8[4] + p8[5]) + (p8[6] + p8[7]));
   }
   acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[w] = acc;
+  __syncthreads();
   double prod = 0.0;
-  if (row < m && l == 0) {
-    mu[row] = acc;
-    prod = acc * cvec[row];
+  if (threadIdx.x < kCoarseRows) {          // thread s finishes row s of this CTA: its warps' sums in warp order
+    constexpr int kWarpsPerRow = kPerRow / 32;
+    double s = 0.0;
+    for (int k = 0; k < kWarpsPerRow; ++k) s += red[threadIdx.x * kWarpsPerRow + k];
+    const int rr = blockIdx.x * kCoarseRows + (int)threadIdx.x;
+    if (rr < m) {
+      mu[rr] = s;
+      prod = s * cvec[rr];
+    }
   }
-  // per-CTA partial of c.mu: the 8 rows of this CTA in warp order
-  if (l == 0) red[w] = prod;
+  __syncthreads();
+  if (threadIdx.x < kCoarseRows) red[threadIdx.x] = prod;
   __syncthreads();
   if (threadIdx.x == 0) {
     double s = 0.0;
-    for (int k = 0; k < kThreads / 32; ++k) s += red[k];
+    for (int k = 0; k < kCoarseRows; ++k) s += red[k];
     part[blockIdx.x] = s;
   }
   if (!last_block(counter, &flag)) return;
@@ -193,8 +235,7 @@ __global__ void __launch_bounds__(kThreads) k_dir_coarse(const CoarseView a, con
   if (r >= a.n_own) return;
   const double beta = sc->beta;
   const int g = a.agg_of[r];
-  const double4 ref = ldg(a.pose + a.agg_rows[a.agg_ptr[g]]);
-  const WBlock w = w_block(ldg(a.pose + r), ref);
+  const WBlock w = w_block(ldg(a.pose + r), ldg(a.ref + g));
   const double m0 = mu[3 * (size_t)g], m1 = mu[3 * (size_t)g + 1], m2 = mu[3 * (size_t)g + 2];
   const size_t o = 3 * (size_t)r;
   const double z0 = z[o] + ((w.c * m0 + w.s * m1) + w.u * m2);

@@ -82,7 +82,8 @@ typedef struct gs_params {
   int rank;                  /* multi-GPU: this process's rank (0)      */
   int world_size;            /* multi-GPU: number of ranks (1)          */
   int solver_flags;          /* GS_SOLVER_* bits (0)                    */
-  int reserved[7];
+  int coarse_aggregate_size; /* two-level preconditioner: poses per aggregate; 0 = automatic (about sqrt(N), >= 128) */
+  int reserved[6];
 } gs_params;
 
 typedef struct gs_stats {

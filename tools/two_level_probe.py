@@ -9,11 +9,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from graphslam_b200 import graph, synth  # noqa: E402
 
-for cid in (sys.argv[1:] or ["C3", "C4", "C2", "C5"]):
+SIZES = [int(a[2:]) for a in sys.argv[1:] if a.startswith("T=")] or [0]
+for cid in ([a for a in sys.argv[1:] if not a.startswith("T=")] or ["C3", "C4", "C2", "C5"]):
     g = synth.config(cid)
     rec = {"config": g.name, "n": g.n, "e": g.e}
-    for name, flags in (("two_level", 0), ("block_jacobi", 32)):
-        with graph.Graph(solver_flags=flags) as G:
+    for name, flags, size in [(f"two_level_T{t}", 0, t) for t in SIZES] + [("block_jacobi", 32, 0)]:
+        with graph.Graph(solver_flags=flags, coarse_aggregate_size=size) as G:
             G.add_graph(g)
             G.prepare()
             rec[name + "_prepare_ms"] = G.structure_timing()
@@ -22,7 +23,7 @@ for cid in (sys.argv[1:] or ["C3", "C4", "C2", "C5"]):
             d, it, rr = G.solve_linear(1e-5)
             dt = time.perf_counter() - t0
             rec[name] = {"pcg_iterations": it, "solve_ms": round(dt * 1e3, 2), "us_per_iteration": round(dt / it * 1e6, 2), "relres": rr}
-            if name == "two_level":
+            if name.startswith("two_level"):
                 rec[name]["kernels_us"] = {k: round(v[0] * 1e3, 2) for k, v in G.profile_pcg(1e-5, 40).items()}
             t0 = time.perf_counter()
             st = G.optimize()
