@@ -174,6 +174,7 @@ struct gs_graph {
   DevBuf<int> d_chol_info;
   DevBuf<double2> d_agg_ref;
   int chol_lwork = 0;
+  int agg_a0 = 0, agg_own = 0;            // this rank's aggregates [agg_a0, agg_a0 + agg_own)
   bool coarse_e0_valid = false;           // R (= W^T H W by columns) and G computed at the current linearisation
   double coarse_lambda = -1.0;            // the lambda d_E (= E^-1) was built for; < 0: none
   double ms_coarse_setup = 0.0;
@@ -318,6 +319,8 @@ gs::CoarseView coarse_view(gs_graph* g) {
   c.agg_rows = g->d_agg_rows.p;
   c.pose = g->d_pose_lin.p;
   c.ref = g->d_agg_ref.p;
+  c.a0 = g->agg_a0;
+  c.n_agg_own = g->agg_own;
   c.n_agg = g->agg.n_agg;
   c.n_own = g->n_own;
   return c;
@@ -371,6 +374,7 @@ gs_status launch_spmv(gs_graph* g, double* p, double* y, int mode) {
 }
 
 gs_status coarse_setup(gs_graph* g, double lambda);
+gs_status coarse_gather(gs_graph* g, double* vec, int width);
 
 template <typename T>
 gs_status upload(gs_graph* g, DevBuf<T>& d, const std::vector<T>& h) {
@@ -461,7 +465,10 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     const int m = 3 * g->agg.n_agg;
     if (stage == 1) {
       gs::k_pcg_update_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), gs::OP_UPDATE_2L);
-      gs::k_restrict<<<g->agg.n_agg, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p);
+      if (gs_status s = finish_reduce(g, 2, gs::OP_UPDATE_2L)) return s;
+      if (g->agg_own)
+        gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p, 3, 0);
+      if (gs_status s = coarse_gather(g, g->d_cvec.p, 3)) return s;
       gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
                                                                     g->d_counter.p + 6, g->d_sc.p, 0);
     } else {
@@ -757,7 +764,8 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   gs::build_local_structure(N, E, g->di.data(), g->dj.data(), g->perm, P, g->dp.data(), g->world, g->rank, g->S);
   const LocalStructure& S = g->S;
   // two-level preconditioner: aggregates of the block rows (one rank; small graphs keep the persistent kernel)
-  g->coarse = g->coarse_wanted && g->world == 1 && N >= 8192;
+  // (several ranks: through the NCCL-per-exchange path; the peer-memory kernels run block-Jacobi only)
+  g->coarse = g->coarse_wanted && N >= 8192 && (g->world == 1 || !g->p2p_wanted);
   if (g->coarse) {
     std::vector<int32_t> rp, ci;
     gs::global_pattern(N, E, g->di.data(), g->dj.data(), rp, ci);
@@ -847,15 +855,26 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (g->coarse) {
     const gs::Aggregation& A = g->agg;
     const size_t m = 3 * (size_t)A.n_agg;
-    if (gs_status s = upload(g, g->d_agg_of, A.agg_of)) return s;
-    if (gs_status s = upload(g, g->d_agg_ptr, A.ptr)) return s;
-    if (gs_status s = upload(g, g->d_agg_rows, A.rows)) return s;
+    // this rank's aggregates: those of its segments; lists in local row indices
+    const int spr = gs::kSegments / g->world;
+    g->agg_a0 = A.seg_agg[g->rank * spr];
+    g->agg_own = A.seg_agg[(g->rank + 1) * spr] - g->agg_a0;
+    std::vector<int> l_of(A.agg_of.begin() + S.v0, A.agg_of.begin() + S.v1);
+    std::vector<int> l_ptr(g->agg_own + 1), l_rows;
+    const int q0 = A.ptr[g->agg_a0];
+    for (int a = 0; a <= g->agg_own; ++a) l_ptr[a] = A.ptr[g->agg_a0 + a] - q0;
+    l_rows.assign(A.rows.begin() + q0, A.rows.begin() + A.ptr[g->agg_a0 + g->agg_own]);
+    for (int& r : l_rows) r -= S.v0;
+    if (gs_status s = upload(g, g->d_agg_of, l_of)) return s;
+    if (gs_status s = upload(g, g->d_agg_ptr, l_ptr)) return s;
+    if (gs_status s = upload(g, g->d_agg_rows, l_rows)) return s;
     if (gs_status s = upload(g, g->d_agg_color, A.color)) return s;
     if (gs_status s = upload(g, g->d_nbr_of_color, A.nbr_of_color)) return s;
     GS_CUDA(g, g->d_cvec.alloc(m));
     GS_CUDA(g, g->d_mu.alloc(m));
     GS_CUDA(g, g->d_cpart.alloc(m / gs::kCoarseRows + 2));
     GS_CUDA(g, g->d_R.alloc((size_t)A.n_colors * 3 * m));
+    GS_CUDA(g, cudaMemsetAsync(g->d_R.p, 0, sizeof(double) * (size_t)A.n_colors * 3 * m, g->stream));
     GS_CUDA(g, g->d_G.alloc(3 * m));
     GS_CUDA(g, g->d_E.alloc(m * m));
     GS_CUDA(g, g->d_basis.alloc(nl3));
@@ -904,6 +923,8 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     if (gs_status s = halo_exchange(g, reinterpret_cast<double*>(g->d_pose_try.p), 4)) return s;
     const size_t chunk = 2 * (size_t)(gs::kSegments / g->world);
     GS_NCCL(g, gs::nccl().AllGather(g->d_segs.p + g->rank * chunk, g->d_segs.p, chunk, ncclDouble, g->comm, g->stream));
+    if (g->coarse)
+      if (gs_status s = coarse_gather(g, g->d_cvec.p, 3)) return s;
     GS_CUDA(g, cudaStreamSynchronize(g->stream));
   }
   const double t_comm = now_ms();
@@ -911,6 +932,23 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   if (gs_status s = capture_pcg_graph(g)) return s;
   g->prep_ms[3] = now_ms() - t_comm;
   if (ms_out) *ms_out = now_ms() - t0;
+  return GS_OK;
+}
+
+// several ranks: vec holds `width` doubles per global aggregate; every rank broadcasts the share of its own aggregates
+gs_status coarse_gather(gs_graph* g, double* vec, int width) {
+  if (g->world == 1) return GS_OK;
+  const gs::Aggregation& A = g->agg;
+  const int spr = gs::kSegments / g->world;
+  gs::NcclApi& nc = gs::nccl();
+  GS_NCCL(g, nc.GroupStart());
+  for (int q = 0; q < g->world; ++q) {
+    const int b = A.seg_agg[q * spr], e = A.seg_agg[(q + 1) * spr];
+    if (e > b)
+      GS_NCCL(g, nc.Broadcast(vec + (size_t)b * width, vec + (size_t)b * width, (size_t)(e - b) * width, ncclDouble, q, g->comm,
+                              g->stream));
+  }
+  GS_NCCL(g, nc.GroupEnd());
   return GS_OK;
 }
 
@@ -925,19 +963,23 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
   if (!g->coarse_e0_valid) {
     GS_CUDA(g, cudaMemcpyAsync(g->d_pose_lin.p, g->d_pose.p, sizeof(double4) * (size_t)g->n_loc, cudaMemcpyDeviceToDevice, g->stream));
     const gs::CoarseView cv = coarse_view(g);
-    gs::k_agg_ref<<<(A.n_agg + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(g->d_agg_ptr.p, g->d_agg_rows.p,
-                                                                                             g->d_pose_lin.p, A.n_agg, g->d_agg_ref.p);
+    const int nc9 = A.n_colors * 9;
+    const int own = std::max(g->agg_own, 1);
+    gs::k_agg_ref<<<(own + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_ref.p);
     for (int c = 0; c < A.n_colors; ++c)
       for (int mode = 0; mode < 3; ++mode) {
         gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, c, mode, g->d_basis.p);
-        if (gs_status s = launch_spmv(g, g->d_basis.p, g->d_Ap.p, 1)) return s;
-        gs::k_restrict<<<A.n_agg, gs::kThreads, 0, g->stream>>>(cv, g->d_Ap.p, g->d_sc.p, 0,
-                                                                 g->d_R.p + ((size_t)c * 3 + mode) * m);
+        if (gs_status s = launch_spmv(g, g->d_basis.p, g->d_Ap.p, 1)) return s;   // several ranks: halo exchange of the basis vector
+        if (g->agg_own)
+          gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_Ap.p, g->d_sc.p, 0, g->d_R.p, nc9, (c * 3 + mode) * 3);
       }
     for (int mode = 0; mode < 3; ++mode) {
       gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, -1, mode, g->d_basis.p);
-      gs::k_restrict<<<A.n_agg, gs::kThreads, 0, g->stream>>>(cv, g->d_basis.p, g->d_sc.p, 0, g->d_G.p + (size_t)mode * m);
+      if (g->agg_own) gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_basis.p, g->d_sc.p, 0, g->d_G.p, 9, mode * 3);
     }
+    // every rank needs the whole coarse matrix: its aggregates' rows of R and G are contiguous (aggregate-major)
+    if (gs_status s = coarse_gather(g, g->d_R.p, nc9)) return s;
+    if (gs_status s = coarse_gather(g, g->d_G.p, 9)) return s;
     g->launches += 3 * (int64_t)A.n_colors * 3 + 6;
     g->coarse_e0_valid = true;
     g->coarse_lambda = -1.0;
@@ -1022,7 +1064,7 @@ gs_status launch_chi2(gs_graph* g, const double4* pose) {
   return GS_OK;
 }
 
-void launch_pcg_setup(gs_graph* g) {
+gs_status launch_pcg_setup(gs_graph* g) {
   gs::k_minv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(g->d_Hd.p, g->prm.diagonal_damping ? g->d_dscale.p : nullptr,
                                                            g->d_sc.p, g->d_Minv.p, g->n_own);
   const bool two = coarse_active(g);
@@ -1030,12 +1072,17 @@ void launch_pcg_setup(gs_graph* g) {
   g->launches += 2;
   if (two) {   // p(0) = z(0) = M^-1 r + W E^-1 W^T r
     const int m = 3 * g->agg.n_agg;
-    gs::k_restrict<<<g->agg.n_agg, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p);
+    if (gs_status s = finish_reduce(g, 2, gs::OP_INIT_2L)) return s;
+    if (g->agg_own)
+      gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p, 3, 0);
+    if (gs_status s = coarse_gather(g, g->d_cvec.p, 3)) return s;
     gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
                                                                   g->d_counter.p + 6, g->d_sc.p, 1);
     gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
     g->launches += 3;
+    return GS_OK;
   }
+  return finish_reduce(g, 2, gs::OP_INIT);
 }
 
 // peer-memory path: ghost rows of p(0) by the ordinary halo exchange, then mark them valid
@@ -1057,7 +1104,7 @@ gs_status begin_p2p_solve(gs_graph* g) {
 
 int64_t launches_per_pcg_iteration(const gs_graph* g) {
   if (g->dir_otf && g->p2p) return 2;
-  if (coarse_active(g)) return 5;
+  if (coarse_active(g)) return g->world == 1 ? 5 : 5 + 2 + (g->S.send_rows.empty() ? 0 : 1);
   if (g->world == 1 || g->p2p) return 3;
   return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
 }
@@ -1072,8 +1119,7 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
   h->tol2 = g->prm.pcg_rel_tol * g->prm.pcg_rel_tol;
   h->max_iters = g->prm.pcg_max_iters;
   if (gs_status s = write_scalars(g)) return s;
-  launch_pcg_setup(g);
-  if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
+  if (gs_status s = launch_pcg_setup(g)) return s;
   if (gs_status s = begin_p2p_solve(g)) return s;
   GS_CUDA(g, cudaGetLastError());
   const int64_t keep = g->launches;
@@ -1133,6 +1179,9 @@ gs_status create_common(gs_graph* g) {
   g->p2p_wanted = !(flags & GS_SOLVER_NCCL_PER_OP);
   g->p2p_staged = (flags & GS_X_P2P_STAGED) != 0;
   g->coarse_wanted = !(flags & GS_SOLVER_BLOCK_JACOBI_ONLY);
+  // several ranks: the two-level preconditioner runs over the NCCL-per-exchange path; the peer-memory kernels
+  // (collectives fused into the PCG kernels) run block-Jacobi only and are chosen with GS_SOLVER_BLOCK_JACOBI_ONLY
+  if (g->coarse_wanted && g->world > 1) g->p2p_wanted = false;
   {
     int per_sm = 0, sms = 0, dev = 0, coop = 0;
     GS_CUDA(g, cudaGetDevice(&dev));
@@ -1918,8 +1967,7 @@ gs_status gs_profile_pcg(gs_graph* g, double lambda, int iters, double ms[3], do
   if (coarse_active(g))
     if (gs_status s = coarse_setup(g, lambda)) return s;
   if (gs_status s = write_scalars(g)) return s;
-  launch_pcg_setup(g);
-  if (gs_status s = finish_reduce(g, 2, gs::OP_INIT)) return s;
+  if (gs_status s = launch_pcg_setup(g)) return s;
   if (gs_status s = begin_p2p_solve(g)) return s;
   for (int w = 0; w < 3; ++w)
     if (gs_status s = launch_pcg_iteration(g, (unsigned int)w)) return s;  // warm-up

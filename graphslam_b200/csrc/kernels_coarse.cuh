@@ -24,13 +24,17 @@
 
 namespace gs {
 
+// Aggregates never cross segment boundaries, so a rank owns the contiguous range [a0, a0 + n_agg_own) of the global
+// aggregate numbering; coarse vectors (3 per aggregate) are indexed globally, lists and rows locally.
 struct CoarseView {
-  const int* agg_of;        // per owned row: aggregate
-  const int* agg_ptr;       // per aggregate: range in agg_rows
+  const int* agg_of;        // per owned row: GLOBAL aggregate
+  const int* agg_ptr;       // per OWNED aggregate (local index): range in agg_rows
   const int* agg_rows;      // local rows, ascending; the first one is the aggregate's reference row
   const double4* pose;      // the linearisation point
-  const double2* ref;       // per aggregate: position of its reference row at the linearisation point (k_agg_ref)
-  int n_agg;
+  const double2* ref;       // per global aggregate: position of its reference row (only the owned entries are used)
+  int a0;                   // first owned aggregate
+  int n_agg_own;
+  int n_agg;                // global
   int n_own;
 };
 
@@ -57,12 +61,11 @@ __device__ __forceinline__ void w_column(const WBlock& w, int mode, double out[3
 }
 
 // reference position of every aggregate = its first row's
-__global__ void __launch_bounds__(kThreads) k_agg_ref(const int* __restrict__ agg_ptr, const int* __restrict__ agg_rows,
-                                                       const double4* __restrict__ pose, int n_agg, double2* __restrict__ ref) {
+__global__ void __launch_bounds__(kThreads) k_agg_ref(const CoarseView a, double2* __restrict__ ref) {
   const int g = blockIdx.x * kThreads + threadIdx.x;
-  if (g >= n_agg) return;
-  const double4 p = ldg(pose + agg_rows[agg_ptr[g]]);
-  ref[g] = make_double2(p.x, p.y);
+  if (g >= a.n_agg_own) return;
+  const double4 p = ldg(a.pose + a.agg_rows[a.agg_ptr[g]]);
+  ref[a.a0 + g] = make_double2(p.x, p.y);
 }
 
 // color < 0: every aggregate
@@ -80,15 +83,15 @@ __global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, cons
   v[3 * (size_t)r + 2] = o[2];
 }
 
-// out[3 a .. 3 a + 3) = sum over the aggregate's rows (list order) of W_i^T r_i.  Thread t takes rows t, t+T, ...;
-// then the fixed shuffle / shared-memory tree of block_sum.
+// out[a * ostride + ooff .. + 3) = sum over the rows of owned aggregate a (list order) of W_i^T r_i (a = global index).
+// Thread t takes rows t, t+T, ...; then the fixed shuffle / shared-memory tree of block_sum.
 __global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
-                                                        int honour_done, double* __restrict__ out) {
+                                                        int honour_done, double* __restrict__ out, int ostride, int ooff) {
   __shared__ double red[8];
   if (honour_done && sc->done) return;
-  const int g = blockIdx.x;
+  const int g = blockIdx.x;                   // local aggregate
   const int q0 = a.agg_ptr[g], q1 = a.agg_ptr[g + 1];
-  const double2 ref = ldg(a.ref + g);
+  const double2 ref = ldg(a.ref + a.a0 + g);
   double s0 = 0.0, s1 = 0.0, s2 = 0.0;
   // four rows per thread and trip: the four row indices, then their poses and residuals, are requested together;
   // the sums run over the thread's rows in list order
@@ -119,15 +122,16 @@ __global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, co
   const double t1 = block_sum(s1, red);
   const double t2 = block_sum(s2, red);
   if (threadIdx.x == 0) {
-    out[3 * (size_t)g] = t0;
-    out[3 * (size_t)g + 1] = t1;
-    out[3 * (size_t)g + 2] = t2;
+    double* o = out + (size_t)(a.a0 + g) * ostride + ooff;
+    o[0] = t0;
+    o[1] = t1;
+    o[2] = t2;
   }
 }
 
-// Dense E (column-major, m = 3 n_agg) from the restricted products: R[(color * 3 + mode) * m + 3 a + k] is row
-// 3a+k of the column (b, mode), b = the aggregate of that colour next to a; Gm[mode * m + 3 a + k] likewise for
-// G = W^T W (block diagonal).  One thread per (row block a, colour, mode).
+// Dense E (column-major, m = 3 n_agg) from the restricted products, stored aggregate-major so that a rank's share is
+// contiguous: R[((a * n_colors + c) * 3 + mode) * 3 + k] is entry (3a+k, 3b+mode) of E0, b = the aggregate of colour c
+// next to a; Gm[(a * 3 + mode) * 3 + k] likewise for G = W^T W (block diagonal).  One thread per (a, colour, mode).
 __global__ void __launch_bounds__(kThreads) k_coarse_E(const double* __restrict__ R, const double* __restrict__ Gm,
                                                         const int* __restrict__ nbr_of_color, int n_agg, int n_colors,
                                                         double lambda, double* __restrict__ Em) {
@@ -141,8 +145,8 @@ __global__ void __launch_bounds__(kThreads) k_coarse_E(const double* __restrict_
   const size_t col = 3 * (size_t)b + mode;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    double e = R[((size_t)c * 3 + mode) * m + 3 * (size_t)a + k];
-    if (a == b) e += lambda * Gm[(size_t)mode * m + 3 * (size_t)a + k];
+    double e = R[(((size_t)a * n_colors + c) * 3 + mode) * 3 + k];
+    if (a == b) e += lambda * Gm[((size_t)a * 3 + mode) * 3 + k];
     Em[col * m + 3 * (size_t)a + k] = e;
   }
 }

@@ -227,6 +227,7 @@ inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const s
   Partition part;
   part.init(N, 1);
   A.target = target;
+  A.n_agg = 0;
   A.agg_of.assign(N, -1);
   A.ptr.assign(1, 0);
   A.rows.clear();

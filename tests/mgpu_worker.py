@@ -38,9 +38,9 @@ def main():
     G.close()
     ok = True
     if rank == 0:
-        # the single-GPU reference runs the same preconditioner as the ranks (block-Jacobi; the two-level default of one
-        # GPU solves the same systems to the same tolerance but not with the same bits)
-        with graph.Graph(device=local, solver_flags=32) as G1:
+        # the single-GPU reference runs the same preconditioner as the ranks (flag 32 = block-Jacobi only): the two
+        # preconditioners solve the same systems to the same tolerance, but not with the same bits
+        with graph.Graph(device=local, solver_flags=flags & 32) as G1:
             G1.add_graph(g)
             chi0_1 = G1.chi2()
             st1 = G1.optimize()

@@ -29,10 +29,13 @@ def _free_port():
 # execution paths of the multi-GPU PCG iteration (gs_params.solver_flags; the worker takes the flag word as argv[3]).
 # The staged x/r/z update inside the peer-memory kernels (GS_X_P2P_STAGED, csrc/kernels_p2p.cuh) is a candidate under
 # measurement and only exercised on request (GS_TEST_CANDIDATES=1, read by this test harness, not by the library).
-_NCCL, _DIRK, _OTF, _XSTAGED = 2, 8, 16, 1 << 17
-_FORMS = [("peer-memory-2-kernels", _OTF), ("peer-memory-3-kernels", _DIRK), ("nccl-per-op", _NCCL), ("default", 0)]
+_NCCL, _DIRK, _OTF, _BJ, _XSTAGED = 2, 8, 16, 32, 1 << 17
+# block-Jacobi PCG: peer-memory kernels (two or three per iteration) or one NCCL call per exchange; default = the
+# two-level preconditioner over the NCCL-per-exchange path.  Each is compared with ONE GPU running the same preconditioner.
+_FORMS = [("peer-memory-2-kernels", _BJ | _OTF), ("peer-memory-3-kernels", _BJ | _DIRK), ("nccl-per-op", _BJ | _NCCL),
+          ("two-level-default", 0)]
 if os.environ.get("GS_TEST_CANDIDATES") == "1":
-    _FORMS += [("peer-memory-2-kernels-staged", _OTF | _XSTAGED), ("peer-memory-3-kernels-staged", _DIRK | _XSTAGED)]
+    _FORMS += [("peer-memory-2-kernels-staged", _BJ | _OTF | _XSTAGED), ("peer-memory-3-kernels-staged", _BJ | _DIRK | _XSTAGED)]
 
 
 def _run_worker(world, flags, cid, n, timeout=900):
@@ -54,11 +57,12 @@ def test_multi_gpu_path_bitwise_equals_single_gpu(world, form):
     _run_worker(world, form[1], "C3", 30000)
 
 
+@pytest.mark.parametrize("flags", [0, _BJ], ids=["two-level", "block-jacobi-peer-memory"])
 @pytest.mark.parametrize("cid,n", [("C3", 250000), ("C4", 40000)])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_multi_gpu_bitwise_at_scale(world, cid, n):
+def test_multi_gpu_bitwise_at_scale(world, cid, n, flags):
     """The same bit-for-bit check on graphs whose ranks are large enough for the two-kernel iteration (C3, 250k poses)
     and on the dense loop-closure graph, whose halo is scattered over many tiles (C4)."""
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
-    _run_worker(world, 0, cid, n)
+    _run_worker(world, flags, cid, n)
