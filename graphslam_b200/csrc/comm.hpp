@@ -3,7 +3,8 @@
 // all, and inside a PyTorch process the loader hands back the copy torch already mapped (same
 // soname) instead of a second one.  Only the handful of entry points the path uses are bound:
 // halo exchange = grouped ncclSend/ncclRecv, scalar reductions = ncclAllGather of segment sums
-// (summed in fixed order by every rank), pose read-back = grouped ncclBroadcast.
+// (summed in fixed order by every rank), pose read-back = grouped ncclBroadcast; ncclCommGetAsyncError is polled
+// once per PCG batch so that a failed peer surfaces as GS_ENCCL instead of a hang.
 #pragma once
 #include <dlfcn.h>
 #include <nccl.h>
@@ -18,6 +19,7 @@ struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*CommGetAsyncError)(ncclComm_t, ncclResult_t*) = nullptr;
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -40,6 +42,7 @@ struct NcclApi {
       void** slot;
     } syms[] = {{"ncclGetVersion", (void**)&GetVersion},     {"ncclGetUniqueId", (void**)&GetUniqueId},
                 {"ncclCommInitRank", (void**)&CommInitRank}, {"ncclCommDestroy", (void**)&CommDestroy},
+                {"ncclCommGetAsyncError", (void**)&CommGetAsyncError},
                 {"ncclSend", (void**)&Send},                 {"ncclRecv", (void**)&Recv},
                 {"ncclAllGather", (void**)&AllGather},       {"ncclBroadcast", (void**)&Broadcast},
                 {"ncclGroupStart", (void**)&GroupStart},     {"ncclGroupEnd", (void**)&GroupEnd},

@@ -12,6 +12,7 @@
 // the dot products, which every rank then adds in the same fixed order.
 #include <cuda_runtime.h>
 #include <cusolverDn.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
 #include <chrono>
@@ -48,6 +49,12 @@ using gs::spd_upper;
 constexpr int kPcgBatch = 32;  // PCG iterations per CUDA-graph launch
 constexpr int kFusedBatch = 128;  // PCG iterations per launch of the persistent small-graph kernel
 static_assert(kFusedBatch % 2 == 0, "an even batch leaves the latest direction in the graph's own p vector");
+
+// NVTX range per stage (prepare / linearise / solve / coarse setup / update): visible in nsys / ncu timelines
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 double now_ms() {
   using namespace std::chrono;
@@ -134,6 +141,9 @@ struct gs_graph {
 
   bool topo_dirty = true;         // factors/vertices added since the last structure build
   bool host_values_fresh = true;  // host xyt newer than (or equal to) device poses
+  bool theta_wrapped = false;     // every host theta is already in (-pi, pi] (they all came back from the device)
+  double4* h_stage = nullptr;     // pinned staging of the pose transfers
+  size_t h_stage_n = 0;
   bool device_values_valid = false;
   bool system_valid = false;      // H, b assembled at the current device poses
 
@@ -692,11 +702,23 @@ void build_dense_order(gs_graph* g) {
   for (int k = 0; k < n; ++k) g->ins2dense[g->dense2ins[k]] = k;
 }
 
+gs_status ensure_stage(gs_graph* g, size_t n) {
+  if (n <= g->h_stage_n) return GS_OK;
+  if (g->h_stage) cudaFreeHost(g->h_stage);
+  g->h_stage = nullptr;
+  g->h_stage_n = 0;
+  const size_t want = n + n / 8 + 1024;
+  GS_CUDA(g, cudaMallocHost(&g->h_stage, sizeof(double4) * want));
+  g->h_stage_n = want;
+  return GS_OK;
+}
+
 // device values -> host xyt.  Multi-rank: collective (every rank broadcasts its owned range).
 gs_status download_values(gs_graph* g) {
   if (!g->device_values_valid || g->host_values_fresh) return GS_OK;
   const int n = g->N;  // vertices present at the last upload
-  std::vector<double4> tmp(n);
+  if (gs_status s = ensure_stage(g, (size_t)n)) return s;
+  double4* tmp = g->h_stage;
   const double4* src = g->d_pose.p;
   if (g->world > 1) {
     gs::NcclApi& nc = gs::nccl();
@@ -709,29 +731,35 @@ gs_status download_values(gs_graph* g) {
     GS_NCCL(g, nc.GroupEnd());
     src = g->d_pose_all.p;
   }
-  GS_CUDA(g, cudaMemcpyAsync(tmp.data(), src, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaMemcpyAsync(tmp, src, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   g->d2h_bytes += sizeof(double4) * (double)n;
-  for (int d = 0; d < n; ++d) {
-    const int k = g->dense2ins[d];
-    g->xyt[3 * k] = tmp[d].x;
-    g->xyt[3 * k + 1] = tmp[d].y;
-    g->xyt[3 * k + 2] = std::atan2(tmp[d].w, tmp[d].z);
-  }
+  gs::parallel_for((size_t)n, [g, tmp](size_t b, size_t e) {
+    for (size_t d = b; d < e; ++d) {
+      const int k = g->dense2ins[d];
+      g->xyt[3 * k] = tmp[d].x;
+      g->xyt[3 * k + 1] = tmp[d].y;
+      g->xyt[3 * k + 2] = std::atan2(tmp[d].w, tmp[d].z);
+    }
+  });
   g->host_values_fresh = true;
+  g->theta_wrapped = (size_t)n == g->keys.size();
   return GS_OK;
 }
 
 // host xyt -> device poses of this rank (owned rows, then ghosts)
 gs_status upload_values(gs_graph* g) {
   const int n = g->n_loc;
-  std::vector<double4> tmp(std::max(n, 1));
-  for (int l = 0; l < n; ++l) {
-    const int d = l < g->n_own ? g->S.v0 + l : g->S.ghosts[l - g->n_own];
-    const int k = g->dense2ins[d];
-    tmp[l] = make_double4(g->xyt[3 * k], g->xyt[3 * k + 1], std::cos(g->xyt[3 * k + 2]), std::sin(g->xyt[3 * k + 2]));
-  }
-  if (n) GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp.data(), sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
+  if (gs_status s = ensure_stage(g, (size_t)std::max(n, 1))) return s;
+  double4* tmp = g->h_stage;
+  gs::parallel_for((size_t)n, [g, tmp](size_t b, size_t e) {
+    for (size_t l = b; l < e; ++l) {
+      const int d = (int)l < g->n_own ? g->S.v0 + (int)l : g->S.ghosts[l - g->n_own];
+      const int k = g->dense2ins[d];
+      tmp[l] = make_double4(g->xyt[3 * k], g->xyt[3 * k + 1], std::cos(g->xyt[3 * k + 2]), std::sin(g->xyt[3 * k + 2]));
+    }
+  });
+  if (n) GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp, sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
   g->h2d_bytes += sizeof(double4) * (double)n;
   g->device_values_valid = true;
@@ -741,6 +769,7 @@ gs_status upload_values(gs_graph* g) {
 
 gs_status prepare(gs_graph* g, double* ms_out) {
   if (ms_out) *ms_out = 0.0;
+  NvtxRange nvtx_range(g->topo_dirty ? "gs:prepare (structure build)" : "gs:prepare");
   if (!g->topo_dirty) {
     if (g->host_values_fresh && !g->device_values_valid) return upload_values(g);
     return GS_OK;
@@ -957,6 +986,7 @@ gs_status coarse_gather(gs_graph* g, double* vec, int width) {
 //   G = W^T W, once per linearisation;  E = E0 + lambda G, Cholesky-factored and inverted (cuSOLVER potrf / potri: a
 //   dense 3 n_agg square, <= 3072), once per lambda.  d_E then holds E^-1 in full.
 gs_status coarse_setup(gs_graph* g, double lambda) {
+  NvtxRange nvtx_range("gs:coarse setup");
   const double t0 = now_ms();
   const gs::Aggregation& A = g->agg;
   const int m = 3 * A.n_agg;
@@ -1030,6 +1060,7 @@ gs_status write_scalars(gs_graph* g) {
 
 // linearise + assemble at the current device poses (async)
 gs_status launch_assemble(gs_graph* g) {
+  NvtxRange nvtx_range("gs:linearise+assemble");
   const gs::AsmView av = asm_view(g, g->d_pose.p);
   const gs::ReduceCtx rc = reduce_ctx(g, 2);
   // no vertex pair carries two factors (every BASELINE config): the form without the run accumulator, 80 registers and
@@ -1057,6 +1088,7 @@ gs_status launch_assemble(gs_graph* g) {
 
 // chi2 at `pose` (ghost slots must be current)
 gs_status launch_chi2(gs_graph* g, const double4* pose) {
+  NvtxRange nvtx_range("gs:chi2");
   gs::k_chi2<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, pose), reduce_ctx(g, 3));
   g->launches += 1;
   if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
@@ -1111,6 +1143,7 @@ int64_t launches_per_pcg_iteration(const gs_graph* g) {
 
 // Solve (H + lambda D) x = -b by block-Jacobi PCG; result in d_x.  H, b must be assembled.
 gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_out, int* done_out) {
+  NvtxRange nvtx_range("gs:pcg solve");
   Scalars* h = g->h_sc;
   if (coarse_active(g))
     if (gs_status s = coarse_setup(g, lambda)) return s;
@@ -1134,6 +1167,11 @@ gs_status pcg_solve(gs_graph* g, double lambda, int* iters_out, double* relres_o
       if (gs_status s = launch_pcg_batch(g, kPcgBatch)) return s;
     }
     if (gs_status s = read_scalars(g)) return s;
+    if (g->comm) {   // a failed peer / transport error surfaces here instead of as a hang in the next batch
+      ncclResult_t async = ncclSuccess;
+      if (gs::nccl().CommGetAsyncError(g->comm, &async) != ncclSuccess || async != ncclSuccess)
+        return g->fail(GS_ENCCL, "NCCL asynchronous error during PCG: %s", gs::nccl().GetErrorString(async));
+    }
     if (h->done) break;
   }
   if (g->p2p)
@@ -1323,6 +1361,7 @@ gs_status gs_destroy(gs_graph* g) try {
   if (g->win) cudaFree(g->win);
   if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
+  if (g->h_stage) cudaFreeHost(g->h_stage);
   if (g->ev0) cudaEventDestroy(g->ev0);
   if (g->ev1) cudaEventDestroy(g->ev1);
   if (g->ev_begin) cudaEventDestroy(g->ev_begin);
@@ -1365,6 +1404,7 @@ gs_status gs_add_vertex(gs_graph* g, uint64_t key, const double pose[3]) try {
   }
   if (!g->keys_sequential) g->key2ins[key] = idx;
   g->keys.push_back(key);
+  g->theta_wrapped = false;
   g->xyt.insert(g->xyt.end(), pose, pose + 3);
   g->topo_dirty = true;
   return GS_OK;
@@ -1376,6 +1416,7 @@ gs_status gs_add_prior(gs_graph* g, uint64_t key, const double pose[3], const do
   if (!g || !pose || !cov9) return GS_EINVAL;
   const int v = g->find(key);
   if (v < 0) return g->fail(GS_ENOKEY, "prior on unknown key %llu", (unsigned long long)key);
+  if (!(std::isfinite(pose[0]) && std::isfinite(pose[1]) && std::isfinite(pose[2]))) return g->fail(GS_EINVAL, "non-finite prior");
   double om[6];
   if (!spd_information(cov9, om)) return g->fail(GS_ENOTSPD, "prior covariance on key %llu is not SPD", (unsigned long long)key);
   g->pr_v.push_back(v);
@@ -1469,6 +1510,8 @@ gs_status gs_load_g2o(gs_graph* g, const char* path, gs_g2o_counts* counts) try 
     for (size_t k = 0; k < d.pkey.size(); ++k) {
       if (!known(d.pkey[k])) return g->fail(GS_ENOKEY, "%s: prior %zu names an unknown vertex", path, k);
       if (!spd_upper(&d.pinfo[6 * k])) return g->fail(GS_ENOTSPD, "%s: information of prior %zu is not SPD", path, k);
+      if (!(std::isfinite(d.pxyt[3 * k]) && std::isfinite(d.pxyt[3 * k + 1]) && std::isfinite(d.pxyt[3 * k + 2])))
+        return g->fail(GS_EINVAL, "%s: non-finite pose in prior %zu", path, k);
     }
     for (size_t k = 0; k < d.vkey.size(); ++k)
       if (!(std::isfinite(d.vxyt[3 * k]) && std::isfinite(d.vxyt[3 * k + 1]) && std::isfinite(d.vxyt[3 * k + 2])))
@@ -1590,7 +1633,10 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   gs_status rc = GS_OK;
   const double eps = std::numeric_limits<double>::epsilon();
 
-  while (iterations < P.max_iterations) {
+  // NonlinearOptimizer::defaultOptimize: nothing to do when the initial error is already below errorTol
+  const bool nothing_to_do = error <= P.error_tol;
+  if (nothing_to_do) local.converged = 1;
+  while (!nothing_to_do && iterations < P.max_iterations) {
     const double current_error = error;
     // ---- iterate(): linearise once
     GS_CUDA(g, cudaEventRecord(g->ev0, g->stream));
@@ -1721,15 +1767,19 @@ gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, siz
   if (cap < nv) return g->fail(GS_EINVAL, "capacity %zu < %zu vertices", cap, nv);
   if (gs_status s = download_values(g)) return s;
   if (g->dense2ins.size() != nv) build_dense_order(g);
-  for (size_t d = 0; d < nv; ++d) {
-    const int k = g->dense2ins[d];
-    if (keys) keys[d] = g->keys[k];
-    if (xyt) {
-      xyt[3 * d] = g->xyt[3 * k];
-      xyt[3 * d + 1] = g->xyt[3 * k + 1];
-      xyt[3 * d + 2] = std::atan2(std::sin(g->xyt[3 * k + 2]), std::cos(g->xyt[3 * k + 2]));
+  const bool wrapped = g->theta_wrapped;
+  gs::parallel_for(nv, [g, keys, xyt, wrapped](size_t b, size_t e) {
+    for (size_t d = b; d < e; ++d) {
+      const int k = g->dense2ins[d];
+      if (keys) keys[d] = g->keys[k];
+      if (xyt) {
+        const double th = g->xyt[3 * k + 2];
+        xyt[3 * d] = g->xyt[3 * k];
+        xyt[3 * d + 1] = g->xyt[3 * k + 1];
+        xyt[3 * d + 2] = wrapped ? th : std::atan2(std::sin(th), std::cos(th));   // values read back from the device are atan2 results already
+      }
     }
-  }
+  });
   return GS_OK;
 } catch (...) {
   return on_exception(g);
@@ -1738,14 +1788,22 @@ gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, siz
 gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt) try {
   if (!g || (n && (!keys || !xyt))) return GS_EINVAL;
   if (gs_status s = download_values(g)) return s;
+  // validate everything before touching the values: an unknown key or a non-finite pose leaves the graph as it was
   for (size_t k = 0; k < n; ++k) {
-    const int v = g->find(keys[k]);
-    if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[k]);
-    g->xyt[3 * v] = xyt[3 * k];
-    g->xyt[3 * v + 1] = xyt[3 * k + 1];
-    g->xyt[3 * v + 2] = xyt[3 * k + 2];
+    if (g->find(keys[k]) < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[k]);
+    if (!(std::isfinite(xyt[3 * k]) && std::isfinite(xyt[3 * k + 1]) && std::isfinite(xyt[3 * k + 2])))
+      return g->fail(GS_EINVAL, "non-finite pose for key %llu", (unsigned long long)keys[k]);
   }
+  gs::parallel_for(n, [g, keys, xyt](size_t b, size_t e) {
+    for (size_t k = b; k < e; ++k) {
+      const int v = g->find(keys[k]);
+      g->xyt[3 * v] = xyt[3 * k];
+      g->xyt[3 * v + 1] = xyt[3 * k + 1];
+      g->xyt[3 * v + 2] = xyt[3 * k + 2];
+    }
+  });
   g->host_values_fresh = true;
+  g->theta_wrapped = false;
   g->device_values_valid = false;
   g->system_valid = false;
   if (!g->topo_dirty) return upload_values(g);

@@ -1,9 +1,33 @@
 // Host-side checks shared by the library and the test-only debug library.
 #pragma once
+#include <algorithm>
 #include <cmath>
+#include <thread>
+#include <vector>
 #include "se2.cuh"
 
 namespace gs {
+
+// fn(begin, end) over [0, n) on up to 16 host threads (per-pose conversions between the caller's (x, y, theta) and the
+// device's (x, y, cos, sin): a million sin/cos/atan2 on one thread is 20-50 ms, which a 140-ms LM step notices)
+template <typename F>
+inline void parallel_for(size_t n, F fn) {
+  const size_t min_chunk = 32768;
+  size_t nt = std::min<size_t>(std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 16), (n + min_chunk - 1) / min_chunk);
+  if (nt <= 1) {
+    fn((size_t)0, n);
+    return;
+  }
+  std::vector<std::thread> th;
+  th.reserve(nt - 1);
+  const size_t chunk = (n + nt - 1) / nt;
+  for (size_t t = 1; t < nt; ++t) {
+    const size_t b = t * chunk, e = std::min(n, b + chunk);
+    if (b < e) th.emplace_back([=] { fn(b, e); });
+  }
+  fn((size_t)0, std::min(n, chunk));
+  for (auto& t : th) t.join();
+}
 
 // noiseModel::Gaussian::Covariance(Q): symmetrise, Cholesky test (GTSAM throws on a non-SPD Q), invert -> information
 inline bool spd_information(const double* cov9, double* om6) {

@@ -144,7 +144,10 @@ GS_HD void normal_pieces(const Sym3& O, const Mat3& Ar, const Mat3& Ac, const do
   }
 }
 
-// Values::retract for Pose2: p o (dx, dy, dth); Rot2 product then renormalise (Rot2::fromCosSin).
+// Values::retract for Pose2: p o (dx, dy, dth).  The rotation product is ALWAYS renormalised here (so (c, s) cannot drift
+// over thousands of accepted steps of a resident graph); gtsam::Rot2::fromCosSin renormalises only when c^2 + s^2 is
+// off 1 by more than 1e-10, i.e. never for one product: the two differ by less than an ulp of theta = atan2(s, c),
+// which is scale-invariant.  The C port and the numpy oracle normalise the same way.
 GS_HD double4 retract(const double4 p, const double dx, const double dy, const double dth) {
   double sd, cd;
   sincos(dth, &sd, &cd);

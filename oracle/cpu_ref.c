@@ -454,7 +454,9 @@ int gs_cpu_optimize(int n, int e, const int* ei, const int* ej, const double* z,
   if (trace_err && trace_cap >= 0) trace_err[0] = error;
   double lambda = p->lambda_initial;
   int iterations = 0, rc = 0, ntrace = 0, capped = 0;
-  while (iterations < p->max_iterations && !capped) {
+  /* NonlinearOptimizer::defaultOptimize: nothing to do when the initial error is already <= errorTol */
+  if (error <= p->error_tol) S.converged = 1;
+  while (error > p->error_tol && iterations < p->max_iterations && !capped) {
     const double current_error = error;
     double t0 = now_ms();
     linearize(&G, pose, p->jacobian_mode);

@@ -351,7 +351,9 @@ def lm_optimize(prob: Problem, init, params: LMParams | None = None, solver=None
     tr.errors.append(error)
     iterations = 0
     eps = np.finfo(np.float64).eps
-    while True:
+    # NonlinearOptimizer::defaultOptimize: return before iterating when the initial error is already <= errorTol
+    nothing_to_do = error <= p.error_tol
+    while not nothing_to_do:
         if iterations >= p.max_iterations:
             break
         current_error = error

@@ -396,7 +396,8 @@ def test_fused_pcg_bitwise(cid, n):
     g = synth.config(cid, n=n)
     out = {}
     for fused in ("0", "1"):
-        with _load(g, solver_flags=0 if fused == "1" else _lib.GS_SOLVER_NO_PERSISTENT) as G:
+        bj = _lib.GS_SOLVER_BLOCK_JACOBI_ONLY       # (the persistent kernel is a block-Jacobi path)
+        with _load(g, solver_flags=bj if fused == "1" else bj | _lib.GS_SOLVER_NO_PERSISTENT) as G:
             st = G.optimize()
             _, x = G.poses()
             out[fused] = (st["chi2_final"], st["pcg_iterations_total"], st["iterations"], x, st["gpu_launches"])

@@ -54,7 +54,7 @@ def run(n0=10_000, batch=100, updates=400, cpu_updates=3, verbose=True):
               f"{st0['pcg_iterations_total']} PCG iterations, chi2 {st0['chi2_initial']:.5g} -> {st0['chi2_final']:.5g}",
               file=sys.stderr, flush=True)
 
-    lat, ms_struct, ms_solve, lm_its, pcg_its, chi2 = [], [], [], [], [], []
+    lat, ms_struct, ms_solve, lm_its, pcg_its, chi2, parts = [], [], [], [], [], [], []
     cpu_cases = []
     cpu_at = set(np.linspace(0, updates - 1, cpu_updates).astype(int).tolist()) if cpu_updates else set()
     for u in range(updates):
@@ -77,6 +77,7 @@ def run(n0=10_000, batch=100, updates=400, cpu_updates=3, verbose=True):
         dt = time.perf_counter() - t0
         lat.append(dt * 1e3)
         ms_struct.append(st["ms_structure"])
+        parts.append(st["ms_structure_parts"])
         ms_solve.append(st["ms_solve"])
         lm_its.append(st["iterations"])
         pcg_its.append(st["pcg_iterations_total"])
@@ -118,7 +119,10 @@ def run(n0=10_000, batch=100, updates=400, cpu_updates=3, verbose=True):
                                      (n0, n_final, updates, batch)),
                 p50=float(np.percentile(lat, 50)), p99=float(np.percentile(lat, 99)), mean=float(lat.mean()),
                 max=float(lat.max()), first_solve_ms=t_first * 1e3,
-                mean_structure_ms=float(np.mean(ms_struct)), mean_solve_ms=float(np.mean(ms_solve)),
+                mean_structure_ms=float(np.mean(ms_struct)),
+                mean_structure_parts_ms={k: float(np.mean([p_[k] for p_ in parts])) for k in parts[0]},
+                p50_structure_ms=float(np.percentile(ms_struct, 50)), p50_solve_ms=float(np.percentile(ms_solve, 50)),
+                mean_solve_ms=float(np.mean(ms_solve)),
                 mean_lm_iterations=float(np.mean(lm_its)), mean_pcg_iterations=float(np.mean(pcg_its)),
                 final_chi2=chi2[-1], n_final=n_final, cpu_baseline=cpu, dtype="f64", data="synthetic")
 
