@@ -65,12 +65,15 @@ template <typename T>
 struct DevBuf {
   T* p = nullptr;
   size_t n = 0;
+  // grows geometrically: a graph that gains a hundred poses per update (incremental mode) must not free and
+  // reallocate its forty buffers every time (cudaFree / cudaMalloc synchronise the device)
   cudaError_t alloc(size_t count) {
     if (count <= n && p) return cudaSuccess;
+    const bool growing = p != nullptr;
     release();
-    n = count;
     if (count == 0) return cudaSuccess;
-    return cudaMalloc(&p, count * sizeof(T));
+    n = growing ? count + count / 4 + 64 : count;
+    return cudaMalloc(&p, n * sizeof(T));
   }
   void release() {
     if (p) cudaFree(p);
@@ -1753,7 +1756,8 @@ gs_status gs_get_pose(gs_graph* g, uint64_t key, double out[3]) try {
   if (gs_status s = download_values(g)) return s;
   out[0] = g->xyt[3 * v];
   out[1] = g->xyt[3 * v + 1];
-  out[2] = std::atan2(std::sin(g->xyt[3 * v + 2]), std::cos(g->xyt[3 * v + 2]));
+  const double th = g->xyt[3 * v + 2];
+  out[2] = (th > -M_PI && th <= M_PI) ? th : std::atan2(std::sin(th), std::cos(th));
   return GS_OK;
 } catch (...) {
   return on_exception(g);
@@ -1776,7 +1780,9 @@ gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, siz
         const double th = g->xyt[3 * k + 2];
         xyt[3 * d] = g->xyt[3 * k];
         xyt[3 * d + 1] = g->xyt[3 * k + 1];
-        xyt[3 * d + 2] = wrapped ? th : std::atan2(std::sin(th), std::cos(th));   // values read back from the device are atan2 results already
+        // theta in (-pi, pi]: values already there are returned as they are (bit-exact save -> load -> read), only
+        // others are wrapped (values read back from the device are atan2 results, always in range)
+        xyt[3 * d + 2] = (wrapped || (th > -M_PI && th <= M_PI)) ? th : std::atan2(std::sin(th), std::cos(th));
       }
     }
   });

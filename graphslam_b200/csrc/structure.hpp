@@ -209,7 +209,7 @@ struct LocalStructure {
 // coarse unknowns (its rigid-body motion).  Aggregates never cross the fixed segment boundaries of the partition, so an
 // aggregate belongs to one rank whatever the number of ranks, and the aggregation does not depend on that number.
 // Built by recursive bisection: a breadth-first order of the vertex set from a far-away vertex (two sweeps), cut at
-// its median, until a set has at most `target` vertices.  Deterministic (no hashing, no randomness).
+// its median, until a set has at most `target` vertices (two sweeps per cut: one to find the far-away vertex, one for the order).  Deterministic (no hashing, no randomness).
 //   colour : distance-2 colouring of the aggregate adjacency graph — aggregates of one colour have no common
 //            neighbour, so the coarse matrix E = W^T H W is formed with one product H w per (colour, rigid mode)
 //            instead of one per aggregate.
@@ -293,9 +293,8 @@ inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const s
         continue;
       }
       bfs_order(j.verts, j.rid, j.verts[0], order);
-      const int far = order.back();
+      const int far = order.back();                   // a vertex far from an arbitrary one: (pseudo-)peripheral
       bfs_order(j.verts, j.rid, far, order);
-      bfs_order(j.verts, j.rid, order.back(), order);
       const int half = cnt / 2;
       Job lo, hi;
       lo.rid = next_region++;
