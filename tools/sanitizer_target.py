@@ -13,7 +13,7 @@ from graphslam_b200 import graph, synth  # noqa: E402
 for name, g, flags, iters in (("persistent", synth.config("C1", n=1500), 0, 2),
                               ("two-level", synth.config("C3", n=9000), 0, 2),
                               ("three-kernel block-Jacobi", synth.config("C3", n=9000), 32 | 4, 1)):
-    with graph.Graph(solver_flags=flags, max_iterations=iters, pcg_max_iters=400) as G:
+    with graph.Graph(solver_flags=flags, max_iterations=iters, pcg_max_iters=20000) as G:
         G.add_graph(g)
         st = G.optimize()
         key, dist = G.closest_keyframe(int(g.keys[-1]), 10)
