@@ -90,6 +90,7 @@ SIGNATURES = {
     "gs_compose_reference": (None, [c_double_p, c_double_p, c_double_p]),
     "gs_compose": (None, [c_double_p, c_double_p, c_double_p]),
     "gs_closest_keyframe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, c_u64_p, c_double_p]),
+    "gs_closest_keyframe_noalloc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, c_u64_p, c_double_p]),
 }
 
 class GsEmuProblem(C.Structure):

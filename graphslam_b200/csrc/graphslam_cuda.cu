@@ -2207,4 +2207,88 @@ gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out
   return on_exception(g);
 }
 
+// ---- closest_keyframe without any allocation ---------------------------------------------------------------------
+// gs_closest_keyframe keeps its per-CTA partial results, its result word and its last-CTA counter in a device buffer
+// that it allocates (and grows) on demand.  Callers that must not allocate — code under CUDA-graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc — get the same kernel with that scratch in a file-scope device
+// array of fixed size instead.  Every GPU that loads the library holds the array (64 KB + 32 B) until the process
+// exits.  The array's name is a host-side stand-in in host code, not a device address: the address is resolved once
+// per device with cudaGetSymbolAddress, with that device current, and handed to the kernel.
+constexpr int kClosestStaticMaxCtas = 4096;                                                 // partials the array holds
+constexpr int kClosestStaticMaxPoses = kClosestStaticMaxCtas * gs::kThreads * gs::kClosestPerThread;   // 8,388,608
+static_assert(kClosestStaticMaxPoses == GS_CLOSEST_NOALLOC_MAX_POSES, "header and scratch array disagree");
+// [0] result, [1] last-CTA counter (first word), [2 ...] one partial per CTA
+static __device__ __align__(256) gs::ClosestOut g_closest_static[2 + kClosestStaticMaxCtas];
+
+namespace {
+struct ClosestStaticAddr {
+  std::mutex mu;
+  gs::ClosestOut* ptr[64] = {nullptr};
+};
+ClosestStaticAddr& closest_static_addr() {
+  static ClosestStaticAddr a;
+  return a;
+}
+}  // namespace
+
+gs_status gs_closest_keyframe_noalloc(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist) try {
+  if (!g || !out_key || skip < 0) return GS_EINVAL;
+  if (g->world != 1) return g->fail(GS_EINVAL, "gs_closest_keyframe_noalloc runs on a single-rank graph");
+  const int v = g->find(key);
+  if (v < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)key);
+  const int nv = (int)g->keys.size();
+  if (nv <= skip) return g->fail(GS_ENOKEY, "not enough keyframes (%d <= skip %d)", nv, skip);
+  // everything that would allocate must have happened before: structure built, values on the device
+  if (g->topo_dirty || !g->device_values_valid)
+    return g->fail(GS_EINVAL, "gs_closest_keyframe_noalloc needs a prepared graph with its values on the device (call gs_prepare "
+                              "or gs_optimize after the last gs_add_* / gs_set_poses): it allocates nothing itself");
+  const int count = nv - skip;
+  if (count > kClosestStaticMaxPoses)
+    return g->fail(GS_EINVAL, "gs_closest_keyframe_noalloc handles at most %d candidate keyframes (%d asked for): its scratch is a "
+                              "fixed device array; use gs_closest_keyframe", kClosestStaticMaxPoses, count);
+  const int* order = nullptr;
+  if (!g->identity_order) {   // the insertion-order -> row table is uploaded (and allocated) by gs_closest_keyframe only
+    if (g->closest_order_n != nv)
+      return g->fail(GS_EINVAL, "gs_closest_keyframe_noalloc: keys were not inserted in increasing order and the order table is not "
+                                "on the device yet; call gs_closest_keyframe once after the last topology change");
+    order = g->d_closest_order.p;
+  }
+  int dev = 0;
+  GS_CUDA(g, cudaGetDevice(&dev));
+  if (g->prm.device >= 0 && dev != g->prm.device) {
+    GS_CUDA(g, cudaSetDevice(g->prm.device));
+    dev = g->prm.device;
+  }
+  if (dev < 0 || dev >= 64) return g->fail(GS_EINVAL, "device ordinal %d out of range", dev);
+  gs::ClosestOut* scratch = nullptr;
+  {
+    ClosestStaticAddr& A = closest_static_addr();
+    std::lock_guard<std::mutex> lock(A.mu);
+    if (!A.ptr[dev]) {   // once per device, with that device current
+      void* p = nullptr;
+      GS_CUDA(g, cudaGetSymbolAddress(&p, g_closest_static));
+      A.ptr[dev] = static_cast<gs::ClosestOut*>(p);
+    }
+    scratch = A.ptr[dev];
+  }
+  const int grid = (count + gs::kThreads * gs::kClosestPerThread - 1) / (gs::kThreads * gs::kClosestPerThread);
+  // the array keeps the last call's contents: the counter must start at zero (a call that failed mid-way could have
+  // left it otherwise); result and partials are fully overwritten before they are read
+  GS_CUDA(g, cudaMemsetAsync(scratch + 1, 0, sizeof(gs::ClosestOut), g->stream));
+  gs::k_closest<<<grid, gs::kThreads, 0, g->stream>>>(g->d_pose.p, order, count, g->d_pose.p + g->ins2dense[v], 0, g->n_own,
+                                                       scratch + 2, reinterpret_cast<unsigned int*>(scratch + 1), scratch);
+  g->launches += 1;
+  gs::ClosestOut res;
+  GS_CUDA(g, cudaMemcpyAsync(&res, scratch, sizeof res, cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  GS_CUDA(g, cudaGetLastError());
+  g->d2h_bytes += sizeof res;
+  if (res.idx < 0 || res.idx >= nv) return g->fail(GS_ECUDA, "closest_keyframe: no candidate found");
+  *out_key = g->keys[res.idx];
+  if (out_dist) *out_dist = res.dist;
+  return GS_OK;
+} catch (...) {
+  return on_exception(g);
+}
+
 }  // extern "C"

@@ -270,6 +270,13 @@ class Graph:
         self._ck(self._lib.gs_closest_keyframe(self._h, int(key), int(skip), C.byref(out), C.byref(dist)))
         return out.value, dist.value
 
+    def closest_keyframe_noalloc(self, key: int, skip: int = 10):
+        """gs_closest_keyframe_noalloc: the same query with its scratch in a fixed device array (allocates nothing)."""
+        out = C.c_uint64()
+        dist = C.c_double()
+        self._ck(self._lib.gs_closest_keyframe_noalloc(self._h, int(key), int(skip), C.byref(out), C.byref(dist)))
+        return out.value, dist.value
+
 
 def nccl_unique_id() -> bytes:
     """ncclUniqueId bytes for gs_create_distributed; call on ONE rank and hand the bytes to all."""

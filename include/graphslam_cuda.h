@@ -220,6 +220,19 @@ void gs_compose(const double a_xyt[3], const double b_xyt[3], double out_xyt[3])
  * Returns GS_ENOKEY if fewer than skip+1 vertices exist (service returns false). */
 gs_status gs_closest_keyframe(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist);
 
+/* The same query for callers that must not allocate (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree / allocating library routine: the reduction's scratch (per-CTA partial results,
+ * result, last-CTA counter) lives in a fixed file-scope device array that every GPU loading the library holds until
+ * process exit (64 KB), which bounds the candidate count: at most GS_CLOSEST_NOALLOC_MAX_POSES keyframes
+ * (GS_EINVAL with a message beyond that).  Requirements, each answered with GS_EINVAL and a message instead of an
+ * allocation: a single-rank graph that is prepared with its values on the device (gs_prepare / gs_optimize after the
+ * last gs_add_* or gs_set_poses); keys inserted in increasing order, or one earlier gs_closest_keyframe call since the
+ * last topology change.  Same result as gs_closest_keyframe, bit for bit.  All calls (of all graphs on one GPU) share
+ * the array: calls that overlap on the GPU race; calls on one graph, or serialised by the caller, do not. */
+#define GS_CLOSEST_NOALLOC_MAX_POSES 8388608
+gs_status gs_closest_keyframe_noalloc(gs_graph* g, uint64_t key, int skip, uint64_t* out_key, double* out_dist);
+
 #ifdef __cplusplus
 }
 #endif
