@@ -111,6 +111,7 @@ struct gs_graph {
   bool p2p = false;                       // windows exchanged, peer-memory kernels in use
   char* win = nullptr;                    // this rank's exported window: header + p
   size_t win_bytes = 0;
+  size_t win_ghost_off = gs::kWindowHeaderBytes;   // where the ghost rows of p start inside a window (same on every rank)
   int win_generation = 0;
   char* peer_win[gs::kMaxRanks] = {nullptr};   // peer mappings (allocation base + offset)
   void* peer_base[gs::kMaxRanks] = {nullptr};  // what cudaIpcOpenMemHandle returned
@@ -451,6 +452,29 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     }
     return GS_OK;
   }
+  if (g->p2p && coarse_active(g)) {
+    // two-level preconditioner over peer memory: six kernels, no NCCL call (kernels_p2p.cuh)
+    const gs::P2PCtx x = p2p_ctx(g, k_local);
+    const int m = 3 * g->agg.n_agg;
+    if (stage == 0) {
+      gs::k_spmv_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->pvec, g->pghost, g->d_Ap.p,
+                                                                   reduce_ctx(g, 0), x);
+    } else if (stage == 1) {
+      gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
+      if (g->agg_own) gs::k_restrict_p2p<<<g->agg_own, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, x);
+      gs::k_c_unpack_p2p<<<(m + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(x, g->agg.n_agg, g->d_cvec.p, g->d_sc.p);
+      gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(
+          g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p, g->d_counter.p + 6, g->d_sc.p, 0);
+    } else {
+      gs::HaloPush h;
+      h.row = g->d_hp_row.p;
+      h.dst = g->d_hp_dst.p;
+      h.n_push_tiles = g->n_push_tiles;
+      h.order = g->d_hp_order.p;
+      gs::k_dir_coarse_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p, x, h);
+    }
+    return GS_OK;
+  }
   if (g->p2p) {
     const gs::P2PCtx x = p2p_ctx(g, k_local);
     if (stage == 0) {
@@ -591,7 +615,10 @@ void close_peer(gs_graph* g, int q) {
 // (re)build the window, exchange handles, map the peers, and lay out the halo pushes.  Collective.
 gs_status prepare_p2p(gs_graph* g) {
   const LocalStructure& S = g->S;
-  const size_t need = gs::kWindowHeaderBytes + sizeof(double) * 3 * (size_t)std::max(S.n_ghost, 1);
+  // window = header | landing zone of the coarse vector c (two-level preconditioner; 2 parities x 6 n_agg flagged words,
+  // the same size on every rank) | ghost rows of p
+  g->win_ghost_off = gs::kWindowHeaderBytes + (g->coarse ? ((2 * 6 * (size_t)g->agg.n_agg * 8 + 255) / 256) * 256 : 0);
+  const size_t need = g->win_ghost_off + sizeof(double) * 3 * (size_t)std::max(S.n_ghost, 1);
   XchgRecord mine;
   std::memset(&mine, 0, sizeof mine);
   mine.will_realloc = (need > g->win_bytes) ? 1 : 0;
@@ -612,7 +639,9 @@ gs_status prepare_p2p(gs_graph* g) {
     // the sequence numbering restarts with the fresh (zeroed) flags on every rank at once?  No: only this
     // rank's flags are new, so keep counting — stamps only ever need to exceed what a waiter asks for.
   }
-  g->pghost = reinterpret_cast<double*>(g->win + gs::kWindowHeaderBytes);
+  g->pghost = reinterpret_cast<double*>(g->win + g->win_ghost_off);
+  if (g->win_ghost_off > gs::kWindowHeaderBytes)   // stamps of an earlier layout must not survive in the landing zone
+    GS_CUDA(g, cudaMemsetAsync(g->win + gs::kWindowHeaderBytes, 0, g->win_ghost_off - gs::kWindowHeaderBytes, g->stream));
   GS_CUDA(g, cudaMemsetAsync(g->pghost, 0, sizeof(double) * 3 * (size_t)std::max(S.n_ghost, 1), g->stream));
   GS_CUDA(g, cudaIpcGetMemHandle(&mine.handle, g->win));
   mine.offset = allocation_offset(g->win);
@@ -639,7 +668,7 @@ gs_status prepare_p2p(gs_graph* g) {
   g->nbr_mask = 0;
   for (const gs::HaloPeer& hp : S.peers) {
     g->nbr_mask |= 1u << hp.rank;
-    double* peer_p = reinterpret_cast<double*>(g->peer_win[hp.rank] + gs::kWindowHeaderBytes);
+    double* peer_p = reinterpret_cast<double*>(g->peer_win[hp.rank] + g->win_ghost_off);
     const size_t slot0 = (size_t)all[hp.rank].ghost_off[g->rank];
     for (int k = 0; k < hp.send_cnt; ++k) ent.push_back({S.send_rows[hp.send_off + k], peer_p + 3 * (slot0 + k)});
   }
@@ -795,9 +824,8 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   gs::canonical_order(N, E, g->di.data(), g->dj.data(), g->perm);
   gs::build_local_structure(N, E, g->di.data(), g->dj.data(), g->perm, P, g->dp.data(), g->world, g->rank, g->S);
   const LocalStructure& S = g->S;
-  // two-level preconditioner: aggregates of the block rows (one rank; small graphs keep the persistent kernel)
-  // (several ranks: through the NCCL-per-exchange path; the peer-memory kernels run block-Jacobi only)
-  g->coarse = g->coarse_wanted && N >= 8192 && (g->world == 1 || !g->p2p_wanted);
+  // two-level preconditioner: aggregates of the block rows (small graphs keep block-Jacobi: persistent kernel on one GPU)
+  g->coarse = g->coarse_wanted && N >= 8192;
   if (g->coarse) {
     std::vector<int32_t> rp, ci;
     gs::global_pattern(N, E, g->di.data(), g->dj.data(), rp, ci);
@@ -937,6 +965,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     if (!can || (f & GS_SOLVER_DIR_KERNEL)) g->dir_otf = false;
     else if (f & GS_SOLVER_DIR_ON_THE_FLY) g->dir_otf = true;
     else g->dir_otf = g->world > 1 ? (N / g->world >= 200000) : false;
+    if (g->coarse) g->dir_otf = false;   // the two-level iteration folds the prolongation into its own direction kernel
   }
   if (g->fused) GS_CUDA(g, g->d_p_alt.alloc(3 * (size_t)std::max(g->n_own, 1) + 3));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));  // staging vectors go out of scope
@@ -1139,6 +1168,7 @@ gs_status begin_p2p_solve(gs_graph* g) {
 
 int64_t launches_per_pcg_iteration(const gs_graph* g) {
   if (g->dir_otf && g->p2p) return 2;
+  if (coarse_active(g) && g->p2p) return 6;
   if (coarse_active(g)) return g->world == 1 ? 5 : 5 + 2 + (g->S.send_rows.empty() ? 0 : 1);
   if (g->world == 1 || g->p2p) return 3;
   return 3 + 2 + (g->S.send_rows.empty() ? 0 : 1);  // + two k_scalars + k_pack
@@ -1220,9 +1250,6 @@ gs_status create_common(gs_graph* g) {
   g->p2p_wanted = !(flags & GS_SOLVER_NCCL_PER_OP);
   g->p2p_staged = (flags & GS_X_P2P_STAGED) != 0;
   g->coarse_wanted = !(flags & GS_SOLVER_BLOCK_JACOBI_ONLY);
-  // several ranks: the two-level preconditioner runs over the NCCL-per-exchange path; the peer-memory kernels
-  // (collectives fused into the PCG kernels) run block-Jacobi only and are chosen with GS_SOLVER_BLOCK_JACOBI_ONLY
-  if (g->coarse_wanted && g->world > 1) g->p2p_wanted = false;
   {
     int per_sm = 0, sms = 0, dev = 0, coop = 0;
     GS_CUDA(g, cudaGetDevice(&dev));

@@ -83,16 +83,15 @@ __global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, cons
   v[3 * (size_t)r + 2] = o[2];
 }
 
-// out[a * ostride + ooff .. + 3) = sum over the rows of owned aggregate a (list order) of W_i^T r_i (a = global index).
-// Thread t takes rows t, t+T, ...; then the fixed shuffle / shared-memory tree of block_sum.
-__global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
-                                                        int honour_done, double* __restrict__ out, int ostride, int ooff) {
-  __shared__ double red[8];
-  if (honour_done && sc->done) return;
-  const int g = blockIdx.x;                   // local aggregate
+// this thread's share of sum_{i in aggregate g} W_i^T r_i (g = local aggregate index): rows threadIdx.x, + T, ... of
+// the aggregate's list, in list order — ONE spelling for the single-GPU and the peer-memory kernel
+__device__ __forceinline__ void restrict_sums(const CoarseView& a, const double* __restrict__ r, int g, double& s0, double& s1,
+                                              double& s2) {
   const int q0 = a.agg_ptr[g], q1 = a.agg_ptr[g + 1];
   const double2 ref = ldg(a.ref + a.a0 + g);
-  double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+  s0 = 0.0;
+  s1 = 0.0;
+  s2 = 0.0;
   // four rows per thread and trip: the four row indices, then their poses and residuals, are requested together;
   // the sums run over the thread's rows in list order
   for (int q = q0 + (int)threadIdx.x; q < q1; q += 4 * kThreads) {
@@ -118,6 +117,17 @@ __global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, co
       s2 += (w.u * rv[u][0] + w.v * rv[u][1]) + rv[u][2];
     }
   }
+}
+
+// out[a * ostride + ooff .. + 3) = sum over the rows of owned aggregate a (list order) of W_i^T r_i (a = global index).
+// Thread t takes rows t, t+T, ...; then the fixed shuffle / shared-memory tree of block_sum.
+__global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
+                                                        int honour_done, double* __restrict__ out, int ostride, int ooff) {
+  __shared__ double red[8];
+  if (honour_done && sc->done) return;
+  const int g = blockIdx.x;                   // local aggregate
+  double s0, s1, s2;
+  restrict_sums(a, r, g, s0, s1, s2);
   const double t0 = block_sum(s0, red);
   const double t1 = block_sum(s1, red);
   const double t2 = block_sum(s2, red);
@@ -226,18 +236,16 @@ __global__ void __launch_bounds__(kThreads, 4) k_coarse_mv(const double* __restr
       sc->beta = rz_new / sc->rz;
       sc->rz = rz_new;
     }
+    sc->rzv[0] = rz_new;   // the peer-memory update kernel reads r.z of the previous iterate from here
+    sc->rzv[1] = rz_new;
     *counter = 0u;
   }
 }
 
-// p = (z + W mu) + beta p, one thread per row
-__global__ void __launch_bounds__(kThreads) k_dir_coarse(const CoarseView a, const double* __restrict__ z,
-                                                          const double* __restrict__ mu, double* __restrict__ p,
-                                                          const Scalars* sc) {
-  if (sc->done) return;
-  const int r = blockIdx.x * kThreads + threadIdx.x;
-  if (r >= a.n_own) return;
-  const double beta = sc->beta;
+// one row of p = (z + W mu) + beta p — ONE spelling for the single-GPU and the peer-memory kernel (same contraction,
+// same bits)
+__device__ __forceinline__ void dir_coarse_row(const CoarseView& a, const double* __restrict__ z, const double* __restrict__ mu,
+                                               double* __restrict__ p, double beta, int r) {
   const int g = a.agg_of[r];
   const WBlock w = w_block(ldg(a.pose + r), ldg(a.ref + g));
   const double m0 = mu[3 * (size_t)g], m1 = mu[3 * (size_t)g + 1], m2 = mu[3 * (size_t)g + 2];
@@ -248,6 +256,16 @@ __global__ void __launch_bounds__(kThreads) k_dir_coarse(const CoarseView a, con
   p[o] = dir_value(z0, beta, p[o]);
   p[o + 1] = dir_value(z1, beta, p[o + 1]);
   p[o + 2] = dir_value(z2, beta, p[o + 2]);
+}
+
+// p = (z + W mu) + beta p, one thread per row
+__global__ void __launch_bounds__(kThreads) k_dir_coarse(const CoarseView a, const double* __restrict__ z,
+                                                          const double* __restrict__ mu, double* __restrict__ p,
+                                                          const Scalars* sc) {
+  if (sc->done) return;
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  if (r >= a.n_own) return;
+  dir_coarse_row(a, z, mu, p, sc->beta, r);
 }
 
 }  // namespace gs

@@ -27,6 +27,7 @@
 // single-GPU kernels cost on a 500k-row graph, except the direction update (18 us against 10 us).
 #pragma once
 #include "kernels.cuh"
+#include "kernels_coarse.cuh"
 
 namespace gs {
 
@@ -567,6 +568,117 @@ __global__ void __launch_bounds__(kThreads) k_updpush_p2p_staged(const PcgView a
     __syncthreads();
   }
   reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_upd[0][0]; }, red, &flag, job.x);
+}
+
+// ---- two-level preconditioner over peer memory ----------------------------------------------------------------
+// The iteration of kernels_coarse.cuh with its exchanges fused into the kernels (six launches, no NCCL call):
+//
+//   k_spmv_p2p          as above (waits for the neighbours' rows of p, sends p.Ap)
+//   k_update_p2p        as above (waits for p.Ap; x, r, z = M^-1 r; sends r.M^-1 r and r.r)
+//   k_restrict_p2p      c_a = W_a^T r for the rank's own aggregates, stored into EVERY rank's window as flagged words
+//   k_c_unpack_p2p      waits for all 3 n_agg entries of c (and, in block 0, for r.M^-1 r / r.r: the scalar step
+//                       OP_UPDATE_2L) and writes c as plain doubles
+//   k_coarse_mv         unchanged: every rank multiplies the whole E^-1 (same arithmetic as one GPU, hence the same
+//                       bits and no further exchange for c.mu), forms r.z and beta
+//   k_dir_coarse_p2p    p = (z + W mu) + beta p; rows the neighbours need go straight into their ghost slots
+//
+// The landing zone of c sits in the window between the header and the ghost rows: 2 parities x 6 n_agg words, the
+// same size on every rank (n_agg is global).
+__device__ __forceinline__ unsigned long long* coarse_words(P2PWindow* w) {
+  return reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(w) + kWindowHeaderBytes);
+}
+
+__global__ void __launch_bounds__(kThreads, 4) k_restrict_p2p(const CoarseView a, const double* __restrict__ r, const Scalars* sc,
+                                                               const P2PCtx x) {
+  __shared__ double red[8];
+  __shared__ double tot[3];
+  if (sc->done) return;
+  const unsigned int S = *x.seq_base + x.k_local;
+  const int g = blockIdx.x;                   // local aggregate
+  double s0, s1, s2;
+  restrict_sums(a, r, g, s0, s1, s2);
+  const double t0 = block_sum(s0, red);
+  const double t1 = block_sum(s1, red);
+  const double t2 = block_sum(s2, red);
+  if (threadIdx.x == 0) {
+    tot[0] = t0;
+    tot[1] = t1;
+    tot[2] = t2;
+  }
+  __syncthreads();
+  // one thread per (destination rank, component, half): an aligned 8-byte store arrives whole
+  const int t = threadIdx.x;
+  if (t < 6 * x.world) {
+    const int d = t / 6, u = t - 6 * d;
+    const double val = tot[u >> 1];
+    const unsigned int bits = (unsigned int)((u & 1) ? __double2hiint(val) : __double2loint(val));
+    unsigned long long* dst = coarse_words(x.win[d]) + (size_t)(S & 1u) * (6 * (size_t)a.n_agg) + 6 * (size_t)(a.a0 + g) + u;
+    st_relaxed64(dst, ((unsigned long long)(S + 1) << 32) | bits);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_c_unpack_p2p(const P2PCtx x, int n_agg, double* __restrict__ cvec, Scalars* sc) {
+  __shared__ WaitOut wo;
+  if (sc->done) return;
+  const unsigned int S = *x.seq_base + x.k_local;
+  const unsigned int stamp = S + 1;
+  const int i = blockIdx.x * kThreads + threadIdx.x;
+  if (i < 3 * n_agg) {
+    const unsigned long long* w = coarse_words(x.me) + (size_t)(S & 1u) * (6 * (size_t)n_agg) + 2 * (size_t)i;
+    unsigned long long lo = 0, hi = 0;
+    const long long w0 = clock64();
+    bool ok = true;
+    for (;;) {
+      lo = ld_relaxed64(w);
+      hi = ld_relaxed64(w + 1);
+      if ((unsigned int)(lo >> 32) == stamp && (unsigned int)(hi >> 32) == stamp) break;
+      if (clock64() - w0 > x.spin_limit) {
+        ok = false;
+        break;
+      }
+    }
+    if (ok) cvec[i] = __hiloint2double((int)(unsigned int)(hi & 0xffffffffull), (int)(unsigned int)(lo & 0xffffffffull));
+    else sc->done = 4;
+  }
+  if (blockIdx.x == 0) {   // the scalar step the single-GPU update kernel's last CTA takes (OP_UPDATE_2L)
+    if (!wait_sums<2>(x.me->ll_upd[S & 1u], stamp, sc, x.spin_limit, &wo, 2)) return;
+    if (threadIdx.x == 0) apply_scalars(sc, OP_UPDATE_2L, wo.tot[0], wo.tot[1]);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_dir_coarse_p2p(const CoarseView a, const double* __restrict__ z,
+                                                              const double* __restrict__ mu, double* __restrict__ p,
+                                                              const Scalars* sc, const P2PCtx x, const HaloPush h) {
+  __shared__ int flag;
+  if (sc->done) return;
+  const unsigned int S = *x.seq_base + x.k_local;
+  const int4 job = ldg(h.order + blockIdx.x);   // (tile, first entry, end entry): sending tiles first
+  const int r = job.x * kThreads + (int)threadIdx.x;
+  if (r < a.n_own) dir_coarse_row(a, z, mu, p, sc->beta, r);
+  const int h0 = job.y, h1 = job.z;
+  if (h1 == h0) return;   // nothing to send from this tile (uniform over the CTA)
+  __syncthreads();        // the tile's new p is visible to the CTA
+  bool pushed = false;
+  for (int e = h0 + (int)threadIdx.x; e < h1; e += kThreads) {
+    const double* src = p + 3 * (size_t)h.row[e];
+    double* dst = h.dst[e];
+    dst[0] = __ldcg(src);
+    dst[1] = __ldcg(src + 1);
+    dst[2] = __ldcg(src + 2);
+    pushed = true;
+  }
+  if (pushed) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(x.ticket, 1u);
+    flag = (t == (unsigned int)h.n_push_tiles - 1u);
+  }
+  __syncthreads();
+  if (flag) {   // the last sending tile: every neighbour's rows are in place
+    if ((int)threadIdx.x < x.world && ((x.nbr_mask >> threadIdx.x) & 1u))
+      st_release_sys(&x.win[threadIdx.x]->halo_flag[x.rank], S + 2);
+    if (threadIdx.x == 0) *x.ticket = 0u;
+  }
 }
 
 // start of a solve: the ghost rows of p(0) arrived by the ordinary halo exchange, so mark them

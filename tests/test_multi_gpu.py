@@ -30,10 +30,11 @@ def _free_port():
 # The staged x/r/z update inside the peer-memory kernels (GS_X_P2P_STAGED, csrc/kernels_p2p.cuh) is a candidate under
 # measurement and only exercised on request (GS_TEST_CANDIDATES=1, read by this test harness, not by the library).
 _NCCL, _DIRK, _OTF, _BJ, _XSTAGED = 2, 8, 16, 32, 1 << 17
-# block-Jacobi PCG: peer-memory kernels (two or three per iteration) or one NCCL call per exchange; default = the
-# two-level preconditioner over the NCCL-per-exchange path.  Each is compared with ONE GPU running the same preconditioner.
+# block-Jacobi PCG: peer-memory kernels (two or three per iteration) or one NCCL call per exchange; two-level
+# preconditioner: peer-memory kernels (default) or NCCL per exchange.  Each is compared with ONE GPU running the same
+# preconditioner.
 _FORMS = [("peer-memory-2-kernels", _BJ | _OTF), ("peer-memory-3-kernels", _BJ | _DIRK), ("nccl-per-op", _BJ | _NCCL),
-          ("two-level-default", 0)]
+          ("two-level-default", 0), ("two-level-nccl-per-op", _NCCL)]
 if os.environ.get("GS_TEST_CANDIDATES") == "1":
     _FORMS += [("peer-memory-2-kernels-staged", _BJ | _OTF | _XSTAGED), ("peer-memory-3-kernels-staged", _BJ | _DIRK | _XSTAGED)]
 
