@@ -187,6 +187,7 @@ struct gs_graph {
   DevBuf<double> d_cvec, d_mu, d_cpart, d_R, d_G, d_E, d_chol_work, d_basis;
   DevBuf<int> d_chol_info;
   DevBuf<double2> d_agg_ref;
+  DevBuf<int> d_coarse_seg_row;           // [kSegments + 1] rows of the coarse vector per fixed reduction segment (3 x seg_agg)
   int chol_lwork = 0;
   int agg_a0 = 0, agg_own = 0;            // this rank's aggregates [agg_a0, agg_a0 + agg_own)
   bool coarse_e0_valid = false;           // R (= W^T H W by columns) and G computed at the current linearisation
@@ -463,8 +464,11 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
       if (g->agg_own) gs::k_restrict_p2p<<<g->agg_own, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, x);
       gs::k_c_unpack_p2p<<<(m + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(x, g->agg.n_agg, g->d_cvec.p, g->d_sc.p);
-      gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(
-          g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p, g->d_counter.p + 6, g->d_sc.p, 0);
+      const int nrows = 3 * g->agg_own;
+      if (nrows)
+        gs::k_coarse_mv_p2p<<<(nrows + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(
+            g->d_E.p, g->d_cvec.p, m, 3 * g->agg_a0, nrows, g->d_mu.p, g->d_cpart.p, g->d_coarse_seg_row.p, g->d_counter.p + 6,
+            g->d_sc.p, x);
     } else {
       gs::HaloPush h;
       h.row = g->d_hp_row.p;
@@ -506,8 +510,8 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       if (g->agg_own)
         gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p, 3, 0);
       if (gs_status s = coarse_gather(g, g->d_cvec.p, 3)) return s;
-      gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
-                                                                    g->d_counter.p + 6, g->d_sc.p, 0);
+      gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(
+          g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p, g->d_coarse_seg_row.p, g->d_counter.p + 6, g->d_sc.p, 0);
     } else {
       gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
     }
@@ -932,7 +936,12 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     if (gs_status s = upload(g, g->d_nbr_of_color, A.nbr_of_color)) return s;
     GS_CUDA(g, g->d_cvec.alloc(m));
     GS_CUDA(g, g->d_mu.alloc(m));
-    GS_CUDA(g, g->d_cpart.alloc(m / gs::kCoarseRows + 2));
+    GS_CUDA(g, g->d_cpart.alloc(m + 2));   // per-row products mu_i c_i
+    {
+      std::vector<int> seg_row(gs::kSegments + 1);
+      for (int k = 0; k <= gs::kSegments; ++k) seg_row[k] = 3 * A.seg_agg[k];
+      if (gs_status s = upload(g, g->d_coarse_seg_row, seg_row)) return s;
+    }
     GS_CUDA(g, g->d_R.alloc((size_t)A.n_colors * 3 * m));
     GS_CUDA(g, cudaMemsetAsync(g->d_R.p, 0, sizeof(double) * (size_t)A.n_colors * 3 * m, g->stream));
     GS_CUDA(g, g->d_G.alloc(3 * m));
@@ -1140,8 +1149,8 @@ gs_status launch_pcg_setup(gs_graph* g) {
     if (g->agg_own)
       gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_r.p, g->d_sc.p, 1, g->d_cvec.p, 3, 0);
     if (gs_status s = coarse_gather(g, g->d_cvec.p, 3)) return s;
-    gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p,
-                                                                  g->d_counter.p + 6, g->d_sc.p, 1);
+    gs::k_coarse_mv<<<(m + gs::kCoarseRows - 1) / gs::kCoarseRows, gs::kThreads, 0, g->stream>>>(
+        g->d_E.p, g->d_cvec.p, m, g->d_mu.p, g->d_cpart.p, g->d_coarse_seg_row.p, g->d_counter.p + 6, g->d_sc.p, 1);
     gs::k_dir_coarse<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(coarse_view(g), g->d_z.p, g->d_mu.p, g->pvec, g->d_sc.p);
     g->launches += 3;
     return GS_OK;

@@ -170,24 +170,25 @@ __global__ void __launch_bounds__(kThreads) k_symmetrize(double* __restrict__ Em
 }
 
 // mu = Einv c (dense, symmetric, column-major = row-major): kCoarseRows rows per CTA, kThreads / kCoarseRows threads
-// per row, every thread eight columns at a time (eight loads in flight), all sums in one fixed order.  The last CTA
-// to finish adds c.mu in fixed order and takes the scalar step that closes the preconditioner application:
-//     r.z = r.M^-1 r (from the update kernel) + c.mu      — the corrected z is never formed for the dot product.
-//   init != 0: start of a solve (r.z of the initial residual, no beta)
+// per row, every thread eight columns at a time (eight loads in flight), all sums in one fixed order.
 constexpr int kCoarseRows = 2;
-__global__ void __launch_bounds__(kThreads, 4) k_coarse_mv(const double* __restrict__ Einv, const double* __restrict__ cvec, int m,
-                                                         double* __restrict__ mu, double* __restrict__ part,
-                                                         unsigned int* counter, Scalars* sc, int init) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  if (sc->done) return;
+
+// Rows [row0, row0 + nrows) of mu = Einv c (this rank's aggregates; one GPU: all of them), the per-row products
+// mu_i c_i, and — in the last CTA to finish — their sums over the fixed reduction segments s0 .. s1-1 (segment s =
+// rows seg_row[s] .. seg_row[s+1]-1 of the coarse vector: aggregates never cross segment boundaries), left in
+// csegs[s0 .. s1).  The segment structure makes c.mu, like every other dot product, independent of the number of
+// ranks.  Returns true in every thread of that last CTA.
+__device__ __forceinline__ bool coarse_mv_rows(const double* __restrict__ Einv, const double* __restrict__ cvec, int m, int row0,
+                                               int nrows, double* __restrict__ mu, double* __restrict__ rowprod,
+                                               const int* __restrict__ seg_row, int s0, int s1, double* csegs,
+                                               unsigned int* counter, double* red, int* flag) {
   constexpr int kPerRow = kThreads / kCoarseRows;        // threads per row
   const int w = threadIdx.x >> 5;
   const int sub = threadIdx.x / kPerRow, t = threadIdx.x % kPerRow;
-  const int row = blockIdx.x * kCoarseRows + sub;
+  const int lrow = blockIdx.x * kCoarseRows + sub;
   double acc = 0.0;
-  if (row < m) {
-    const double* e = Einv + (size_t)row * m;
+  if (lrow < nrows) {
+    const double* e = Einv + (size_t)(row0 + lrow) * m;
     double p8[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     for (int j = t; j < m; j += 8 * kPerRow) {      // the tail is predicated, not a second loop: p8 stays in registers
       double ev[8], cv[8];
@@ -206,28 +207,45 @@ __global__ void __launch_bounds__(kThreads, 4) k_coarse_mv(const double* __restr
   acc = warp_sum(acc);
   if ((threadIdx.x & 31) == 0) red[w] = acc;
   __syncthreads();
-  double prod = 0.0;
   if (threadIdx.x < kCoarseRows) {          // thread s finishes row s of this CTA: its warps' sums in warp order
     constexpr int kWarpsPerRow = kPerRow / 32;
     double s = 0.0;
     for (int k = 0; k < kWarpsPerRow; ++k) s += red[threadIdx.x * kWarpsPerRow + k];
     const int rr = blockIdx.x * kCoarseRows + (int)threadIdx.x;
-    if (rr < m) {
-      mu[rr] = s;
-      prod = s * cvec[rr];
+    if (rr < nrows) {
+      mu[row0 + rr] = s;
+      rowprod[row0 + rr] = s * cvec[row0 + rr];
     }
   }
-  __syncthreads();
-  if (threadIdx.x < kCoarseRows) red[threadIdx.x] = prod;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double s = 0.0;
-    for (int k = 0; k < kCoarseRows; ++k) s += red[k];
-    part[blockIdx.x] = s;
+  if (!last_block(counter, flag)) return false;
+  // warp w folds segment s0 + w (, + 8, ...): lane l adds rows l, l + 32, ... of the segment in order, then the butterfly
+  const int l = threadIdx.x & 31;
+  for (int s = s0 + w; s < s1; s += (int)(blockDim.x >> 5)) {
+    double a = 0.0;
+    for (int i = seg_row[s] + l; i < seg_row[s + 1]; i += 32) a += __ldcg(rowprod + i);
+    a = warp_sum(a);
+    if (l == 0) csegs[s] = a;
   }
-  if (!last_block(counter, &flag)) return;
-  const double cmu = final_sum(part, (int)gridDim.x, red);
+  __syncthreads();
+  return true;
+}
+
+// One GPU (and the start of a solve on any number of ranks, where c has been gathered and every rank multiplies all
+// rows): mu = Einv c, then the scalar step that closes the preconditioner application,
+//     r.z = r.M^-1 r (from the update kernel) + c.mu      — the corrected z is never formed for the dot product.
+//   init != 0: start of a solve (r.z of the initial residual, no beta)
+__global__ void __launch_bounds__(kThreads, 4) k_coarse_mv(const double* __restrict__ Einv, const double* __restrict__ cvec, int m,
+                                                         double* __restrict__ mu, double* __restrict__ rowprod,
+                                                         const int* __restrict__ seg_row, unsigned int* counter, Scalars* sc,
+                                                         int init) {
+  __shared__ double red[8];
+  __shared__ double csegs[kSegments];
+  __shared__ int flag;
+  if (sc->done) return;
+  if (!coarse_mv_rows(Einv, cvec, m, 0, m, mu, rowprod, seg_row, 0, kSegments, csegs, counter, red, &flag)) return;
   if (threadIdx.x == 0) {
+    double cmu = 0.0;
+    for (int s = 0; s < kSegments; ++s) cmu += csegs[s];
     const double rz_new = sc->rz_bj + cmu;
     if (init) {
       sc->rz = rz_new;
@@ -236,7 +254,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_coarse_mv(const double* __restr
       sc->beta = rz_new / sc->rz;
       sc->rz = rz_new;
     }
-    sc->rzv[0] = rz_new;   // the peer-memory update kernel reads r.z of the previous iterate from here
+    sc->rzv[0] = rz_new;   // the peer-memory kernels read r.z of the previous iterate from here
     sc->rzv[1] = rz_new;
     *counter = 0u;
   }

@@ -44,6 +44,7 @@ struct P2PWindow {
   unsigned int pad[24];                // keeps the word arrays on their own 128-byte lines
   unsigned long long ll_pap[2][kLLWordsPerQuantity];       // [iteration parity][2 * global segment + half]
   unsigned long long ll_upd[2][2 * kLLWordsPerQuantity];   // r.z words, then r.r words
+  unsigned long long ll_cmu[2][kLLWordsPerQuantity];       // two-level preconditioner: c.mu segment sums
 };
 static_assert(sizeof(P2PWindow) <= kWindowHeaderBytes, "window header too small");
 
@@ -578,9 +579,10 @@ __global__ void __launch_bounds__(kThreads) k_updpush_p2p_staged(const PcgView a
 //   k_restrict_p2p      c_a = W_a^T r for the rank's own aggregates, stored into EVERY rank's window as flagged words
 //   k_c_unpack_p2p      waits for all 3 n_agg entries of c (and, in block 0, for r.M^-1 r / r.r: the scalar step
 //                       OP_UPDATE_2L) and writes c as plain doubles
-//   k_coarse_mv         unchanged: every rank multiplies the whole E^-1 (same arithmetic as one GPU, hence the same
-//                       bits and no further exchange for c.mu), forms r.z and beta
-//   k_dir_coarse_p2p    p = (z + W mu) + beta p; rows the neighbours need go straight into their ghost slots
+//   k_coarse_mv_p2p     mu = E^-1 c for the rows of the rank's OWN aggregates (1/P of the dense product), c.mu summed
+//                       per fixed segment and sent to every rank like the other dot products
+//   k_dir_coarse_p2p    waits for the c.mu sums, forms r.z and beta, p = (z + W mu) + beta p; rows the neighbours need
+//                       go straight into their ghost slots
 //
 // The landing zone of c sits in the window between the header and the ghost rows: 2 parities x 6 n_agg words, the
 // same size on every rank (n_agg is global).
@@ -646,15 +648,50 @@ __global__ void __launch_bounds__(kThreads) k_c_unpack_p2p(const P2PCtx x, int n
   }
 }
 
+__global__ void __launch_bounds__(kThreads, 4) k_coarse_mv_p2p(const double* __restrict__ Einv, const double* __restrict__ cvec,
+                                                                int m, int row0, int nrows, double* __restrict__ mu,
+                                                                double* __restrict__ rowprod, const int* __restrict__ seg_row,
+                                                                unsigned int* counter, const Scalars* sc, const P2PCtx x) {
+  __shared__ double red[8];
+  __shared__ double csegs[kSegments];
+  __shared__ int flag;
+  if (sc->done) return;
+  const unsigned int S = *x.seq_base + x.k_local;
+  const int s0 = x.rank * x.spr, s1 = s0 + x.spr;
+  if (!coarse_mv_rows(Einv, cvec, m, row0, nrows, mu, rowprod, seg_row, s0, s1, csegs, counter, red, &flag)) return;
+  // one thread per (destination rank, own segment, half)
+  const int per_rank = x.spr * 2;
+  for (int t = threadIdx.x; t < x.world * per_rank; t += blockDim.x) {
+    const int d = t / per_rank, sh = t - d * per_rank;
+    const int s = sh >> 1, hh = sh & 1;
+    const double val = csegs[s0 + s];
+    const unsigned int bits = (unsigned int)(hh ? __double2hiint(val) : __double2loint(val));
+    unsigned long long* dst = &x.win[d]->ll_cmu[S & 1u][2 * (s0 + s) + hh];
+    st_relaxed64(dst, ((unsigned long long)(S + 1) << 32) | bits);
+  }
+  if (threadIdx.x == 0) *counter = 0u;
+}
+
 __global__ void __launch_bounds__(kThreads) k_dir_coarse_p2p(const CoarseView a, const double* __restrict__ z,
                                                               const double* __restrict__ mu, double* __restrict__ p,
-                                                              const Scalars* sc, const P2PCtx x, const HaloPush h) {
+                                                              Scalars* sc, const P2PCtx x, const HaloPush h) {
   __shared__ int flag;
+  __shared__ WaitOut wo;
   if (sc->done) return;
   const unsigned int S = *x.seq_base + x.k_local;
   const int4 job = ldg(h.order + blockIdx.x);   // (tile, first entry, end entry): sending tiles first
   const int r = job.x * kThreads + (int)threadIdx.x;
-  if (r < a.n_own) dir_coarse_row(a, z, mu, p, sc->beta, r);
+  // close the preconditioner application: r.z = r.M^-1 r + c.mu (the 8 segment sums of c.mu in global order), beta.
+  // r.z of the previous iterate is read from the other parity slot than the one written here.
+  if (!wait_sums<1>(x.me->ll_cmu[S & 1u], S + 1, sc, x.spin_limit, &wo, 2)) return;
+  const double rz_new = sc->rz_bj + wo.tot[0];
+  const double beta = rz_new / sc->rzv[(S + 1u) & 1u];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    sc->rzv[S & 1u] = rz_new;
+    sc->rz = rz_new;
+    sc->beta = beta;
+  }
+  if (r < a.n_own) dir_coarse_row(a, z, mu, p, beta, r);
   const int h0 = job.y, h1 = job.z;
   if (h1 == h0) return;   // nothing to send from this tile (uniform over the CTA)
   __syncthreads();        // the tile's new p is visible to the CTA
