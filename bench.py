@@ -373,13 +373,15 @@ def run_ours(args):
         G2.optimize()
         _, x = G2.poses()
     x_warm = x.copy()
+    keys_buf = np.zeros(g.n, dtype=np.uint64)      # the caller's host buffers, reused every step
+    x = np.ascontiguousarray(x)
     barrier()
     h2d0, d2h0 = G2.transfer_bytes()
     t0 = time.time()
     for _ in range(K):
         G2.set_poses(keys, x)            # host -> device (this rank's rows + halo, (x,y,cos,sin) doubles)
         G2.optimize()
-        _, x = G2.poses()                # device -> host
+        G2.poses(keys_buf, x)            # device -> host, into the same host buffers
     barrier()
     e2e_s = vmax(time.time() - t0)
     e2e = K / e2e_s

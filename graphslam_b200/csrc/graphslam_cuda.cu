@@ -15,6 +15,7 @@
 #include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -1831,10 +1832,26 @@ gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double
   if (!g || (n && (!keys || !xyt))) return GS_EINVAL;
   if (gs_status s = download_values(g)) return s;
   // validate everything before touching the values: an unknown key or a non-finite pose leaves the graph as it was
-  for (size_t k = 0; k < n; ++k) {
-    if (g->find(keys[k]) < 0) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[k]);
-    if (!(std::isfinite(xyt[3 * k]) && std::isfinite(xyt[3 * k + 1]) && std::isfinite(xyt[3 * k + 2])))
-      return g->fail(GS_EINVAL, "non-finite pose for key %llu", (unsigned long long)keys[k]);
+  {
+    std::atomic<size_t> bad_key(n), bad_val(n);   // lowest offending index of each kind
+    gs::parallel_for(n, [&](size_t b, size_t e) {
+      for (size_t k = b; k < e; ++k) {
+        if (g->find(keys[k]) < 0) {
+          size_t cur = bad_key.load();
+          while (k < cur && !bad_key.compare_exchange_weak(cur, k)) {
+          }
+          return;
+        }
+        if (!(std::isfinite(xyt[3 * k]) && std::isfinite(xyt[3 * k + 1]) && std::isfinite(xyt[3 * k + 2]))) {
+          size_t cur = bad_val.load();
+          while (k < cur && !bad_val.compare_exchange_weak(cur, k)) {
+          }
+          return;
+        }
+      }
+    });
+    if (bad_key.load() < n) return g->fail(GS_ENOKEY, "unknown key %llu", (unsigned long long)keys[bad_key.load()]);
+    if (bad_val.load() < n) return g->fail(GS_EINVAL, "non-finite pose for key %llu", (unsigned long long)keys[bad_val.load()]);
   }
   gs::parallel_for(n, [g, keys, xyt](size_t b, size_t e) {
     for (size_t k = b; k < e; ++k) {

@@ -203,10 +203,15 @@ class Graph:
         self._ck(self._lib.gs_get_pose(self._h, int(key), _dp(out)))
         return out
 
-    def poses(self):
+    def poses(self, keys_out=None, xyt_out=None):
+        """(keys, xyt) of all vertices in sorted-key order.  `keys_out` (uint64[n]) / `xyt_out` (float64[n,3]) are
+        caller-owned buffers to fill (a caller that reads the poses every step should not fault in 32 MB of fresh pages
+        each time); new arrays otherwise."""
         n = self.num_vertices
-        keys = np.zeros(n, dtype=np.uint64)
-        xyt = np.zeros((n, 3))
+        keys = keys_out if keys_out is not None else np.zeros(n, dtype=np.uint64)
+        xyt = xyt_out if xyt_out is not None else np.zeros((n, 3))
+        assert keys.dtype == np.uint64 and keys.shape == (n,) and keys.flags.c_contiguous
+        assert xyt.dtype == np.float64 and xyt.shape == (n, 3) and xyt.flags.c_contiguous
         m = C.c_size_t()
         self._ck(self._lib.gs_get_poses(self._h, n, keys.ctypes.data_as(c_u64_p), _dp(xyt), C.byref(m)))
         return keys, xyt
