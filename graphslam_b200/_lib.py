@@ -24,7 +24,8 @@ class GsParams(C.Structure):
                 ("lambda_upper", C.c_double), ("lambda_lower", C.c_double), ("min_model_fidelity", C.c_double),
                 ("diagonal_damping", C.c_int), ("jacobian_mode", C.c_int), ("pcg_rel_tol", C.c_double),
                 ("pcg_max_iters", C.c_int), ("device", C.c_int), ("rank", C.c_int), ("world_size", C.c_int),
-                ("solver_flags", C.c_int), ("coarse_aggregate_size", C.c_int), ("reserved", C.c_int * 6)]
+                ("solver_flags", C.c_int), ("coarse_aggregate_size", C.c_int), ("peer_wait_limit_ms", C.c_int),
+                ("reserved", C.c_int * 5)]
 
 
 class GsStats(C.Structure):

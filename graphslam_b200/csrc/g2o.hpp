@@ -11,6 +11,8 @@
 // '#' starts a comment.  Unknown tags are counted and skipped, malformed known lines are errors.
 // Pure C++ (no CUDA): the CPU tests parse with exactly this code.
 #pragma once
+#include <locale.h>
+#include <stdlib.h>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -33,11 +35,16 @@ struct G2oData {
 };
 
 namespace g2o_detail {
+// the "C" locale, whatever the host program has set with setlocale (a decimal comma would split "1.5" in two)
+inline locale_t c_locale() {
+  static locale_t loc = newlocale(LC_ALL_MASK, "C", (locale_t)0);
+  return loc;
+}
 // parse `n` doubles from *p; advances *p; false when fewer are present
 inline bool take_doubles(const char** p, int n, double* out) {
   for (int k = 0; k < n; ++k) {
     char* end = nullptr;
-    out[k] = std::strtod(*p, &end);
+    out[k] = strtod_l(*p, &end, c_locale());
     if (end == *p) return false;
     *p = end;
   }

@@ -111,6 +111,7 @@ struct gs_graph {
   bool p2p_wanted = true;                 // !GS_SOLVER_NCCL_PER_OP
   bool p2p = false;                       // windows exchanged, peer-memory kernels in use
   char* win = nullptr;                    // this rank's exported window: header + p
+  long long spin_limit_ticks = 60000000000LL;   // peer_wait_limit_ms x SM clock: how long a kernel waits for another GPU
   size_t win_bytes = 0;
   size_t win_ghost_off = gs::kWindowHeaderBytes;   // where the ghost rows of p start inside a window (same on every rank)
   int win_generation = 0;
@@ -412,7 +413,7 @@ gs::P2PCtx p2p_ctx(gs_graph* g, unsigned int k_local) {
   x.seq_base = g->d_seq.p;
   x.k_local = k_local;
   x.ticket = g->d_seq.p + 32;   // its own 128-byte line
-  x.spin_limit = 2000000000LL;
+  x.spin_limit = g->spin_limit_ticks;
   x.tile_halo = g->d_tile_halo.p;
   return x;
 }
@@ -592,10 +593,10 @@ long long allocation_offset(void* ptr) {
     tried = true;
     if (void* h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL)) fn = (Fn)dlsym(h, "cuMemGetAddressRange_v2");
   }
-  if (!fn) return 0;
+  if (!fn) return -1;   // cannot be resolved: the caller fails instead of letting peers write at a wrong address
   unsigned long long base = 0;
   size_t size = 0;
-  if (fn(&base, &size, (unsigned long long)(uintptr_t)ptr) != 0) return 0;
+  if (fn(&base, &size, (unsigned long long)(uintptr_t)ptr) != 0) return -1;
   return (long long)((unsigned long long)(uintptr_t)ptr - base);
 }
 
@@ -650,6 +651,9 @@ gs_status prepare_p2p(gs_graph* g) {
   GS_CUDA(g, cudaMemsetAsync(g->pghost, 0, sizeof(double) * 3 * (size_t)std::max(S.n_ghost, 1), g->stream));
   GS_CUDA(g, cudaIpcGetMemHandle(&mine.handle, g->win));
   mine.offset = allocation_offset(g->win);
+  if (mine.offset < 0)
+    return g->fail(GS_ECUDA, "cuMemGetAddressRange unavailable: the peer-memory window cannot be located inside its allocation "
+                             "(create the graph with GS_SOLVER_NCCL_PER_OP)");
   mine.generation = g->win_generation;
   mine.n_own = g->n_own;
   for (const gs::HaloPeer& hp : S.peers) mine.ghost_off[hp.rank] = hp.ghost_off;
@@ -1270,6 +1274,15 @@ gs_status create_common(gs_graph* g) {
   }
   GS_CUDA(g, g->d_bar.alloc(1));
   GS_CUDA(g, cudaMemsetAsync(g->d_bar.p, 0, sizeof(gs::GridBarrier), g->stream));
+  {
+    // a wait for another GPU gives up after peer_wait_limit_ms (default 30 s: long enough for a descheduled or
+    // page-faulting peer process, short enough to turn a dead peer into GS_ENCCL instead of a hang)
+    int dev = 0, khz = 0;
+    GS_CUDA(g, cudaGetDevice(&dev));
+    GS_CUDA(g, cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+    const long long ms = g->prm.peer_wait_limit_ms > 0 ? g->prm.peer_wait_limit_ms : 30000;
+    g->spin_limit_ticks = ms * (long long)std::max(khz, 1000000);
+  }
   GS_CUDA(g, g->d_seq.alloc(64));
   GS_CUDA(g, cudaMemsetAsync(g->d_seq.p, 0, 64 * sizeof(unsigned int), g->stream));
   GS_CUDA(g, cudaStreamSynchronize(g->stream));

@@ -83,7 +83,9 @@ typedef struct gs_params {
   int world_size;            /* multi-GPU: number of ranks (1)          */
   int solver_flags;          /* GS_SOLVER_* bits (0)                    */
   int coarse_aggregate_size; /* two-level preconditioner: poses per aggregate; 0 = automatic (about sqrt(N), >= 128) */
-  int reserved[6];
+  int peer_wait_limit_ms;    /* multi-GPU, peer-memory path: how long a kernel waits for another GPU before the solve fails
+                                with GS_ENCCL (re-run gs_optimize to recover); 0 = 30000 */
+  int reserved[5];
 } gs_params;
 
 typedef struct gs_stats {
