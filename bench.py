@@ -457,9 +457,9 @@ def run_ours(args):
                "cholesky": chol, "pcg": pcg, "superlu_oracle": slu,
                "edges_linearized_per_sec": pcg["edges_linearized_per_sec"]}
 
-    two_level = world == 1 and g.n >= 8192
-    run = {"preconditioner": ("two-level: 3x3 block-Jacobi + rigid-body coarse space over graph aggregates (one GPU)" if two_level
-                              else "3x3 block-Jacobi" + (" (the multi-GPU path has no coarse correction yet)" if world > 1 else "")),
+    two_level = g.n >= 1024
+    run = {"preconditioner": ("two-level: 3x3 block-Jacobi + rigid-body coarse space over graph aggregates" if two_level
+                              else "3x3 block-Jacobi"),
            "partition": (f"vertex ranges over {world} ranks; halo rows and dot-product segment sums travel by stores into peer "
                          f"memory (NVLink) from inside the PCG kernels; NCCL only for setup and the final pose gather")
            if world > 1 else "single GPU",

@@ -48,6 +48,7 @@ using gs::spd_information;
 using gs::spd_upper;
 
 constexpr int kPcgBatch = 32;  // PCG iterations per CUDA-graph launch
+constexpr int kCoarseMinPoses = 1024;  // smaller graphs keep block-Jacobi PCG (persistent kernel)
 constexpr int kFusedBatch = 128;  // PCG iterations per launch of the persistent small-graph kernel
 static_assert(kFusedBatch % 2 == 0, "an even batch leaves the latest direction in the graph's own p vector");
 
@@ -834,14 +835,15 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   gs::build_local_structure(N, E, g->di.data(), g->dj.data(), g->perm, P, g->dp.data(), g->world, g->rank, g->S);
   const LocalStructure& S = g->S;
   // two-level preconditioner: aggregates of the block rows (small graphs keep block-Jacobi: persistent kernel on one GPU)
-  g->coarse = g->coarse_wanted && N >= 8192;
+  // (from 1,024 poses: C1, 3,500 poses, converges in 115 ms with it and in 208 ms with the persistent block-Jacobi kernel)
+  g->coarse = g->coarse_wanted && N >= kCoarseMinPoses;
   if (g->coarse) {
     std::vector<int32_t> rp, ci;
     gs::global_pattern(N, E, g->di.data(), g->dj.data(), rp, ci);
     // about sqrt(N) aggregates of about sqrt(N) poses: the dense coarse product (9 n_agg^2 doubles per PCG iteration)
     // stays a fraction of the fine-level traffic (~600 N bytes) at every size; at most 1024 aggregates
     int target = g->prm.coarse_aggregate_size > 0 ? g->prm.coarse_aggregate_size
-                                                  : std::max(128, (int)std::ceil(std::sqrt((double)N)));
+                                                  : std::max(48, (int)std::ceil(std::sqrt((double)N)));
     target = std::max(target, (N + 4095) / 4096);   // the dense coarse inverse is (3 n_agg)^2 doubles: at most 1.2 GB
     gs::build_aggregation(N, rp, ci, target, g->agg);
   }
@@ -964,6 +966,25 @@ gs_status prepare(gs_graph* g, double* ms_out) {
       return g->fail(GS_ECUDA, "cusolver workspace query failed");
     g->chol_lwork = std::max(l1, l2);
     GS_CUDA(g, g->d_chol_work.alloc((size_t)std::max(g->chol_lwork, 1)));
+    // one Cholesky + inverse of an identity of this size now: cuSOLVER loads its kernels on first use (hundreds of
+    // milliseconds), which belongs to the structure phase, not to the first solve
+    {
+      int dev = 0;
+      GS_CUDA(g, cudaGetDevice(&dev));
+      static bool warmed[64] = {false};   // under solver_pool().mu
+      if (dev >= 0 && dev < 64 && !warmed[dev]) {
+        GS_CUDA(g, cudaMemsetAsync(g->d_E.p, 0, sizeof(double) * m * m, g->stream));
+        gs::k_set_diagonal<<<(unsigned)((m + gs::kThreads - 1) / gs::kThreads), gs::kThreads, 0, g->stream>>>(g->d_E.p, (int)m, 1.0);
+        if (cusolverDnSetStream(hs, g->stream) != CUSOLVER_STATUS_SUCCESS ||
+            cusolverDnDpotrf(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
+                CUSOLVER_STATUS_SUCCESS ||
+            cusolverDnDpotri(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
+                CUSOLVER_STATUS_SUCCESS)
+          return g->fail(GS_ECUDA, "cuSOLVER warm-up failed");
+        GS_CUDA(g, cudaStreamSynchronize(g->stream));
+        warmed[dev] = true;
+      }
+    }
   }
   g->coarse_e0_valid = false;
   g->coarse_lambda = -1.0;

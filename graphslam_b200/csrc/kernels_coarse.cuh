@@ -161,6 +161,11 @@ __global__ void __launch_bounds__(kThreads) k_coarse_E(const double* __restrict_
   }
 }
 
+__global__ void __launch_bounds__(kThreads) k_set_diagonal(double* __restrict__ Em, int m, double v) {
+  const int i = blockIdx.x * kThreads + threadIdx.x;
+  if (i < m) Em[(size_t)i * m + i] = v;
+}
+
 // potri leaves one triangle of E^-1: mirror it (column-major, lower -> upper)
 __global__ void __launch_bounds__(kThreads) k_symmetrize(double* __restrict__ Em, int m) {
   const size_t t = (size_t)blockIdx.x * kThreads + threadIdx.x;

@@ -57,8 +57,8 @@ enum {
   GS_SOLVER_DIR_KERNEL = 1 << 3,     /* multi-GPU: keep the direction update p = z + beta p as a kernel of its own (three kernels
                                         per iteration); default: formed on the fly inside the product above 200k rows per rank */
   GS_SOLVER_DIR_ON_THE_FLY = 1 << 4, /* multi-GPU: force the on-the-fly form (two kernels per iteration) */
-  GS_SOLVER_BLOCK_JACOBI_ONLY = 1 << 5 /* PCG with the 3x3 block-Jacobi preconditioner alone.  Default (one GPU, lambda*I damping,
-                                        >= 8192 poses): block-Jacobi plus a coarse-space correction over aggregates of poses
+  GS_SOLVER_BLOCK_JACOBI_ONLY = 1 << 5 /* PCG with the 3x3 block-Jacobi preconditioner alone.  Default (lambda*I damping,
+                                        >= 1024 poses): block-Jacobi plus a coarse-space correction over aggregates of poses
                                         (rigid-body modes), which cuts the PCG iterations of large graphs ~20x.  The solution
                                         of the linear system is the same to pcg_rel_tol either way. */
 };
@@ -82,7 +82,7 @@ typedef struct gs_params {
   int rank;                  /* multi-GPU: this process's rank (0)      */
   int world_size;            /* multi-GPU: number of ranks (1)          */
   int solver_flags;          /* GS_SOLVER_* bits (0)                    */
-  int coarse_aggregate_size; /* two-level preconditioner: poses per aggregate; 0 = automatic (about sqrt(N), >= 128) */
+  int coarse_aggregate_size; /* two-level preconditioner: poses per aggregate; 0 = automatic (about sqrt(N), >= 48) */
   int peer_wait_limit_ms;    /* multi-GPU, peer-memory path: how long a kernel waits for another GPU before the solve fails
                                 with GS_ENCCL (re-run gs_optimize to recover); 0 = 30000 */
   int reserved[5];

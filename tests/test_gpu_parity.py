@@ -480,7 +480,7 @@ def test_closest_keyframe_keys_inserted_out_of_order():
 
 @pytest.mark.parametrize("cid,n", [("C3", 60000), ("C4", 20000), ("C2", 100000)])
 def test_two_level_preconditioner_solves_the_same_system(cid, n):
-    """The default PCG on graphs of >= 8192 poses adds a coarse-space correction (rigid-body modes over aggregates) to the
+    """The default PCG on graphs of >= 1024 poses adds a coarse-space correction (rigid-body modes over aggregates) to the
     block-Jacobi preconditioner.  The preconditioner changes the iteration count, not the solution: both variants
     reach pcg_rel_tol on the same system, agree with each other and with the oracle's exact solve, the two-level one in
     far fewer iterations; and it is deterministic (two runs give the same bits)."""
