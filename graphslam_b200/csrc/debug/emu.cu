@@ -215,7 +215,7 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
     return jacobian_mode ? gs::assemble_row<1>(a, r) : gs::assemble_row<0>(a, r);
   });
   out->chi2 = chi2;
-  out->chi2_check = W.reduce([&](VRank& me, int r) { return gs::chi2_row(me.av(me.pose.data()), r); });
+  out->chi2_check = W.reduce([&](VRank& me, int r) { return gs::chi2_row<1>(me.av(me.pose.data()), r); });
 
   // ---- system on the global pattern
   if (out->blocks || out->b) {
@@ -353,7 +353,7 @@ static gs_status emu_run(const gs_emu_problem* pb, int world, int jacobian_mode,
     for (int r = 0; r < me.n_own; ++r)
       me.pose_try[r] = gs::retract(me.pose[r], me.x[3 * (size_t)r], me.x[3 * (size_t)r + 1], me.x[3 * (size_t)r + 2]);
   W.halo([](VRank& v) { return reinterpret_cast<double*>(v.pose_try.data()); }, 4);
-  out->chi2_new = W.reduce([&](VRank& me, int r) { return gs::chi2_row(me.av(me.pose_try.data()), r); });
+  out->chi2_new = W.reduce([&](VRank& me, int r) { return gs::chi2_row<2>(me.av(me.pose_try.data()), r); });
   for (VRank& me : W.R)
     for (int r = 0; r < me.n_own; ++r) {
       const int g = me.S.v0 + r;

@@ -151,6 +151,8 @@ struct gs_graph {
   bool theta_wrapped = false;     // every host theta is already in (-pi, pi] (they all came back from the device)
   double4* h_stage = nullptr;     // pinned staging of the pose transfers
   size_t h_stage_n = 0;
+  char* h_struct = nullptr;       // pinned staging of the structure upload (factor cells, contribution and reference words)
+  size_t h_struct_bytes = 0;
   bool device_values_valid = false;
   bool system_valid = false;      // H, b assembled at the current device poses
 
@@ -755,6 +757,20 @@ gs_status ensure_stage(gs_graph* g, size_t n) {
   return GS_OK;
 }
 
+// pinned staging of the structure upload: grows geometrically, lives as long as the graph (an incremental update
+// rebuilds and re-uploads the structure every few keyframes: fresh pageable vectors cost a page fault per 4 KB and a
+// synchronous staged copy each time)
+gs_status ensure_struct_stage(gs_graph* g, size_t bytes) {
+  if (bytes <= g->h_struct_bytes) return GS_OK;
+  if (g->h_struct) cudaFreeHost(g->h_struct);
+  g->h_struct = nullptr;
+  g->h_struct_bytes = 0;
+  const size_t want = bytes + bytes / 4 + (1u << 20);
+  GS_CUDA(g, cudaMallocHost(&g->h_struct, want));
+  g->h_struct_bytes = want;
+  return GS_OK;
+}
+
 // device values -> host xyt.  Multi-rank: collective (every rank broadcasts its owned range).
 gs_status download_values(gs_graph* g) {
   if (!g->device_values_valid || g->host_values_fresh) return GS_OK;
@@ -854,16 +870,39 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->P = P;
   g->n_own = S.n_own;
   g->n_loc = S.n_own + S.n_ghost;
-  // factor arrays in storage (SELL) order; padding slots are never referenced
+  // factor arrays in storage (SELL) order and the contribution / reference words, written straight into pinned memory
+  // on several host threads; padding slots are never referenced
   const int FS = S.csell.slots;
-  gs::FactorStage fst;
-  fst.init(FS);
-  for (int q = 0; q < FS; ++q) {
-    const int s = S.f_src[q];
-    if (s < 0) continue;
-    fst.set(q, S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q], &g->ez[3 * (size_t)s], &g->eom[6 * (size_t)s]);
+  g->fstride = gs::factor_stride(FS);
+  const size_t n_cw = S.c_code.size(), n_refs = S.r_col.size();
+  auto up256 = [](size_t b) { return (b + 255) & ~(size_t)255; };
+  const size_t off_ij = 0, off_data = off_ij + up256(sizeof(int2) * g->fstride);
+  const size_t off_cw = off_data + up256(sizeof(double2) * 5 * g->fstride), off_refs = off_cw + up256(sizeof(int4) * n_cw);
+  if (gs_status s = ensure_struct_stage(g, off_refs + up256(sizeof(int2) * n_refs))) return s;
+  int2* st_ij = reinterpret_cast<int2*>(g->h_struct + off_ij);
+  double2* st_data = reinterpret_cast<double2*>(g->h_struct + off_data);
+  int4* st_cw = reinterpret_cast<int4*>(g->h_struct + off_cw);
+  int2* st_refs = reinterpret_cast<int2*>(g->h_struct + off_refs);
+  {
+    const size_t fstride = g->fstride;
+    const double* ez = g->ez.data();
+    const double* eom = g->eom.data();
+    gs::parallel_for(fstride, [&S, st_ij, st_data, fstride, FS, ez, eom](size_t b, size_t e) {
+      for (size_t q = b; q < e; ++q) {
+        const int s = q < (size_t)FS ? S.f_src[q] : -1;
+        if (s < 0) gs::factor_cell_default(st_ij, st_data, fstride, (int)q);
+        else
+          gs::factor_cell_set(st_ij, st_data, fstride, (int)q, S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q],
+                              ez + 3 * (size_t)s, eom + 6 * (size_t)s);
+      }
+    });
+    gs::parallel_for(n_cw, [&S, st_cw](size_t b, size_t e) {
+      for (size_t q = b; q < e; ++q) st_cw[q] = make_int4((int)S.c_code[q], S.c_blk[q], S.c_col[q], 0);
+    });
+    gs::parallel_for(n_refs, [&S, st_refs](size_t b, size_t e) {
+      for (size_t q = b; q < e; ++q) st_refs[q] = make_int2(S.r_col[q], S.r_blk[q]);
+    });
   }
-  g->fstride = fst.fstride;
   g->e_count = 0;
   for (uint32_t code : S.c_code)
     if (code != gs::kPadCode && (code & 4u) && (code & 3u) < 2) g->e_count++;
@@ -875,22 +914,20 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     for (int m = 0; m < 6; ++m) prom[6 * (size_t)k + m] = g->pr_om[6 * (size_t)s + m];
   }
   std::vector<int> segtile(S.seg_tile, S.seg_tile + gs::kSegments + 1);
-  if (gs_status s = upload(g, g->d_eij, fst.ij)) return s;
-  if (gs_status s = upload(g, g->d_fdata, fst.data)) return s;
+  GS_CUDA(g, g->d_eij.alloc(g->fstride));
+  GS_CUDA(g, g->d_fdata.alloc(5 * g->fstride));
+  GS_CUDA(g, g->d_cw.alloc(std::max<size_t>(n_cw, 1)));
+  GS_CUDA(g, g->d_refs.alloc(std::max<size_t>(n_refs, 1)));
+  GS_CUDA(g, cudaMemcpyAsync(g->d_eij.p, st_ij, sizeof(int2) * g->fstride, cudaMemcpyHostToDevice, g->stream));
+  GS_CUDA(g, cudaMemcpyAsync(g->d_fdata.p, st_data, sizeof(double2) * 5 * g->fstride, cudaMemcpyHostToDevice, g->stream));
+  if (n_cw) GS_CUDA(g, cudaMemcpyAsync(g->d_cw.p, st_cw, sizeof(int4) * n_cw, cudaMemcpyHostToDevice, g->stream));
+  if (n_refs) GS_CUDA(g, cudaMemcpyAsync(g->d_refs.p, st_refs, sizeof(int2) * n_refs, cudaMemcpyHostToDevice, g->stream));
+  g->h2d_bytes += (double)(sizeof(int2) * g->fstride + sizeof(double2) * 5 * g->fstride + sizeof(int4) * n_cw + sizeof(int2) * n_refs);
   if (gs_status s = upload(g, g->d_pr_row, S.pr_row)) return s;
   if (gs_status s = upload(g, g->d_pr_pose, prp)) return s;
   if (gs_status s = upload(g, g->d_pr_om, prom)) return s;
   if (gs_status s = upload(g, g->d_cbase, S.csell.base)) return s;
   if (gs_status s = upload(g, g->d_cwidth, S.csell.width)) return s;
-  {
-    std::vector<int4> cw(S.c_code.size());
-    for (size_t q = 0; q < cw.size(); ++q) cw[q] = make_int4((int)S.c_code[q], S.c_blk[q], S.c_col[q], 0);
-    if (gs_status s = upload(g, g->d_cw, cw)) return s;
-    std::vector<int2> refs(S.r_col.size());
-    for (size_t q = 0; q < refs.size(); ++q) refs[q] = make_int2(S.r_col[q], S.r_blk[q]);
-    if (gs_status s = upload(g, g->d_refs, refs)) return s;
-    GS_CUDA(g, cudaStreamSynchronize(g->stream));
-  }
   if (gs_status s = upload(g, g->d_rbase, S.rsell.base)) return s;
   if (gs_status s = upload(g, g->d_rwidth, S.rsell.width)) return s;
   if (gs_status s = upload(g, g->d_segtile, segtile)) return s;
@@ -1156,7 +1193,14 @@ gs_status launch_assemble(gs_graph* g) {
 // chi2 at `pose` (ghost slots must be current)
 gs_status launch_chi2(gs_graph* g, const double4* pose) {
   NvtxRange nvtx_range("gs:chi2");
-  gs::k_chi2<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, pose), reduce_ctx(g, 3));
+  // rows.cuh chi2_row: how far the slot loop runs ahead; GS_CHI2_PIPE (a compile-time switch of the variant probe) forces one
+#ifndef GS_CHI2_PIPE
+#define GS_CHI2_PIPE -1
+#endif
+  const int pipe = GS_CHI2_PIPE >= 0 ? GS_CHI2_PIPE : ((long long)g->e_count >= 8ll * g->n_own ? 2 : 1);
+  if (pipe == 2) gs::k_chi2<2><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, pose), reduce_ctx(g, 3));
+  else if (pipe == 1) gs::k_chi2<1><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, pose), reduce_ctx(g, 3));
+  else gs::k_chi2<0><<<g->grid_rows, gs::kThreads, 0, g->stream>>>(asm_view(g, pose), reduce_ctx(g, 3));
   g->launches += 1;
   if (gs_status s = finish_reduce(g, 1, gs::OP_CHI2)) return s;
   GS_CUDA(g, cudaGetLastError());
@@ -1436,6 +1480,7 @@ gs_status gs_destroy(gs_graph* g) try {
   if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->h_stage) cudaFreeHost(g->h_stage);
+  if (g->h_struct) cudaFreeHost(g->h_struct);
   if (g->ev0) cudaEventDestroy(g->ev0);
   if (g->ev1) cudaEventDestroy(g->ev1);
   if (g->ev_begin) cudaEventDestroy(g->ev_begin);

@@ -248,12 +248,13 @@ __global__ void __launch_bounds__(kThreads, 3) k_assemble_nodup(const AsmView a,
   reduce_finish<1>(c, v, OP_CHI2, red, &flag);
 }
 
+template <int PIPE>
 __global__ void __launch_bounds__(kThreads) k_chi2(const AsmView a, const ReduceCtx c) {
   __shared__ double red[8];
   __shared__ int flag;
   const int r = blockIdx.x * kThreads + threadIdx.x;
   double v[1] = {0.0};
-  if (r < a.n_own) v[0] = chi2_row(a, r);
+  if (r < a.n_own) v[0] = chi2_row<PIPE>(a, r);
   reduce_finish<1>(c, v, OP_CHI2, red, &flag);
 }
 

@@ -117,26 +117,44 @@ GS_HD FactorData load_factor(const FactorView& f, int cell) {
 
 // host staging of the factor cells in the device layout (the structure build's f_src / f_i / f_j / f_count say
 // which cells hold data); `cells` = csell.slots, a multiple of 32
+// one cell of the staged factor arrays (ij: fstride entries, data: 5 * fstride), raw storage
+inline void factor_cell_default(int2* ij, double2* data, size_t fstride, int q) {
+  ij[q] = make_int2(-1, -1);
+  double2* p = data + f_base(q);
+  const size_t st = f_step(fstride);
+  p[0] = make_double2(0.0, 0.0);
+  p[st] = make_double2(1.0, 0.0);   // unit rotation
+  p[2 * st] = make_double2(0.0, 0.0);
+  p[3 * st] = make_double2(0.0, 0.0);
+  p[4 * st] = make_double2(0.0, 0.0);
+}
+
+// z = (dx, dy, dtheta), om = information upper triangle (6)
+inline void factor_cell_set(int2* ij, double2* data, size_t fstride, int q, int i, int j, const double* z, const double* om) {
+  ij[q] = make_int2(i, j);
+  double2* p = data + f_base(q);
+  const size_t st = f_step(fstride);
+  p[0] = make_double2(z[0], z[1]);
+  p[st] = make_double2(std::cos(z[2]), std::sin(z[2]));
+  p[2 * st] = make_double2(om[0], om[1]);
+  p[3 * st] = make_double2(om[2], om[3]);
+  p[4 * st] = make_double2(om[4], om[5]);
+}
+
+inline size_t factor_stride(int cells) { return (size_t)((std::max(cells, 1) + kSlice - 1) / kSlice) * kSlice; }
+
 struct FactorStage {
   std::vector<int2> ij;
   std::vector<double2> data;
   size_t fstride = kSlice;
   void init(int cells) {
-    fstride = (size_t)((std::max(cells, 1) + kSlice - 1) / kSlice) * kSlice;
-    ij.assign(fstride, make_int2(-1, -1));
-    data.assign(5 * fstride, make_double2(0.0, 0.0));
-    for (size_t q = 0; q < fstride; ++q) data[f_base((int)q) + f_step(fstride)] = make_double2(1.0, 0.0);  // unit rotation
+    fstride = factor_stride(cells);
+    ij.resize(fstride);
+    data.resize(5 * fstride);
+    for (size_t q = 0; q < fstride; ++q) factor_cell_default(ij.data(), data.data(), fstride, (int)q);
   }
-  // z = (dx, dy, dtheta), om = information upper triangle (6)
   void set(int q, int i, int j, const double* z, const double* om) {
-    ij[q] = make_int2(i, j);
-    double2* p = data.data() + f_base(q);
-    const size_t st = f_step(fstride);
-    p[0] = make_double2(z[0], z[1]);
-    p[st] = make_double2(std::cos(z[2]), std::sin(z[2]));
-    p[2 * st] = make_double2(om[0], om[1]);
-    p[3 * st] = make_double2(om[2], om[3]);
-    p[4 * st] = make_double2(om[4], om[5]);
+    factor_cell_set(ij.data(), data.data(), fstride, q, i, j, z, om);
   }
 };
 
@@ -454,9 +472,41 @@ GS_HD double assemble_row(const AsmView& a, int r) {
   return asm_end<NODUP>(A, a, r);
 }
 
+// one counting cell of k_chi2 in flight: the factor and the poses of its two vertices
+struct Chi2Stage {
+  FactorData fd;
+  double4 pi, pj;
+  bool ok;
+};
+
+GS_HD void chi2_request(const AsmView& a, int cell, const int2 ij, Chi2Stage& S) {
+  S.ok = ij.x >= 0 && !(ij.x & kNoCountBit);
+  if (S.ok) {
+    S.fd = load_factor(a.f, cell);
+    S.pi = ldg(a.pose + ij.x);
+    S.pj = ldg(a.pose + ij.y);
+  }
+}
+
+GS_HD double chi2_value(const Chi2Stage& S) {
+  double e[3];
+  between_error(S.pi, S.pj, S.fd.zt, S.fd.zr, e);
+  const Sym3 O{S.fd.o01.x, S.fd.o01.y, S.fd.o23.x, S.fd.o23.y, S.fd.o45.x, S.fd.o45.y};
+  return quad_form(O, e);
+}
+
 // graph.error contribution of row r at `pose`: its priors, then the factors whose counting side is
 // one of its own cells (same set and order as assemble_row's chi2).  The factor arrays are read
 // directly in cell order: 32 consecutive rows read 32 consecutive cells.
+// PIPE: how far the slot loop runs ahead of its arithmetic.  A slot is two dependent round trips (the cell's vertex
+// pair, then the two poses and the factor) followed by ~150 dependent FP64 instructions (atan2).
+//   0  one slot after the other (what the plain loop compiles to): 2 n round trips per row of n factors
+//   1  the pair of slot k+1 is requested before slot k's data: n + 1 round trips, two more registers
+//   2  the pair of slot k+2 AND the data of slot k+1 are requested before the arithmetic of slot k: the thread always
+//      has a factor in flight, at 104 registers (two CTAs per SM instead of four)
+// Same factors in the same order: same bits.  Measured (profiles/r2_summary.md): rows of three factors (C3) are
+// fastest at 1, rows of twenty (C4) at 2; the library picks by the mean number of factors per row.
+template <int PIPE>
 GS_HD double chi2_row(const AsmView& a, int r) {
   double chi2 = 0.0;
   {  // priors of this row: lower_bound in the ascending row list
@@ -478,16 +528,40 @@ GS_HD double chi2_row(const AsmView& a, int r) {
   const int sl = r / kSlice, lane = r % kSlice;
   const int base = a.cs.base[sl] + lane, w = a.cs.width[sl];
   const int first = a.c_first[r];
+  const int n = w - first;            // slots first .. w-1 are the row's counting cells
+  if (n <= 0) return chi2;
+  const int2 none = make_int2(-1, -1);
+  const int cell0 = base + first * kSlice;
+  const int2* cell_ij = a.f.ij + cell0;
+  if (PIPE == 2) {
+    int2 ij_next = n > 1 ? ldg(cell_ij + kSlice) : none;
+    Chi2Stage cur;
+    chi2_request(a, cell0, ldg(cell_ij), cur);
+#pragma unroll 1
+    for (int k = 0; k < n; ++k) {
+      const int2 ij_after = k + 2 < n ? ldg(cell_ij + (k + 2) * kSlice) : none;
+      Chi2Stage nxt;
+      chi2_request(a, cell0 + (k + 1) * kSlice, ij_next, nxt);   // ij_next is (-1, -1) past the end: nothing requested
+      if (cur.ok) chi2 += chi2_value(cur);
+      cur = nxt;
+      ij_next = ij_after;
+    }
+  } else if (PIPE == 1) {
+    int2 ij = ldg(cell_ij);
+#pragma unroll 1
+    for (int k = 0; k < n; ++k) {
+      const int2 ij_next = k + 1 < n ? ldg(cell_ij + (k + 1) * kSlice) : none;
+      Chi2Stage cur;
+      chi2_request(a, cell0 + k * kSlice, ij, cur);
+      if (cur.ok) chi2 += chi2_value(cur);
+      ij = ij_next;
+    }
+  } else {
 #pragma unroll 4
-  for (int s = 0; s < w; ++s) {
-    const int idx = base + s * kSlice;
-    const int2 ij = s >= first ? ldg(a.f.ij + idx) : make_int2(-1, -1);
-    if (ij.x >= 0 && !(ij.x & kNoCountBit)) {
-      const FactorData fd = load_factor(a.f, idx);
-      double e[3];
-      between_error(ldg(a.pose + ij.x), ldg(a.pose + ij.y), fd.zt, fd.zr, e);
-      const Sym3 O{fd.o01.x, fd.o01.y, fd.o23.x, fd.o23.y, fd.o45.x, fd.o45.y};
-      chi2 += quad_form(O, e);
+    for (int k = 0; k < n; ++k) {
+      Chi2Stage cur;
+      chi2_request(a, cell0 + k * kSlice, ldg(cell_ij + k * kSlice), cur);
+      if (cur.ok) chi2 += chi2_value(cur);
     }
   }
   return chi2;

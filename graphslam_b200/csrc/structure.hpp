@@ -27,6 +27,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 namespace gs {
@@ -196,6 +197,11 @@ struct LocalStructure {
   std::vector<HaloPeer> peers;
   std::vector<int> send_rows;         // local owned row indices, grouped by peer, each group sorted
   int max_degree = 0;
+  // scratch of build_local_structure, kept between builds: an incremental update rebuilds the structure every few
+  // keyframes, and fresh vectors of this size cost a page fault per 4 KB each time
+  struct Work {
+    std::vector<int> loc, ccnt, ccol, chome, cfac, fill, rcnt, rptr, nbr, rhome;
+  } work;
 
   int local_of(int g) const {
     if (g >= v0 && g < v1) return g - v0;
@@ -220,7 +226,82 @@ struct Aggregation {
   std::vector<int> color;         // per aggregate
   std::vector<int> nbr_of_color;  // [a * n_colors + c]: the aggregate of colour c in the closed neighbourhood of a, or -1
   int seg_agg[kSegments + 1] = {0};
+  std::vector<int> work_region, work_mark;   // scratch of build_aggregation, kept between builds (no fresh pages per build)
 };
+
+// One segment's aggregates (each a sorted row list), in the order the bisection produces them.  Touches only the
+// entries [r0, r1) of region / mark, so the eight segments can run on eight host threads.
+inline void aggregate_segment(int r0, int r1, const std::vector<int32_t>& rowptr, const std::vector<int32_t>& colidx, int target,
+                              std::vector<int>& region, std::vector<int>& mark, std::vector<std::vector<int>>& out) {
+  out.clear();
+  if (r1 <= r0) return;
+  std::vector<int> order;
+  int next_region = 1, stamp = 0;
+  // breadth-first order of `verts` (all of region rid), component after component, starting at `root`
+  auto bfs_order = [&](const std::vector<int>& verts, int rid, int root, std::vector<int>& o) {
+    ++stamp;
+    o.clear();
+    size_t scan = 0;
+    int start = root;
+    for (;;) {
+      size_t head = o.size();
+      o.push_back(start);
+      mark[start] = stamp;
+      while (head < o.size()) {
+        const int v = o[head++];
+        for (int k = rowptr[v]; k < rowptr[v + 1]; ++k) {
+          const int u = colidx[k];
+          if (u < r0 || u >= r1 || region[u] != rid || mark[u] == stamp) continue;
+          mark[u] = stamp;
+          o.push_back(u);
+        }
+      }
+      if (o.size() == verts.size()) break;
+      while (mark[verts[scan]] == stamp) ++scan;   // next component
+      start = verts[scan];
+    }
+  };
+  struct Job {
+    std::vector<int> verts;
+    int rid;
+  };
+  std::vector<Job> stack;
+  {
+    Job j;
+    j.rid = next_region++;
+    j.verts.resize(r1 - r0);
+    for (int r = r0; r < r1; ++r) {
+      j.verts[r - r0] = r;
+      region[r] = j.rid;
+      mark[r] = 0;
+    }
+    stack.push_back(std::move(j));
+  }
+  while (!stack.empty()) {
+    Job j = std::move(stack.back());
+    stack.pop_back();
+    const int cnt = (int)j.verts.size();
+    if (cnt <= target) {
+      std::sort(j.verts.begin(), j.verts.end());
+      for (int v : j.verts) region[v] = -1;
+      out.push_back(std::move(j.verts));
+      continue;
+    }
+    bfs_order(j.verts, j.rid, j.verts[0], order);
+    const int far = order.back();                   // a vertex far from an arbitrary one: (pseudo-)peripheral
+    bfs_order(j.verts, j.rid, far, order);
+    const int half = cnt / 2;
+    Job lo, hi;
+    lo.rid = next_region++;
+    hi.rid = next_region++;
+    lo.verts.assign(order.begin(), order.begin() + half);
+    hi.verts.assign(order.begin() + half, order.end());
+    for (int v : lo.verts) region[v] = lo.rid;
+    for (int v : hi.verts) region[v] = hi.rid;
+    stack.push_back(std::move(hi));   // lo is processed first
+    stack.push_back(std::move(lo));
+  }
+}
 
 inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const std::vector<int32_t>& colidx, int target,
                               Aggregation& A) {
@@ -232,93 +313,57 @@ inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const s
   A.ptr.assign(1, 0);
   A.rows.clear();
   A.rows.reserve(N);
-  std::vector<int> region(N, 0), mark(N, -1), order, queue;
-  int next_region = 1, stamp = 0;
-  // breadth-first order of `verts` (all of region rid), component after component, starting at `root`
-  auto bfs_order = [&](const std::vector<int>& verts, int rid, int root, std::vector<int>& out) {
-    ++stamp;
-    out.clear();
-    size_t scan = 0;
-    int start = root;
-    for (;;) {
-      size_t head = out.size();
-      out.push_back(start);
-      mark[start] = stamp;
-      while (head < out.size()) {
-        const int v = out[head++];
-        for (int k = rowptr[v]; k < rowptr[v + 1]; ++k) {
-          const int u = colidx[k];
-          if (region[u] != rid || mark[u] == stamp) continue;
-          mark[u] = stamp;
-          out.push_back(u);
-        }
-      }
-      if (out.size() == verts.size()) break;
-      while (mark[verts[scan]] == stamp) ++scan;   // next component
-      start = verts[scan];
+  A.work_region.resize(N);
+  A.work_mark.resize(N);
+  std::vector<std::vector<int>> seg_out[kSegments];
+  {
+    // the segments are independent: one host thread each on graphs where a segment is worth a thread
+    std::vector<std::thread> th;
+    for (int sgm = 0; sgm < kSegments; ++sgm) {
+      const int r0 = part.seg_row[sgm], r1 = part.seg_row[sgm + 1];
+      auto work = [&, sgm, r0, r1] { aggregate_segment(r0, r1, rowptr, colidx, target, A.work_region, A.work_mark, seg_out[sgm]); };
+      if (N >= 8192 && sgm + 1 < kSegments && r1 > r0) th.emplace_back(work);
+      else work();
     }
-  };
-  struct Job {
-    std::vector<int> verts;
-    int rid;
-  };
+    for (auto& t : th) t.join();
+  }
   for (int sgm = 0; sgm < kSegments; ++sgm) {
     A.seg_agg[sgm] = A.n_agg;
-    const int r0 = part.seg_row[sgm], r1 = part.seg_row[sgm + 1];
-    if (r1 <= r0) continue;
-    std::vector<Job> stack;
-    {
-      Job j;
-      j.rid = next_region++;
-      j.verts.resize(r1 - r0);
-      for (int r = r0; r < r1; ++r) {
-        j.verts[r - r0] = r;
-        region[r] = j.rid;
+    for (const std::vector<int>& verts : seg_out[sgm]) {
+      for (int v : verts) {
+        A.agg_of[v] = A.n_agg;
+        A.rows.push_back(v);
       }
-      stack.push_back(std::move(j));
-    }
-    while (!stack.empty()) {
-      Job j = std::move(stack.back());
-      stack.pop_back();
-      const int cnt = (int)j.verts.size();
-      if (cnt <= target) {
-        std::sort(j.verts.begin(), j.verts.end());
-        for (int v : j.verts) {
-          A.agg_of[v] = A.n_agg;
-          A.rows.push_back(v);
-          region[v] = -1;
-        }
-        A.ptr.push_back((int)A.rows.size());
-        A.n_agg++;
-        continue;
-      }
-      bfs_order(j.verts, j.rid, j.verts[0], order);
-      const int far = order.back();                   // a vertex far from an arbitrary one: (pseudo-)peripheral
-      bfs_order(j.verts, j.rid, far, order);
-      const int half = cnt / 2;
-      Job lo, hi;
-      lo.rid = next_region++;
-      hi.rid = next_region++;
-      lo.verts.assign(order.begin(), order.begin() + half);
-      hi.verts.assign(order.begin() + half, order.end());
-      for (int v : lo.verts) region[v] = lo.rid;
-      for (int v : hi.verts) region[v] = hi.rid;
-      stack.push_back(std::move(hi));   // lo is processed first
-      stack.push_back(std::move(lo));
+      A.ptr.push_back((int)A.rows.size());
+      A.n_agg++;
     }
   }
   A.seg_agg[kSegments] = A.n_agg;
   // aggregate adjacency (closed neighbourhoods), then greedy distance-2 colouring in aggregate order
   const int na = A.n_agg;
   std::vector<std::vector<int>> adj(na);
-  for (int a = 0; a < na; ++a) {
-    std::vector<int>& l = adj[a];
-    for (int q = A.ptr[a]; q < A.ptr[a + 1]; ++q) {
-      const int v = A.rows[q];
-      for (int k = rowptr[v]; k < rowptr[v + 1]; ++k) l.push_back(A.agg_of[colidx[k]]);
-    }
-    std::sort(l.begin(), l.end());
-    l.erase(std::unique(l.begin(), l.end()), l.end());   // contains a itself (diagonal entry)
+  {
+    auto adjacency = [&](int a_begin, int a_end) {
+      for (int a = a_begin; a < a_end; ++a) {
+        std::vector<int>& l = adj[a];
+        int last = -1;
+        for (int q = A.ptr[a]; q < A.ptr[a + 1]; ++q) {
+          const int v = A.rows[q];
+          for (int k = rowptr[v]; k < rowptr[v + 1]; ++k) {
+            const int b = A.agg_of[colidx[k]];
+            if (b != last) l.push_back(b);   // most neighbours lie in the row's own aggregate
+            last = b;
+          }
+        }
+        std::sort(l.begin(), l.end());
+        l.erase(std::unique(l.begin(), l.end()), l.end());   // contains a itself (diagonal entry)
+      }
+    };
+    const int nt = N >= 8192 ? std::min(kSegments, na) : 1;
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(adjacency, (int)((int64_t)na * t / nt), (int)((int64_t)na * (t + 1) / nt));
+    adjacency(0, nt > 1 ? (int)((int64_t)na / nt) : na);
+    for (auto& t : th) t.join();
   }
   A.color.assign(na, -1);
   A.n_colors = 0;
@@ -341,6 +386,26 @@ inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const s
   for (int a = 0; a < na; ++a)
     for (int b : adj[a]) A.nbr_of_color[(size_t)a * A.n_colors + A.color[b]] = b;
 }
+
+// fn(begin, end, part) over [0, n) in up to kSegments contiguous parts of at least `grain` items, one host thread each;
+// returns the number of parts (sums a pass needs are kept per part and added in part order)
+template <typename F>
+inline int for_parts(int n, int grain, F fn) {
+  const int parts = std::max(1, std::min(kSegments, n / std::max(grain, 1)));
+  if (parts == 1) {
+    fn(0, n, 0);
+    return 1;
+  }
+  std::vector<std::thread> th;
+  th.reserve(parts - 1);
+  for (int t = 1; t < parts; ++t)
+    th.emplace_back([=] { fn((int)((int64_t)n * t / parts), (int)((int64_t)n * (t + 1) / parts), t); });
+  fn(0, (int)((int64_t)n / parts), 0);
+  for (auto& t : th) t.join();
+  return parts;
+}
+constexpr int kRowGrain = 8192;     // rows per host thread in the per-row passes of the structure build
+constexpr int kSliceGrain = kRowGrain / kSlice;
 
 // distinct values of key(x) over a small array (<= 32 entries)
 template <typename F>
@@ -374,7 +439,8 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   auto owned = [&](int g) { return g >= v0 && g < v1; };
 
   // ---- local factors in canonical order, ghosts
-  std::vector<int> loc;  // canonical positions (index into perm) of local factors
+  std::vector<int>& loc = S.work.loc;  // canonical positions (index into perm) of local factors
+  loc.clear();
   loc.reserve(world == 1 ? (size_t)E : (size_t)E / world + 1024);
   S.ghosts.clear();
   for (int c = 0; c < E; ++c) {
@@ -402,7 +468,8 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
 
   // ---- contribution lists: priors first, then factor sides in canonical order (which visits a
   //      row's neighbours in ascending global column order)
-  std::vector<int> ccnt(n_own, 0);
+  std::vector<int>& ccnt = S.work.ccnt;
+  ccnt.assign(n_own, 0);
   for (int p = 0; p < S.P_loc; ++p) ccnt[S.pr_row[p]]++;
   for (int q = 0; q < EL; ++q) {
     const int k = perm[loc[q]];
@@ -418,11 +485,13 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   S.f_i.assign(CS, -1);
   S.f_j.assign(CS, -1);
   S.f_count.assign(CS, 0);
-  std::vector<int> ccol(CS, -1);    // global column of each contribution (-1 prior / padding)
-  std::vector<int> chome(CS, -1);   // home cell of the contribution's factor
-  std::vector<int> cfac(CS, -1);    // caller's factor index
+  std::vector<int>&ccol = S.work.ccol, &chome = S.work.chome, &cfac = S.work.cfac;
+  ccol.assign(CS, -1);    // global column of each contribution (-1 prior / padding)
+  chome.assign(CS, -1);   // home cell of the contribution's factor
+  cfac.assign(CS, -1);    // caller's factor index
   {
-    std::vector<int> fill(n_own, 0);
+    std::vector<int>& fill = S.work.fill;
+    fill.assign(n_own, 0);
     for (int p = 0; p < S.P_loc; ++p) {
       const int row = S.pr_row[p];
       const int c = S.csell.pos(row, fill[row]++);
@@ -453,68 +522,88 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   // slice's 32 pointers stay within a few lines
   S.n_factor_copies = 0;
   {
+    // a slice's cells are written by the part that owns the slice only (chome of its own cells), then finished there
     const int ns = (n_own + kSlice - 1) / kSlice;
-    int away[kSlice], awaycell[kSlice];
-    for (int sl = 0; sl < ns; ++sl)
-      for (int s = 0; s < S.csell.width[sl]; ++s) {
-        int na = 0;
-        for (int l = 0; l < kSlice && sl * kSlice + l < n_own; ++l) {
-          const int c = S.csell.base[sl] + s * kSlice + l;
-          if (cfac[c] >= 0 && chome[c] != c) {
-            away[na] = chome[c];
-            awaycell[na++] = c;
+    int sums[kSegments] = {0};
+    for_parts(ns, kSliceGrain, [&](int sl0, int sl1, int part) {
+      int away[kSlice], awaycell[kSlice];
+      int copies = 0;
+      for (int sl = sl0; sl < sl1; ++sl)
+        for (int s = 0; s < S.csell.width[sl]; ++s) {
+          int na = 0;
+          for (int l = 0; l < kSlice && sl * kSlice + l < n_own; ++l) {
+            const int c = S.csell.base[sl] + s * kSlice + l;
+            if (cfac[c] >= 0 && chome[c] != c) {
+              away[na] = chome[c];
+              awaycell[na++] = c;
+            }
+          }
+          if (na && distinct_count(away, na, [](int p) { return p >> 3; }) > kShareMaxLinesFactor) {
+            for (int a = 0; a < na; ++a) chome[awaycell[a]] = awaycell[a];  // keep a copy in the own cell
+            copies += na;
           }
         }
-        if (na && distinct_count(away, na, [](int p) { return p >> 3; }) > kShareMaxLinesFactor) {
-          for (int a = 0; a < na; ++a) chome[awaycell[a]] = awaycell[a];  // keep a copy in the own cell
-          S.n_factor_copies += na;
+      for (int c = S.csell.base[sl0]; c < S.csell.base[sl1]; ++c) {
+        if (cfac[c] < 0) continue;
+        const int k = cfac[c];
+        S.c_code[c] |= (uint32_t)chome[c] << 3;
+        S.c_col[c] = S.local_of(ccol[c]);
+        if (chome[c] == c) {  // data cell
+          S.f_src[c] = k;
+          S.f_i[c] = S.local_of(ei[k]);
+          S.f_j[c] = S.local_of(ej[k]);
+          S.f_count[c] = (S.c_code[c] & 4u) ? 1 : 0;
         }
       }
-  }
-  for (int c = 0; c < CS; ++c) {
-    if (cfac[c] < 0) continue;
-    const int k = cfac[c];
-    S.c_code[c] |= (uint32_t)chome[c] << 3;
-    S.c_col[c] = S.local_of(ccol[c]);
-    if (chome[c] == c) {  // data cell
-      S.f_src[c] = k;
-      S.f_i[c] = S.local_of(ei[k]);
-      S.f_j[c] = S.local_of(ej[k]);
-      S.f_count[c] = (S.c_code[c] & 4u) ? 1 : 0;
-    }
+      sums[part] = copies;
+    });
+    for (int t = 0; t < kSegments; ++t) S.n_factor_copies += sums[t];
   }
 
   // ---- reference lists = unique neighbours per owned row, ascending global column (the
   //      contribution lists are already in that order)
-  std::vector<int> rcnt(n_own, 0);
+  std::vector<int>& rcnt = S.work.rcnt;
+  rcnt.assign(n_own, 0);
   S.max_degree = 0;
-  for (int row = 0; row < n_own; ++row) {
-    int last = -1, deg = 0;
-    for (int s = 0; s < ccnt[row]; ++s) {
-      const int col = ccol[S.csell.pos(row, s)];
-      if (col < 0 || col == last) continue;
-      last = col;
-      ++deg;
-    }
-    rcnt[row] = deg;
-    S.max_degree = std::max(S.max_degree, deg);
+  {
+    int maxdeg[kSegments] = {0};
+    for_parts(n_own, kRowGrain, [&](int row0, int row1, int part) {
+      int md = 0;
+      for (int row = row0; row < row1; ++row) {
+        int last = -1, deg = 0;
+        for (int s = 0; s < ccnt[row]; ++s) {
+          const int col = ccol[S.csell.pos(row, s)];
+          if (col < 0 || col == last) continue;
+          last = col;
+          ++deg;
+        }
+        rcnt[row] = deg;
+        md = std::max(md, deg);
+      }
+      maxdeg[part] = md;
+    });
+    for (int t = 0; t < kSegments; ++t) S.max_degree = std::max(S.max_degree, maxdeg[t]);
   }
   S.rsell.build(rcnt);
   const int RS = S.rsell.slots;
   S.r_col.assign(RS, -1);
   S.r_blk.assign(RS, 0);
-  std::vector<int> rptr(n_own + 1, 0);
+  std::vector<int>& rptr = S.work.rptr;
+  rptr.assign(n_own + 1, 0);
   for (int row = 0; row < n_own; ++row) rptr[row + 1] = rptr[row] + rcnt[row];
-  std::vector<int> nbr((size_t)rptr[n_own]);  // global columns, CSR
-  for (int row = 0; row < n_own; ++row) {
-    int last = -1, w = rptr[row];
-    for (int s = 0; s < ccnt[row]; ++s) {
-      const int col = ccol[S.csell.pos(row, s)];
-      if (col < 0 || col == last) continue;
-      last = col;
-      nbr[w++] = col;
+  std::vector<int>& nbr = S.work.nbr;  // global columns, CSR
+  nbr.resize((size_t)rptr[n_own]);
+  for_parts(n_own, kRowGrain, [&](int row0, int row1, int) {
+    for (int row = row0; row < row1; ++row) {
+      int last = -1, w = rptr[row];
+      for (int s = 0; s < ccnt[row]; ++s) {
+        const int col = ccol[S.csell.pos(row, s)];
+        if (col < 0 || col == last) continue;
+        last = col;
+        nbr[w++] = col;
+      }
     }
-  }
+  });
   auto ref_cell = [&](int row, int gcol) {  // block cell of reference (row -> gcol)
     const int* b = nbr.data() + rptr[row];
     const int* e = nbr.data() + rptr[row + 1];
@@ -522,84 +611,107 @@ inline void build_local_structure(int N, int E, const int* ei, const int* ej, co
   };
   // The block of pair {a, b} is computed by its writer row: the lo endpoint, or the hi one when lo
   // belongs to another rank.  The writer's own cell holds it in canonical orientation.
-  std::vector<int> rhome(RS, -1);  // per reference cell: the cell that holds the canonical block
+  std::vector<int>& rhome = S.work.rhome;  // per reference cell: the cell that holds the canonical block
+  rhome.assign(RS, -1);
   S.n_pairs = 0;
   S.nnzo_own = rptr[n_own];
-  for (int row = 0; row < n_own; ++row) {
-    const int g = v0 + row;
-    for (int s = 0; s < rcnt[row]; ++s) {
-      const int col = nbr[rptr[row] + s];
-      const int cell = S.rsell.pos(row, s);
-      const int lo = std::min(g, col);
-      const bool writer = (g == lo) || !owned(lo);
-      S.r_col[cell] = S.local_of(col);
-      if (writer) {
-        rhome[cell] = cell;
-        S.n_pairs++;
-      } else {
-        rhome[cell] = ref_cell(lo - v0, g);
+  {
+    int pairs[kSegments] = {0};
+    for_parts(n_own, kRowGrain, [&](int row0, int row1, int part) {
+      int np = 0;
+      for (int row = row0; row < row1; ++row) {
+        const int g = v0 + row;
+        for (int s = 0; s < rcnt[row]; ++s) {
+          const int col = nbr[rptr[row] + s];
+          const int cell = S.rsell.pos(row, s);
+          const int lo = std::min(g, col);
+          const bool writer = (g == lo) || !owned(lo);
+          S.r_col[cell] = S.local_of(col);
+          if (writer) {
+            rhome[cell] = cell;
+            np++;
+          } else {
+            rhome[cell] = ref_cell(lo - v0, g);
+          }
+        }
       }
-    }
+      pairs[part] = np;
+    });
+    for (int t = 0; t < kSegments; ++t) S.n_pairs += pairs[t];
   }
   // share or copy, per (slice, slot)
   S.n_block_copies = 0;
   {
     const int ns = (n_own + kSlice - 1) / kSlice;
-    int away[kSlice], awaycell[kSlice];
-    for (int sl = 0; sl < ns; ++sl)
-      for (int s = 0; s < S.rsell.width[sl]; ++s) {
-        int na = 0;
-        for (int l = 0; l < kSlice && sl * kSlice + l < n_own; ++l) {
-          const int c = S.rsell.base[sl] + s * kSlice + l;
-          if (rhome[c] >= 0 && rhome[c] != c) {
-            away[na] = rhome[c];
-            awaycell[na++] = c;
+    int sums[kSegments] = {0};
+    for_parts(ns, kSliceGrain, [&](int sl0, int sl1, int part) {
+      int away[kSlice], awaycell[kSlice];
+      int copies = 0;
+      for (int sl = sl0; sl < sl1; ++sl)
+        for (int s = 0; s < S.rsell.width[sl]; ++s) {
+          int na = 0;
+          for (int l = 0; l < kSlice && sl * kSlice + l < n_own; ++l) {
+            const int c = S.rsell.base[sl] + s * kSlice + l;
+            if (rhome[c] >= 0 && rhome[c] != c) {
+              away[na] = rhome[c];
+              awaycell[na++] = c;
+            }
+          }
+          if (na && distinct_count(away, na, [](int p) { return p >> 4; }) > kShareMaxLinesBlock) {
+            for (int a = 0; a < na; ++a) rhome[awaycell[a]] = awaycell[a];  // this row computes its own copy
+            copies += na;
           }
         }
-        if (na && distinct_count(away, na, [](int p) { return p >> 4; }) > kShareMaxLinesBlock) {
-          for (int a = 0; a < na; ++a) rhome[awaycell[a]] = awaycell[a];  // this row computes its own copy
-          S.n_block_copies += na;
+      for (int row = sl0 * kSlice; row < std::min(n_own, sl1 * kSlice); ++row) {
+        const int g = v0 + row;
+        for (int s = 0; s < rcnt[row]; ++s) {
+          const int col = nbr[rptr[row] + s];
+          const int cell = S.rsell.pos(row, s);
+          // every stored block is canonical (lo orientation): the hi row uses it transposed, whether
+          // it reads the lo row's cell or its own copy
+          S.r_blk[cell] = (rhome[cell] << 1) | (g != std::min(g, col) ? 1 : 0);
         }
       }
-  }
-  for (int row = 0; row < n_own; ++row) {
-    const int g = v0 + row;
-    for (int s = 0; s < rcnt[row]; ++s) {
-      const int col = nbr[rptr[row] + s];
-      const int cell = S.rsell.pos(row, s);
-      // every stored block is canonical (lo orientation): the hi row uses it transposed, whether
-      // it reads the lo row's cell or its own copy
-      S.r_blk[cell] = (rhome[cell] << 1) | (g != std::min(g, col) ? 1 : 0);
-    }
+      sums[part] = copies;
+    });
+    for (int t = 0; t < kSegments; ++t) S.n_block_copies += sums[t];
   }
   // block words of the contributions whose row computes the pair's block into its own cell
   S.c_first.assign(std::max(n_own, 1), 0);
   S.n_merged = 0;
-  for (int row = 0; row < n_own; ++row) {
-    const int g = v0 + row;
-    int last = -1, s_ref = -1;
-    int first = ccnt[row];
-    for (int s = ccnt[row] - 1; s >= 0; --s) {
-      const int col = ccol[S.csell.pos(row, s)];
-      if (col > g) first = s;
-      else break;
-    }
-    S.c_first[row] = first;
-    for (int s = 0; s < ccnt[row]; ++s) {
-      const int c = S.csell.pos(row, s);
-      const int col = ccol[c];
-      if (col < 0) continue;
-      const bool head = (col != last);
-      if (head) {
-        last = col;
-        ++s_ref;
+  {
+    int merged[kSegments] = {0};
+    for_parts(n_own, kRowGrain, [&](int row0, int row1, int part) {
+      int nm = 0;
+      for (int row = row0; row < row1; ++row) {
+        const int g = v0 + row;
+        int last = -1, s_ref = -1;
+        int first = ccnt[row];
+        for (int s = ccnt[row] - 1; s >= 0; --s) {
+          const int col = ccol[S.csell.pos(row, s)];
+          if (col > g) first = s;
+          else break;
+        }
+        S.c_first[row] = first;
+        for (int s = 0; s < ccnt[row]; ++s) {
+          const int c = S.csell.pos(row, s);
+          const int col = ccol[c];
+          if (col < 0) continue;
+          const bool head = (col != last);
+          if (head) {
+            last = col;
+            ++s_ref;
+          }
+          const int lo = std::min(g, col);
+          const int cell = S.rsell.pos(row, s_ref);
+          if (rhome[cell] != cell) continue;  // the lo row's cell is shared
+          S.c_blk[c] = (cell << 2) | ((g != lo) ? 2 : 0) | (head ? 1 : 0);
+          if (!head) nm++;
+        }
       }
-      const int lo = std::min(g, col);
-      const int cell = S.rsell.pos(row, s_ref);
-      if (rhome[cell] != cell) continue;  // the lo row's cell is shared
-      S.c_blk[c] = (cell << 2) | ((g != lo) ? 2 : 0) | (head ? 1 : 0);
-      if (!head) S.n_merged++;
-    }
+      merged[part] = nm;
+    });
+    for (int t = 0; t < kSegments; ++t) S.n_merged += merged[t];
   }
 
   // ---- halo lists.  Rank q needs my row a iff a factor joins a with a row q owns; its ghost list

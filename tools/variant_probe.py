@@ -32,6 +32,9 @@ LIBS = {                       # name -> -D switches ([] = the in-tree default l
     "spmv_minb5": ["GS_SPMV_MINB=5"],             # 48 registers: 1.6 us faster on C3, 8 us slower on C4
     "spmv_nopre": ["GS_SPMV_PRELOAD=0"],
     "h0f0": ["GS_H_LAYOUT=0", "GS_F_LAYOUT=0"],   # round 1's plane layouts
+    "chi2_0": ["GS_CHI2_PIPE=0"],                 # k_chi2 with one slot after the other (56 registers)
+    "chi2_1": ["GS_CHI2_PIPE=1"],                 # next slot's vertex pair requested ahead
+    "chi2_2": ["GS_CHI2_PIPE=2"],                 # next slot's pair, poses and factor requested ahead (104 registers)
 }
 NP = 4
 FLAGSETS = {                   # name -> solver_flags (persistent kernel off everywhere: the probe is about the big-graph path);
