@@ -31,7 +31,6 @@
 #include <vector>
 
 #include "../../include/graphslam_cuda.h"
-#include "../../include/graphslam_cuda_debug.h"  // GS_X_* experiment bits only
 #include "comm.hpp"
 #include "g2o.hpp"
 #include "host_util.hpp"
@@ -102,7 +101,6 @@ struct gs_graph {
   bool dir_otf = false;                   // direction formed on the fly inside the product: two kernels per iteration
                                           // (k_spmvdir[_p2p] + update) instead of three; decided in prepare()
   int ghost_chunk = 0;                    // ghost doubles of p advanced per halo tile in k_spmvdir_p2p
-  bool p2p_staged = false;                // GS_X_P2P_STAGED (experiment): k_update_p2p_staged / k_updpush_p2p_staged
   bool fused_wanted = true;               // !GS_SOLVER_NO_PERSISTENT
   bool fused = false;                     // this graph's tiles are all co-resident: one persistent kernel per batch
   int fused_capacity = 0;                 // CTAs of k_pcg_fused the device holds at once
@@ -451,10 +449,7 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
     } else if (stage == 1) {
       gs::PcgView pv = pcg_view(g);
       pv.p = next;
-      if (g->p2p_staged)
-        gs::k_updpush_p2p_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
-      else
-        gs::k_updpush_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
+      gs::k_updpush_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pv, reduce_ctx(g, 1), x, h);
     }
     return GS_OK;
   }
@@ -490,10 +485,7 @@ gs_status launch_pcg_stage(gs_graph* g, int stage, unsigned int k_local) {
       gs::k_spmv_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->pvec, g->pghost, g->d_Ap.p,
                                                                    reduce_ctx(g, 0), x);
     } else if (stage == 1) {
-      if (g->p2p_staged)
-        gs::k_update_p2p_staged<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
-      else
-        gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
+      gs::k_update_p2p<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(pcg_view(g), reduce_ctx(g, 1), x);
     } else {
       gs::HaloPush h;
       h.row = g->d_hp_row.p;
@@ -1327,7 +1319,6 @@ gs_status create_common(gs_graph* g) {
   g->use_graph = !(flags & GS_SOLVER_NO_CUDA_GRAPH);
   g->fused_wanted = !(flags & GS_SOLVER_NO_PERSISTENT);
   g->p2p_wanted = !(flags & GS_SOLVER_NCCL_PER_OP);
-  g->p2p_staged = (flags & GS_X_P2P_STAGED) != 0;
   g->coarse_wanted = !(flags & GS_SOLVER_BLOCK_JACOBI_ONLY);
   {
     int per_sm = 0, sms = 0, dev = 0, coop = 0;

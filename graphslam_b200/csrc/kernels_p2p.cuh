@@ -445,132 +445,6 @@ __global__ void __launch_bounds__(kThreads) k_updpush_p2p(const PcgView a, const
   reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_upd[0][0]; }, red, &flag, job.x);
 }
 
-// ---- round-2 candidates (GS_P2P_STAGED=1, off by default; not yet run on several GPUs) -----------------------
-// k_update_p2p / k_updpush_p2p with the tile's x, r, z moved as in k_pcg_update_staged (kernels.cuh): full-width
-// double2 accesses, the new r and z handed between the flat and the per-row view through shared memory.  Worth
-// ~4 us per launch at 500k rows on one GPU.  The body below restates k_pcg_update_staged's (that kernel keeps its
-// own copy so that its verified machine code does not change); same expressions, same reduction: same bits.
-__device__ __forceinline__ void update_tile_staged(const PcgView& a, int tile, double alpha, double* sv, double (&v)[2]) {
-  const int row0 = tile * kThreads;
-  const int nrow = min(kThreads, a.n_own - row0);
-  const size_t base = 3 * (size_t)row0;
-  const int nd = 3 * nrow, nd2 = nd >> 1;
-  const double2* p2 = reinterpret_cast<const double2*>(a.p + base);
-  const double2* q2 = reinterpret_cast<const double2*>(a.Ap + base);
-  double2* x2 = reinterpret_cast<double2*>(a.x + base);
-  double2* r2 = reinterpret_cast<double2*>(a.r + base);
-  double2* s2 = reinterpret_cast<double2*>(sv);
-  for (int i = threadIdx.x; i < nd2; i += kThreads) {
-    const double2 pv = p2[i], qv = q2[i], xv = x2[i], rv = r2[i];
-    const double2 xn = make_double2(xv.x + alpha * pv.x, xv.y + alpha * pv.y);
-    const double2 rn = make_double2(rv.x - alpha * qv.x, rv.y - alpha * qv.y);
-    x2[i] = xn;
-    r2[i] = rn;
-    s2[i] = rn;
-  }
-  if ((nd & 1) && threadIdx.x == 0) {
-    const size_t e = base + (size_t)nd - 1;
-    a.x[e] = a.x[e] + alpha * a.p[e];
-    const double rn = a.r[e] - alpha * a.Ap[e];
-    a.r[e] = rn;
-    sv[nd - 1] = rn;
-  }
-  __syncthreads();
-  v[0] = 0.0;
-  v[1] = 0.0;
-  double z0 = 0.0, z1 = 0.0, z2 = 0.0;
-  const int t = threadIdx.x;
-  if (t < nrow) {
-    const double r0 = sv[3 * t], r1 = sv[3 * t + 1], r2v = sv[3 * t + 2];
-    apply_minv(a.Minv, (size_t)a.n_own, (size_t)(row0 + t), r0, r1, r2v, z0, z1, z2);
-    v[0] = (r0 * z0 + r1 * z1) + r2v * z2;
-    v[1] = (r0 * r0 + r1 * r1) + r2v * r2v;
-  }
-  __syncthreads();
-  if (t < nrow) {
-    sv[3 * t] = z0;
-    sv[3 * t + 1] = z1;
-    sv[3 * t + 2] = z2;
-  }
-  __syncthreads();
-  double2* z2p = reinterpret_cast<double2*>(a.z + base);
-  for (int i = threadIdx.x; i < nd2; i += kThreads) z2p[i] = s2[i];
-  if ((nd & 1) && threadIdx.x == 0) a.z[base + (size_t)nd - 1] = sv[nd - 1];
-  __syncthreads();   // the tile's z is complete for whoever reads it next (halo push)
-}
-
-__global__ void __launch_bounds__(kThreads) k_update_p2p_staged(const PcgView a, const ReduceCtx c, const P2PCtx x) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  __shared__ WaitOut wo;
-  __shared__ __align__(16) double sv[3 * kThreads];
-  if (c.sc->done) return;
-  const unsigned int S = *x.seq_base + x.k_local;
-  P2PWindow* me = x.me;
-  if (!wait_sums<1>(me->ll_pap[S & 1u], S + 1, c.sc, x.spin_limit, &wo, 1)) return;
-  const double pAp = wo.tot[0];
-  if (!(pAp > 0.0)) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-      c.sc->pAp = pAp;
-      c.sc->done = 2;
-    }
-    return;
-  }
-  const double alpha = c.sc->rzv[(S + 1u) & 1u] / pAp;
-  double v[2];
-  update_tile_staged(a, (int)blockIdx.x, alpha, sv, v);
-  reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_upd[0][0]; }, red, &flag);
-}
-
-__global__ void __launch_bounds__(kThreads) k_updpush_p2p_staged(const PcgView a, const ReduceCtx c, const P2PCtx x,
-                                                                  const HaloPush h) {
-  __shared__ double red[8];
-  __shared__ int flag;
-  __shared__ WaitOut wo;
-  __shared__ __align__(16) double sv[3 * kThreads];
-  if (c.sc->done) return;
-  const int4 job = ldg(h.order + blockIdx.x);
-  const unsigned int S = *x.seq_base + x.k_local;
-  P2PWindow* me = x.me;
-  if (!wait_sums<1>(me->ll_pap[S & 1u], S + 1, c.sc, x.spin_limit, &wo, 1)) return;
-  const double pAp = wo.tot[0];
-  if (!(pAp > 0.0)) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-      c.sc->pAp = pAp;
-      c.sc->done = 2;
-    }
-    return;
-  }
-  const double alpha = c.sc->rzv[(S + 1u) & 1u] / pAp;
-  double v[2];
-  update_tile_staged(a, job.x, alpha, sv, v);
-  if (job.z > job.y) {   // a sending tile: its new z rows go to the neighbours' ghost slots (as k_updpush_p2p)
-    bool pushed = false;
-    for (int e = job.y + (int)threadIdx.x; e < job.z; e += kThreads) {
-      const double* src = a.z + 3 * (size_t)h.row[e];
-      double* dst = h.dst[e];
-      dst[0] = __ldcg(src);
-      dst[1] = __ldcg(src + 1);
-      dst[2] = __ldcg(src + 2);
-      pushed = true;
-    }
-    if (pushed) __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned int t = atomicAdd(x.ticket, 1u);
-      flag = (t == (unsigned int)h.n_push_tiles - 1u);
-    }
-    __syncthreads();
-    if (flag) {
-      if ((int)threadIdx.x < x.world && ((x.nbr_mask >> threadIdx.x) & 1u))
-        st_release_sys(&x.win[threadIdx.x]->halo_flag[x.rank], S + 2);
-      if (threadIdx.x == 0) *x.ticket = 0u;
-    }
-    __syncthreads();
-  }
-  reduce_push<2>(c, x, v, S & 1u, S + 1, [](P2PWindow* w) { return &w->ll_upd[0][0]; }, red, &flag, job.x);
-}
-
 // ---- two-level preconditioner over peer memory ----------------------------------------------------------------
 // The iteration of kernels_coarse.cuh with its exchanges fused into the kernels (six launches, no NCCL call):
 //

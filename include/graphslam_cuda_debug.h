@@ -16,13 +16,6 @@
 extern "C" {
 #endif
 
-/* Experiments: candidate kernels under measurement, selected by high bits of gs_params.solver_flags.  Every candidate
- * gives the same bits as the default path; a bit disappears once its candidate has won (becomes the default) or
- * lost (is deleted). */
-enum {
-  GS_X_P2P_STAGED = 1 << 17        /* staged x/r/z update inside the peer-memory kernels */
-};
-
 /* sorted unique block pattern (rowptr[n+1], colidx[nnzb]) and the canonical factor order `perm`
  * of a graph over dense indices 0..n-1; any output may be NULL */
 gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,

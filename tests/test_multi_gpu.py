@@ -27,16 +27,12 @@ def _free_port():
 
 
 # execution paths of the multi-GPU PCG iteration (gs_params.solver_flags; the worker takes the flag word as argv[3]).
-# The staged x/r/z update inside the peer-memory kernels (GS_X_P2P_STAGED, csrc/kernels_p2p.cuh) is a candidate under
-# measurement and only exercised on request (GS_TEST_CANDIDATES=1, read by this test harness, not by the library).
-_NCCL, _DIRK, _OTF, _BJ, _XSTAGED = 2, 8, 16, 32, 1 << 17
+_NCCL, _DIRK, _OTF, _BJ = 2, 8, 16, 32
 # block-Jacobi PCG: peer-memory kernels (two or three per iteration) or one NCCL call per exchange; two-level
 # preconditioner: peer-memory kernels (default) or NCCL per exchange.  Each is compared with ONE GPU running the same
 # preconditioner.
 _FORMS = [("peer-memory-2-kernels", _BJ | _OTF), ("peer-memory-3-kernels", _BJ | _DIRK), ("nccl-per-op", _BJ | _NCCL),
           ("two-level-default", 0), ("two-level-nccl-per-op", _NCCL)]
-if os.environ.get("GS_TEST_CANDIDATES") == "1":
-    _FORMS += [("peer-memory-2-kernels-staged", _BJ | _OTF | _XSTAGED), ("peer-memory-3-kernels-staged", _BJ | _DIRK | _XSTAGED)]
 
 
 def _run_worker(world, flags, cid, n, timeout=900):

@@ -1,6 +1,5 @@
 """Short GPU probe of kernel variants: compile-time variants of the library (storage layouts, built by
-graphslam_b200.build.build_variant into lib/variants/) x run-time execution paths (gs_params.solver_flags, including
-the GS_X_* experiment bits of include/graphslam_cuda_debug.h).  For each combination, on one config:
+graphslam_b200.build.build_variant into lib/variants/) x run-time execution paths (gs_params.solver_flags).  For each combination, on one config:
 
   * CUDA-event time of every kernel inside the real sequence (gs_profile_pcg / gs_profile_outer),
   * wall time per PCG iteration of a capped solve replayed from the captured CUDA graph (how gs_optimize runs it),
