@@ -149,8 +149,8 @@ struct gs_graph {
   bool theta_wrapped = false;     // every host theta is already in (-pi, pi] (they all came back from the device)
   double4* h_stage = nullptr;     // pinned staging of the pose transfers
   size_t h_stage_n = 0;
-  char* h_struct = nullptr;       // pinned staging of the structure upload (factor cells, contribution and reference words)
-  size_t h_struct_bytes = 0;
+  char* h_struct[2] = {nullptr, nullptr};   // pinned staging of the structure upload, two chunks in flight
+  cudaEvent_t ev_struct[2] = {nullptr, nullptr};
   bool device_values_valid = false;
   bool system_valid = false;      // H, b assembled at the current device poses
 
@@ -749,17 +749,19 @@ gs_status ensure_stage(gs_graph* g, size_t n) {
   return GS_OK;
 }
 
-// pinned staging of the structure upload: grows geometrically, lives as long as the graph (an incremental update
-// rebuilds and re-uploads the structure every few keyframes: fresh pageable vectors cost a page fault per 4 KB and a
-// synchronous staged copy each time)
-gs_status ensure_struct_stage(gs_graph* g, size_t bytes) {
-  if (bytes <= g->h_struct_bytes) return GS_OK;
-  if (g->h_struct) cudaFreeHost(g->h_struct);
-  g->h_struct = nullptr;
-  g->h_struct_bytes = 0;
-  const size_t want = bytes + bytes / 4 + (1u << 20);
-  GS_CUDA(g, cudaMallocHost(&g->h_struct, want));
-  g->h_struct_bytes = want;
+// Pinned staging of the structure upload.  The factor cells and the contribution / reference words (90 % of the
+// structure's bytes) are written by several host threads into one of two fixed pinned chunks while the other one is
+// on its way to the device: no pageable vectors (a page fault per 4 KB and a synchronous staged copy on every
+// rebuild of an incremental graph), and no pinned allocation that grows with the graph (pinning 800 MB for the
+// one-shot upload of a million poses costs more than the copy).
+constexpr size_t kStructChunkCells = 131072;                  // cells per chunk, a multiple of kSlice
+constexpr size_t kStructChunkBytes = kStructChunkCells * 96;  // 8 (pair) + 80 (factor) per factor cell is the largest item
+
+gs_status ensure_struct_stage(gs_graph* g) {
+  for (int b = 0; b < 2; ++b) {
+    if (!g->h_struct[b]) GS_CUDA(g, cudaMallocHost(&g->h_struct[b], kStructChunkBytes));
+    if (!g->ev_struct[b]) GS_CUDA(g, cudaEventCreateWithFlags(&g->ev_struct[b], cudaEventDisableTiming));
+  }
   return GS_OK;
 }
 
@@ -862,39 +864,10 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   g->P = P;
   g->n_own = S.n_own;
   g->n_loc = S.n_own + S.n_ghost;
-  // factor arrays in storage (SELL) order and the contribution / reference words, written straight into pinned memory
-  // on several host threads; padding slots are never referenced
+  // factor arrays in storage (SELL) order and the contribution / reference words: through the pinned chunks, below
   const int FS = S.csell.slots;
   g->fstride = gs::factor_stride(FS);
   const size_t n_cw = S.c_code.size(), n_refs = S.r_col.size();
-  auto up256 = [](size_t b) { return (b + 255) & ~(size_t)255; };
-  const size_t off_ij = 0, off_data = off_ij + up256(sizeof(int2) * g->fstride);
-  const size_t off_cw = off_data + up256(sizeof(double2) * 5 * g->fstride), off_refs = off_cw + up256(sizeof(int4) * n_cw);
-  if (gs_status s = ensure_struct_stage(g, off_refs + up256(sizeof(int2) * n_refs))) return s;
-  int2* st_ij = reinterpret_cast<int2*>(g->h_struct + off_ij);
-  double2* st_data = reinterpret_cast<double2*>(g->h_struct + off_data);
-  int4* st_cw = reinterpret_cast<int4*>(g->h_struct + off_cw);
-  int2* st_refs = reinterpret_cast<int2*>(g->h_struct + off_refs);
-  {
-    const size_t fstride = g->fstride;
-    const double* ez = g->ez.data();
-    const double* eom = g->eom.data();
-    gs::parallel_for(fstride, [&S, st_ij, st_data, fstride, FS, ez, eom](size_t b, size_t e) {
-      for (size_t q = b; q < e; ++q) {
-        const int s = q < (size_t)FS ? S.f_src[q] : -1;
-        if (s < 0) gs::factor_cell_default(st_ij, st_data, fstride, (int)q);
-        else
-          gs::factor_cell_set(st_ij, st_data, fstride, (int)q, S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q],
-                              ez + 3 * (size_t)s, eom + 6 * (size_t)s);
-      }
-    });
-    gs::parallel_for(n_cw, [&S, st_cw](size_t b, size_t e) {
-      for (size_t q = b; q < e; ++q) st_cw[q] = make_int4((int)S.c_code[q], S.c_blk[q], S.c_col[q], 0);
-    });
-    gs::parallel_for(n_refs, [&S, st_refs](size_t b, size_t e) {
-      for (size_t q = b; q < e; ++q) st_refs[q] = make_int2(S.r_col[q], S.r_blk[q]);
-    });
-  }
   g->e_count = 0;
   for (uint32_t code : S.c_code)
     if (code != gs::kPadCode && (code & 4u) && (code & 3u) < 2) g->e_count++;
@@ -910,11 +883,76 @@ gs_status prepare(gs_graph* g, double* ms_out) {
   GS_CUDA(g, g->d_fdata.alloc(5 * g->fstride));
   GS_CUDA(g, g->d_cw.alloc(std::max<size_t>(n_cw, 1)));
   GS_CUDA(g, g->d_refs.alloc(std::max<size_t>(n_refs, 1)));
-  GS_CUDA(g, cudaMemcpyAsync(g->d_eij.p, st_ij, sizeof(int2) * g->fstride, cudaMemcpyHostToDevice, g->stream));
-  GS_CUDA(g, cudaMemcpyAsync(g->d_fdata.p, st_data, sizeof(double2) * 5 * g->fstride, cudaMemcpyHostToDevice, g->stream));
-  if (n_cw) GS_CUDA(g, cudaMemcpyAsync(g->d_cw.p, st_cw, sizeof(int4) * n_cw, cudaMemcpyHostToDevice, g->stream));
-  if (n_refs) GS_CUDA(g, cudaMemcpyAsync(g->d_refs.p, st_refs, sizeof(int2) * n_refs, cudaMemcpyHostToDevice, g->stream));
-  g->h2d_bytes += (double)(sizeof(int2) * g->fstride + sizeof(double2) * 5 * g->fstride + sizeof(int4) * n_cw + sizeof(int2) * n_refs);
+  {
+    if (gs_status s = ensure_struct_stage(g)) return s;
+    const size_t fstride = g->fstride;
+    const double* ez = g->ez.data();
+    const double* eom = g->eom.data();
+    int turn = 0;
+    // one chunk: wait until the buffer's previous copy has left, fill it on the host threads, send it
+    auto chunk = [&](auto&& fill_and_send) -> gs_status {
+      const int b = turn++ & 1;
+      GS_CUDA(g, cudaEventSynchronize(g->ev_struct[b]));
+      if (gs_status s = fill_and_send(g->h_struct[b])) return s;
+      GS_CUDA(g, cudaEventRecord(g->ev_struct[b], g->stream));
+      return GS_OK;
+    };
+    for (size_t q0 = 0; q0 < fstride; q0 += kStructChunkCells) {          // factor cells [q0, q1): pair + five components
+      const size_t q1 = std::min(fstride, q0 + kStructChunkCells), nc = q1 - q0;
+      if (gs_status s = chunk([&](char* buf) -> gs_status {
+            int2* c_ij = reinterpret_cast<int2*>(buf);
+            double2* c_data = reinterpret_cast<double2*>(buf + sizeof(int2) * kStructChunkCells);
+            // the chunk is laid out like an array of nc cells (q0 is a multiple of kSlice): slice-major chunks are one
+            // contiguous piece of the device array, plane-major ones five
+            gs::parallel_for(nc, [&S, c_ij, c_data, nc, q0, FS, ez, eom](size_t b, size_t e) {
+              for (size_t l = b; l < e; ++l) {
+                const size_t q = q0 + l;
+                const int src = q < (size_t)FS ? S.f_src[q] : -1;
+                if (src < 0) gs::factor_cell_default(c_ij, c_data, nc, (int)l);
+                else
+                  gs::factor_cell_set(c_ij, c_data, nc, (int)l, S.f_i[q] | (S.f_count[q] ? 0 : gs::kNoCountBit), S.f_j[q],
+                                      ez + 3 * (size_t)src, eom + 6 * (size_t)src);
+              }
+            }, 8192);
+            GS_CUDA(g, cudaMemcpyAsync(g->d_eij.p + q0, c_ij, sizeof(int2) * nc, cudaMemcpyHostToDevice, g->stream));
+            if (gs::f_step(fstride) == (size_t)gs::kSlice) {
+              GS_CUDA(g, cudaMemcpyAsync(g->d_fdata.p + gs::f_base((int)q0), c_data, sizeof(double2) * 5 * nc, cudaMemcpyHostToDevice,
+                                         g->stream));
+            } else {
+              for (int k = 0; k < 5; ++k)
+                GS_CUDA(g, cudaMemcpyAsync(g->d_fdata.p + gs::f_base((int)q0) + k * gs::f_step(fstride), c_data + k * gs::f_step(nc),
+                                           sizeof(double2) * nc, cudaMemcpyHostToDevice, g->stream));
+            }
+            return GS_OK;
+          }))
+        return s;
+    }
+    for (size_t q0 = 0; q0 < n_cw; q0 += kStructChunkCells) {             // contribution words
+      const size_t nc = std::min(n_cw, q0 + kStructChunkCells) - q0;
+      if (gs_status s = chunk([&](char* buf) -> gs_status {
+            int4* c = reinterpret_cast<int4*>(buf);
+            gs::parallel_for(nc, [&S, c, q0](size_t b, size_t e) {
+              for (size_t l = b; l < e; ++l) c[l] = make_int4((int)S.c_code[q0 + l], S.c_blk[q0 + l], S.c_col[q0 + l], 0);
+            }, 16384);
+            GS_CUDA(g, cudaMemcpyAsync(g->d_cw.p + q0, c, sizeof(int4) * nc, cudaMemcpyHostToDevice, g->stream));
+            return GS_OK;
+          }))
+        return s;
+    }
+    for (size_t q0 = 0; q0 < n_refs; q0 += kStructChunkCells) {           // reference words
+      const size_t nc = std::min(n_refs, q0 + kStructChunkCells) - q0;
+      if (gs_status s = chunk([&](char* buf) -> gs_status {
+            int2* c = reinterpret_cast<int2*>(buf);
+            gs::parallel_for(nc, [&S, c, q0](size_t b, size_t e) {
+              for (size_t l = b; l < e; ++l) c[l] = make_int2(S.r_col[q0 + l], S.r_blk[q0 + l]);
+            }, 16384);
+            GS_CUDA(g, cudaMemcpyAsync(g->d_refs.p + q0, c, sizeof(int2) * nc, cudaMemcpyHostToDevice, g->stream));
+            return GS_OK;
+          }))
+        return s;
+    }
+    g->h2d_bytes += (double)(sizeof(int2) * fstride + sizeof(double2) * 5 * fstride + sizeof(int4) * n_cw + sizeof(int2) * n_refs);
+  }
   if (gs_status s = upload(g, g->d_pr_row, S.pr_row)) return s;
   if (gs_status s = upload(g, g->d_pr_pose, prp)) return s;
   if (gs_status s = upload(g, g->d_pr_om, prom)) return s;
@@ -1471,7 +1509,10 @@ gs_status gs_destroy(gs_graph* g) try {
   if (g->comm) gs::nccl().CommDestroy(g->comm);
   if (g->h_sc) cudaFreeHost(g->h_sc);
   if (g->h_stage) cudaFreeHost(g->h_stage);
-  if (g->h_struct) cudaFreeHost(g->h_struct);
+  for (int b = 0; b < 2; ++b) {
+    if (g->h_struct[b]) cudaFreeHost(g->h_struct[b]);
+    if (g->ev_struct[b]) cudaEventDestroy(g->ev_struct[b]);
+  }
   if (g->ev0) cudaEventDestroy(g->ev0);
   if (g->ev1) cudaEventDestroy(g->ev1);
   if (g->ev_begin) cudaEventDestroy(g->ev_begin);

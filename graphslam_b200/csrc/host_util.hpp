@@ -11,8 +11,7 @@ namespace gs {
 // fn(begin, end) over [0, n) on up to 16 host threads (per-pose conversions between the caller's (x, y, theta) and the
 // device's (x, y, cos, sin): a million sin/cos/atan2 on one thread is 20-50 ms, which a 140-ms LM step notices)
 template <typename F>
-inline void parallel_for(size_t n, F fn) {
-  const size_t min_chunk = 32768;
+inline void parallel_for(size_t n, F fn, size_t min_chunk = 32768) {
   size_t nt = std::min<size_t>(std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 16), (n + min_chunk - 1) / min_chunk);
   if (nt <= 1) {
     fn((size_t)0, n);

@@ -26,14 +26,10 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-LIBS = {                       # name -> -D switches ([] = the in-tree default library); losers of earlier probes are deleted
-    "default": [],
-    "spmv_minb5": ["GS_SPMV_MINB=5"],             # 48 registers: 1.6 us faster on C3, 8 us slower on C4
-    "spmv_nopre": ["GS_SPMV_PRELOAD=0"],
+LIBS = {                       # name -> -D switches ([] = the in-tree default library); decided probes are deleted, their
+    "default": [],             # records stay under profiles/ (r2_variant_probe2.jsonl, r2_chi2_pipeline_probe.jsonl)
     "h0f0": ["GS_H_LAYOUT=0", "GS_F_LAYOUT=0"],   # round 1's plane layouts
-    "chi2_0": ["GS_CHI2_PIPE=0"],                 # k_chi2 with one slot after the other (56 registers)
-    "chi2_1": ["GS_CHI2_PIPE=1"],                 # next slot's vertex pair requested ahead
-    "chi2_2": ["GS_CHI2_PIPE=2"],                 # next slot's pair, poses and factor requested ahead (104 registers)
+    "chi2_0": ["GS_CHI2_PIPE=0"],                 # k_chi2 with one slot after the other
 }
 NP = 4
 FLAGSETS = {                   # name -> solver_flags (persistent kernel off everywhere: the probe is about the big-graph path);
