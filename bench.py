@@ -477,7 +477,10 @@ def run_ours(args):
                          "frac": achieved / peak, "traffic": traffic,
                          "traffic_source": "ncu --set full capture committed under profiles/ (not measured by this run)",
                          "peak_source": peak_src, "kernels": kernels,
-                         "note": "rank 0's kernels on its own rows" if world > 1 else "whole graph"},
+                         "note": ("rank 0's kernels on its own rows" if world > 1 else "whole graph") +
+                                 ("; two-level iteration: 'pcg_update' = k_pcg_update_staged + k_restrict + k_coarse_mv timed "
+                                  "together and 'pcg_dir' = k_dir_coarse, against SURVEY 8(d)'s bytes of the update and the "
+                                  "direction alone (per-kernel times: profiles/r2_launches_C3_1M.csv)" if two_level else "")},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step},
             "gpu_launches": int(launches), "clocks": clocks,
