@@ -116,6 +116,7 @@ DEBUG_SIGNATURES = {
                              C.POINTER(GsEmuResult)]),
     "gs_emu_run_form": (C.c_int, [C.POINTER(GsEmuProblem), C.c_int, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int,
                                   C.POINTER(GsEmuResult)]),
+    "gs_host_aggregation": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, C.c_int32, c_i32_p, c_i32_p, c_i32_p, c_i32_p]),
     "gs_host_pattern": (C.c_int, [C.c_int32, C.c_int32, c_i32_p, c_i32_p, c_i32_p, c_i32_p, C.POINTER(C.c_size_t),
                                   c_i32_p]),
     "gs_host_g2o": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_size_t), c_u64_p, c_double_p, c_u64_p, c_u64_p,

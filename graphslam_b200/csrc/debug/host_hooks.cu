@@ -1,6 +1,7 @@
 // TEST-ONLY host entry points (include/graphslam_cuda_debug.h), built into libgraphslam_cuda_debug.so together with
 // the CPU emulator (emu.cu) — never into the product library.  They call the product's own headers (structure build,
 // g2o reader/writer, per-factor inline functions), so the CPU tests exercise the code the product compiles.
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -26,6 +27,27 @@ gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t
     gs::canonical_order(n, e, ei, ej, pm);
     std::memcpy(perm, pm.data(), sizeof(int32_t) * e);
   }
+  return GS_OK;
+} catch (...) {
+  return GS_ENOMEM;
+}
+
+// the aggregates of the two-level preconditioner's coarse space (structure.hpp: build_aggregation, as prepare() calls it):
+// counts = {aggregates, colours, target size}; agg_of (n), color (n_agg, sized from a first call), seg_agg (9) may be NULL
+gs_status gs_host_aggregation(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t target, int32_t counts[3],
+                              int32_t* agg_of, int32_t* color, int32_t* seg_agg) try {
+  if (n <= 0 || e < 0 || (e && (!ei || !ej)) || !counts) return GS_EINVAL;
+  std::vector<int32_t> rp, ci;
+  gs::global_pattern(n, e, ei, ej, rp, ci);
+  const int t = target > 0 ? target : std::max(48, (int)std::ceil(std::sqrt((double)n)));
+  gs::Aggregation A;
+  gs::build_aggregation(n, rp, ci, std::max(t, (n + 4095) / 4096), A);
+  counts[0] = A.n_agg;
+  counts[1] = A.n_colors;
+  counts[2] = A.target;
+  if (agg_of) std::memcpy(agg_of, A.agg_of.data(), sizeof(int32_t) * (size_t)n);
+  if (color) std::memcpy(color, A.color.data(), sizeof(int32_t) * (size_t)A.n_agg);
+  if (seg_agg) std::memcpy(seg_agg, A.seg_agg, sizeof(int32_t) * (gs::kSegments + 1));
   return GS_OK;
 } catch (...) {
   return GS_ENOMEM;

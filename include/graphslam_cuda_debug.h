@@ -21,6 +21,12 @@ extern "C" {
 gs_status gs_host_pattern(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t* rowptr, int32_t* colidx,
                           size_t* nnzb, int32_t* perm);
 
+/* the aggregates of the two-level preconditioner's coarse space, as gs_prepare builds them (target <= 0: the automatic
+ * size max(48, sqrt n)); counts = {aggregates, colours of the distance-2 colouring, target}; agg_of[n], color[aggregates]
+ * (size it from a first call) and seg_agg[9] (first aggregate of each fixed reduction segment) may be NULL */
+gs_status gs_host_aggregation(int32_t n, int32_t e, const int32_t* ei, const int32_t* ej, int32_t target, int32_t counts[3],
+                              int32_t* agg_of, int32_t* color, int32_t* seg_agg);
+
 /* one BetweenFactor evaluated on the host by the inline functions the kernels compile */
 gs_status gs_host_between(const double pi[3], const double pj[3], const double z[3], const double cov9[9], int mode,
                           double e[3], double Ai[9], double Aj[9], double Hii[9], double Hij[9], double Hjj[9],

@@ -166,3 +166,54 @@ def test_cpp_shim_and_ros_free_example_build_against_the_library(lib, tmp_path):
     if not _cuda_present():
         assert run.returncode != 0 and run.returncode > 0, (run.returncode, run.stderr)
         assert "CUDA" in (run.stderr + run.stdout)
+
+
+@pytest.mark.parametrize("cid,n", [("C1", None), ("C5", 6000), ("C3", 40000), ("C4", 12000)])
+def test_coarse_space_aggregation_invariants(dbg, cid, n):
+    """The aggregates of the two-level preconditioner (structure.hpp: build_aggregation; from 8,192 rows the eight fixed
+    segments run on eight host threads): every row in exactly one aggregate of at most `target` rows, aggregates numbered
+    segment by segment and never across a segment boundary (so they belong to one rank for any number of ranks), a valid
+    distance-2 colouring of the aggregate graph (what lets one product H w serve all aggregates of a colour), and the same
+    answer on every call."""
+    g = synth.config(cid, n=n)
+    prob = O.Problem.from_graph(g)
+    ei = np.ascontiguousarray(prob.ei, np.int32)
+    ej = np.ascontiguousarray(prob.ej, np.int32)
+    p = _lib.c_i32_p
+
+    def run():
+        counts = np.zeros(3, np.int32)
+        agg_of, seg = np.zeros(g.n, np.int32), np.zeros(9, np.int32)
+        assert dbg.gs_host_aggregation(g.n, len(ei), ei.ctypes.data_as(p), ej.ctypes.data_as(p), 0, counts.ctypes.data_as(p),
+                                       agg_of.ctypes.data_as(p), None, seg.ctypes.data_as(p)) == 0
+        color = np.zeros(counts[0], np.int32)
+        assert dbg.gs_host_aggregation(g.n, len(ei), ei.ctypes.data_as(p), ej.ctypes.data_as(p), 0, counts.ctypes.data_as(p),
+                                       None, color.ctypes.data_as(p), None) == 0
+        return counts, agg_of, color, seg
+
+    counts, agg_of, color, seg = run()
+    n_agg, n_colors, target = (int(v) for v in counts)
+    assert target == max(48, int(np.ceil(np.sqrt(g.n))))
+    sizes = np.bincount(agg_of, minlength=n_agg)
+    assert agg_of.min() == 0 and agg_of.max() == n_agg - 1 and sizes.min() >= 1 and sizes.max() <= target
+    # segments: fixed multiples of 256 rows, aggregates numbered segment by segment
+    tiles = (g.n + 255) // 256
+    seg_row = np.minimum(g.n, (tiles * np.arange(9) // 8) * 256)
+    assert seg[0] == 0 and seg[8] == n_agg and np.all(np.diff(seg) >= 0)
+    for s in range(8):
+        rows = agg_of[seg_row[s]:seg_row[s + 1]]
+        if len(rows):
+            assert rows.min() == seg[s] and rows.max() == seg[s + 1] - 1
+    # distance-2 colouring: two aggregates of one colour share no neighbour (closed neighbourhoods)
+    a, b = agg_of[prob.ei], agg_of[prob.ej]
+    nb = [set([k]) for k in range(n_agg)]
+    for x, y in zip(a.tolist(), b.tolist()):
+        nb[x].add(y)
+        nb[y].add(x)
+    assert color.min() == 0 and color.max() == n_colors - 1
+    for k in range(n_agg):
+        seen = {}
+        for m in nb[k]:
+            assert seen.setdefault(int(color[m]), m) == m, "two aggregates of one colour next to aggregate %d" % k
+    again = run()
+    assert np.array_equal(again[1], agg_of) and np.array_equal(again[2], color)

@@ -157,3 +157,20 @@ def test_assemble_without_run_accumulator_is_bitwise_the_same(lib, cid, n, mode)
     dup.cov = np.concatenate([dup.cov, dup.cov[-1:]])
     with pytest.raises(AssertionError):
         emu_run(lib, O.Problem.from_graph(dup), dup.init, form=2)
+
+
+@pytest.mark.parametrize("cid,n", [("C3", 20000), ("C4", 18000)])
+def test_structure_passes_on_host_threads(lib, cid, n):
+    """From 16,384 owned rows the per-row / per-slice passes of build_local_structure run on several host threads
+    (structure.hpp: for_parts): the assembled system must still be the oracle's, shared cells and copies included."""
+    g = synth.config(cid, n=n)
+    prob = O.Problem.from_graph(g)
+    out = emu_run(lib, prob, g.init, max_iters=2)
+    h, ob, ochi2 = prob.linearize(g.init, 0)
+    _, _, oblocks = prob.bsr(h)
+    assert np.abs(out["blocks"] - oblocks).max() <= 1e-11 * np.abs(oblocks).max()
+    assert np.abs(out["b"] - ob).max() <= 1e-11 * np.abs(ob).max()
+    assert out["chi2"] == pytest.approx(ochi2, rel=1e-12)
+    assert out["chi2_check"] == pytest.approx(prob.chi2(g.init), rel=1e-12)
+    if cid == "C4":
+        assert out["bcopies"] > 0 and out["fcopies"] > 0
