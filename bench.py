@@ -8,8 +8,8 @@ to pcg_rel_tol, retract, chi2, accept/reject) on the resident graph, continuing 
 from the synthetic initial guess.  One JSON line on stdout (rank 0); everything else goes to stderr.
 
   value     device-resident throughput: K steps / device time (CUDA events on the library's stream)
-  e2e       the same through the C ABI with HOST buffers, every step: gs_set_poses (H2D) + gs_optimize(1) +
-            gs_get_poses (D2H)
+  e2e       the same through the C ABI with HOST buffers, every step: gs_set_local_poses (H2D) + gs_optimize(1) +
+            gs_get_local_poses (D2H) — each rank moves the rows it owns
   roofline  dominant kernel (BSR SpMV): SURVEY §8(d) algorithmic bytes / CUDA-event launch duration
   cpu_baseline / --impl reference: oracle/cpu_ref.c (C + OpenMP port of the path, all host threads) on a bounded
             sample of the same workload.  The reference's own optimiser is GTSAM (absent, unpinned) — see DESIGN.md.
@@ -373,15 +373,20 @@ def run_ours(args):
         G2.optimize()
         _, x = G2.poses()
     x_warm = x.copy()
-    keys_buf = np.zeros(g.n, dtype=np.uint64)      # the caller's host buffers, reused every step
-    x = np.ascontiguousarray(x)
+    # every rank moves the rows it owns and nothing else (gs_set_local_poses / gs_get_local_poses: 32 N / P bytes each way per
+    # rank; the ghost rows follow device to device) — with the collective gs_get_poses every rank would receive and convert all
+    # N poses every step.  One GPU owns every row: the same bytes as gs_set_poses / gs_get_poses.
+    first, count = G2.local_range()
+    xl = np.ascontiguousarray(x[first:first + count])   # the caller's host buffers, reused every step
+    kl, _ = G2.local_poses(xyt_out=xl.copy())           # the keys of the owned rows: read once
+    assert np.array_equal(kl, np.sort(keys)[first:first + count])
     barrier()
     h2d0, d2h0 = G2.transfer_bytes()
     t0 = time.time()
     for _ in range(K):
-        G2.set_poses(keys, x)            # host -> device (this rank's rows + halo, (x,y,cos,sin) doubles)
+        G2.set_local_poses(xl)           # host -> device ((x,y,cos,sin) doubles of this rank's rows)
         G2.optimize()
-        G2.poses(keys_buf, x)            # device -> host, into the same host buffers
+        G2.local_poses(xyt_out=xl, want_keys=False)   # device -> host, into the same host buffer
     barrier()
     e2e_s = vmax(time.time() - t0)
     e2e = K / e2e_s
@@ -482,7 +487,9 @@ def run_ours(args):
                                   "together and 'pcg_dir' = k_dir_coarse, against SURVEY 8(d)'s bytes of the update and the "
                                   "direction alone (per-kernel times: profiles/r2_launches_C3_1M.csv)" if two_level else "")},
             "cpu_baseline": cpu,
-            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step,
+                    "calls": "gs_set_local_poses + gs_optimize + gs_get_local_poses per step on every rank (host buffers; bytes "
+                             "summed over ranks, counted by the library)"},
             "gpu_launches": int(launches), "clocks": clocks,
             "breakdown_ms_per_step": {"linearize_assemble": ms_lin / K, "pcg": ms_solve / K, "update": ms_upd / K}}
     line.update(extra)

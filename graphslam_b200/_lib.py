@@ -75,6 +75,9 @@ SIGNATURES = {
     "gs_get_pose": (C.c_int, [C.c_void_p, C.c_uint64, c_double_p]),
     "gs_get_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p, C.POINTER(C.c_size_t)]),
     "gs_set_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p]),
+    "gs_local_range": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "gs_get_local_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_u64_p, c_double_p, C.POINTER(C.c_size_t)]),
+    "gs_set_local_poses": (C.c_int, [C.c_void_p, C.c_size_t, c_double_p]),
     "gs_chi2": (C.c_int, [C.c_void_p, c_double_p]),
     "gs_num_vertices": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
     "gs_get_transfer_bytes": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),

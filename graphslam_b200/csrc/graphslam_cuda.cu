@@ -1939,6 +1939,106 @@ gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, siz
   return on_exception(g);
 }
 
+// ---- rank-local pose transfers: what a rank owns, and nothing else, crosses its PCIe link ------------------------
+gs_status gs_local_range(gs_graph* g, size_t* first, size_t* count) try {
+  if (!g) return GS_EINVAL;
+  if (g->topo_dirty) return g->fail(GS_EINVAL, "gs_local_range: the structure is not built (call gs_prepare after the last gs_add_*)");
+  if (first) *first = (size_t)g->S.v0;
+  if (count) *count = (size_t)g->n_own;
+  return GS_OK;
+} catch (...) {
+  return on_exception(g);
+}
+
+gs_status gs_get_local_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* count) try {
+  if (!g) return GS_EINVAL;
+  if (g->topo_dirty) return g->fail(GS_EINVAL, "gs_get_local_poses: the structure is not built (call gs_prepare after the last gs_add_*)");
+  const size_t n = (size_t)g->n_own, v0 = (size_t)g->S.v0;
+  if (count) *count = n;
+  if (!keys && !xyt) return GS_OK;
+  if (cap < n) return g->fail(GS_EINVAL, "capacity %zu < %zu owned vertices", cap, n);
+  if (keys) {
+    gs::parallel_for(n, [g, keys, v0](size_t b, size_t e) {
+      for (size_t l = b; l < e; ++l) keys[l] = g->keys[g->dense2ins[v0 + l]];
+    });
+  }
+  if (!xyt) return GS_OK;
+  if (g->device_values_valid && !g->host_values_fresh) {
+    // the optimised values live on the device: this rank's rows only, through the pinned stage
+    if (gs_status s = ensure_stage(g, std::max<size_t>(n, 1))) return s;
+    double4* tmp = g->h_stage;
+    if (n) GS_CUDA(g, cudaMemcpyAsync(tmp, g->d_pose.p, sizeof(double4) * n, cudaMemcpyDeviceToHost, g->stream));
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+    g->d2h_bytes += sizeof(double4) * (double)n;
+    gs::parallel_for(n, [tmp, xyt](size_t b, size_t e) {
+      for (size_t l = b; l < e; ++l) {
+        xyt[3 * l] = tmp[l].x;
+        xyt[3 * l + 1] = tmp[l].y;
+        xyt[3 * l + 2] = std::atan2(tmp[l].w, tmp[l].z);
+      }
+    });
+  } else {
+    const bool wrapped = g->theta_wrapped;
+    gs::parallel_for(n, [g, xyt, v0, wrapped](size_t b, size_t e) {
+      for (size_t l = b; l < e; ++l) {
+        const int k = g->dense2ins[v0 + l];
+        const double th = g->xyt[3 * k + 2];
+        xyt[3 * l] = g->xyt[3 * k];
+        xyt[3 * l + 1] = g->xyt[3 * k + 1];
+        xyt[3 * l + 2] = (wrapped || (th > -M_PI && th <= M_PI)) ? th : std::atan2(std::sin(th), std::cos(th));
+      }
+    });
+  }
+  return GS_OK;
+} catch (...) {
+  return on_exception(g);
+}
+
+gs_status gs_set_local_poses(gs_graph* g, size_t n, const double* xyt) try {
+  if (!g || (n && !xyt)) return GS_EINVAL;
+  if (g->topo_dirty) return g->fail(GS_EINVAL, "gs_set_local_poses: the structure is not built (call gs_prepare after the last gs_add_*)");
+  if (n != (size_t)g->n_own) return g->fail(GS_EINVAL, "gs_set_local_poses: %zu poses given, this rank owns %d", n, g->n_own);
+  {
+    // the other rows of the device copy must exist (a graph whose values were only ever on the host)
+    if (!g->device_values_valid)
+      if (gs_status s = upload_values(g)) return s;
+    // one pass: validate and convert into the pinned stage; nothing of the graph is touched before every value passed
+    if (gs_status s = ensure_stage(g, std::max<size_t>(n, 1))) return s;
+    double4* tmp = g->h_stage;
+    std::atomic<size_t> bad(n);
+    gs::parallel_for(n, [&bad, tmp, xyt](size_t b, size_t e) {
+      for (size_t l = b; l < e; ++l) {
+        const double x = xyt[3 * l], y = xyt[3 * l + 1], th = xyt[3 * l + 2];
+        if (!(std::isfinite(x) && std::isfinite(y) && std::isfinite(th))) {
+          size_t cur = bad.load();
+          while (l < cur && !bad.compare_exchange_weak(cur, l)) {
+          }
+          return;
+        }
+        tmp[l] = make_double4(x, y, std::cos(th), std::sin(th));
+      }
+    });
+    // several ranks: the call is collective, so a rank with a bad value still takes part in the exchange below with
+    // its old rows and reports afterwards
+    const bool ok = bad.load() >= n;
+    if (!ok && g->world == 1) return g->fail(GS_EINVAL, "non-finite pose in owned row %zu", bad.load());
+    if (ok) {
+      if (n) GS_CUDA(g, cudaMemcpyAsync(g->d_pose.p, tmp, sizeof(double4) * n, cudaMemcpyHostToDevice, g->stream));
+      g->h2d_bytes += sizeof(double4) * (double)n;
+    }
+    // ghost rows: the neighbours' new values, device to device
+    if (gs_status s = halo_exchange(g, reinterpret_cast<double*>(g->d_pose.p), 4)) return s;
+    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+    g->host_values_fresh = false;   // the host copy is stale on every rank (gs_get_poses / gs_prepare bring it back)
+    g->device_values_valid = true;
+    g->system_valid = false;
+    if (!ok) return g->fail(GS_EINVAL, "non-finite pose in owned row %zu (the rank's rows were left as they were)", bad.load());
+  }
+  return GS_OK;
+} catch (...) {
+  return on_exception(g);
+}
+
 gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt) try {
   if (!g || (n && (!keys || !xyt))) return GS_EINVAL;
   if (gs_status s = download_values(g)) return s;

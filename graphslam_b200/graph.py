@@ -221,6 +221,33 @@ class Graph:
         xyt = _f64(xyt, (-1, 3))
         self._ck(self._lib.gs_set_poses(self._h, keys.shape[0], keys.ctypes.data_as(c_u64_p), _dp(xyt)))
 
+    # -- rank-local transfers (several GPUs: a rank moves its own rows only; see include/graphslam_cuda.h)
+    def local_range(self):
+        """(first, count): the rows of the sorted-key order this rank owns (all of them on one GPU)."""
+        first, count = C.c_size_t(), C.c_size_t()
+        self._ck(self._lib.gs_local_range(self._h, C.byref(first), C.byref(count)))
+        return first.value, count.value
+
+    def local_poses(self, keys_out=None, xyt_out=None, want_keys=True):
+        """(keys, xyt) of the owned rows; not collective.  Buffers as in poses(); want_keys=False skips the keys (a caller
+        that reads the poses every step knows them from its first read) and returns (None, xyt)."""
+        _, n = self.local_range()
+        keys = None
+        if want_keys:
+            keys = keys_out if keys_out is not None else np.zeros(n, dtype=np.uint64)
+            assert keys.dtype == np.uint64 and keys.shape == (n,) and keys.flags.c_contiguous
+        xyt = xyt_out if xyt_out is not None else np.zeros((n, 3))
+        assert xyt.dtype == np.float64 and xyt.shape == (n, 3) and xyt.flags.c_contiguous
+        m = C.c_size_t()
+        self._ck(self._lib.gs_get_local_poses(self._h, n, keys.ctypes.data_as(c_u64_p) if want_keys else None, _dp(xyt),
+                                              C.byref(m)))
+        return keys, xyt
+
+    def set_local_poses(self, xyt):
+        """New values for the owned rows (collective on several GPUs: the ghost rows are exchanged on the device)."""
+        xyt = _f64(xyt, (-1, 3))
+        self._ck(self._lib.gs_set_local_poses(self._h, xyt.shape[0], _dp(xyt)))
+
     # -- parity hooks
     def pattern(self):
         nnzb = C.c_size_t()

@@ -178,6 +178,21 @@ gs_status gs_get_pose(gs_graph* g, uint64_t key, double out_xyt[3]);
 gs_status gs_get_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* n);
 /* overwrite current values (initial.update)                     */
 gs_status gs_set_poses(gs_graph* g, size_t n, const uint64_t* keys, const double* xyt);
+
+/* Rank-local transfers (several GPUs: what scales; one GPU: the same as the calls above without the key lookups).
+ * The library keeps the poses in sorted-key ("dense") order and a rank owns a contiguous range of them.  With
+ * gs_get_poses every rank receives ALL poses (a broadcast per rank, 32 N bytes over every rank's PCIe link, N
+ * conversions on every rank's host); with these a rank moves its own rows only — 32 N / P bytes each way — and the
+ * neighbours' rows it needs as ghosts are refreshed device to device.  Valid once the structure is built (gs_prepare /
+ * gs_optimize after the last gs_add_*).  No counterpart in graph.cpp (one process, one optimiser); the write-back loop
+ * graph.cpp:122-125 maps to gs_get_local_poses on each rank. */
+/* the dense rows [first, first + count) this rank owns */
+gs_status gs_local_range(gs_graph* g, size_t* first, size_t* count);
+/* keys and (x, y, theta) of the owned rows, in dense order; keys / xyt may be NULL; NOT collective */
+gs_status gs_get_local_poses(gs_graph* g, size_t cap, uint64_t* keys, double* xyt, size_t* count);
+/* new values for the owned rows (n == count, dense order).  COLLECTIVE on several GPUs: every rank sets its rows, then
+ * the ghost rows are exchanged.  Non-finite input: GS_EINVAL, the rank's rows stay as they were. */
+gs_status gs_set_local_poses(gs_graph* g, size_t n, const double* xyt);
 /* 2 * graph.error(values) at the current values                 */
 gs_status gs_chi2(gs_graph* g, double* chi2);
 gs_status gs_num_vertices(const gs_graph* g, size_t* n);

@@ -39,7 +39,24 @@ def main():
     G.set_poses(g.keys, g.init)
     G.set_params(diagonal_damping=1)
     st3 = G.optimize()
+    # rank-local transfers: a rank reads its own rows (same bits as its slice of the collective read), writes them back
+    # displaced (the ghost rows follow on the device), and the next solve must be the one a single GPU runs after
+    # gs_set_poses with the same values
+    _, x3 = G.poses()
+    first, count = G.local_range()
+    lk, lx = G.local_poses()
+    local_ok = np.array_equal(lk, np.sort(g.keys)[first:first + count]) and np.array_equal(lx, x3[first:first + count])
+    shift = np.array([0.01, -0.02, 0.003])
+    G.set_local_poses(lx + shift)
+    _, x4 = G.poses()                        # collective: every rank sees everybody's new rows
+    d4 = x4 - (x3 + shift)
+    d4[:, 2] = (d4[:, 2] + np.pi) % (2 * np.pi) - np.pi          # theta comes back in (-pi, pi]
+    local_ok = local_ok and float(np.abs(d4).max()) <= 1e-12
+    st4 = G.optimize()
     G.close()
+    cnt = torch.tensor([count, 1 if local_ok else 0], device="cuda")
+    dist.all_reduce(cnt)
+    local_ok = int(cnt[0].item()) == g.n and int(cnt[1].item()) == dist.get_world_size()   # the ranges tile the rows
     ok = True
     if rank == 0:
         # the single-GPU reference runs the same preconditioner as the ranks (flag 32 = block-Jacobi only): the two
@@ -56,9 +73,15 @@ def main():
             G1.set_poses(g.keys, g.init)
             G1.set_params(diagonal_damping=1)
             st1c = G1.optimize()
-        ok = (st3["chi2_final"] == st1c["chi2_final"] and st3["pcg_iterations_total"] == st1c["pcg_iterations_total"] and
+            _, y3 = G1.poses()
+            G1.set_poses(np.sort(g.keys), y3 + shift)
+            st1d = G1.optimize()
+        ok = (local_ok and st4["chi2_final"] == st1d["chi2_final"] and st4["pcg_iterations_total"] == st1d["pcg_iterations_total"] and
+              st3["chi2_final"] == st1c["chi2_final"] and st3["pcg_iterations_total"] == st1c["pcg_iterations_total"] and
               near == near1 and np.array_equal(cov, cov1) and chi0 == chi0_1 and np.array_equal(x, x1) and np.array_equal(errors, e1) and tries.tolist() == t1.tolist()
               and st["pcg_iterations_total"] == st1["pcg_iterations_total"] and st2["chi2_final"] == st1b["chi2_final"])
+        print(f"[mgpu] local transfers ok={local_ok} st4 {st4['chi2_final']!r}/{st4['pcg_iterations_total']} 1 GPU {st1d['chi2_final']!r}/"
+              f"{st1d['pcg_iterations_total']}", flush=True)
         print(f"[mgpu] world={dist.get_world_size()} N={g.n} iterations={st['iterations']} pcg={st['pcg_iterations_total']} "
               f"chi2 {st['chi2_initial']:.6g}->{st['chi2_final']:.6g} bitwise_equal_to_single_gpu={ok} "
               f"ms_solve {st['ms_solve']:.1f} (1 GPU: {st1['ms_solve']:.1f})", flush=True)

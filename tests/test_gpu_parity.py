@@ -212,6 +212,39 @@ def test_incremental_warm_start_matches_oracle():
     assert _pose_diff(x, x2) <= POSE_ATOL
 
 
+def test_rank_local_pose_transfers_on_one_gpu():
+    """gs_local_range / gs_get_local_poses / gs_set_local_poses: on one GPU the rank owns every row, the local read is
+    the global read, and a solve after a local write is the solve after gs_set_poses with the same values."""
+    g = synth.config("C2", n=3000)
+    with _load(g) as G, _load(g) as H:
+        with pytest.raises(RuntimeError):
+            G.local_range()                                   # structure not built yet
+        G.prepare()
+        assert G.local_range() == (0, g.n)
+        lk, lx = G.local_poses()                              # values still on the host
+        k0, x0 = G.poses()
+        assert np.array_equal(lk, k0) and np.array_equal(lx, x0)
+        G.optimize()
+        H.optimize()
+        k1, x1 = G.poses()
+        lk, lx = G.local_poses()                              # values on the device
+        assert np.array_equal(lk, k1) and np.array_equal(lx, x1)
+        moved = x1 + np.array([0.02, -0.01, 0.004])
+        G.set_local_poses(moved)
+        H.set_poses(k1, moved)
+        assert _pose_diff(G.poses()[1], moved) <= 1e-12
+        sg, sh = G.optimize(), H.optimize()
+        assert sg["chi2_final"] == sh["chi2_final"] and sg["pcg_iterations_total"] == sh["pcg_iterations_total"]
+        assert np.array_equal(G.poses()[1], H.poses()[1])
+        bad = moved.copy()
+        bad[7, 1] = np.nan
+        with pytest.raises(RuntimeError):
+            G.set_local_poses(bad)
+        with pytest.raises(RuntimeError):
+            G.set_local_poses(moved[:-1])
+        assert np.array_equal(G.poses()[1], H.poses()[1])     # refused writes changed nothing
+
+
 def test_graph_node_verbs_replay():
     """prior_factor / new_factor / loop_factor / solve in the reference's call order (graph.cpp:180-200)."""
     g = synth.manhattan(300, seed=5, target_edges=420)
