@@ -335,6 +335,7 @@ def run_ours(args):
     launches = vsum(float(sum(s["gpu_launches"] for s in stats)))
     ms_lin = vmax(sum(s["ms_linearize"] for s in stats))
     ms_solve = vmax(sum(s["ms_solve"] for s in stats))
+    ms_coarse = vmax(sum(s.get("ms_coarse_setup", 0.0) for s in stats))
     ms_upd = vmax(sum(s["ms_update"] for s in stats))
     waits = None
     if world > 1:   # peer-memory path: what CTA 0 of this rank spent waiting for other GPUs, per PCG iteration (SM clock ticks)
@@ -491,7 +492,8 @@ def run_ours(args):
                     "calls": "gs_set_local_poses + gs_optimize + gs_get_local_poses per step on every rank (host buffers; bytes "
                              "summed over ranks, counted by the library)"},
             "gpu_launches": int(launches), "clocks": clocks,
-            "breakdown_ms_per_step": {"linearize_assemble": ms_lin / K, "pcg": ms_solve / K, "update": ms_upd / K}}
+            "breakdown_ms_per_step": {"linearize_assemble": ms_lin / K, "pcg": ms_solve / K, "update": ms_upd / K,
+                                      "coarse_setup_inside_pcg": ms_coarse / K}}
     line.update(extra)
     if rank == 0:
         print(json.dumps(line), flush=True)

@@ -36,7 +36,7 @@ class GsStats(C.Structure):
                 ("ms_total", C.c_double), ("edges_per_sec", C.c_double), ("gn_iters_per_sec", C.c_double),
                 ("gpu_launches", C.c_double), ("ms_device", C.c_double), ("h2d_bytes", C.c_double),
                 ("d2h_bytes", C.c_double), ("p2p_wait_ticks", C.c_double * 3), ("p2p_waits", C.c_double),
-                ("ms_structure_parts", C.c_double * 4)]
+                ("ms_structure_parts", C.c_double * 4), ("ms_coarse_setup", C.c_double)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("ms_structure_parts", "p2p_wait_ticks")}

@@ -19,7 +19,8 @@ NVCC_FLAGS = [
     "--fmad=true",                       # FP64 FMA contraction on; never --use_fast_math
     "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function,-Wno-unknown-pragmas",
     "-shared", "-cudart", "static",
-    "-lcusolver",                        # dense Cholesky + inverse of the two-level preconditioner's coarse matrix (setup only)
+    "-lcusolver", "-lcublas",            # dense Cholesky (potrf) and inverse (trsm + syrk) of the two-level preconditioner's
+                                         # coarse matrix (setup only)
 ]
 
 

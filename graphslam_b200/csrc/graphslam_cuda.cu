@@ -11,6 +11,7 @@
 // exchange of p (per SpMV) and of the poses (per retract), and all-gathers of the segment sums of
 // the dot products, which every rank then adds in the same fixed order.
 #include <cuda_runtime.h>
+#include <cublas_v2.h>
 #include <cusolverDn.h>
 #include <nvtx3/nvToolsExt.h>
 
@@ -190,6 +191,7 @@ struct gs_graph {
   DevBuf<double> d_cvec, d_mu, d_cpart, d_R, d_G, d_E, d_chol_work, d_basis;
   DevBuf<int> d_chol_info;
   DevBuf<double2> d_agg_ref;
+  DevBuf<double> d_Ework;                 // m x m scratch of coarse_inverse (L^-1)
   DevBuf<int> d_coarse_seg_row;           // [kSegments + 1] rows of the coarse vector per fixed reduction segment (3 x seg_agg)
   int chol_lwork = 0;
   int agg_a0 = 0, agg_own = 0;            // this rank's aggregates [agg_a0, agg_a0 + agg_own)
@@ -317,6 +319,7 @@ bool coarse_active(const gs_graph* g) { return g->coarse && !g->prm.diagonal_dam
 struct SolverPool {
   std::mutex mu;
   cusolverDnHandle_t h[64] = {nullptr};
+  cublasHandle_t hb[64] = {nullptr};
 };
 SolverPool& solver_pool() {
   static SolverPool p;
@@ -328,6 +331,42 @@ cusolverDnHandle_t device_cusolver() {   // call with solver_pool().mu held
   SolverPool& p = solver_pool();
   if (!p.h[dev] && cusolverDnCreate(&p.h[dev]) != CUSOLVER_STATUS_SUCCESS) p.h[dev] = nullptr;
   return p.h[dev];
+}
+
+cublasHandle_t device_cublas() {   // call with solver_pool().mu held
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  SolverPool& p = solver_pool();
+  if (!p.hb[dev] && cublasCreate(&p.hb[dev]) != CUBLAS_STATUS_SUCCESS) p.hb[dev] = nullptr;
+  return p.hb[dev];
+}
+
+// E (lower triangle of an SPD matrix, column-major, m x m, in Em) -> E^-1 (both triangles) in Em; X: m x m scratch.
+// Cholesky by cuSOLVER, then E^-1 = L^-T L^-1 with L^-1 = trsm(L, I) and one syrk — 1.2 + 2.6 + 0.9 ms at m = 3072 on a
+// B200, where cusolverDnDpotri alone takes 7.9 ms (microbenchmark recorded in profiles/r2_summary.md).  Call with
+// solver_pool().mu held.  `info` receives potrf's status word (0 = positive definite) after a stream synchronisation.
+gs_status coarse_inverse(gs_graph* g, int m, double* Em, double* X, int* info) {
+  cusolverDnHandle_t hs = device_cusolver();
+  cublasHandle_t hb = device_cublas();
+  if (!hs || !hb || cusolverDnSetStream(hs, g->stream) != CUSOLVER_STATUS_SUCCESS || cublasSetStream(hb, g->stream) != CUBLAS_STATUS_SUCCESS)
+    return g->fail(GS_ECUDA, "cuSOLVER / cuBLAS handle unavailable");
+  if (cusolverDnDpotrf(hs, CUBLAS_FILL_MODE_LOWER, m, Em, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) != CUSOLVER_STATUS_SUCCESS)
+    return g->fail(GS_ECUDA, "cusolverDnDpotrf failed");
+  *info = 0;
+  GS_CUDA(g, cudaMemcpyAsync(info, g->d_chol_info.p, sizeof(int), cudaMemcpyDeviceToHost, g->stream));
+  GS_CUDA(g, cudaStreamSynchronize(g->stream));
+  if (*info != 0) return GS_OK;
+  const size_t mm = (size_t)m * m;
+  const double one = 1.0, zero = 0.0;
+  GS_CUDA(g, cudaMemsetAsync(X, 0, sizeof(double) * mm, g->stream));
+  gs::k_set_diagonal<<<(unsigned)((m + gs::kThreads - 1) / gs::kThreads), gs::kThreads, 0, g->stream>>>(X, m, 1.0);
+  if (cublasDtrsm(hb, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, m, m, &one, Em, m, X, m) !=
+          CUBLAS_STATUS_SUCCESS ||
+      cublasDsyrk(hb, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, m, m, &one, X, m, &zero, Em, m) != CUBLAS_STATUS_SUCCESS)
+    return g->fail(GS_ECUDA, "cuBLAS trsm / syrk failed");
+  gs::k_symmetrize<<<(unsigned)((mm + gs::kThreads - 1) / gs::kThreads), gs::kThreads, 0, g->stream>>>(Em, m);
+  g->launches += 3;
+  return GS_OK;
 }
 
 gs::CoarseView coarse_view(gs_graph* g) {
@@ -997,7 +1036,8 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     const int spr = gs::kSegments / g->world;
     g->agg_a0 = A.seg_agg[g->rank * spr];
     g->agg_own = A.seg_agg[(g->rank + 1) * spr] - g->agg_a0;
-    std::vector<int> l_of(A.agg_of.begin() + S.v0, A.agg_of.begin() + S.v1);
+    std::vector<int> l_of(A.agg_of.begin() + S.v0, A.agg_of.begin() + S.v1);   // owned rows, then ghost rows
+    for (int gr : S.ghosts) l_of.push_back(A.agg_of[gr]);
     std::vector<int> l_ptr(g->agg_own + 1), l_rows;
     const int q0 = A.ptr[g->agg_a0];
     for (int a = 0; a <= g->agg_own; ++a) l_ptr[a] = A.ptr[g->agg_a0 + a] - q0;
@@ -1024,17 +1064,17 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     GS_CUDA(g, g->d_pose_lin.alloc(std::max(g->n_loc, 1)));
     GS_CUDA(g, g->d_chol_info.alloc(1));
     GS_CUDA(g, g->d_agg_ref.alloc((size_t)A.n_agg));
+    GS_CUDA(g, g->d_Ework.alloc(m * m));
     std::lock_guard<std::mutex> lock(solver_pool().mu);
     cusolverDnHandle_t hs = device_cusolver();
     if (!hs) return g->fail(GS_ECUDA, "cusolverDnCreate failed");
-    int l1 = 0, l2 = 0;
-    if (cusolverDnDpotrf_bufferSize(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l1) != CUSOLVER_STATUS_SUCCESS ||
-        cusolverDnDpotri_bufferSize(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l2) != CUSOLVER_STATUS_SUCCESS)
+    int l1 = 0;
+    if (cusolverDnDpotrf_bufferSize(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, &l1) != CUSOLVER_STATUS_SUCCESS)
       return g->fail(GS_ECUDA, "cusolver workspace query failed");
-    g->chol_lwork = std::max(l1, l2);
+    g->chol_lwork = l1;
     GS_CUDA(g, g->d_chol_work.alloc((size_t)std::max(g->chol_lwork, 1)));
-    // one Cholesky + inverse of an identity of this size now: cuSOLVER loads its kernels on first use (hundreds of
-    // milliseconds), which belongs to the structure phase, not to the first solve
+    // one Cholesky + inverse of an identity of this size now: cuSOLVER and cuBLAS load their kernels on first use
+    // (hundreds of milliseconds), which belongs to the structure phase, not to the first solve
     {
       int dev = 0;
       GS_CUDA(g, cudaGetDevice(&dev));
@@ -1042,13 +1082,10 @@ gs_status prepare(gs_graph* g, double* ms_out) {
       if (dev >= 0 && dev < 64 && !warmed[dev]) {
         GS_CUDA(g, cudaMemsetAsync(g->d_E.p, 0, sizeof(double) * m * m, g->stream));
         gs::k_set_diagonal<<<(unsigned)((m + gs::kThreads - 1) / gs::kThreads), gs::kThreads, 0, g->stream>>>(g->d_E.p, (int)m, 1.0);
-        if (cusolverDnSetStream(hs, g->stream) != CUSOLVER_STATUS_SUCCESS ||
-            cusolverDnDpotrf(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
-                CUSOLVER_STATUS_SUCCESS ||
-            cusolverDnDpotri(hs, CUBLAS_FILL_MODE_LOWER, (int)m, g->d_E.p, (int)m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
-                CUSOLVER_STATUS_SUCCESS)
-          return g->fail(GS_ECUDA, "cuSOLVER warm-up failed");
+        int info = 0;
+        if (gs_status s = coarse_inverse(g, (int)m, g->d_E.p, g->d_Ework.p, &info)) return s;
         GS_CUDA(g, cudaStreamSynchronize(g->stream));
+        if (info != 0) return g->fail(GS_ECUDA, "cuSOLVER warm-up failed");
         warmed[dev] = true;
       }
     }
@@ -1130,15 +1167,21 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
     const int nc9 = A.n_colors * 9;
     const int own = std::max(g->agg_own, 1);
     gs::k_agg_ref<<<(own + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_ref.p);
+    // several ranks: every rank learns the reference position of every aggregate once, and then forms the ghost rows of
+    // each basis vector itself (a ghost row's block of W follows from its pose, which the rank holds, and its
+    // aggregate's reference) — no halo exchange and no all-gather per product
+    if (gs_status s = coarse_gather(g, reinterpret_cast<double*>(g->d_agg_ref.p), 2)) return s;
+    const int grid_loc = (g->n_loc + gs::kThreads - 1) / gs::kThreads;
     for (int c = 0; c < A.n_colors; ++c)
       for (int mode = 0; mode < 3; ++mode) {
-        gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, c, mode, g->d_basis.p);
-        if (gs_status s = launch_spmv(g, g->d_basis.p, g->d_Ap.p, 1)) return s;   // several ranks: halo exchange of the basis vector
+        gs::k_basis_vec<<<std::max(grid_loc, 1), gs::kThreads, 0, g->stream>>>(cv, g->n_loc, g->d_agg_color.p, c, mode, g->d_basis.p);
+        gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->d_basis.p, g->d_basis.p + 3 * (size_t)g->n_own,
+                                                                 g->d_Ap.p, reduce_ctx(g, 0), 1);
         if (g->agg_own)
           gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_Ap.p, g->d_sc.p, 0, g->d_R.p, nc9, (c * 3 + mode) * 3);
       }
     for (int mode = 0; mode < 3; ++mode) {
-      gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_color.p, -1, mode, g->d_basis.p);
+      gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->n_own, g->d_agg_color.p, -1, mode, g->d_basis.p);
       if (g->agg_own) gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_basis.p, g->d_sc.p, 0, g->d_G.p, 9, mode * 3);
     }
     // every rank needs the whole coarse matrix: its aggregates' rows of R and G are contiguous (aggregate-major)
@@ -1154,23 +1197,11 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
     gs::k_coarse_E<<<(total + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(
         g->d_R.p, g->d_G.p, g->d_nbr_of_color.p, A.n_agg, A.n_colors, lambda, g->d_E.p);
     std::lock_guard<std::mutex> lock(solver_pool().mu);
-    cusolverDnHandle_t hs = device_cusolver();
-    if (!hs || cusolverDnSetStream(hs, g->stream) != CUSOLVER_STATUS_SUCCESS) return g->fail(GS_ECUDA, "cuSOLVER handle unavailable");
-    if (cusolverDnDpotrf(hs, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
-        CUSOLVER_STATUS_SUCCESS)
-      return g->fail(GS_ECUDA, "cusolverDnDpotrf failed");
     int info = 0;
-    GS_CUDA(g, cudaMemcpyAsync(&info, g->d_chol_info.p, sizeof(int), cudaMemcpyDeviceToHost, g->stream));
-    GS_CUDA(g, cudaStreamSynchronize(g->stream));
+    if (gs_status s = coarse_inverse(g, m, g->d_E.p, g->d_Ework.p, &info)) return s;
     if (info != 0)
       return g->fail(GS_ENAN, "coarse matrix of the two-level preconditioner is not positive definite (leading minor %d): is the "
                               "graph anchored by a prior?", info);
-    if (cusolverDnDpotri(hs, CUBLAS_FILL_MODE_LOWER, m, g->d_E.p, m, g->d_chol_work.p, g->chol_lwork, g->d_chol_info.p) !=
-        CUSOLVER_STATUS_SUCCESS)
-      return g->fail(GS_ECUDA, "cusolverDnDpotri failed");
-    const size_t mm = (size_t)m * m;
-    gs::k_symmetrize<<<(unsigned)((mm + gs::kThreads - 1) / gs::kThreads), gs::kThreads, 0, g->stream>>>(g->d_E.p, m);
-    g->launches += 2;
     g->coarse_lambda = lambda;
   }
   GS_CUDA(g, cudaStreamSynchronize(g->stream));
@@ -1770,6 +1801,7 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   g->tr_lambda.clear();
   g->tr_tries.clear();
   g->launches = 0;
+  g->ms_coarse_setup = 0.0;
   for (double& w : g->p2p_wait) w = 0.0;
 
   // error at the initial values
@@ -1880,6 +1912,7 @@ gs_status gs_optimize(gs_graph* g, gs_stats* st) try {
   const double t_iter = local.ms_total - local.ms_structure;
   local.gn_iters_per_sec = t_iter > 0 ? local.outer_loops / (t_iter * 1e-3) : 0.0;
   local.gpu_launches = (double)g->launches;
+  local.ms_coarse_setup = g->ms_coarse_setup;
   GS_CUDA(g, cudaEventRecord(g->ev_end, g->stream));
   GS_CUDA(g, cudaEventSynchronize(g->ev_end));
   {

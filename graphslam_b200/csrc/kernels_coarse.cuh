@@ -27,11 +27,11 @@ namespace gs {
 // Aggregates never cross segment boundaries, so a rank owns the contiguous range [a0, a0 + n_agg_own) of the global
 // aggregate numbering; coarse vectors (3 per aggregate) are indexed globally, lists and rows locally.
 struct CoarseView {
-  const int* agg_of;        // per owned row: GLOBAL aggregate
+  const int* agg_of;        // per local row (owned rows, then ghost rows): GLOBAL aggregate
   const int* agg_ptr;       // per OWNED aggregate (local index): range in agg_rows
   const int* agg_rows;      // local rows, ascending; the first one is the aggregate's reference row
   const double4* pose;      // the linearisation point
-  const double2* ref;       // per global aggregate: position of its reference row (only the owned entries are used)
+  const double2* ref;       // per global aggregate: position of its reference row (several ranks: gathered per linearisation)
   int a0;                   // first owned aggregate
   int n_agg_own;
   int n_agg;                // global
@@ -68,11 +68,11 @@ __global__ void __launch_bounds__(kThreads) k_agg_ref(const CoarseView a, double
   ref[a.a0 + g] = make_double2(p.x, p.y);
 }
 
-// color < 0: every aggregate
-__global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, const int* __restrict__ agg_color, int color, int mode,
-                                                         double* __restrict__ v) {
+// color < 0: every aggregate.  rows = n_own, or n_own + n_ghost when the product that follows reads the ghost rows
+__global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, int rows, const int* __restrict__ agg_color, int color,
+                                                         int mode, double* __restrict__ v) {
   const int r = blockIdx.x * kThreads + threadIdx.x;
-  if (r >= a.n_own) return;
+  if (r >= rows) return;
   const int g = a.agg_of[r];
   double o[3] = {0.0, 0.0, 0.0};
   if (color < 0 || agg_color[g] == color) {

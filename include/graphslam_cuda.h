@@ -112,6 +112,8 @@ typedef struct gs_stats {
   double p2p_waits;          /*   update / direction kernels during this call, and the iterations they cover        */
   double ms_structure_parts[4]; /* ms_structure split: host structure build, staging + upload, communicator setup
                                    (multi-GPU: peer-memory windows, first NCCL exchanges), CUDA-graph capture        */
+  double ms_coarse_setup;    /* two-level preconditioner: coarse-matrix products, Cholesky and inverse (host wall time,
+                                part of ms_solve); does not shrink with the number of GPUs                            */
 } gs_stats;
 
 void gs_default_params(gs_params* p);
