@@ -1154,8 +1154,8 @@ gs_status coarse_gather(gs_graph* g, double* vec, int width) {
 
 // Two-level preconditioner, setup for the solve with damping `lambda` at the current linearisation:
 //   E0 = W^T H W by columns — one undamped product H w per (colour, rigid mode), restricted per aggregate — and
-//   G = W^T W, once per linearisation;  E = E0 + lambda G, Cholesky-factored and inverted (cuSOLVER potrf / potri: a
-//   dense 3 n_agg square, <= 3072), once per lambda.  d_E then holds E^-1 in full.
+//   G = W^T W, once per linearisation;  E = E0 + lambda G, Cholesky-factored and inverted (coarse_inverse: a dense
+//   3 n_agg square, 3072 on C3, at most 12,288), once per lambda.  d_E then holds E^-1 in full.
 gs_status coarse_setup(gs_graph* g, double lambda) {
   NvtxRange nvtx_range("gs:coarse setup");
   const double t0 = now_ms();

@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kThreads) k_set_diagonal(double* __restrict__ 
   if (i < m) Em[(size_t)i * m + i] = v;
 }
 
-// potri leaves one triangle of E^-1: mirror it (column-major, lower -> upper)
+// syrk leaves the lower triangle of E^-1: mirror it (column-major, lower -> upper)
 __global__ void __launch_bounds__(kThreads) k_symmetrize(double* __restrict__ Em, int m) {
   const size_t t = (size_t)blockIdx.x * kThreads + threadIdx.x;
   if (t >= (size_t)m * m) return;
