@@ -192,6 +192,7 @@ struct gs_graph {
   DevBuf<int> d_chol_info;
   DevBuf<double2> d_agg_ref;
   DevBuf<double> d_Ework;                 // m x m scratch of coarse_inverse (L^-1)
+  DevBuf<double> d_Y;                     // 9 doubles per owned row: H W_c of one colour (coarse set-up)
   DevBuf<int> d_coarse_seg_row;           // [kSegments + 1] rows of the coarse vector per fixed reduction segment (3 x seg_agg)
   int chol_lwork = 0;
   int agg_a0 = 0, agg_own = 0;            // this rank's aggregates [agg_a0, agg_a0 + agg_own)
@@ -1061,6 +1062,7 @@ gs_status prepare(gs_graph* g, double* ms_out) {
     GS_CUDA(g, g->d_G.alloc(3 * m));
     GS_CUDA(g, g->d_E.alloc(m * m));
     GS_CUDA(g, g->d_basis.alloc(nl3));
+    GS_CUDA(g, g->d_Y.alloc(3 * n3));
     GS_CUDA(g, g->d_pose_lin.alloc(std::max(g->n_loc, 1)));
     GS_CUDA(g, g->d_chol_info.alloc(1));
     GS_CUDA(g, g->d_agg_ref.alloc((size_t)A.n_agg));
@@ -1167,19 +1169,13 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
     const int nc9 = A.n_colors * 9;
     const int own = std::max(g->agg_own, 1);
     gs::k_agg_ref<<<(own + gs::kThreads - 1) / gs::kThreads, gs::kThreads, 0, g->stream>>>(cv, g->d_agg_ref.p);
-    // several ranks: every rank learns the reference position of every aggregate once, and then forms the ghost rows of
-    // each basis vector itself (a ghost row's block of W follows from its pose, which the rank holds, and its
-    // aggregate's reference) — no halo exchange and no all-gather per product
+    // several ranks: every rank learns the reference position of every aggregate once; the products below then form the
+    // blocks of W of ghost columns themselves (from the ghost poses the rank holds) — no exchange per product
     if (gs_status s = coarse_gather(g, reinterpret_cast<double*>(g->d_agg_ref.p), 2)) return s;
-    const int grid_loc = (g->n_loc + gs::kThreads - 1) / gs::kThreads;
-    for (int c = 0; c < A.n_colors; ++c)
-      for (int mode = 0; mode < 3; ++mode) {
-        gs::k_basis_vec<<<std::max(grid_loc, 1), gs::kThreads, 0, g->stream>>>(cv, g->n_loc, g->d_agg_color.p, c, mode, g->d_basis.p);
-        gs::k_spmv<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), g->d_basis.p, g->d_basis.p + 3 * (size_t)g->n_own,
-                                                                 g->d_Ap.p, reduce_ctx(g, 0), 1);
-        if (g->agg_own)
-          gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_Ap.p, g->d_sc.p, 0, g->d_R.p, nc9, (c * 3 + mode) * 3);
-      }
+    for (int c = 0; c < A.n_colors; ++c) {
+      gs::k_coarse_product<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(spmv_view(g), cv, g->d_agg_color.p, c, g->d_Y.p);
+      if (g->agg_own) gs::k_restrict_modes<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_Y.p, g->d_R.p, nc9, c * 9);
+    }
     for (int mode = 0; mode < 3; ++mode) {
       gs::k_basis_vec<<<g->grid_rows, gs::kThreads, 0, g->stream>>>(cv, g->n_own, g->d_agg_color.p, -1, mode, g->d_basis.p);
       if (g->agg_own) gs::k_restrict<<<g->agg_own, gs::kThreads, 0, g->stream>>>(cv, g->d_basis.p, g->d_sc.p, 0, g->d_G.p, 9, mode * 3);
@@ -1187,7 +1183,7 @@ gs_status coarse_setup(gs_graph* g, double lambda) {
     // every rank needs the whole coarse matrix: its aggregates' rows of R and G are contiguous (aggregate-major)
     if (gs_status s = coarse_gather(g, g->d_R.p, nc9)) return s;
     if (gs_status s = coarse_gather(g, g->d_G.p, 9)) return s;
-    g->launches += 3 * (int64_t)A.n_colors * 3 + 6;
+    g->launches += 2 * (int64_t)A.n_colors + 7;
     g->coarse_e0_valid = true;
     g->coarse_lambda = -1.0;
   }

@@ -4,12 +4,14 @@
 #include <cmath>
 #include <thread>
 #include <vector>
+#include "host_pool.hpp"
 #include "se2.cuh"
 
 namespace gs {
 
-// fn(begin, end) over [0, n) on up to 16 host threads (per-pose conversions between the caller's (x, y, theta) and the
-// device's (x, y, cos, sin): a million sin/cos/atan2 on one thread is 20-50 ms, which a 140-ms LM step notices)
+// fn(begin, end) over [0, n) on up to 16 host threads of the process-wide pool (per-pose conversions between the caller's
+// (x, y, theta) and the device's (x, y, cos, sin): a million sin/cos/atan2 on one thread is 20-50 ms, which a 140-ms LM
+// step notices)
 template <typename F>
 inline void parallel_for(size_t n, F fn, size_t min_chunk = 32768) {
   size_t nt = std::min<size_t>(std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 16), (n + min_chunk - 1) / min_chunk);
@@ -17,15 +19,11 @@ inline void parallel_for(size_t n, F fn, size_t min_chunk = 32768) {
     fn((size_t)0, n);
     return;
   }
-  std::vector<std::thread> th;
-  th.reserve(nt - 1);
   const size_t chunk = (n + nt - 1) / nt;
-  for (size_t t = 1; t < nt; ++t) {
-    const size_t b = t * chunk, e = std::min(n, b + chunk);
-    if (b < e) th.emplace_back([=] { fn(b, e); });
-  }
-  fn((size_t)0, std::min(n, chunk));
-  for (auto& t : th) t.join();
+  HostPool::get().run((int)nt, [&](int t) {
+    const size_t b = (size_t)t * chunk, e = std::min(n, b + chunk);
+    if (b < e) fn(b, e);
+  });
 }
 
 // noiseModel::Gaussian::Covariance(Q): symmetrise, Cholesky test (GTSAM throws on a non-SPD Q), invert -> information

@@ -14,7 +14,8 @@
 // 1M-pose graph 14,700 iterations per solve become about 700.  W is never stored: a row's
 // block follows from its pose and the reference pose.  Everything is deterministic (fixed-order sums, no atomics).
 //
-//   k_basis_vec   v = column `mode` of W for the aggregates of one colour (zero elsewhere)  -> E's columns, via k_spmv
+//   k_coarse_product  Y = H W_c for the three columns of W of one colour's aggregates (set-up: E's columns), k_restrict_modes
+//   k_basis_vec   v = column `mode` of W (set-up: G = W^T W)
 //   k_restrict    c_a = sum_{i in a} W_i^T r_i                       one CTA per aggregate, rows in list order
 //   k_coarse_E    dense E = E0 + lambda G from the restricted products (layout: column-major, 3 n_agg square)
 //   k_coarse_mv   mu = E^-1 c (dense symmetric product, one warp per row) and c.mu, then the scalar step
@@ -85,6 +86,8 @@ __global__ void __launch_bounds__(kThreads) k_basis_vec(const CoarseView a, int 
 
 // this thread's share of sum_{i in aggregate g} W_i^T r_i (g = local aggregate index): rows threadIdx.x, + T, ... of
 // the aggregate's list, in list order — ONE spelling for the single-GPU and the peer-memory kernel
+// (STRIDE doubles between consecutive rows of r: 3 for the PCG vectors, 9 for the three-column products of the set-up)
+template <int STRIDE = 3>
 __device__ __forceinline__ void restrict_sums(const CoarseView& a, const double* __restrict__ r, int g, double& s0, double& s1,
                                               double& s2) {
   const int q0 = a.agg_ptr[g], q1 = a.agg_ptr[g + 1];
@@ -104,9 +107,9 @@ __device__ __forceinline__ void restrict_sums(const CoarseView& a, const double*
     for (int u = 0; u < 4; ++u) {
       const int i = idx[u] < 0 ? 0 : idx[u];
       ps[u] = ldg(a.pose + i);
-      rv[u][0] = r[3 * (size_t)i];
-      rv[u][1] = r[3 * (size_t)i + 1];
-      rv[u][2] = r[3 * (size_t)i + 2];
+      rv[u][0] = r[STRIDE * (size_t)i];
+      rv[u][1] = r[STRIDE * (size_t)i + 1];
+      rv[u][2] = r[STRIDE * (size_t)i + 2];
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -136,6 +139,75 @@ __global__ void __launch_bounds__(kThreads, 4) k_restrict(const CoarseView a, co
     o[0] = t0;
     o[1] = t1;
     o[2] = t2;
+  }
+}
+
+// Set-up: the three columns of E0 = W^T H W that belong to the aggregates of ONE colour, in one pass over H.
+// Y[9 r + 3 mode + k] = (H w_mode)_r,k where w_mode is column `mode` of W restricted to the aggregates of that colour: a
+// column's block of W is formed on the fly from its pose and its aggregate's reference (ghost columns included: the
+// rank holds their poses), so there is no basis vector in memory, no exchange, and H is read once instead of three
+// times.  Per right-hand side the arithmetic is the product kernel's (spmv_slot per stored block in slot order, then the
+// diagonal block).
+__global__ void __launch_bounds__(kThreads) k_coarse_product(const SpmvView a, const CoarseView cv, const int* __restrict__ agg_color,
+                                                              int color, double* __restrict__ Y) {
+  const int r = blockIdx.x * kThreads + threadIdx.x;
+  if (r >= a.n_own) return;
+  const int sl = r / kSlice, lane = r % kSlice;
+  const int base = a.rs.base[sl] + lane, w = a.rs.width[sl];
+  const size_t n = (size_t)a.n_own, rr = (size_t)r;
+  double y[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+  double d[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) d[k] = ldg(a.Hd + (size_t)k * n + rr);
+  int2 nref = w > 0 ? ldg(a.refs + base) : make_int2(-1, 0);
+  for (int s = 0; s < w; ++s) {
+    const int2 ref = nref;
+    if (s + 1 < w) nref = ldg(a.refs + base + (s + 1) * kSlice);
+    if (ref.x < 0) continue;
+    const int g = cv.agg_of[ref.x];
+    if (agg_color[g] != color) continue;          // a zero column adds nothing
+    double h[9];
+    load_block_as(a.Ho, a.hstride, ref.y >> 1, ref.y & 1, h);
+    const WBlock wb = w_block(ldg(cv.pose + ref.x), ldg(cv.ref + g));
+#pragma unroll
+    for (int mode = 0; mode < 3; ++mode) {
+      double v[3];
+      w_column(wb, mode, v);
+      spmv_slot(h, v[0], v[1], v[2], y[mode][0], y[mode][1], y[mode][2]);
+    }
+  }
+  const int g = cv.agg_of[r];
+  const bool mine = agg_color[g] == color;
+  const WBlock wb = w_block(ldg(cv.pose + r), ldg(cv.ref + g));
+#pragma unroll
+  for (int mode = 0; mode < 3; ++mode) {
+    double q[3] = {0.0, 0.0, 0.0};
+    if (mine) w_column(wb, mode, q);
+    double* o = Y + 9 * rr + 3 * mode;
+    o[0] = y[mode][0] + ((d[0] * q[0] + d[1] * q[1]) + d[2] * q[2]);
+    o[1] = y[mode][1] + ((d[1] * q[0] + d[3] * q[1]) + d[4] * q[2]);
+    o[2] = y[mode][2] + ((d[2] * q[0] + d[4] * q[1]) + d[5] * q[2]);
+  }
+}
+
+// the three restrictions that follow k_coarse_product: out[a * ostride + ooff + 3 mode + k] = sum over the rows of owned
+// aggregate a of (W_i^T Y_i,mode)_k, each by the very sums of k_restrict (same thread / row order, same tree)
+__global__ void __launch_bounds__(kThreads, 4) k_restrict_modes(const CoarseView a, const double* __restrict__ Y, double* __restrict__ out,
+                                                              int ostride, int ooff) {
+  __shared__ double red[8];
+  const int g = blockIdx.x;                   // local aggregate
+  for (int mode = 0; mode < 3; ++mode) {
+    double s0, s1, s2;
+    restrict_sums<9>(a, Y + 3 * mode, g, s0, s1, s2);
+    const double t0 = block_sum(s0, red);
+    const double t1 = block_sum(s1, red);
+    const double t2 = block_sum(s2, red);
+    if (threadIdx.x == 0) {
+      double* o = out + (size_t)(a.a0 + g) * ostride + ooff + 3 * mode;
+      o[0] = t0;
+      o[1] = t1;
+      o[2] = t2;
+    }
   }
 }
 

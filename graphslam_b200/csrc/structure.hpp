@@ -27,8 +27,9 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
-#include <thread>
 #include <vector>
+
+#include "host_pool.hpp"
 
 namespace gs {
 
@@ -318,14 +319,12 @@ inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const s
   std::vector<std::vector<int>> seg_out[kSegments];
   {
     // the segments are independent: one host thread each on graphs where a segment is worth a thread
-    std::vector<std::thread> th;
-    for (int sgm = 0; sgm < kSegments; ++sgm) {
-      const int r0 = part.seg_row[sgm], r1 = part.seg_row[sgm + 1];
-      auto work = [&, sgm, r0, r1] { aggregate_segment(r0, r1, rowptr, colidx, target, A.work_region, A.work_mark, seg_out[sgm]); };
-      if (N >= 8192 && sgm + 1 < kSegments && r1 > r0) th.emplace_back(work);
-      else work();
-    }
-    for (auto& t : th) t.join();
+    auto work = [&](int sgm) {
+      aggregate_segment(part.seg_row[sgm], part.seg_row[sgm + 1], rowptr, colidx, target, A.work_region, A.work_mark, seg_out[sgm]);
+    };
+    if (N >= 8192) HostPool::get().run(kSegments, work);
+    else
+      for (int sgm = 0; sgm < kSegments; ++sgm) work(sgm);
   }
   for (int sgm = 0; sgm < kSegments; ++sgm) {
     A.seg_agg[sgm] = A.n_agg;
@@ -360,10 +359,7 @@ inline void build_aggregation(int N, const std::vector<int32_t>& rowptr, const s
       }
     };
     const int nt = N >= 8192 ? std::min(kSegments, na) : 1;
-    std::vector<std::thread> th;
-    for (int t = 1; t < nt; ++t) th.emplace_back(adjacency, (int)((int64_t)na * t / nt), (int)((int64_t)na * (t + 1) / nt));
-    adjacency(0, nt > 1 ? (int)((int64_t)na / nt) : na);
-    for (auto& t : th) t.join();
+    HostPool::get().run(nt, [&](int t) { adjacency((int)((int64_t)na * t / nt), (int)((int64_t)na * (t + 1) / nt)); });
   }
   A.color.assign(na, -1);
   A.n_colors = 0;
@@ -396,12 +392,7 @@ inline int for_parts(int n, int grain, F fn) {
     fn(0, n, 0);
     return 1;
   }
-  std::vector<std::thread> th;
-  th.reserve(parts - 1);
-  for (int t = 1; t < parts; ++t)
-    th.emplace_back([=] { fn((int)((int64_t)n * t / parts), (int)((int64_t)n * (t + 1) / parts), t); });
-  fn(0, (int)((int64_t)n / parts), 0);
-  for (auto& t : th) t.join();
+  HostPool::get().run(parts, [&](int t) { fn((int)((int64_t)n * t / parts), (int)((int64_t)n * (t + 1) / parts), t); });
   return parts;
 }
 constexpr int kRowGrain = 8192;     // rows per host thread in the per-row passes of the structure build
