@@ -3,16 +3,17 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C3] [--n POSES]
 
-A "step" is one outer Levenberg-Marquardt iteration of the hot path (linearise + assemble, block-Jacobi PCG
-to pcg_rel_tol, retract, chi2, accept/reject) on the resident graph, continuing one optimisation trajectory
-from the synthetic initial guess.  One JSON line on stdout (rank 0); everything else goes to stderr.
+A "step" is one outer Levenberg-Marquardt iteration of the hot path (linearise + assemble, PCG to pcg_rel_tol with
+the two-level preconditioner — block-Jacobi plus a rigid-body coarse space — that is the library's default, retract,
+chi2, accept/reject) on the resident graph, continuing one optimisation trajectory from the synthetic initial guess;
+the line's `block_jacobi_only` block repeats the steps with the plain block-Jacobi preconditioner.  One JSON line on stdout (rank 0); everything else goes to stderr.
 
   value     device-resident throughput: K steps / device time (CUDA events on the library's stream)
   e2e       the same through the C ABI with HOST buffers, every step: gs_set_local_poses (H2D) + gs_optimize(1) +
             gs_get_local_poses (D2H) — each rank moves the rows it owns
   roofline  dominant kernel (BSR SpMV): SURVEY §8(d) algorithmic bytes / CUDA-event launch duration
-  cpu_baseline / --impl reference: oracle/cpu_ref.c (C + OpenMP port of the path, all host threads) on a bounded
-            sample of the same workload.  The reference's own optimiser is GTSAM (absent, unpinned) — see DESIGN.md.
+  cpu_baseline / --impl reference: oracle/cpu_ref.c (C + OpenMP port of the path with a sparse multifrontal Cholesky, what
+            GTSAM's default solver does; all host threads): real un-capped LM steps of the same workload.  The reference's own optimiser is GTSAM (absent, unpinned) — see DESIGN.md.
 """
 from __future__ import annotations
 
